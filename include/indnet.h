@@ -1,0 +1,124 @@
+/* libindnet - C-ABI of the B200-native (sm_100a) Induction-Network episode pipeline.
+ *
+ * The reference (wws0815/Induction-Network-on-FewRel) has no FFI: its boundary is the Python API of
+ * model/layer_module.py, model/graph.py, model/base.py and util/data_loader.py, and everything below
+ * that API runs inside TensorFlow ops.  Each entry point here replaces the TF op group named in its
+ * comment (file:line in /root/reference).  The Python host (induction_b200.model.*, .util.*) binds
+ * these with ctypes; INTEGRATION.md shows the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only; every pointer is a DEVICE pointer unless the comment says host.
+ *    All matrices are row-major, dense unless a leading dimension is given.
+ *  - indnet_stream is a cudaStream_t; all work is enqueued on it, nothing synchronises, nothing
+ *    allocates.  Scratch, when an op needs it, is passed in by the caller.
+ *  - Return 0 on success; non-zero (INDNET_ERR_*) on error with a message in indnet_last_error()
+ *    (thread-local).  Nothing throws across this boundary.
+ *  - FP32 entry points are the "parity mode" (1e-5 vs the reference graph); *_tc entry points are the
+ *    bf16 tensor-core mode (tcgen05/TMEM, FP32 accumulation, 2e-2).
+ *  - Symbols: N classes, K shots, Q queries/class, L sequence length, E word dim, P=5 position dim,
+ *    D=E+2P, u LSTM units, H=2u, S NTN slices, X sentences, T=X*L tokens.
+ */
+#ifndef INDNET_H_
+#define INDNET_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define INDNET_ABI_VERSION 1
+
+typedef void* indnet_stream; /* cudaStream_t */
+
+/* Host string describing the last error on this thread. */
+const char* indnet_last_error(void);
+int indnet_abi_version(void);
+
+/* ---- dense building blocks (FP32 parity mode) -------------------------------------------------
+ * C = alpha*op(A)*op(B) + beta*C (+ bias[n]) (act: 0 none, 1 tanh, 2 relu).  Two-level batching:
+ * batch index z -> (zo = z / inner, zi = z % inner), operand offset zo*s?o + zi*s?i.  splitk <= 0
+ * picks a split automatically (atomic accumulation) when the output is small and K long.
+ * Replaces tf.matmul / tf.layers.Dense / tf.tensordot at model/layer_module.py:24,30,45,65,76,132 and
+ * the LSTM kernel matmul of model/graph.py:44, plus their autodiff counterparts. */
+int indnet_sgemm(indnet_stream st, int transA, int transB, int M, int N, int K, float alpha, const float* A, int lda,
+                 const float* B, int ldb, float beta, float* C, int ldc, const float* bias, int act, int batch,
+                 int inner, long long sAo, long long sAi, long long sBo, long long sBi, long long sCo, long long sCi,
+                 int splitk);
+/* out[c] (+)= sum_r A[r, c]  - bias gradients (autodiff of the bias adds at layer_module.py:45,65). */
+int indnet_colsum(indnet_stream st, const float* A, int rows, int cols, int lda, float* out, int accumulate);
+/* out[d0][d2][d1] = in[d0][d1][d2]  - converts TF's M[H,H,S] (layer_module.py:16) to the internal M'[H,S,H]. */
+int indnet_permute021(indnet_stream st, const float* in, float* out, int d0, int d1, int d2);
+
+/* cudaMemsetAsync on the stream (gradient regions that accumulate must start at zero). */
+int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);
+
+/* ---- a2: Base.get_embedding, model/base.py:76-86 --------------------------------------------- */
+int indnet_embed_fwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* word_table,
+                     const float* pos1_table, const float* pos2_table, float* x /*[T][D]*/, long long T, int E, int P);
+/* Scatter-add dx into dpos1/dpos2 [pos_rows][P] (and dword_table [vocab][E] when not NULL, i.e. when
+ * the word table is trainable, base.py:62-65).  Accumulates (+=). */
+int indnet_embed_bwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* dx,
+                     float* dword_table, float* dpos1, float* dpos2, long long T, int E, int P, int pos_rows);
+
+/* ---- a3: rnn.BasicLSTMCell x2 + bidirectional_dynamic_rnn, model/graph.py:34-49 ---------------
+ * xproj [2][X][L][4u] = x*W_x + bias per direction (gate order i,j,f,o); Wh_* [u][4u] (row stride 4u:
+ * the last u rows of the TF kernel [D+u,4u]).  Writes hout [X][L][2u] (fw | bw, output dropout applied
+ * when keep_prob < 1), and for BPTT: gates [2][X][L][4u] (post-activation), cstate [2][X][L][u],
+ * hprev [2][X][L][u] (recurrent input of each step).  Dropout stream = seed + *seed_step * 1000003
+ * (seed_step: optional device int64, e.g. global_step, so a replayed CUDA graph draws fresh masks). */
+int indnet_lstm_fwd(indnet_stream st, const float* xproj, const float* Wh_fw, const float* Wh_bw, float* hout,
+                    float* gates, float* cstate, float* hprev, int X, int L, int u, float keep_prob,
+                    unsigned long long seed, const long long* seed_step);
+/* BPTT: dz [2][X][L][4u] = dLoss/d(pre-activation gates).  whT_scratch: caller-provided [2][4u][u]
+ * floats (transposed recurrent weights, rebuilt on every call). */
+int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, const float* cstate, const float* Wh_fw,
+                    const float* Wh_bw, float* whT_scratch, float* dz, int X, int L, int u, float keep_prob,
+                    unsigned long long seed, const long long* seed_step);
+
+/* ---- a4/a5: self_attention, model/layer_module.py:49-98 (pooling part; Dense+tanh is a GEMM) and
+ * the support/query split of model/graph.py:57-62 ------------------------------------------------
+ * proj [X][L][H] = tanh(hout*Wa1+ba1); mask [X][L] raw {0,1,2,3} (binarised as model/graph.py:52).
+ * alphas [X][L].  Sentences come in episodes of `group` rows; the first `split` rows of each episode
+ * are written densely to enc_a [X/group][split][H], the others to enc_b [X/group][group-split][H]
+ * (split == group: everything to enc_a, enc_b may be NULL). */
+int indnet_attn_pool_fwd(indnet_stream st, const float* hout, const float* proj, const int* mask, const float* w_a2,
+                         float* enc_a, float* enc_b, float* alphas, int X, int L, int H, int group, int split);
+/* Reads denc_a/denc_b in the same split layout.  Writes dhout = alpha_t*denc (caller adds
+ * dpre*Wa1^T), dpre [X][L][H], dw2_part [X][H]. */
+int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* denc_b, const float* hout,
+                         const float* proj, const float* alphas, const float* w_a2, float* dhout, float* dpre,
+                         float* dw2_part, int X, int L, int H, int group, int split);
+
+/* ---- a6/a7: dynamic_routing + squash, model/layer_module.py:101-162 ---------------------------
+ * ehat [BC][K][H] = e_s*W_s; b_in [BC][K] or NULL (zeros, model/graph.py:71); cvec [BC][H]. K <= 32. */
+int indnet_routing_fwd(indnet_stream st, const float* ehat, const float* b_in, float* cvec, int BC, int K, int H,
+                       int iters);
+int indnet_routing_bwd(indnet_stream st, const float* ehat, const float* b_in, const float* dcvec, float* dehat,
+                       int BC, int K, int H, int iters);
+int indnet_squash_fwd(indnet_stream st, const float* v, float* out, int rows, int H);
+int indnet_squash_bwd(indnet_stream st, const float* v, const float* dout, float* dv, int rows, int H);
+
+/* ---- a8-a10: neural_tensor_layer head + build_loss + build_predict/accuracy ---------------------
+ * model/layer_module.py:35-47, model/graph.py:92-94, model/base.py:101-107.
+ * V [rows][N*S] pre-ReLU bilinear products, column c*S+k; w [(k*N+c)][N] in the reference's row order;
+ * labels [rows]; probs [rows][N]; loss_part [rows] = sum_c (p-y)^2; correct [rows] = argmax hit. */
+int indnet_ntn_head_fwd(indnet_stream st, const float* V, const float* w, const float* b, const int* labels,
+                        float* probs, float* loss_part, int* correct, int rows, int N, int S);
+/* out2[0] = loss (mean over rows*N), out2[1] = accuracy. */
+int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, int rows, int N);
+/* Upstream gradient: dprobs [rows][N] when not NULL, else the fused mean-squared-error gradient
+ * scale*2(p-y) with scale = 1/(rows*N).  Overwrites dlogit [rows][N], dV [rows][N*S], dw, db. */
+int indnet_ntn_head_bwd(indnet_stream st, const float* V, const float* w, const float* probs, const int* labels,
+                        const float* dprobs, float* dlogit, float* dV, float* dw, float* db, int rows, int N, int S,
+                        float scale);
+
+/* ---- a11: build_optimize, model/base.py:94-99 ---------------------------------------------------
+ * One fused TF-form Adam update over a flat buffer.  global_step: device int64, read for the staircase
+ * decay then incremented; hyper: device float[2] receiving {lr_t, lr}.  grad_scale multiplies g. */
+int indnet_adam_step(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
+                     long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate, float beta1,
+                     float beta2, float eps, float grad_scale);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INDNET_H_ */

@@ -1,0 +1,59 @@
+// a11: build_optimize (model/base.py:94-99): staircase exponential decay + tf.train.AdamOptimizer as
+// driven by optimize_loss, fused over ONE flat parameter buffer (all trainables of the graph live in
+// one allocation, so the data-parallel gradient all-reduce and this update are each a single call).
+//   lr   = lr0 * decay_rate ^ floor(global_step / decay_steps)          (global_step BEFORE the step)
+//   lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t),  t = global_step + 1
+//   m = b1 m + (1-b1) g ; v = b2 v + (1-b2) g^2 ; theta -= lr_t * m / (sqrt(v) + eps)   (SURVEY A.6:
+//   epsilon is outside the bias correction, unlike torch.optim.Adam)
+// global_step lives on the device so the whole train step can sit in one CUDA graph.
+#include "common.cuh"
+#include "indnet_internal.h"
+#include "../../include/indnet.h"
+
+namespace indnet {
+
+__global__ void adam_prep_kernel(long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate,
+                                 float beta1, float beta2) {
+  const long long gs = *global_step;
+  const float lr = lr0 * powf(decay_rate, floorf((float)gs / (float)decay_steps));
+  const double t = (double)(gs + 1);
+  const float lr_t = (float)((double)lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t)));
+  hyper[0] = lr_t;
+  hyper[1] = lr;
+  *global_step = gs + 1;
+}
+
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, long long n, const float* __restrict__ hyper, float beta1,
+                            float beta2, float eps, float gscale) {
+  const float lr_t = hyper[0];
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gscale;
+    const float mi = beta1 * m[i] + (1.0f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+}  // namespace indnet
+
+using namespace indnet;
+
+extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* grads, float* m, float* v, long long n,
+                                long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate,
+                                float beta1, float beta2, float eps, float grad_scale) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(n >= 0 && decay_steps > 0, "adam_step: bad sizes");
+  IN_REQUIRE(global_step && hyper, "adam_step: null step/hyper pointer");
+  adam_prep_kernel<<<1, 1, 0, st>>>(global_step, hyper, lr0, decay_steps, decay_rate, beta1, beta2);
+  IN_LAUNCH_CHECK("adam_prep_kernel");
+  if (n == 0) return INDNET_OK;
+  IN_REQUIRE(params && grads && m && v, "adam_step: null pointer");
+  int blocks = ceil_div(n, 256 * 4);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale);
+  IN_LAUNCH_CHECK("adam_kernel");
+  return INDNET_OK;
+}

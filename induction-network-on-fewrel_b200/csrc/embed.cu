@@ -1,0 +1,100 @@
+// a2: Base.get_embedding (model/base.py:76-86): three table lookups concatenated on the feature
+// axis, x[t, :] = [word_table[word[t]] (E) ; pos1_table[pos1[t]] (P) ; pos2_table[pos2[t]] (P)],
+// and its backward (scatter-add of dx into the trainable tables).
+#include "common.cuh"
+#include "indnet_internal.h"
+#include "../../include/indnet.h"
+
+namespace indnet {
+
+__global__ void embed_fwd_kernel(const int* __restrict__ word, const int* __restrict__ pos1,
+                                 const int* __restrict__ pos2, const float* __restrict__ wt,
+                                 const float* __restrict__ p1t, const float* __restrict__ p2t,
+                                 float* __restrict__ x, long long T, int E, int P) {
+  const int D = E + 2 * P;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= T * D) return;
+  long long t = i / D;
+  int d = (int)(i % D);
+  float v;
+  if (d < E) v = wt[(long long)word[t] * E + d];
+  else if (d < E + P) v = p1t[(long long)pos1[t] * P + (d - E)];
+  else v = p2t[(long long)pos2[t] * P + (d - E - P)];
+  x[i] = v;
+}
+
+// Position tables are tiny ([2L, P]) and every token hits them: accumulate in shared memory per
+// block, then one atomic per table entry per block.
+__global__ void embed_pos_bwd_kernel(const int* __restrict__ pos1, const int* __restrict__ pos2,
+                                     const float* __restrict__ dx, float* __restrict__ dp1,
+                                     float* __restrict__ dp2, long long T, int E, int P, int pos_rows,
+                                     long long tokens_per_block) {
+  extern __shared__ float sm[];  // [2][pos_rows*P]
+  const int n = pos_rows * P;
+  for (int i = threadIdx.x; i < 2 * n; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const int D = E + 2 * P;
+  long long t0 = blockIdx.x * tokens_per_block;
+  long long t1 = min(T, t0 + tokens_per_block);
+  long long work = (t1 - t0) * (2 * P);
+  for (long long w = threadIdx.x; w < work; w += blockDim.x) {
+    long long t = t0 + w / (2 * P);
+    int j = (int)(w % (2 * P));
+    float g = dx[t * D + E + j];
+    if (j < P) atomicAdd(&sm[pos1[t] * P + j], g);
+    else atomicAdd(&sm[n + pos2[t] * P + (j - P)], g);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float a = sm[i], b = sm[n + i];
+    if (a != 0.f) atomicAdd(dp1 + i, a);
+    if (b != 0.f) atomicAdd(dp2 + i, b);
+  }
+}
+
+__global__ void embed_word_bwd_kernel(const int* __restrict__ word, const float* __restrict__ dx,
+                                      float* __restrict__ dwt, long long T, int E, int D) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= T * E) return;
+  long long t = i / E;
+  int d = (int)(i % E);
+  atomicAdd(dwt + (long long)word[t] * E + d, dx[t * D + d]);
+}
+
+}  // namespace indnet
+
+using namespace indnet;
+
+extern "C" int indnet_embed_fwd(indnet_stream st_, const int* word, const int* pos1, const int* pos2,
+                                const float* word_table, const float* pos1_table, const float* pos2_table,
+                                float* x, long long T, int E, int P) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(T >= 0 && E > 0 && P > 0, "embed_fwd: bad sizes T=%lld E=%d P=%d", T, E, P);
+  if (T == 0) return INDNET_OK;
+  IN_REQUIRE(word && pos1 && pos2 && word_table && pos1_table && pos2_table && x, "embed_fwd: null pointer");
+  long long n = T * (E + 2 * P);
+  embed_fwd_kernel<<<ceil_div(n, 256), 256, 0, st>>>(word, pos1, pos2, word_table, pos1_table, pos2_table, x, T, E, P);
+  IN_LAUNCH_CHECK("embed_fwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_embed_bwd(indnet_stream st_, const int* word, const int* pos1, const int* pos2,
+                                const float* dx, float* dword_table, float* dpos1, float* dpos2,
+                                long long T, int E, int P, int pos_rows) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(T >= 0 && E > 0 && P > 0 && pos_rows > 0, "embed_bwd: bad sizes");
+  if (T == 0) return INDNET_OK;
+  IN_REQUIRE(pos1 && pos2 && dx && dpos1 && dpos2, "embed_bwd: null pointer");
+  size_t smem = sizeof(float) * 2 * pos_rows * P;
+  IN_REQUIRE(smem <= 48 * 1024, "embed_bwd: position tables too large for the shared-memory accumulator (%zu B)", smem);
+  long long tpb = 2048;
+  int blocks = ceil_div(T, tpb);
+  embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx, dpos1, dpos2, T, E, P, pos_rows, tpb);
+  IN_LAUNCH_CHECK("embed_pos_bwd_kernel");
+  if (dword_table) {
+    IN_REQUIRE(word != nullptr, "embed_bwd: word ids needed for the trainable word table");
+    embed_word_bwd_kernel<<<ceil_div(T * E, 256), 256, 0, st>>>(word, dx, dword_table, T, E, E + 2 * P);
+    IN_LAUNCH_CHECK("embed_word_bwd_kernel");
+  }
+  return INDNET_OK;
+}

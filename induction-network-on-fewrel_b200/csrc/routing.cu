@@ -1,0 +1,241 @@
+// a6/a7: the induction module, model/layer_module.py:101-162, one warp per (episode, class).
+//   e_hat = e_s * W_s is loop invariant (the reference rebuilds it in each unrolled iteration, :132)
+//   and is produced once by the GEMM path; this kernel runs the routing iterations:
+//   d = softmax_K(b) (:127) ; c_hat = sum_k d_k e_hat_k (:136) ; c = squash(c_hat) (:139,153-162) ;
+//   b += e_hat . c (:143-147).  The coupling logits live one-per-lane (K <= 32) and every reduction is
+//   a warp shuffle.  The backward recomputes the iterations and back-propagates through all of them
+//   (TF autodiff has no stop_gradient on this path).
+#include "common.cuh"
+#include "indnet_internal.h"
+#include "../../include/indnet.h"
+
+namespace indnet {
+
+constexpr int RT_WARPS = 4;
+constexpr float SQ_EPS = 1e-9f;
+
+__device__ __forceinline__ float squash_factor(float s) { return s / (1.0f + s) / sqrtf(s + SQ_EPS); }
+// d/ds [ s / (1+s) / sqrt(s+eps) ] written without 1/s
+__device__ __forceinline__ float squash_factor_grad(float s) {
+  const float r = sqrtf(s + SQ_EPS);
+  return 1.0f / ((1.0f + s) * (1.0f + s) * r) - 0.5f * s / ((1.0f + s) * (s + SQ_EPS) * r);
+}
+
+__global__ void __launch_bounds__(RT_WARPS * 32)
+routing_fwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in, float* __restrict__ cvec,
+                   int BC, int K, int H, int iters) {
+  extern __shared__ float sm[];
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int w = blockIdx.x * RT_WARPS + warp;
+  if (w >= BC) return;   // whole warp leaves together; no block-level barrier below
+  float* cv = sm + warp * (H + 32);
+  float* dk = cv + H;
+  const float* __restrict__ e = ehat + (long long)w * K * H;
+  float b = (lane < K) ? (b_in ? b_in[(long long)w * K + lane] : 0.f) : -INFINITY;
+  for (int it = 0; it < iters; ++it) {
+    const float mx = warp_max(b);
+    const float ex = (lane < K) ? expf(b - mx) : 0.f;
+    const float sum = warp_sum(ex);
+    dk[lane] = ex / sum;
+    __syncwarp();
+    float n2 = 0.f;
+    for (int h = lane; h < H; h += 32) {
+      float acc = 0.f;
+      for (int k = 0; k < K; ++k) acc = fmaf(dk[k], e[(long long)k * H + h], acc);
+      cv[h] = acc;
+      n2 = fmaf(acc, acc, n2);
+    }
+    n2 = warp_sum(n2);
+    const float f = squash_factor(n2);
+    for (int h = lane; h < H; h += 32) cv[h] *= f;
+    __syncwarp();
+    if (it + 1 < iters) {
+      for (int k = 0; k < K; ++k) {
+        float dot = 0.f;
+        for (int h = lane; h < H; h += 32) dot = fmaf(e[(long long)k * H + h], cv[h], dot);
+        dot = warp_sum(dot);
+        if (lane == k) b += dot;
+      }
+    }
+    __syncwarp();
+  }
+  for (int h = lane; h < H; h += 32) cvec[(long long)w * H + h] = cv[h];
+}
+
+__global__ void __launch_bounds__(RT_WARPS * 32)
+routing_bwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in,
+                   const float* __restrict__ dcvec, float* __restrict__ dehat, int BC, int K, int H, int iters) {
+  extern __shared__ float sm[];
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int w = blockIdx.x * RT_WARPS + warp;
+  if (w >= BC) return;
+  // per-warp layout: chat[iters][H], cs[iters][H], gc[H], dch[H], d[iters][32], dbs[32], sn[iters rounded to 32]
+  const int per_warp = (2 * iters + 2) * H + (iters + 2) * 32;
+  float* chat = sm + (long long)warp * per_warp;
+  float* cs = chat + iters * H;
+  float* gc = cs + iters * H;
+  float* dch = gc + H;
+  float* dsm = dch + H;
+  float* dbs = dsm + iters * 32;
+  float* sn = dbs + 32;
+  const float* __restrict__ e = ehat + (long long)w * K * H;
+  float* __restrict__ de = dehat + (long long)w * K * H;
+
+  // ---- recompute the forward iterations, keeping d, c_hat, c and |c_hat|^2 of each
+  float b = (lane < K) ? (b_in ? b_in[(long long)w * K + lane] : 0.f) : -INFINITY;
+  for (int it = 0; it < iters; ++it) {
+    const float mx = warp_max(b);
+    const float ex = (lane < K) ? expf(b - mx) : 0.f;
+    const float sum = warp_sum(ex);
+    dsm[it * 32 + lane] = ex / sum;
+    __syncwarp();
+    float n2 = 0.f;
+    for (int h = lane; h < H; h += 32) {
+      float acc = 0.f;
+      for (int k = 0; k < K; ++k) acc = fmaf(dsm[it * 32 + k], e[(long long)k * H + h], acc);
+      chat[it * H + h] = acc;
+      n2 = fmaf(acc, acc, n2);
+    }
+    n2 = warp_sum(n2);
+    if (lane == 0) sn[it] = n2;
+    const float f = squash_factor(n2);
+    for (int h = lane; h < H; h += 32) cs[it * H + h] = chat[it * H + h] * f;
+    __syncwarp();
+    if (it + 1 < iters) {
+      for (int k = 0; k < K; ++k) {
+        float dot = 0.f;
+        for (int h = lane; h < H; h += 32) dot = fmaf(e[(long long)k * H + h], cs[it * H + h], dot);
+        dot = warp_sum(dot);
+        if (lane == k) b += dot;
+      }
+    }
+    __syncwarp();
+  }
+
+  // ---- reverse sweep
+  float dbn = 0.f;           // gradient w.r.t. b^{r+1}_lane
+  dbs[lane] = 0.f;
+  __syncwarp();
+  for (int r = iters - 1; r >= 0; --r) {
+    const bool last = (r == iters - 1);
+    float vg = 0.f;
+    for (int h = lane; h < H; h += 32) {
+      float g = last ? dcvec[(long long)w * H + h] : 0.f;
+      if (!last)
+        for (int k = 0; k < K; ++k) g = fmaf(dbs[k], e[(long long)k * H + h], g);
+      gc[h] = g;
+      vg = fmaf(chat[r * H + h], g, vg);
+    }
+    vg = warp_sum(vg);
+    const float s = sn[r];
+    const float f = squash_factor(s);
+    const float coef = 2.0f * squash_factor_grad(s) * vg;
+    for (int h = lane; h < H; h += 32) dch[h] = f * gc[h] + chat[r * H + h] * coef;
+    __syncwarp();
+    float dd = 0.f;
+    for (int k = 0; k < K; ++k) {
+      float dot = 0.f;
+      for (int h = lane; h < H; h += 32) dot = fmaf(dch[h], e[(long long)k * H + h], dot);
+      dot = warp_sum(dot);
+      if (lane == k) dd = dot;
+    }
+    const float d = (lane < K) ? dsm[r * 32 + lane] : 0.f;
+    const float dsum = warp_sum(d * dd);
+    const float db = (lane < K) ? (d * (dd - dsum) + dbn) : 0.f;
+    for (int k = 0; k < K; ++k) {
+      const float dkk = dsm[r * 32 + k];
+      const float dbk = dbs[k];
+      for (int h = lane; h < H; h += 32) {
+        const float val = dkk * dch[h] + dbk * cs[r * H + h];
+        const long long o = (long long)k * H + h;
+        de[o] = last ? val : de[o] + val;
+      }
+    }
+    __syncwarp();
+    dbn = db;
+    dbs[lane] = db;
+    __syncwarp();
+  }
+}
+
+__global__ void squash_fwd_kernel(const float* __restrict__ v, float* __restrict__ out, int rows, int H) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
+  if (w >= rows) return;
+  float n2 = 0.f;
+  for (int h = lane; h < H; h += 32) { float a = v[(long long)w * H + h]; n2 = fmaf(a, a, n2); }
+  n2 = warp_sum(n2);
+  const float f = squash_factor(n2);
+  for (int h = lane; h < H; h += 32) out[(long long)w * H + h] = v[(long long)w * H + h] * f;
+}
+
+__global__ void squash_bwd_kernel(const float* __restrict__ v, const float* __restrict__ dout,
+                                  float* __restrict__ dv, int rows, int H) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
+  if (w >= rows) return;
+  float n2 = 0.f, vg = 0.f;
+  for (int h = lane; h < H; h += 32) {
+    float a = v[(long long)w * H + h];
+    n2 = fmaf(a, a, n2);
+    vg = fmaf(a, dout[(long long)w * H + h], vg);
+  }
+  n2 = warp_sum(n2);
+  vg = warp_sum(vg);
+  const float f = squash_factor(n2), coef = 2.0f * squash_factor_grad(n2) * vg;
+  for (int h = lane; h < H; h += 32)
+    dv[(long long)w * H + h] = f * dout[(long long)w * H + h] + v[(long long)w * H + h] * coef;
+}
+
+}  // namespace indnet
+
+using namespace indnet;
+
+extern "C" int indnet_routing_fwd(indnet_stream st_, const float* ehat, const float* b_in, float* cvec, int BC, int K,
+                                  int H, int iters) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(BC >= 0 && K > 0 && H > 0 && iters > 0, "routing_fwd: bad sizes BC=%d K=%d H=%d iters=%d", BC, K, H, iters);
+  IN_REQUIRE(K <= 32, "routing_fwd: K=%d support instances per class exceeds the warp-per-class limit of 32", K);
+  if (BC == 0) return INDNET_OK;
+  IN_REQUIRE(ehat && cvec, "routing_fwd: null pointer");
+  size_t smem = sizeof(float) * RT_WARPS * (H + 32);
+  IN_REQUIRE(smem <= 48 * 1024, "routing_fwd: H=%d too large", H);
+  routing_fwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, cvec, BC, K, H, iters);
+  IN_LAUNCH_CHECK("routing_fwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_routing_bwd(indnet_stream st_, const float* ehat, const float* b_in, const float* dcvec,
+                                  float* dehat, int BC, int K, int H, int iters) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(BC >= 0 && K > 0 && H > 0 && iters > 0, "routing_bwd: bad sizes BC=%d K=%d H=%d iters=%d", BC, K, H, iters);
+  IN_REQUIRE(K <= 32, "routing_bwd: K=%d support instances per class exceeds the warp-per-class limit of 32", K);
+  IN_REQUIRE(iters <= 30, "routing_bwd: too many routing iterations (%d)", iters);
+  if (BC == 0) return INDNET_OK;
+  IN_REQUIRE(ehat && dcvec && dehat, "routing_bwd: null pointer");
+  size_t smem = sizeof(float) * RT_WARPS * ((size_t)(2 * iters + 2) * H + (iters + 2) * 32);
+  IN_REQUIRE(smem <= 227 * 1024, "routing_bwd: H=%d x iters=%d does not fit shared memory", H, iters);
+  if (smem > 48 * 1024)
+    IN_CUDA(cudaFuncSetAttribute(routing_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  routing_bwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, dcvec, dehat, BC, K, H, iters);
+  IN_LAUNCH_CHECK("routing_bwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_squash_fwd(indnet_stream st_, const float* v, float* out, int rows, int H) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(rows >= 0 && H > 0, "squash_fwd: bad sizes");
+  if (rows == 0) return INDNET_OK;
+  IN_REQUIRE(v && out, "squash_fwd: null pointer");
+  squash_fwd_kernel<<<ceil_div((long long)rows * 32, 128), 128, 0, st>>>(v, out, rows, H);
+  IN_LAUNCH_CHECK("squash_fwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_squash_bwd(indnet_stream st_, const float* v, const float* dout, float* dv, int rows, int H) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(rows >= 0 && H > 0, "squash_bwd: bad sizes");
+  if (rows == 0) return INDNET_OK;
+  IN_REQUIRE(v && dout && dv, "squash_bwd: null pointer");
+  squash_bwd_kernel<<<ceil_div((long long)rows * 32, 128), 128, 0, st>>>(v, dout, dv, rows, H);
+  IN_LAUNCH_CHECK("squash_bwd_kernel");
+  return INDNET_OK;
+}

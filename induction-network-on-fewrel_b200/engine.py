@@ -1,0 +1,406 @@
+"""Episode pipeline engine: parameter store + the fused forward / backward / update sequence.
+
+This is the host-side orchestration of the reference's ``sess.run([loss, accuracy, optimize, ...])``
+(model/base.py:143-152): one call enqueues every kernel of InductionGraph.forward
+(model/graph.py:29-86), build_loss (:88-109), build_predict/accuracy (model/base.py:101-107), the
+hand-written backward of each, and the TF-form Adam update (model/base.py:94-99) on the current CUDA
+stream through the C-ABI.  Shapes are static per pipeline, buffers are preallocated, and nothing in
+a step synchronises with the host, so a whole step can be captured into one CUDA graph.
+
+torch is used for device memory and streams only; every arithmetic kernel is in csrc/.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from ._lib import LIB, IndnetError, current_stream, ptr, require_cuda
+
+POS_DIM = 5  # model/base.py:25
+
+
+@dataclass
+class EpisodeConfig:
+    N: int            # classes per episode            (train.py:11)
+    K: int            # support instances per class    (train.py:12)
+    Q: int = 5        # query instances per class      (train.py:33)
+    B: int = 1        # episodes per step (reference: 1, model/base.py:137)
+    L: int = 40       # sequence_length                (model/base.py:13)
+    E: int = 50       # embed_size                     (model/base.py:15)
+    u: int = 100      # hidden_size                    (model/base.py:16)
+    S: int = 100      # NTN slices (out_size)          (model/layer_module.py:8)
+    iters: int = 3    # routing iterations             (model/layer_module.py:101)
+    keep_prob: float = 1.0
+    mode: str = "fp32"   # "fp32" parity mode | "bf16" tensor-core mode
+
+    @property
+    def D(self): return self.E + 2 * POS_DIM
+    @property
+    def H(self): return 2 * self.u
+    @property
+    def n_s(self): return self.N * (self.K + self.Q)
+    @property
+    def n_q(self): return self.N * self.Q
+    @property
+    def NK(self): return self.N * self.K
+    @property
+    def X(self): return self.B * self.n_s
+    @property
+    def T(self): return self.X * self.L
+
+
+# TF variable names
+FW_K = "bidirectional_rnn/fw/basic_lstm_cell/kernel"
+FW_B = "bidirectional_rnn/fw/basic_lstm_cell/bias"
+BW_K = "bidirectional_rnn/bw/basic_lstm_cell/kernel"
+BW_B = "bidirectional_rnn/bw/basic_lstm_cell/bias"
+ATT_K = "self_attn/dense/kernel"
+ATT_B = "self_attn/dense/bias"
+ATT_W2 = "self_attn/W_a2"
+
+
+def tf_param_shapes(N, L, E, u, S, vocab_rows=None):
+    """Names and TF-layout shapes of the trainables (model/base.py:62-74, model/graph.py:34-35,
+    model/layer_module.py:16-17,39-42,65-72,116-119).  ``vocab_rows`` is set only when the word table
+    is trainable (no ``pred_embed``, base.py:62-65)."""
+    D, H = E + 2 * POS_DIM, 2 * u
+    shapes = {
+        "M": (H, H, S), "w": (N * S, N), "b": (N,), "W_s": (H, H),
+        ATT_K: (H, H), ATT_B: (H,), ATT_W2: (H, 1),
+        FW_K: (D + u, 4 * u), FW_B: (4 * u,), BW_K: (D + u, 4 * u), BW_B: (4 * u,),
+        "pos1_embedding": (2 * L, POS_DIM), "pos2_embedding": (2 * L, POS_DIM),
+    }
+    if vocab_rows is not None:
+        shapes["word_embedding"] = (vocab_rows, E)
+    return shapes
+
+
+def _fans(shape):
+    if len(shape) == 1:
+        return shape[0], shape[0]
+    if len(shape) == 2:
+        return shape[0], shape[1]
+    rf = int(np.prod(shape[:-2]))
+    return shape[-2] * rf, shape[-1] * rf
+
+
+def _trunc_normal(gen, shape, std):
+    out = torch.empty(shape, dtype=torch.float64)
+    flat = out.view(-1)
+    todo = torch.ones(flat.numel(), dtype=torch.bool)
+    while todo.any():
+        n = int(todo.sum())
+        draw = torch.randn(n, generator=gen, dtype=torch.float64)
+        flat[todo] = draw
+        todo[todo.clone()] = draw.abs() > 2.0
+    return (out * std).float()
+
+
+def init_tf_params(shapes: Dict[str, tuple], seed: int = 0, pos_std: float = 0.1) -> Dict[str, torch.Tensor]:
+    """CPU float32 initial values in TF layouts with the reference's initialisers (A.8):
+    glorot-uniform for the LSTM and Dense kernels (scope default), glorot-normal (truncated) for
+    W_a2 / W_s / M / w / b, N(0, 0.1^2) for the embedding tables (base.py:19), zero biases."""
+    gen = torch.Generator().manual_seed(seed)
+    out = {}
+    for name, shape in shapes.items():
+        fi, fo = _fans(shape)
+        if name in (FW_B, BW_B, ATT_B):
+            t = torch.zeros(shape)
+        elif name in (FW_K, BW_K, ATT_K):
+            lim = math.sqrt(6.0 / (fi + fo))
+            t = (torch.rand(shape, generator=gen, dtype=torch.float64) * 2 - 1).mul(lim).float()
+        elif name in ("pos1_embedding", "pos2_embedding", "word_embedding"):
+            t = (torch.randn(shape, generator=gen, dtype=torch.float64) * pos_std).float()
+        else:
+            t = _trunc_normal(gen, shape, math.sqrt(2.0 / (fi + fo)) / 0.87962566103423978)
+        out[name] = t.contiguous()
+    return out
+
+
+class ParamStore:
+    """All trainables in ONE flat fp32 device buffer (+ grads, Adam m/v), addressed by TF name.
+    ``M`` is stored as M' = M.permute(0, 2, 1) ([H_i][S][H_j]) so both NTN contractions are plain
+    row-major GEMMs (see csrc/ntn.cu); ``state_dict`` / ``load_state_dict`` speak TF layouts."""
+
+    ALIGN = 64  # floats (256 B)
+
+    def __init__(self, shapes: Dict[str, tuple], device="cuda"):
+        require_cuda()
+        self.tf_shapes = dict(shapes)
+        self.offsets = {}
+        off = 0
+        for name, shape in shapes.items():
+            self.offsets[name] = off
+            off += (int(np.prod(shape)) + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.numel = off
+        self.device = torch.device(device)
+        self.params = torch.zeros(off, dtype=torch.float32, device=self.device)
+        self.grads = torch.zeros_like(self.params)
+        self.m = torch.zeros_like(self.params)
+        self.v = torch.zeros_like(self.params)
+        self.global_step = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.hyper = torch.zeros(2, dtype=torch.float32, device=self.device)   # {lr_t, lr}
+
+    def internal_shape(self, name):
+        s = self.tf_shapes[name]
+        return (s[0], s[2], s[1]) if name == "M" else s
+
+    def view(self, name, buf=None):
+        buf = self.params if buf is None else buf
+        n = int(np.prod(self.tf_shapes[name]))
+        o = self.offsets[name]
+        return buf[o:o + n].view(self.internal_shape(name))
+
+    def grad(self, name):
+        return self.view(name, self.grads)
+
+    def load_state_dict(self, tf_params: Dict[str, torch.Tensor]):
+        for name in self.tf_shapes:
+            t = tf_params[name].to(torch.float32)
+            if tuple(t.shape) != tuple(self.tf_shapes[name]):
+                raise ValueError("parameter %s has shape %s, expected %s" % (name, tuple(t.shape), self.tf_shapes[name]))
+            if name == "M":
+                t = t.permute(0, 2, 1)
+            self.view(name).copy_(t.contiguous().to(self.device))
+
+    def _export(self, buf):
+        out = {}
+        for name in self.tf_shapes:
+            t = self.view(name, buf).detach().clone()
+            out[name] = t.permute(0, 2, 1).contiguous() if name == "M" else t
+        return out
+
+    def state_dict(self):
+        return self._export(self.params)
+
+    def grad_dict(self):
+        return self._export(self.grads)
+
+
+def dropout_keep_mask(seed: int, shape, keep_prob: float, step: int = 0) -> np.ndarray:
+    """Host restatement of the device dropout stream (csrc/common.cuh ``dropout_keep``) so a mask the
+    LSTM kernel drew can be replayed through the oracle.  Element i of the flattened [X, L, 2u] output
+    is kept iff (mix32(seed + step*1000003, i) >> 8) / 2^24 < keep_prob."""
+    n = int(np.prod(shape))
+    M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+    with np.errstate(over="ignore"):
+        s = np.uint64((seed + step * 1000003) & 0xFFFFFFFFFFFFFFFF)
+        idx = np.arange(n, dtype=np.uint64)
+        z = (s + np.uint64(0x9E3779B97F4A7C15) * (idx + np.uint64(1))) & M64
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & M64
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & M64
+        z = z ^ (z >> np.uint64(31))
+    r = (z >> np.uint64(32)).astype(np.uint32) >> np.uint32(8)
+    u = r.astype(np.float32) * np.float32(1.0 / 16777216.0)
+    return (u < np.float32(keep_prob)).reshape(shape)
+
+
+class EpisodePipeline:
+    """Forward / backward / Adam over a batch of B episodes with preallocated buffers.
+
+    ``word_table``: float32 [V+2, E] frozen embedding (``pred_embed``, model/base.py:56-59) or None
+    when ``word_embedding`` is trainable and lives in the parameter store.
+    """
+
+    def __init__(self, cfg: EpisodeConfig, store: ParamStore, word_table: Optional[torch.Tensor],
+                 lr: float = 1e-3, decay_steps: int = 100, decay_rate: float = 0.9, seed: int = 0):
+        require_cuda()
+        LIB.load()
+        if cfg.mode not in ("fp32", "bf16"):
+            raise ValueError("mode must be 'fp32' or 'bf16'")
+        if cfg.K > 32:
+            raise ValueError("K=%d exceeds the warp-per-class routing limit of 32" % cfg.K)
+        self.cfg, self.p = cfg, store
+        self.dev = store.device
+        self.word_table = None if word_table is None else word_table.to(self.dev, torch.float32).contiguous()
+        self.trainable_words = word_table is None
+        if self.trainable_words and "word_embedding" not in store.tf_shapes:
+            raise ValueError("no pred_embed given and the store has no word_embedding")
+        self.lr0, self.decay_steps, self.decay_rate = float(lr), int(decay_steps), float(decay_rate)
+        self.seed = int(seed)
+        self.launches = 0
+        c = cfg
+        f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
+        i32 = lambda *s: torch.zeros(*s, dtype=torch.int32, device=self.dev)  # noqa: E731
+        # inputs ("placeholders", model/base.py:44-52)
+        self.word, self.pos1, self.pos2, self.mask = (i32(c.B, c.n_s, c.L) for _ in range(4))
+        self.label = i32(c.B, c.n_q)
+        # forward activations
+        self.x = f(c.T, c.D)
+        self.xproj = f(2, c.T, 4 * c.u)
+        self.hout = f(c.T, c.H)
+        self.gates = f(2, c.T, 4 * c.u)
+        self.cstate = f(2, c.T, c.u)
+        self.hprev = f(2, c.T, c.u)
+        self.proj = f(c.T, c.H)
+        self.alphas = f(c.X, c.L)
+        self.es = f(c.B, c.NK, c.H)          # support encodings (model/graph.py:57-58)
+        self.eq = f(c.B, c.n_q, c.H)         # query encodings   (model/graph.py:60-62)
+        self.ehat = f(c.B * c.NK, c.H)
+        self.cvec = f(c.B * c.N, c.H)
+        self.Tp = f(c.B * c.N, c.S * c.H)
+        self.V = f(c.B * c.n_q, c.N * c.S)
+        self.probs = f(c.B, c.n_q, c.N)
+        self.loss_part = f(c.B * c.n_q)
+        self.correct = i32(c.B * c.n_q)
+        self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
+        self._bwd_ready = False
+
+    # ------------------------------------------------------------------ helpers
+    def _call(self, name, *args):
+        LIB.call(name, current_stream(), *args)
+        self.launches += 1
+
+    def _gemm(self, tA, tB, M, N, K, A, lda, Bm, ldb, C, ldc, alpha=1.0, beta=0.0, bias=None, act=0,
+              batch=1, inner=1, sA=(0, 0), sB=(0, 0), sC=(0, 0), splitk=0):
+        self._call("indnet_sgemm", int(tA), int(tB), M, N, K, alpha, A, lda, Bm, ldb, beta, C, ldc,
+                   ptr(bias) if isinstance(bias, torch.Tensor) else bias, act, batch, inner,
+                   sA[0], sA[1], sB[0], sB[1], sC[0], sC[1], splitk)
+
+    def set_inputs(self, inputs, query_label):
+        """Copies one batch into the static input buffers.  Accepts torch tensors (any device) or
+        numpy arrays shaped [B, n_s, L] (or [n_s, L] when B == 1)."""
+        c = self.cfg
+        for k, buf in (("word", self.word), ("pos1", self.pos1), ("pos2", self.pos2), ("mask", self.mask)):
+            t = torch.as_tensor(inputs[k])
+            buf.copy_(t.reshape(c.B, c.n_s, c.L).to(torch.int32), non_blocking=True)
+        self.label.copy_(torch.as_tensor(query_label).reshape(c.B, c.n_q).to(torch.int32), non_blocking=True)
+
+    # ------------------------------------------------------------------ forward (model/graph.py:29-86)
+    def forward(self, train: bool = False):
+        c, p = self.cfg, self.p
+        keep = c.keep_prob if train else 1.0
+        wt = p.view("word_embedding") if self.trainable_words else self.word_table
+        u4 = 4 * c.u
+        # a2: embedding lookups + concat (model/base.py:76-86)
+        self._call("indnet_embed_fwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(wt),
+                   ptr(p.view("pos1_embedding")), ptr(p.view("pos2_embedding")), ptr(self.x), c.T, c.E, POS_DIM)
+        # a3: input projection for all timesteps (first D rows of the TF LSTM kernel) + recurrence
+        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+            self._gemm(0, 0, c.T, u4, c.D, ptr(self.x), c.D, ptr(p.view(kn)), u4, ptr(self.xproj[d]), u4,
+                       bias=p.view(bn))
+        wh_fw = p.view(FW_K)[c.D:]
+        wh_bw = p.view(BW_K)[c.D:]
+        self._call("indnet_lstm_fwd", ptr(self.xproj), ptr(wh_fw), ptr(wh_bw), ptr(self.hout), ptr(self.gates),
+                   ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
+        # a4: Dense+tanh, then score/softmax/pool, split into support | query (a5)
+        self._gemm(0, 0, c.T, c.H, c.H, ptr(self.hout), c.H, ptr(p.view(ATT_K)), c.H, ptr(self.proj), c.H,
+                   bias=p.view(ATT_B), act=1)
+        self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
+                   ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
+        # a6/a7: e_hat = e_s W_s once, then the routing iterations
+        self._gemm(0, 0, c.B * c.NK, c.H, c.H, ptr(self.es), c.H, ptr(p.view("W_s")), c.H, ptr(self.ehat), c.H)
+        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
+        # a8: T'[b,c][k][j] = cv M' ; V[b][q][c*S+k] = qe_b T'_b^T
+        self._gemm(0, 0, c.B * c.N, c.S * c.H, c.H, ptr(self.cvec), c.H, ptr(p.view("M")), c.S * c.H,
+                   ptr(self.Tp), c.S * c.H)
+        NS = c.N * c.S
+        self._gemm(0, 1, c.n_q, NS, c.H, ptr(self.eq), c.H, ptr(self.Tp), c.H, ptr(self.V), NS,
+                   batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0))
+        # a8-a10: relu, FC, sigmoid, squared error, argmax hit
+        self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
+                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
+        self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
+                   c.B * c.n_q, c.N)
+        self._last_keep = keep
+
+    # ------------------------------------------------------------------ backward
+    def _alloc_bwd(self):
+        c = self.cfg
+        f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
+        self.dlogit = f(c.B * c.n_q, c.N)
+        self.dV = f(c.B * c.n_q, c.N * c.S)
+        self.dTp = f(c.B * c.N, c.S * c.H)
+        self.dcvec = f(c.B * c.N, c.H)
+        self.dehat = f(c.B * c.NK, c.H)
+        self.des = f(c.B, c.NK, c.H)
+        self.deq = f(c.B, c.n_q, c.H)
+        self.dhout = f(c.T, c.H)
+        self.dpre = self.proj                  # in place: attn_pool_bwd reads proj[i] then writes dpre[i]
+        self.dw2_part = f(c.X, c.H)
+        self.dz = self.xproj                   # xproj is dead after the forward recurrence
+        self.dx = f(c.T, c.D)
+        self.whT = f(2, 4 * c.u, c.u)
+        self._bwd_ready = True
+
+    def backward(self):
+        """Hand-written backward of every forward op, in reverse order; fills ``self.p.grads``."""
+        if not self._bwd_ready:
+            self._alloc_bwd()
+        c, p = self.cfg, self.p
+        u4, NS = 4 * c.u, c.N * c.S
+        rows = c.B * c.n_q
+        # loss + head
+        self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
+                   None, ptr(self.dlogit), ptr(self.dV), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
+                   1.0 / (rows * c.N))
+        # dqe_b = dV_b T'_b ; dT'_b = dV_b^T qe_b
+        self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0))
+        self._gemm(1, 0, NS, c.H, c.n_q, ptr(self.dV), NS, ptr(self.eq), c.H, ptr(self.dTp), c.H,
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(c.n_q * c.H, 0), sC=(NS * c.H, 0))
+        # dM' = cv^T dT' ; dcv = dT' M'^T
+        self._gemm(1, 0, c.H, c.S * c.H, c.B * c.N, ptr(self.cvec), c.H, ptr(self.dTp), c.S * c.H,
+                   ptr(p.grad("M")), c.S * c.H)
+        self._gemm(0, 1, c.B * c.N, c.H, c.S * c.H, ptr(self.dTp), c.S * c.H, ptr(p.view("M")), c.S * c.H,
+                   ptr(self.dcvec), c.H)
+        # routing
+        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
+                   c.B * c.N, c.K, c.H, c.iters)
+        self._gemm(0, 1, c.B * c.NK, c.H, c.H, ptr(self.dehat), c.H, ptr(p.view("W_s")), c.H, ptr(self.des), c.H)
+        self._gemm(1, 0, c.H, c.H, c.B * c.NK, ptr(self.es), c.H, ptr(self.dehat), c.H, ptr(p.grad("W_s")), c.H)
+        # attention
+        self._call("indnet_attn_pool_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout), ptr(self.proj),
+                   ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre), ptr(self.dw2_part),
+                   c.X, c.L, c.H, c.n_s, c.NK)
+        self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
+        self._gemm(1, 0, c.H, c.H, c.T, ptr(self.hout), c.H, ptr(self.dpre), c.H, ptr(p.grad(ATT_K)), c.H)
+        self._call("indnet_colsum", ptr(self.dpre), c.T, c.H, c.H, ptr(p.grad(ATT_B)), 0)
+        self._gemm(0, 1, c.T, c.H, c.H, ptr(self.dpre), c.H, ptr(p.view(ATT_K)), c.H, ptr(self.dhout), c.H, beta=1.0)
+        # BPTT
+        wh_fw = p.view(FW_K)[c.D:]
+        wh_bw = p.view(BW_K)[c.D:]
+        self._call("indnet_lstm_bwd", ptr(self.dhout), ptr(self.gates), ptr(self.cstate), ptr(wh_fw), ptr(wh_bw),
+                   ptr(self.whT), ptr(self.dz), c.X, c.L, c.u, self._last_keep, self.seed, ptr(p.global_step))
+        n0 = 0 if self.trainable_words else c.E     # dx columns actually needed
+        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+            gk = p.grad(kn)
+            self._gemm(1, 0, c.D, u4, c.T, ptr(self.x), c.D, ptr(self.dz[d]), u4, ptr(gk), u4)
+            self._gemm(1, 0, c.u, u4, c.T, ptr(self.hprev[d]), c.u, ptr(self.dz[d]), u4, ptr(gk[c.D:]), u4)
+            self._call("indnet_colsum", ptr(self.dz[d]), c.T, u4, u4, ptr(p.grad(bn)), 0)
+            self._gemm(0, 1, c.T, c.D - n0, u4, ptr(self.dz[d]), u4, ptr(p.view(kn)[n0:]), u4,
+                       self.dx.data_ptr() + 4 * n0, c.D, beta=(0.0 if d == 0 else 1.0))
+        # embedding tables
+        g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
+        self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
+        self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
+        gw = None
+        if self.trainable_words:
+            gw = p.grad("word_embedding")
+            self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
+        self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
+                   ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+
+    # ------------------------------------------------------------------ update (model/base.py:94-99)
+    def adam(self, grad_scale: float = 1.0):
+        p = self.p
+        self._call("indnet_adam_step", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), p.numel,
+                   ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
+                   0.9, 0.999, 1e-8, grad_scale)
+
+    def train_step(self):
+        """fwd + bwd + Adam on the inputs currently in the static buffers (no host sync)."""
+        self.forward(train=True)
+        self.backward()
+        self.adam()
+
+    # ------------------------------------------------------------------ results
+    def loss(self) -> float:
+        return float(self.out2[0].item())
+
+    def accuracy(self) -> float:
+        return float(self.out2[1].item())

@@ -1,0 +1,72 @@
+"""Shared builders for the parity tests: seeded synthetic episodes + parameters in TF layouts."""
+import numpy as np
+import torch
+
+import induction_b200  # noqa: F401
+from induction_b200.engine import EpisodeConfig, init_tf_params, tf_param_shapes
+from induction_b200.util.synthetic import make_tables
+
+# name -> EpisodeConfig kwargs.  "smoke" = the shapes of the reference's only executable check
+# (model/layer_module.py:168-186: 3-way 3-shot 5-query, L=5, H=10, out_size=10).
+CASES = {
+    "smoke": dict(N=3, K=3, Q=5, B=1, L=5, E=6, u=5, S=10),
+    "toy_train_py": dict(N=5, K=2, Q=5, B=2, L=37, E=5, u=20, S=100),     # train.py:24-36 constants
+    "k1": dict(N=5, K=1, Q=5, B=3, L=12, E=8, u=16, S=12),                # degenerate K=1 routing
+    "ragged": dict(N=4, K=3, Q=2, B=5, L=9, E=7, u=13, S=7),              # nothing a multiple of 32/16
+    "cfg0_5w5s": dict(N=5, K=5, Q=5, B=2, L=40, E=50, u=128, S=100),      # BASELINE configs[0] shape, B=2
+}
+
+
+def make_case(name, seed=0, vocab=500, relations=12, per_relation=30, keep_prob=1.0, mode="fp32"):
+    cfg = EpisodeConfig(**CASES[name], keep_prob=keep_prob, mode=mode)
+    tables = make_tables(relations, per_relation, cfg.L, vocab, cfg.E, seed=seed, min_len=min(3, cfg.L))
+    rs = np.random.RandomState(seed + 1)
+    rows = np.zeros((cfg.B, cfg.n_s), dtype=np.int64)
+    label = np.zeros((cfg.B, cfg.n_q), dtype=np.int64)
+    for b in range(cfg.B):
+        classes = rs.choice(relations, cfg.N, replace=False)
+        sup, qry, lab = [], [], []
+        for i, c in enumerate(classes):
+            idx = c * per_relation + rs.permutation(per_relation)[: cfg.K + cfg.Q]
+            sup += list(idx[: cfg.K]); qry += list(idx[cfg.K:]); lab += [i] * cfg.Q
+        perm = rs.permutation(cfg.n_q)
+        rows[b] = np.array(sup + [qry[p] for p in perm])
+        label[b] = np.array([lab[p] for p in perm])
+    inputs = {k: tables[k][rows] for k in ("word", "pos1", "pos2", "mask")}
+    shapes = tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S)
+    params = init_tf_params(shapes, seed=seed)
+    # non-zero biases so their gradients / adds are exercised
+    g = torch.Generator().manual_seed(seed + 7)
+    for k in params:
+        if k.endswith("bias"):
+            params[k] = (torch.randn(params[k].shape, generator=g) * 0.05).float()
+    return cfg, tables, inputs, label, params
+
+
+def to_torch_inputs(inputs, label):
+    ti = {k: torch.from_numpy(np.ascontiguousarray(v)) for k, v in inputs.items()}
+    return ti, torch.from_numpy(label)
+
+
+def oracle_forward(cfg, tables, inputs, label, params, dtype=torch.float64, drop_mask=None):
+    from oracle import induction_oracle as orc
+    p = {k: v.to(dtype) for k, v in params.items()}
+    ti, tl = to_torch_inputs(inputs, label)
+    wt = torch.from_numpy(tables["word_vec_mat"]).to(dtype)
+    return orc.forward(p, wt, ti["word"], ti["pos1"], ti["pos2"], ti["mask"], tl, cfg.N, cfg.K, cfg.Q,
+                       drop_mask=drop_mask, keep_prob=cfg.keep_prob, iter_routing=cfg.iters)
+
+
+def oracle_grads(cfg, tables, inputs, label, params, dtype=torch.float64, drop_mask=None):
+    from oracle import induction_oracle as orc
+    p = {k: v.to(dtype) for k, v in params.items()}
+    ti, tl = to_torch_inputs(inputs, label)
+    wt = torch.from_numpy(tables["word_vec_mat"]).to(dtype)
+    return orc.loss_and_grads(p, wt, ti["word"], ti["pos1"], ti["pos2"], ti["mask"], tl, cfg.N, cfg.K, cfg.Q,
+                              drop_mask=drop_mask, keep_prob=cfg.keep_prob)
+
+
+def rel_err(a, b):
+    a = torch.as_tensor(a, dtype=torch.float64).cpu()
+    b = torch.as_tensor(b, dtype=torch.float64).cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-30))
