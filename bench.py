@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py - train-step episodes/sec of the Induction-Network episode pipeline on B200.
+
+  python bench.py --gpus N --steps K --warmup W          # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K --warmup W   # CPU arm (oracle port; TF 1.x absent)
+
+A "step" is one pass of the hot path over one batch of B synthetic episodes per GPU: (device
+sampler + gather when available) -> forward -> loss -> backward -> gradient all-reduce (N > 1) -> TF
+Adam.  Weak scaling: every rank runs B episodes.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# BASELINE.json configs[i] -> episode shape (Q = 5 everywhere, train.py:33; E = 50; S = 100)
+WORKLOADS = [
+    dict(name="cfg0: 5-way 5-shot, 4 episodes, L=40, u=128", N=5, K=5, B=4, L=40, u=128),
+    dict(name="cfg1: 5-way 1-shot, 64 episodes, L=40, u=128", N=5, K=1, B=64, L=40, u=128),
+    dict(name="cfg2: 10-way 5-shot, 128 episodes, L=40, u=128", N=10, K=5, B=128, L=40, u=128),
+    dict(name="cfg3: 10-way 10-shot, 1024 episodes, L=40, u=128", N=10, K=10, B=1024, L=40, u=128),
+]
+E, S, Q, VOCAB, RELS, PER_REL = 50, 100, 5, 400000, 64, 700
+
+
+def fwd_flops_per_episode(N, K, L, u):
+    """SURVEY.md section 8 FLOP formula (multiply-add = 2), forward, one episode."""
+    D, H, n_s, n_q = E + 10, 2 * u, N * (K + Q), N * Q
+    return (2 * n_s * L * D * 4 * u * 2 + 2 * n_s * L * u * 4 * u * 2 + 2 * n_s * L * H * H + 4 * n_s * L * H
+            + 2 * N * K * H * H + 3 * 4 * N * K * H + 2 * N * H * H * S + 2 * N * n_q * H * S + 2 * n_q * N * N * S)
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(int(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": int(self.samples[0][1]), "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def make_inputs(w, pool, seed=0):
+    """Synthetic FewRel-shaped tables and ``pool`` pre-sampled episode batches (host)."""
+    import numpy as np
+    from induction_b200.util.synthetic import make_tables
+    tables = make_tables(RELS, PER_REL, w["L"], VOCAB, E, seed=seed)
+    rs = np.random.RandomState(seed + 1)
+    n_s, n_q = w["N"] * (w["K"] + Q), w["N"] * Q
+    batches = []
+    for _ in range(pool):
+        rows = np.zeros((w["B"], n_s), dtype=np.int64)
+        label = np.zeros((w["B"], n_q), dtype=np.int32)
+        for b in range(w["B"]):
+            classes = rs.choice(RELS, w["N"], replace=False)
+            sup, qry, lab = [], [], []
+            for i, c in enumerate(classes):
+                idx = c * PER_REL + rs.choice(PER_REL, w["K"] + Q, replace=False)
+                sup += list(idx[: w["K"]]); qry += list(idx[w["K"]:]); lab += [i] * Q
+            perm = rs.permutation(n_q)
+            rows[b] = np.array(sup + [qry[p] for p in perm])
+            label[b] = np.array([lab[p] for p in perm])
+        batches.append(({k: np.ascontiguousarray(tables[k][rows]) for k in ("word", "pos1", "pos2", "mask")}, label))
+    return tables, batches
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_episodes_per_sec(w, tables, batches, steps, warmup, episodes_per_step, budget_s=None):
+    """The CPU arm: oracle port (torch-CPU fp32 autograd + TF-form Adam) on a bounded sample of the
+    same workload, all host threads.  Returns (episodes/s, cores, steps actually timed)."""
+    import torch
+    from oracle import induction_oracle as orc
+    from induction_b200.engine import init_tf_params, tf_param_shapes
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    params = init_tf_params(tf_param_shapes(w["N"], w["L"], E, w["u"], S), seed=0)
+    m = {k: torch.zeros_like(v) for k, v in params.items()}
+    v = {k: torch.zeros_like(x) for k, x in params.items()}
+    wt = torch.from_numpy(tables["word_vec_mat"])
+    Bc = episodes_per_step
+
+    def one(step):
+        inp, lab = batches[step % len(batches)]
+        ti = {k: torch.from_numpy(x[:Bc]) for k, x in inp.items()}
+        _, g = orc.loss_and_grads(params, wt, ti["word"], ti["pos1"], ti["pos2"], ti["mask"],
+                                  torch.from_numpy(lab[:Bc]).long(), w["N"], w["K"], Q)
+        orc.tf_adam_step(params, g, m, v, global_step=step)
+
+    for s in range(warmup):
+        one(s)
+    t0 = time.perf_counter()
+    done = 0
+    for s in range(steps):
+        one(warmup + s)
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return Bc * done / dt, cores, done
+
+
+def run_reference(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    tables, batches = make_inputs(w, pool=2)
+    Bc = min(w["B"], 4)
+    eps, cores, done = cpu_episodes_per_sec(w, tables, batches, args.steps, min(args.warmup, 2), Bc)
+    sample = "%d episodes/step (of B=%d) x %d steps, torch-CPU fp32 oracle port, fwd+autograd bwd+TF Adam" % (Bc, w["B"], done)
+    print(json.dumps({
+        "impl": "reference", "metric": "train-step episodes/sec", "value": eps, "unit": "episodes/s",
+        "n_gpus": args.gpus, "steps": done, "warmup": min(args.warmup, 2), "ms_per_step": 1000.0 * Bc / eps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": w["name"], "note": "reference TF 1.x graph unavailable on this box; CPU oracle port timed"},
+        "cpu_baseline": {"value": eps, "unit": "episodes/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": eps, "unit": "episodes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args, w):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import induction_b200  # noqa: F401
+    from induction_b200._lib import LIB
+    from induction_b200.engine import EpisodeConfig, EpisodePipeline, ParamStore, init_tf_params, tf_param_shapes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+
+    cfg = EpisodeConfig(N=w["N"], K=w["K"], Q=Q, B=w["B"], L=w["L"], E=E, u=w["u"], S=S,
+                        keep_prob=args.keep_prob, mode=args.mode)
+    POOL = 4
+    tables, batches = make_inputs(w, pool=POOL, seed=rank)
+    store = ParamStore(tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S))
+    store.load_state_dict(init_tf_params(store.tf_shapes, seed=0))
+    pipe = EpisodePipeline(cfg, store, torch.from_numpy(tables["word_vec_mat"]), seed=rank)
+    # resident input pool in HBM + pinned host copies for the e2e leg
+    dev_pool, host_pool = [], []
+    for inp, lab in batches:
+        dev_pool.append(({k: torch.from_numpy(v).cuda() for k, v in inp.items()}, torch.from_numpy(lab).cuda()))
+        host_pool.append(({k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}, torch.from_numpy(lab).pin_memory()))
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")   # 256 MB > 126 MB L2
+
+    def grad_sync():
+        if world > 1:
+            dist.all_reduce(store.grads)
+
+    def step_body():
+        pipe.forward(train=True)
+        pipe.backward()
+        grad_sync()
+        pipe.adam(grad_scale=1.0 / world)
+
+    stream = torch.cuda.Stream()
+    graph = None
+    with torch.cuda.stream(stream):
+        pipe.set_inputs(*dev_pool[0])
+        for _ in range(2):          # allocates backward buffers, sets func attributes, warms NCCL
+            step_body()
+        stream.synchronize()
+        l0 = LIB.launch_count()
+        step_body()
+        launches_per_step = LIB.launch_count() - l0
+        stream.synchronize()
+        if not args.no_graph:
+            try:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=stream):
+                    step_body()
+            except Exception as e:   # e.g. NCCL capture refused: fall back to eager launches
+                if rank == 0:
+                    print("cuda graph capture failed, eager launches: %r" % (e,), file=sys.stderr)
+                graph = None
+                torch.cuda.synchronize()
+
+        def run_step(i):
+            pipe.set_inputs(*dev_pool[i % POOL])
+            if graph is not None:
+                graph.replay()
+            else:
+                step_body()
+
+        for i in range(args.warmup):
+            run_step(i)
+        stream.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        sampler = ClockSampler(local)
+        sampler.start()
+        evs = []
+        for i in range(args.steps):
+            flush.fill_(float(i))                   # L2 flush between timed iterations (outside the event pair)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            run_step(args.warmup + i)
+            e1.record(stream)
+            evs.append((e0, e1))
+        stream.synchronize()
+        torch.cuda.synchronize()
+        sampler.stop_flag = True
+        if world > 1:
+            dist.barrier()
+        total_ms = sum(a.elapsed_time(b) for a, b in evs)
+        loss_after = pipe.loss()
+
+        # ---- roofline leg: per-call CUDA-event timing of the same step, eager launches
+        pipe.profile = []
+        for i in range(min(args.steps, 5)):
+            flush.fill_(1.0)
+            pipe.set_inputs(*dev_pool[i % POOL])
+            step_body()
+        prof = pipe.profile_summary()
+        pipe.profile = None
+        prof_steps = min(args.steps, 5)
+
+        # ---- e2e leg: the user-facing call with HOST buffers (pinned), H2D + D2H inside the timed region
+        e2e_steps = max(3, min(args.steps, 20))
+        h2d = sum(v.numel() * 4 for v in host_pool[0][0].values()) + host_pool[0][1].numel() * 4
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            pipe.set_inputs(*host_pool[i % POOL])         # H2D from pinned memory
+            if graph is not None:
+                graph.replay()
+            else:
+                step_body()
+            res = pipe.out2.cpu()                        # D2H {loss, accuracy} (synchronises)
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1000.0
+
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+    ms_per_step = total_ms / args.steps
+    value = world * cfg.B * args.steps / (total_ms / 1000.0)
+    e2e_value = world * cfg.B * e2e_steps / (e2e_ms / 1000.0)
+
+    if rank == 0:
+        # dominant call of the step and its roofline
+        dom = max(prof.items(), key=lambda kv: kv[1][1])
+        share = {k: round(v[1] / sum(x[1] for x in prof.values()), 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])[:8]}
+        dom_ms = dom[1][1] / dom[1][0]
+        calls_per_step = dom[1][0] / prof_steps
+        T = cfg.T
+        flops_tab = {   # algorithmic FLOPs per launch of the calls that can dominate
+            "indnet_lstm_fwd": 2 * T * cfg.u * 4 * cfg.u * 2,
+            "indnet_lstm_bwd": 2 * T * cfg.u * 4 * cfg.u * 2,
+            "sgemm:attn_dense": 2 * T * cfg.H * cfg.H, "sgemm:attn_dW": 2 * T * cfg.H * cfg.H,
+            "sgemm:attn_dh": 2 * T * cfg.H * cfg.H,
+            "sgemm:inproj": 2 * T * cfg.D * 4 * cfg.u, "sgemm:lstm_dWx": 2 * T * cfg.D * 4 * cfg.u,
+            "sgemm:lstm_dWh": 2 * T * cfg.u * 4 * cfg.u, "sgemm:lstm_dx": 2 * T * 10 * 4 * cfg.u,
+            "sgemm:ntn_stage1": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S, "sgemm:ntn_dM": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S,
+            "sgemm:ntn_dcv": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S,
+        }
+        peak_tf = peaks.get("bf16_tflops_sustained")
+        peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+        if peak_tf is None:
+            peak_tf, peak_src = 1400.0, "fallback (B200_PROFILING.md sustained)"
+        if dom[0] in flops_tab:
+            ach = flops_tab[dom[0]] / (dom_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": dom[0], "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                    "frac": ach / peak_tf, "traffic": None, "peak_source": peak_src,
+                    "avg_launch_ms": dom_ms, "launches_per_step": calls_per_step,
+                    "note": "FP32 parity-mode kernels run on FFMA, reported against the bf16 tensor peak"
+                    if args.mode == "fp32" else "bf16 tcgen05 mode"}
+        else:
+            roof = {"bound": "hbm", "kernel": dom[0], "achieved": None, "peak": peaks.get("hbm_gbs", 6650.0),
+                    "unit": "GB/s", "frac": None, "traffic": None, "avg_launch_ms": dom_ms}
+        roof["step_share"] = share
+        # whole-step achieved TFLOP/s (train = 3 x forward)
+        step_tflops = value * 3 * fwd_flops_per_episode(cfg.N, cfg.K, cfg.L, cfg.u) / 1e12
+        # ---- CPU baseline (oracle port) on a bounded sample, rank 0, N = 1 only
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            Bc = min(cfg.B, 4)
+            eps, cores, done = cpu_episodes_per_sec(w, tables, batches, steps=50, warmup=1,
+                                                    episodes_per_step=Bc, budget_s=args.cpu_seconds)
+            cpu = {"value": eps, "unit": "episodes/s", "cores": cores, "kind": "port",
+                   "sample": "%d episodes/step x %d steps of the same workload (fwd + autograd bwd + TF Adam), "
+                             "torch-CPU fp32 oracle; reference TF 1.x unavailable on this box" % (Bc, done)}
+        print(json.dumps({
+            "metric": "train-step episodes/sec", "value": value, "unit": "episodes/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.mode == "fp32" else "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "episodes_per_gpu": cfg.B, "global_batch": cfg.B * world,
+                       "Q": Q, "E": E, "S": S, "routing_iters": 3, "keep_prob": args.keep_prob, "mode": args.mode,
+                       "vocab": VOCAB, "relations": RELS, "instances_per_relation": PER_REL,
+                       "parallelism": "episode-sharded dp%d" % world,
+                       "cuda_graph": graph is not None,
+                       "l2": "256 MB buffer written between timed iterations (outside each step's event pair); "
+                             "step working set itself is >1 GB"},
+            "e2e": {"value": e2e_value, "unit": "episodes/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                    "steps": e2e_steps, "timer": "host perf_counter around pinned H2D + step + D2H of {loss, acc}"},
+            "gpu_launches": int(launches_per_step * args.steps),
+            "launches_per_step": int(launches_per_step),
+            "clocks": sampler.summary(),
+            "roofline": roof,
+            "step_tflops": step_tflops,
+            "cpu_baseline": cpu,
+            "loss_after": loss_after,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (0-3)")
+    ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--keep-prob", type=float, default=1.0)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    w = WORKLOADS[args.config]
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_b200(args, w)
+
+
+if __name__ == "__main__":
+    main()

@@ -32,6 +32,8 @@ typedef void* indnet_stream; /* cudaStream_t */
 /* Host string describing the last error on this thread. */
 const char* indnet_last_error(void);
 int indnet_abi_version(void);
+/* Number of CUDA kernels this library has launched in this process (bench.py's gpu_launches). */
+long long indnet_launch_count(void);
 
 /* ---- dense building blocks (FP32 parity mode) -------------------------------------------------
  * C = alpha*op(A)*op(B) + beta*C (+ bias[n]) (act: 0 none, 1 tanh, 2 relu).  Two-level batching:

@@ -30,9 +30,9 @@ def parse_header(path: str = HEADER):
     src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
     src = re.sub(r"//[^\n]*", " ", src)
     protos = {}
-    for m in re.finditer(r"(const\s+char\s*\*|int)\s+(indnet_\w+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+    for m in re.finditer(r"(const\s+char\s*\*|long long|int)\s+(indnet_\w+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
         ret, name, params = m.group(1), m.group(2), m.group(3)
-        restype = ctypes.c_char_p if "char" in ret else ctypes.c_int
+        restype = ctypes.c_char_p if "char" in ret else (ctypes.c_longlong if "long" in ret else ctypes.c_int)
         args = []
         params = " ".join(params.split())
         if params and params != "void":
@@ -75,6 +75,9 @@ class _Lib:
 
     def last_error(self) -> str:
         return self.load().indnet_last_error().decode("utf-8", "replace")
+
+    def launch_count(self) -> int:
+        return int(self.load().indnet_launch_count())
 
     def call(self, name: str, *args):
         fn = getattr(self.load(), name)

@@ -14,10 +14,13 @@ int set_error(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+static unsigned long long g_launches = 0;
+void count_launches(int n) { __atomic_add_fetch(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
 }  // namespace indnet
 
 using namespace indnet;
 
+extern "C" long long indnet_launch_count(void) { return (long long)__atomic_load_n(&indnet::g_launches, __ATOMIC_RELAXED); }
 extern "C" const char* indnet_last_error(void) { return g_err; }
 extern "C" int indnet_abi_version(void) { return INDNET_ABI_VERSION; }
 

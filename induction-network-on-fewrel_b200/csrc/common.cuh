@@ -12,6 +12,7 @@
 namespace indnet {
 
 int set_error(int code, const char* fmt, ...);
+void count_launches(int n);   // feeds indnet_launch_count(): kernels this library has launched
 
 #define IN_REQUIRE(cond, ...)                                              \
   do {                                                                     \
@@ -27,6 +28,7 @@ int set_error(int code, const char* fmt, ...);
 
 #define IN_LAUNCH_CHECK(name)                                                                 \
   do {                                                                                        \
+    ::indnet::count_launches(1);                                                              \
     cudaError_t _e = cudaGetLastError();                                                      \
     if (_e != cudaSuccess)                                                                    \
       return ::indnet::set_error(INDNET_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(_e)); \

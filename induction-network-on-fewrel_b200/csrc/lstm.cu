@@ -235,6 +235,7 @@ extern "C" int indnet_lstm_bwd(indnet_stream st_, const float* dhout, const floa
   IN_REQUIRE(smem <= 227 * 1024, "lstm_bwd: hidden size %d too large for the FP32 recurrence tile", u);
   dim3 tg(ceil_div(4 * u, 32), ceil_div(u, 32));
   transpose_kernel<<<tg, dim3(32, 8), 0, st>>>(Wh_fw, whT_scratch, u, 4 * u);
+  IN_LAUNCH_CHECK("transpose_kernel");
   transpose_kernel<<<tg, dim3(32, 8), 0, st>>>(Wh_bw, whT_scratch + (long long)4 * u * u, u, 4 * u);
   IN_LAUNCH_CHECK("transpose_kernel");
   if (smem > 48 * 1024)

@@ -223,6 +223,8 @@ class EpisodePipeline:
         self.lr0, self.decay_steps, self.decay_rate = float(lr), int(decay_steps), float(decay_rate)
         self.seed = int(seed)
         self.launches = 0
+        self.profile = None      # set to [] to collect per-call CUDA-event timings
+        self._tag = None
         c = cfg
         f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
         i32 = lambda *s: torch.zeros(*s, dtype=torch.int32, device=self.dev)  # noqa: E731
@@ -252,11 +254,36 @@ class EpisodePipeline:
 
     # ------------------------------------------------------------------ helpers
     def _call(self, name, *args):
-        LIB.call(name, current_stream(), *args)
+        if self.profile is None:
+            LIB.call(name, current_stream(), *args)
+        else:   # per-call CUDA-event timing on the launching stream (bench.py roofline leg)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            LIB.call(name, current_stream(), *args)
+            e1.record()
+            self.profile.append((self._tag or name, e0, e1))
         self.launches += 1
 
+    def profile_summary(self):
+        """{tag: (calls, total_ms)} from the events collected while ``self.profile`` was a list."""
+        torch.cuda.synchronize()
+        out = {}
+        for tag, e0, e1 in self.profile or []:
+            n, ms = out.get(tag, (0, 0.0))
+            out[tag] = (n + 1, ms + e0.elapsed_time(e1))
+        return out
+
     def _gemm(self, tA, tB, M, N, K, A, lda, Bm, ldb, C, ldc, alpha=1.0, beta=0.0, bias=None, act=0,
-              batch=1, inner=1, sA=(0, 0), sB=(0, 0), sC=(0, 0), splitk=0):
+              batch=1, inner=1, sA=(0, 0), sB=(0, 0), sC=(0, 0), splitk=0, tag=None):
+        self._tag = ("sgemm:" + tag) if tag else None
+        try:
+            self._gemm_call(tA, tB, M, N, K, A, lda, Bm, ldb, C, ldc, alpha, beta, bias, act, batch, inner,
+                            sA, sB, sC, splitk)
+        finally:
+            self._tag = None
+
+    def _gemm_call(self, tA, tB, M, N, K, A, lda, Bm, ldb, C, ldc, alpha, beta, bias, act, batch, inner,
+                   sA, sB, sC, splitk):
         self._call("indnet_sgemm", int(tA), int(tB), M, N, K, alpha, A, lda, Bm, ldb, beta, C, ldc,
                    ptr(bias) if isinstance(bias, torch.Tensor) else bias, act, batch, inner,
                    sA[0], sA[1], sB[0], sB[1], sC[0], sC[1], splitk)
@@ -282,25 +309,25 @@ class EpisodePipeline:
         # a3: input projection for all timesteps (first D rows of the TF LSTM kernel) + recurrence
         for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
             self._gemm(0, 0, c.T, u4, c.D, ptr(self.x), c.D, ptr(p.view(kn)), u4, ptr(self.xproj[d]), u4,
-                       bias=p.view(bn))
+                       bias=p.view(bn), tag="inproj")
         wh_fw = p.view(FW_K)[c.D:]
         wh_bw = p.view(BW_K)[c.D:]
         self._call("indnet_lstm_fwd", ptr(self.xproj), ptr(wh_fw), ptr(wh_bw), ptr(self.hout), ptr(self.gates),
                    ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
         # a4: Dense+tanh, then score/softmax/pool, split into support | query (a5)
         self._gemm(0, 0, c.T, c.H, c.H, ptr(self.hout), c.H, ptr(p.view(ATT_K)), c.H, ptr(self.proj), c.H,
-                   bias=p.view(ATT_B), act=1)
+                   bias=p.view(ATT_B), act=1, tag="attn_dense")
         self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
                    ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
         # a6/a7: e_hat = e_s W_s once, then the routing iterations
-        self._gemm(0, 0, c.B * c.NK, c.H, c.H, ptr(self.es), c.H, ptr(p.view("W_s")), c.H, ptr(self.ehat), c.H)
+        self._gemm(0, 0, c.B * c.NK, c.H, c.H, ptr(self.es), c.H, ptr(p.view("W_s")), c.H, ptr(self.ehat), c.H, tag="routing_transform")
         self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
         # a8: T'[b,c][k][j] = cv M' ; V[b][q][c*S+k] = qe_b T'_b^T
         self._gemm(0, 0, c.B * c.N, c.S * c.H, c.H, ptr(self.cvec), c.H, ptr(p.view("M")), c.S * c.H,
-                   ptr(self.Tp), c.S * c.H)
+                   ptr(self.Tp), c.S * c.H, tag="ntn_stage1")
         NS = c.N * c.S
         self._gemm(0, 1, c.n_q, NS, c.H, ptr(self.eq), c.H, ptr(self.Tp), c.H, ptr(self.V), NS,
-                   batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0))
+                   batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0), tag="ntn_stage2")
         # a8-a10: relu, FC, sigmoid, squared error, argmax hit
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
@@ -340,27 +367,27 @@ class EpisodePipeline:
                    1.0 / (rows * c.N))
         # dqe_b = dV_b T'_b ; dT'_b = dV_b^T qe_b
         self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
-                   batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0))
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0), tag="ntn_dqe")
         self._gemm(1, 0, NS, c.H, c.n_q, ptr(self.dV), NS, ptr(self.eq), c.H, ptr(self.dTp), c.H,
-                   batch=c.B, sA=(c.n_q * NS, 0), sB=(c.n_q * c.H, 0), sC=(NS * c.H, 0))
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(c.n_q * c.H, 0), sC=(NS * c.H, 0), tag="ntn_dT")
         # dM' = cv^T dT' ; dcv = dT' M'^T
         self._gemm(1, 0, c.H, c.S * c.H, c.B * c.N, ptr(self.cvec), c.H, ptr(self.dTp), c.S * c.H,
-                   ptr(p.grad("M")), c.S * c.H)
+                   ptr(p.grad("M")), c.S * c.H, tag="ntn_dM")
         self._gemm(0, 1, c.B * c.N, c.H, c.S * c.H, ptr(self.dTp), c.S * c.H, ptr(p.view("M")), c.S * c.H,
-                   ptr(self.dcvec), c.H)
+                   ptr(self.dcvec), c.H, tag="ntn_dcv")
         # routing
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
                    c.B * c.N, c.K, c.H, c.iters)
-        self._gemm(0, 1, c.B * c.NK, c.H, c.H, ptr(self.dehat), c.H, ptr(p.view("W_s")), c.H, ptr(self.des), c.H)
-        self._gemm(1, 0, c.H, c.H, c.B * c.NK, ptr(self.es), c.H, ptr(self.dehat), c.H, ptr(p.grad("W_s")), c.H)
+        self._gemm(0, 1, c.B * c.NK, c.H, c.H, ptr(self.dehat), c.H, ptr(p.view("W_s")), c.H, ptr(self.des), c.H, tag="routing_des")
+        self._gemm(1, 0, c.H, c.H, c.B * c.NK, ptr(self.es), c.H, ptr(self.dehat), c.H, ptr(p.grad("W_s")), c.H, tag="routing_dWs")
         # attention
         self._call("indnet_attn_pool_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout), ptr(self.proj),
                    ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre), ptr(self.dw2_part),
                    c.X, c.L, c.H, c.n_s, c.NK)
         self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
-        self._gemm(1, 0, c.H, c.H, c.T, ptr(self.hout), c.H, ptr(self.dpre), c.H, ptr(p.grad(ATT_K)), c.H)
+        self._gemm(1, 0, c.H, c.H, c.T, ptr(self.hout), c.H, ptr(self.dpre), c.H, ptr(p.grad(ATT_K)), c.H, tag="attn_dW")
         self._call("indnet_colsum", ptr(self.dpre), c.T, c.H, c.H, ptr(p.grad(ATT_B)), 0)
-        self._gemm(0, 1, c.T, c.H, c.H, ptr(self.dpre), c.H, ptr(p.view(ATT_K)), c.H, ptr(self.dhout), c.H, beta=1.0)
+        self._gemm(0, 1, c.T, c.H, c.H, ptr(self.dpre), c.H, ptr(p.view(ATT_K)), c.H, ptr(self.dhout), c.H, beta=1.0, tag="attn_dh")
         # BPTT
         wh_fw = p.view(FW_K)[c.D:]
         wh_bw = p.view(BW_K)[c.D:]
@@ -369,11 +396,11 @@ class EpisodePipeline:
         n0 = 0 if self.trainable_words else c.E     # dx columns actually needed
         for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
             gk = p.grad(kn)
-            self._gemm(1, 0, c.D, u4, c.T, ptr(self.x), c.D, ptr(self.dz[d]), u4, ptr(gk), u4)
-            self._gemm(1, 0, c.u, u4, c.T, ptr(self.hprev[d]), c.u, ptr(self.dz[d]), u4, ptr(gk[c.D:]), u4)
+            self._gemm(1, 0, c.D, u4, c.T, ptr(self.x), c.D, ptr(self.dz[d]), u4, ptr(gk), u4, tag="lstm_dWx")
+            self._gemm(1, 0, c.u, u4, c.T, ptr(self.hprev[d]), c.u, ptr(self.dz[d]), u4, ptr(gk[c.D:]), u4, tag="lstm_dWh")
             self._call("indnet_colsum", ptr(self.dz[d]), c.T, u4, u4, ptr(p.grad(bn)), 0)
             self._gemm(0, 1, c.T, c.D - n0, u4, ptr(self.dz[d]), u4, ptr(p.view(kn)[n0:]), u4,
-                       self.dx.data_ptr() + 4 * n0, c.D, beta=(0.0 if d == 0 else 1.0))
+                       self.dx.data_ptr() + 4 * n0, c.D, beta=(0.0 if d == 0 else 1.0), tag="lstm_dx")
         # embedding tables
         g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
         self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
