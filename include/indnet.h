@@ -76,6 +76,16 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
                     const float* Wh_bw, float* whT_scratch, float* dz, int X, int L, int u, float keep_prob,
                     unsigned long long seed, const long long* seed_step);
 
+/* No counterpart in the reference.  Same computation as indnet_lstm_bwd for callers that must not
+ * allocate device memory (custom-op / plugin callbacks that only get input and output buffers,
+ * loops that cannot afford cudaMalloc's device synchronisation): the [2][4u][u] scratch is a fixed
+ * 512 KiB __device__ array inside the library, so u <= 128 (larger u is rejected with an error).
+ * The first call on each device looks up the array's address - make it before any stream capture.
+ * All calls on a GPU share the array: calls that can overlap on the device race; serialise them. */
+int indnet_lstm_bwd_static(indnet_stream st, const float* dhout, const float* gates, const float* cstate,
+                           const float* Wh_fw, const float* Wh_bw, float* dz, int X, int L, int u, float keep_prob,
+                           unsigned long long seed, const long long* seed_step);
+
 /* ---- a4/a5: self_attention, model/layer_module.py:49-98 (pooling part; Dense+tanh is a GEMM) and
  * the support/query split of model/graph.py:57-62 ------------------------------------------------
  * proj [X][L][H] = tanh(hout*Wa1+ba1); mask [X][L] raw {0,1,2,3} (binarised as model/graph.py:52).

@@ -245,3 +245,71 @@ extern "C" int indnet_lstm_bwd(indnet_stream st_, const float* dhout, const floa
   IN_LAUNCH_CHECK("lstm_bwd_kernel");
   return INDNET_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// indnet_lstm_bwd_static: the BPTT entry point for callers that are not allowed to allocate.
+//
+// indnet_lstm_bwd needs a [2][4u][u] float scratch for the transposed recurrent weights and makes
+// the caller provide it.  Some callers cannot: code running inside a host framework whose device
+// allocator they do not own (a TF / JAX custom-op or a plugin callback that only receives the input
+// and output buffers), real-time loops that forbid cudaMalloc because it synchronises the device,
+// and processes whose whole memory budget was handed to another pool at start-up.  For them the
+// scratch lives in this library's image: a fixed file-scope __device__ array sized for u <= 128
+// (512 KiB).  Every GPU that loads the library carries those 512 KiB until the process exits.
+//
+// Rules that follow from the scratch being one shared array per device:
+//  * u > INDNET_STATIC_MAX_U is rejected with an error - the array is not grown.
+//  * Calls that may overlap on the same GPU (different streams, different host threads) race on it;
+//    serialise them.  The array keeps whatever the last call wrote; nothing in it has to start at
+//    zero because each call rewrites the [2][4u][u] region it uses before reading it.
+//  * The device address of the array is looked up once per device, on the first call made with
+//    that device current (cudaGetSymbolAddress; the array's name in host code is only a host-side
+//    handle, not a device pointer).  Make that first call before starting any stream capture.
+//  * No cudaMalloc / cudaFree / allocating library routine is called here.
+#define INDNET_STATIC_MAX_U 128
+#define INDNET_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_whT_static[2 * 4 * INDNET_STATIC_MAX_U * INDNET_STATIC_MAX_U];
+static float* g_whT_static_addr[INDNET_STATIC_MAX_DEVICES] = {nullptr};
+
+static int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  IN_CUDA(cudaGetDevice(&dev));
+  IN_REQUIRE(dev >= 0 && dev < INDNET_STATIC_MAX_DEVICES, "lstm_bwd_static: device ordinal %d out of range", dev);
+  float* p = __atomic_load_n(&g_whT_static_addr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    IN_CUDA(cudaGetSymbolAddress((void**)&p, g_whT_static));
+    IN_REQUIRE(p != nullptr, "lstm_bwd_static: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_whT_static_addr[dev], p, __ATOMIC_RELEASE);   // same value from any thread
+  }
+  *out = p;
+  return INDNET_OK;
+}
+
+extern "C" int indnet_lstm_bwd_static(indnet_stream st_, const float* dhout, const float* gates, const float* cstate,
+                                      const float* Wh_fw, const float* Wh_bw, float* dz, int X, int L, int u,
+                                      float keep_prob, unsigned long long seed, const long long* seed_step) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(X >= 0 && L > 0 && u > 0, "lstm_bwd_static: bad sizes X=%d L=%d u=%d", X, L, u);
+  IN_REQUIRE(u <= INDNET_STATIC_MAX_U,
+             "lstm_bwd_static: hidden size u=%d exceeds the built-in scratch (max u=%d); use indnet_lstm_bwd with "
+             "caller-provided scratch", u, INDNET_STATIC_MAX_U);
+  IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_bwd_static: keep_prob must be in (0, 1], got %f", keep_prob);
+  if (X == 0) return INDNET_OK;
+  IN_REQUIRE(dhout && gates && cstate && Wh_fw && Wh_bw && dz, "lstm_bwd_static: null pointer");
+  float* whT = nullptr;
+  int rc = static_scratch_for_current_device(&whT);
+  if (rc != INDNET_OK) return rc;
+  size_t smem = sizeof(float) * 6 * u * SB;
+  dim3 tg(ceil_div(4 * u, 32), ceil_div(u, 32));
+  transpose_kernel<<<tg, dim3(32, 8), 0, st>>>(Wh_fw, whT, u, 4 * u);
+  IN_LAUNCH_CHECK("transpose_kernel");
+  transpose_kernel<<<tg, dim3(32, 8), 0, st>>>(Wh_bw, whT + (long long)4 * u * u, u, 4 * u);
+  IN_LAUNCH_CHECK("transpose_kernel");
+  if (smem > 48 * 1024)
+    IN_CUDA(cudaFuncSetAttribute(lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(ceil_div(X, SB), 2);
+  lstm_bwd_kernel<<<grid, LSTM_NT, smem, st>>>(dhout, gates, cstate, whT, dz, X, L, u, keep_prob, seed, seed_step);
+  IN_LAUNCH_CHECK("lstm_bwd_kernel");
+  return INDNET_OK;
+}
