@@ -44,18 +44,27 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
+        self.ready = self.armed = False
 
     def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                if len(f) >= 6:
+        # one long-running nvidia-smi in loop mode (20 ms period) - starting a process per sample is
+        # too slow to land samples inside a sub-second timed region
+        try:
+            proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                     "--format=csv,noheader,nounits", "-lms", "20"],
+                                    stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            return
+        self.ready = True
+        try:
+            for line in proc.stdout:
+                if self.stop_flag:
+                    break
+                f = [x.strip() for x in line.strip().split(",")]
+                if len(f) >= 6 and self.armed:
                     self.samples.append(f)
-            except Exception:
-                pass
-            time.sleep(0.05)
+        finally:
+            proc.terminate()
 
     def summary(self):
         if not self.samples:
@@ -174,6 +183,13 @@ def run_b200(args, w):
     store = ParamStore(tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S))
     store.load_state_dict(init_tf_params(store.tf_shapes, seed=0))
     pipe = EpisodePipeline(cfg, store, torch.from_numpy(tables["word_vec_mat"]), seed=rank)
+    # device episode sampler: per-rank streams seeded random.seed(rank) / np.random.seed(rank)
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    loader = JSONFileDataLoader.from_tables(tables)
+    smp = loader._device()
+    smp.seed(rank)
+    pipe_inputs = dict(word=pipe.word, pos1=pipe.pos1, pos2=pipe.pos2, mask=pipe.mask, label=pipe.label)
+    side = torch.cuda.Stream()
     # resident input pool in HBM + pinned host copies for the e2e leg
     dev_pool, host_pool = [], []
     for inp, lab in batches:
@@ -183,18 +199,30 @@ def run_b200(args, w):
 
     def grad_sync():
         if world > 1:
-            dist.all_reduce(store.grads)
+            dist.all_reduce(store.grads)      # one flat all-reduce (induction_b200.dist.allreduce_sum_)
 
-    def step_body():
+    def train_body():
         pipe.forward(train=True)
         pipe.backward()
         grad_sync()
         pipe.adam(grad_scale=1.0 / world)
 
+    def step_body():
+        # picks drawn during the previous step -> this step's inputs; then the serial stream walk for
+        # the NEXT step runs on a side stream underneath this step's forward/backward/update
+        smp.enqueue_gather(cfg.B, cfg.N, cfg.K, cfg.Q, out=pipe_inputs)
+        cur = torch.cuda.current_stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            smp.enqueue_walk(cfg.B, cfg.N, cfg.K, cfg.Q)
+        train_body()
+        cur.wait_stream(side)
+
     stream = torch.cuda.Stream()
     graph = None
     with torch.cuda.stream(stream):
         pipe.set_inputs(*dev_pool[0])
+        smp.enqueue_walk(cfg.B, cfg.N, cfg.K, cfg.Q)      # prologue: picks for the first step
         for _ in range(2):          # allocates backward buffers, sets func attributes, warms NCCL
             step_body()
         stream.synchronize()
@@ -202,32 +230,39 @@ def run_b200(args, w):
         step_body()
         launches_per_step = LIB.launch_count() - l0
         stream.synchronize()
+        graph_train = None
         if not args.no_graph:
             try:
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph, stream=stream):
                     step_body()
+                graph_train = torch.cuda.CUDAGraph()       # host-fed variant for the e2e leg
+                with torch.cuda.graph(graph_train, stream=stream):
+                    train_body()
             except Exception as e:   # e.g. NCCL capture refused: fall back to eager launches
                 if rank == 0:
                     print("cuda graph capture failed, eager launches: %r" % (e,), file=sys.stderr)
-                graph = None
+                graph = graph_train = None
                 torch.cuda.synchronize()
 
         def run_step(i):
-            pipe.set_inputs(*dev_pool[i % POOL])
             if graph is not None:
                 graph.replay()
             else:
                 step_body()
 
+        sampler = ClockSampler(local)
+        sampler.start()
         for i in range(args.warmup):
             run_step(i)
         stream.synchronize()
+        t_wait = time.time()
+        while not sampler.ready and time.time() - t_wait < 3.0:
+            time.sleep(0.01)
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        sampler = ClockSampler(local)
-        sampler.start()
+        sampler.armed = True
         evs = []
         for i in range(args.steps):
             flush.fill_(float(i))                   # L2 flush between timed iterations (outside the event pair)
@@ -238,6 +273,8 @@ def run_b200(args, w):
             evs.append((e0, e1))
         stream.synchronize()
         torch.cuda.synchronize()
+        time.sleep(0.03)                      # let the last in-flight sample of the region land
+        sampler.armed = False
         sampler.stop_flag = True
         if world > 1:
             dist.barrier()
@@ -246,13 +283,21 @@ def run_b200(args, w):
 
         # ---- roofline leg: per-call CUDA-event timing of the same step, eager launches
         pipe.profile = []
+        smp_ev = []
         for i in range(min(args.steps, 5)):
             flush.fill_(1.0)
-            pipe.set_inputs(*dev_pool[i % POOL])
-            step_body()
+            smp.enqueue_gather(cfg.B, cfg.N, cfg.K, cfg.Q, out=pipe_inputs)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            smp.enqueue_walk(cfg.B, cfg.N, cfg.K, cfg.Q)      # serial here: timed on its own
+            e1.record()
+            smp_ev.append((e0, e1))
+            train_body()
         prof = pipe.profile_summary()
         pipe.profile = None
         prof_steps = min(args.steps, 5)
+        sampler_walk_ms = sum(a.elapsed_time(b) for a, b in smp_ev) / len(smp_ev)
+        smp.check()
 
         # ---- e2e leg: the user-facing call with HOST buffers (pinned), H2D + D2H inside the timed region
         e2e_steps = max(3, min(args.steps, 20))
@@ -263,10 +308,10 @@ def run_b200(args, w):
         t0 = time.perf_counter()
         for i in range(e2e_steps):
             pipe.set_inputs(*host_pool[i % POOL])         # H2D from pinned memory
-            if graph is not None:
-                graph.replay()
+            if graph_train is not None:
+                graph_train.replay()
             else:
-                step_body()
+                train_body()
             res = pipe.out2.cpu()                        # D2H {loss, accuracy} (synchronises)
         torch.cuda.synchronize()
         e2e_ms = (time.perf_counter() - t0) * 1000.0
@@ -341,6 +386,8 @@ def run_b200(args, w):
             "clocks": sampler.summary(),
             "roofline": roof,
             "step_tflops": step_tflops,
+            "sampler": {"where": "device, bit-exact MT19937 x2 (csrc/sampler.cu), walk for step t+1 overlapped on a "
+                                 "side stream inside the step graph", "walk_ms_serial": sampler_walk_ms},
             "cpu_baseline": cpu,
             "loss_after": loss_after,
         }))
@@ -351,7 +398,7 @@ def run_b200(args, w):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (0-3)")

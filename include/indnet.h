@@ -53,6 +53,28 @@ int indnet_permute021(indnet_stream st, const float* in, float* out, int d0, int
 /* cudaMemsetAsync on the stream (gradient regions that accumulate must start at zero). */
 int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);
 
+/* ---- a1: JSONFileDataLoader.next_one_tf, util/data_loader.py:259-309 --------------------------
+ * Samples B consecutive episodes and gathers their rows, bit-exact with the reference's draws.
+ * py_state / np_state: device uint32[625] = MT19937 key[624] + pos, the layouts of random.getstate()
+ * and np.random.get_state(); advanced in place.  scopes [R][2] = rel2scope values in dict order;
+ * t_* the four [instances][L] int32 tables; n_max >= the largest scope.  scratch: caller-provided,
+ * indnet_sampler_scratch_bytes(...) bytes.  Outputs: rows [B][n_s] (row ids, support class-major then
+ * permuted queries), labels [B][N*Q], o_* [B][n_s][L].  status (device int): 0 ok, 1 = a sampled
+ * relation has fewer than K+Q instances, 2 = a scope exceeds n_max. */
+long long indnet_sampler_scratch_bytes(int B, int N, int K, int Q, int n_max);
+int indnet_sample_episodes(indnet_stream st, unsigned int* py_state, unsigned int* np_state, const int* scopes, int R,
+                           const int* t_word, const int* t_pos1, const int* t_pos2, const int* t_mask, int L, int B,
+                           int N, int K, int Q, int n_max, void* scratch, int* rows, int* labels, int* o_word,
+                           int* o_pos1, int* o_pos2, int* o_mask, int* status);
+
+/* The same in two halves so the serial stream walk of step t+1 can overlap the train step t on a
+ * side stream: walk = draws -> picks in `scratch`; gather = picks -> rows/labels/gathered tables. */
+int indnet_sample_walk(indnet_stream st, unsigned int* py_state, unsigned int* np_state, const int* scopes, int R,
+                       int B, int N, int K, int Q, int n_max, void* scratch, int* status);
+int indnet_sample_gather(indnet_stream st, const int* scopes, const int* t_word, const int* t_pos1, const int* t_pos2,
+                         const int* t_mask, int L, int B, int N, int K, int Q, int n_max, const void* scratch,
+                         int* rows, int* labels, int* o_word, int* o_pos1, int* o_pos2, int* o_mask);
+
 /* ---- a2: Base.get_embedding, model/base.py:76-86 --------------------------------------------- */
 int indnet_embed_fwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* word_table,
                      const float* pos1_table, const float* pos2_table, float* x /*[T][D]*/, long long T, int E, int P);

@@ -1,0 +1,119 @@
+"""Device episode sampler: host wrapper of ``indnet_sample_episodes`` (csrc/sampler.cu).
+
+Keeps the two MT19937 streams of the reference's sampler (``random`` and NumPy's legacy global
+stream, util/data_loader.py:260,267,296) on the GPU as (key[624], pos) arrays.  ``load_host_streams``
+/ ``store_host_streams`` move them from / to the ``random`` and ``numpy.random`` modules, so a program
+may mix host draws and device draws and get exactly the sequence the reference would.
+"""
+from __future__ import annotations
+
+import random
+
+import numpy as np
+import torch
+
+from ._lib import LIB, IndnetError, current_stream, ptr, require_cuda
+
+KEYS = ("word", "pos1", "pos2", "mask")
+
+
+class DeviceEpisodeSampler:
+    def __init__(self, loader, device="cuda"):
+        require_cuda()
+        LIB.load()
+        self.device = torch.device(device)
+        self.L = int(loader.max_length)
+        sc = loader.scopes()
+        if len(sc) > 1024:
+            raise ValueError("at most 1024 relations are supported by the device sampler")
+        self.R = len(sc)
+        self.n_max = max(b - a for a, b in sc)
+        self.scopes = torch.tensor(sc, dtype=torch.int32, device=self.device).contiguous()
+        self.tables = {k: torch.from_numpy(np.ascontiguousarray(getattr(loader, "data_" + k), dtype=np.int32))
+                       .to(self.device) for k in KEYS}
+        self.py_state = torch.zeros(625, dtype=torch.int32, device=self.device)
+        self.np_state = torch.zeros(625, dtype=torch.int32, device=self.device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._bufs = {}
+        self.load_host_streams()
+
+    # ------------------------------------------------------------------ stream hand-over
+    def load_host_streams(self):
+        st = random.getstate()[1]
+        self.py_state.copy_(torch.from_numpy(np.array(st, dtype=np.uint32).view(np.int32)))
+        ns = np.random.get_state()
+        arr = np.concatenate([np.asarray(ns[1], dtype=np.uint32), np.array([ns[2]], dtype=np.uint32)])
+        self.np_state.copy_(torch.from_numpy(arr.view(np.int32)))
+
+    def store_host_streams(self):
+        py = self.py_state.cpu().numpy().view(np.uint32)
+        random.setstate((3, tuple(int(x) for x in py), None))
+        ns = self.np_state.cpu().numpy().view(np.uint32)
+        np.random.set_state(("MT19937", ns[:624].copy(), int(ns[624]), 0, 0.0))
+
+    def seed(self, seed: int):
+        """random.seed(seed); np.random.seed(seed) - then move both streams to the device."""
+        random.seed(seed)
+        np.random.seed(seed)
+        self.load_host_streams()
+
+    # ------------------------------------------------------------------ sampling
+    def buffers(self, B, N, K, Q):
+        key = (B, N, K, Q)
+        if key not in self._bufs:
+            n_s, n_q = N * (K + Q), N * Q
+            nbytes = LIB.load().indnet_sampler_scratch_bytes(B, N, K, Q, self.n_max)
+            z = lambda *s: torch.zeros(*s, dtype=torch.int32, device=self.device)  # noqa: E731
+            self._bufs[key] = dict(scratch=torch.zeros(nbytes, dtype=torch.uint8, device=self.device),
+                                   rows=z(B, n_s), label=z(B, n_q), **{k: z(B, n_s, self.L) for k in KEYS})
+        return self._bufs[key]
+
+    def enqueue(self, B, N, K, Q, out=None):
+        """Enqueues sampling + gather of B episodes on the current stream (no host sync).  ``out``:
+        optional dict of preallocated int32 CUDA tensors (word/pos1/pos2/mask [B,n_s,L], label [B,n_q],
+        rows [B,n_s]); the sampler's own static buffers otherwise."""
+        if N > self.R:
+            raise ValueError("Sample larger than population or is negative")
+        bufs = self.buffers(B, N, K, Q)
+        o = dict(bufs)
+        if out is not None:
+            o.update(out)
+        LIB.call("indnet_sample_episodes", current_stream(), ptr(self.py_state), ptr(self.np_state),
+                 ptr(self.scopes), self.R, ptr(self.tables["word"]), ptr(self.tables["pos1"]),
+                 ptr(self.tables["pos2"]), ptr(self.tables["mask"]), self.L, B, N, K, Q, self.n_max,
+                 ptr(bufs["scratch"]), ptr(o["rows"]), ptr(o["label"]), ptr(o["word"]), ptr(o["pos1"]),
+                 ptr(o["pos2"]), ptr(o["mask"]), ptr(self.status))
+        return o
+
+    def enqueue_walk(self, B, N, K, Q):
+        """First half: walk both streams for B episodes and leave the picks in the scratch buffer."""
+        if N > self.R:
+            raise ValueError("Sample larger than population or is negative")
+        bufs = self.buffers(B, N, K, Q)
+        LIB.call("indnet_sample_walk", current_stream(), ptr(self.py_state), ptr(self.np_state), ptr(self.scopes),
+                 self.R, B, N, K, Q, self.n_max, ptr(bufs["scratch"]), ptr(self.status))
+
+    def enqueue_gather(self, B, N, K, Q, out=None):
+        """Second half: picks -> row ids, labels and the gathered [B, n_s, L] tables."""
+        bufs = self.buffers(B, N, K, Q)
+        o = dict(bufs)
+        if out is not None:
+            o.update(out)
+        LIB.call("indnet_sample_gather", current_stream(), ptr(self.scopes), ptr(self.tables["word"]),
+                 ptr(self.tables["pos1"]), ptr(self.tables["pos2"]), ptr(self.tables["mask"]), self.L, B, N, K, Q,
+                 self.n_max, ptr(bufs["scratch"]), ptr(o["rows"]), ptr(o["label"]), ptr(o["word"]), ptr(o["pos1"]),
+                 ptr(o["pos2"]), ptr(o["mask"]))
+        return o
+
+    def check(self):
+        """Synchronising status check (mirrors the ValueError np.random.choice raises on the host)."""
+        s = int(self.status.item())
+        if s == 1:
+            raise ValueError("Cannot take a larger sample than population when 'replace=False'")
+        if s != 0:
+            raise IndnetError("device sampler failed with status %d" % s)
+
+    def sample(self, B, N, K, Q):
+        o = self.enqueue(B, N, K, Q)
+        self.check()
+        return o

@@ -1,0 +1,104 @@
+"""GPU: the device sampler + gather (indnet_sample_episodes through JSONFileDataLoader) is bit-exact
+with fixtures produced by the reference's own next_one_tf, hands the streams back exactly, and at
+BASELINE sizes equals the stdlib-driven oracle on the same seeds."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sampler_oracle as so
+
+pytestmark = pytest.mark.gpu
+KEYS = ("word", "pos1", "pos2", "mask")
+
+
+def _loader_from_golden(z):
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    tables = {"word": z["data_word"], "pos1": z["data_pos1"], "pos2": z["data_pos2"], "mask": z["data_mask"],
+              "length": z["data_length"], "rel2scope": json.loads(str(z["rel2scope"])),
+              "word_vec_mat": z["word_vec_mat"]}
+    return JSONFileDataLoader.from_tables(tables)
+
+
+@pytest.mark.parametrize("name", ["tiny", "wide"])
+def test_next_one_tf_bit_exact_vs_reference_fixtures(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, "sampler_%s.npz" % name))
+    ld = _loader_from_golden(z)
+    seed = int(z["seed"])
+    random.seed(seed); np.random.seed(seed)
+    e = 0
+    for (N, K, Q, count) in z["plan"]:
+        for _ in range(int(count)):
+            inputs, label = ld.next_one_tf(int(N), int(K), int(Q))
+            for k in KEYS:
+                assert inputs[k].dtype == np.int32
+                assert np.array_equal(inputs[k], z["ep%d_%s" % (e, k)]), (name, e, k)
+            assert np.array_equal(label, z["ep%d_label" % e]), (name, e)
+            e += 1
+    # streams handed back to the host modules are where the reference left them
+    assert np.array_equal(np.array(random.getstate()[1], dtype=np.uint64), z["py_state_after"])
+    a = np.random.randint(0, 2 ** 31 - 1, size=8)
+    np.random.set_state(("MT19937", z["np_key_after"], int(z["np_pos_after"]), 0, 0.0))
+    assert np.array_equal(a, np.random.randint(0, 2 ** 31 - 1, size=8))
+
+
+@pytest.mark.parametrize("B,N,K,Q", [(64, 5, 1, 5), (16, 10, 5, 5), (3, 20, 10, 5)])
+def test_next_batch_equals_consecutive_reference_draws_at_baseline_sizes(B, N, K, Q):
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    from induction_b200.util.synthetic import make_tables
+    tables = make_tables(64, 700, 40, 5000, 8, seed=0)      # FewRel train layout: 64 relations x 700
+    ld = JSONFileDataLoader.from_tables(tables)
+    scopes = ld.scopes()
+    for seed in (0, 123):
+        random.seed(seed); np.random.seed(seed)
+        want = [so.next_one_tf_stdlib(tables, scopes, N, K, Q) for _ in range(B)]
+        host_next = (random.random(), float(np.random.rand()))
+        random.seed(seed); np.random.seed(seed)
+        inputs, label = ld.next_batch(B, N, K, Q)
+        assert inputs["word"].is_cuda and inputs["word"].shape == (B, N * (K + Q), 40)
+        for b in range(B):
+            for k in KEYS:
+                assert np.array_equal(inputs[k][b].cpu().numpy(), want[b][0][k]), (seed, b, k)
+            assert np.array_equal(label[b].cpu().numpy(), want[b][1]), (seed, b)
+        rows = ld._device().buffers(B, N, K, Q)["rows"].cpu().numpy()
+        assert np.array_equal(rows, np.stack([w[2] for w in want]))
+        # host draws after the device batch continue the same streams
+        assert (random.random(), float(np.random.rand())) == host_next
+
+
+def test_ragged_scopes_and_two_batches_in_a_row():
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    rs = np.random.RandomState(5)
+    sizes = [7, 33, 64, 9, 128, 700, 12, 1023, 1024, 1025, 8, 31, 32, 65, 17, 300, 6, 21, 22, 40, 41, 513]
+    I, L = sum(sizes), 6
+    lo = np.cumsum([0] + sizes)
+    tables = {k: rs.randint(0, 50, size=(I, L)).astype(np.int32) for k in KEYS}
+    tables.update(length=np.full(I, L, np.int32), word_vec_mat=np.zeros((52, 4), np.float32),
+                  rel2scope={"R%d" % i: [int(lo[i]), int(lo[i + 1])] for i in range(len(sizes))})
+    ld = JSONFileDataLoader.from_tables(tables)
+    random.seed(9); np.random.seed(9)
+    want = [so.next_one_tf_stdlib(tables, ld.scopes(), 6, 2, 4) for _ in range(40)]
+    random.seed(9); np.random.seed(9)
+    got = []
+    for _ in range(2):
+        inputs, label = ld.next_batch(20, 6, 2, 4)
+        got += [({k: inputs[k][b].cpu().numpy() for k in KEYS}, label[b].cpu().numpy()) for b in range(20)]
+    for b in range(40):
+        for k in KEYS:
+            assert np.array_equal(got[b][0][k], want[b][0][k]), (b, k)
+        assert np.array_equal(got[b][1], want[b][1])
+
+
+def test_too_few_instances_raises_like_numpy_choice():
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    tables = {k: np.zeros((12, 4), np.int32) for k in KEYS}
+    tables.update(length=np.full(12, 4, np.int32), word_vec_mat=np.zeros((3, 2), np.float32),
+                  rel2scope={"a": [0, 4], "b": [4, 8], "c": [8, 12]})
+    ld = JSONFileDataLoader.from_tables(tables)
+    with pytest.raises(ValueError, match="larger sample than population"):
+        ld.next_one_tf(2, 3, 2)
+    with pytest.raises(ValueError, match="Sample larger than population"):
+        ld.next_one_tf(4, 1, 1)
