@@ -37,43 +37,43 @@ def fwd_flops_per_episode(N, K, L, u):
 
 
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Samples SM clock and throttle reasons through NVML every few ms while ``armed`` (the timed
+    region).  In-process NVML: spawning nvidia-smi per sample is too slow for sub-second regions."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
         self.ready = self.armed = False
+        self.max_mhz = None
 
     def run(self):
-        # one long-running nvidia-smi in loop mode (20 ms period) - starting a process per sample is
-        # too slow to land samples inside a sub-second timed region
         try:
-            proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                     "--format=csv,noheader,nounits", "-lms", "20"],
-                                    stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons
         except Exception:
             return
         self.ready = True
-        try:
-            for line in proc.stdout:
-                if self.stop_flag:
-                    break
-                f = [x.strip() for x in line.strip().split(",")]
-                if len(f) >= 6 and self.armed:
-                    self.samples.append(f)
-        finally:
-            proc.terminate()
+        while not self.stop_flag:
+            if self.armed:
+                try:
+                    self.samples.append((int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), int(get_reasons(h))))
+                except Exception:
+                    pass
+            time.sleep(0.004)
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        mhz = sorted(int(s[0]) for s in self.samples)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": int(self.samples[0][1]), "reasons": reasons,
-                "samples": len(self.samples)}
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unsampled"]}
+        mhz = sorted(s[0] for s in self.samples)
+        bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                "sw_power_cap": 0x4, "hw_power_brake_slowdown": 0x80}
+        reasons = [n for n, b in bits.items() if any(s[1] & b for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(self.samples), "source": "NVML, 4 ms period, timed region only"}
 
 
 def make_inputs(w, pool, seed=0):

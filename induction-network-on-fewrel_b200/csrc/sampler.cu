@@ -9,9 +9,11 @@
 //   - MT19937 blocks of 624 words are regenerated cooperatively (3-phase parallel twist);
 //   - the Python draws (few) are taken by one thread; the pool / set algorithms of random.sample are
 //     restated literally;
-//   - the NumPy Fisher-Yates draws (~1000 per class) are consumed 32 at a time by one warp: lane l
-//     holds candidate v_l = y_l & mask; "accepted iff v_l <= i - (#accepted before l)" is a
-//     triangular system solved by ballot fixed-point iteration; accepted (i, j) pairs go to a j-list.
+//   - the NumPy Fisher-Yates draws (~1000 per class) are consumed up to 256 at a time by the CTA:
+//     lane p's index is i - (#accepted before p), its mask follows from that index, and "accepted iff
+//     masked draw <= index" is a triangular system solved by a ballot/prefix-count fixed-point
+//     iteration (exact, and it crosses the mask changes inside a batch); accepted (i, j) pairs go to
+//     a j-list.
 // Kernel 2 turns each j-list into the first K+Q entries of its permutation WITHOUT simulating the
 // swaps: the value that ends at position p is found by tracing p backwards through the swap list
 // (identity start), one thread per output.  Kernel 3 assembles support||permuted-query row ids,
@@ -79,11 +81,8 @@ struct SerialMT {
   }
 };
 
-__device__ __forceinline__ uint32_t mask_for(uint32_t mx) {   // NumPy random_interval mask
-  uint32_t m = mx;
-  m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16;
-  return m;
-}
+// NumPy random_interval mask: smallest 2^k - 1 >= mx (mx >= 1): all ones below the top set bit.
+__device__ __forceinline__ uint32_t mask_for(uint32_t mx) { return 0xFFFFFFFFu >> __clz(mx); }
 
 // status codes written to *status
 enum { SMP_OK = 0, SMP_SCOPE_TOO_SMALL = 1, SMP_SCOPE_TOO_LARGE = 2 };
@@ -96,10 +95,8 @@ sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_s
   __shared__ uint32_t nkey[MT_N];
   __shared__ int pool[1024];
   __shared__ uint32_t seen[32];
-  __shared__ int s_flag, s_cur;
   const int tid = threadIdx.x, lane = tid & 31;
   for (int i = tid; i < MT_N; i += SMP_NT) { pkey[i] = py_state[i]; nkey[i] = np_state[i]; }
-  if (tid == 0) s_flag = SMP_OK;
   __syncthreads();
 
   // ---- phase A: the Python stream, random.sample(range(R), N) per episode (thread 0)
@@ -136,78 +133,89 @@ sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_s
   __syncthreads();
 
   // ---- phase B: the NumPy stream.  jobs: for each episode, N class permutations then the query one.
+  // The whole CTA consumes up to 256 draws per round.  Lane p (stream order) needs c_p = number of
+  // draws accepted before it: then its Fisher-Yates index is i_p = i - c_p, its mask is mask(i_p),
+  // and it is accepted iff (y_p & mask(i_p)) <= i_p.  That is a triangular system (lane p depends
+  // only on lanes before it), so iterating "recount, re-decide" from any start reaches the exact
+  // sequential answer; it settles in a few rounds because only draws near a threshold ever flip.
+  // Every thread keeps the same (job, i, cur) in registers - all updates derive from shared counts.
+  __shared__ uint32_t ntemp[MT_N];
+  __shared__ __align__(16) int wcount[SMP_NT / 32];
+  __shared__ int s_pos;
+  const int warp = tid >> 5;
+  const uint32_t below = (1u << lane) - 1u;
   const int jobs = B * (N + 1);
-  int cur = (int)np_state[MT_N];     // position in the current block (uniform across the CTA)
-  // warp-0 state (kept in registers of every lane of warp 0, uniform)
-  int job = 0, i = 0;
-  bool fresh = true;                 // job needs (re)initialising
-  bool done = false;
+  int cur = (int)np_state[MT_N];
+  for (int k = tid; k < MT_N; k += SMP_NT) ntemp[k] = mt_temper(nkey[k]);
+  __syncthreads();
+  int job = 0, i = 0, flag = SMP_OK;
+  bool fresh = true;
   while (true) {
-    if (cur >= MT_N) { mt_twist_block(nkey); cur = 0; }
-    if (tid < 32) {
-      while (!done && cur < MT_N) {
-        if (fresh) {
-          if (job >= jobs) { done = true; break; }
-          const int b = job / (N + 1), ci = job % (N + 1);
-          int n;
-          if (ci < N) {
-            const int c = classes[(long long)b * N + ci];
-            n = scopes[2 * c + 1] - scopes[2 * c];
-            if (n < K + Q) { if (lane == 0) s_flag = SMP_SCOPE_TOO_SMALL; done = true; break; }
-            if (n > n_max) { if (lane == 0) s_flag = SMP_SCOPE_TOO_LARGE; done = true; break; }
-          } else {
-            n = N * Q;
-          }
-          i = n - 1;
-          fresh = false;
-          if (i <= 0) { ++job; fresh = true; continue; }   // permutation(1): no draws
-        }
-        const uint32_t m = mask_for((uint32_t)i);
-        const int i_lo = max(1, (int)(m >> 1) + 1);        // last index that still uses this mask
-        const int rem = i - i_lo + 1;
-        const int idx = cur + lane;
-        const bool valid = idx < MT_N;
-        const uint32_t v = valid ? (mt_temper(nkey[idx]) & m) : 0xFFFFFFFFu;
-        // fixed point of a_l = valid && v_l <= i - popc(a & lanes_below)
-        uint32_t a = __ballot_sync(0xffffffffu, valid && v <= (uint32_t)i);
-        const uint32_t below = (1u << lane) - 1u;
-        while (true) {
-          const int c = __popc(a & below);
-          const uint32_t a2 = __ballot_sync(0xffffffffu, valid && c <= i && v <= (uint32_t)(i - c));
-          if (a2 == a) break;
-          a = a2;
-        }
-        int consumed = min(32, MT_N - cur);
-        int acc = __popc(a);
-        if (acc > rem) {     // the segment ends inside this batch: stop right after its rem-th accept
-          const int pos = __fns(a, 0, rem);                 // position of the rem-th set bit
-          a &= (pos >= 31) ? 0xFFFFFFFFu : ((2u << pos) - 1u);
-          consumed = pos + 1;
-          acc = rem;
-        } else if (acc == rem) {
-          const int pos = 31 - __clz(a);                    // last accepted lane
-          consumed = pos + 1;
-        }
-        if ((a >> lane) & 1u) {
-          const int c = __popc(a & below);
-          jlist[(long long)job * n_max + (i - c)] = (int)v;
-        }
-        i -= acc;
-        cur += consumed;
-        if (i <= 0) { ++job; fresh = true; }
+    if (fresh) {
+      if (job >= jobs) break;
+      const int b = job / (N + 1), ci = job % (N + 1);
+      int n;
+      if (ci < N) {
+        const int c = classes[(long long)b * N + ci];
+        n = scopes[2 * c + 1] - scopes[2 * c];
+        if (n < K + Q) { flag = SMP_SCOPE_TOO_SMALL; break; }
+        if (n > n_max) { flag = SMP_SCOPE_TOO_LARGE; break; }
+      } else {
+        n = N * Q;
       }
-      // all jobs served exactly at a block boundary: stop here, do not twist a block nobody draws from
-      if (!done && fresh && job >= jobs) done = true;
-      if (lane == 0) { s_cur = cur; if (done) s_flag |= 0x100; }
+      i = n - 1;
+      fresh = false;
+      if (i <= 0) { ++job; fresh = true; continue; }   // permutation(1): no draws
     }
-    __syncthreads();
-    cur = s_cur;
-    const bool fin = (s_flag & 0x100) != 0;
-    __syncthreads();
-    if (fin) break;
+    if (cur >= MT_N) {
+      mt_twist_block(nkey);
+      for (int k = tid; k < MT_N; k += SMP_NT) ntemp[k] = mt_temper(nkey[k]);
+      __syncthreads();
+      cur = 0;
+    }
+    const int idx = cur + tid;
+    const bool valid = idx < MT_N;
+    const uint32_t y = valid ? ntemp[idx] : 0u;
+    bool acc_me = valid && ((y & mask_for((uint32_t)i)) <= (uint32_t)i);
+    int c = 0, total = 0;
+    uint32_t v = 0;
+    while (true) {
+      const uint32_t bal = __ballot_sync(0xffffffffu, acc_me);
+      if (lane == 0) wcount[warp] = __popc(bal);
+      __syncthreads();
+      const int4 w0 = *reinterpret_cast<const int4*>(&wcount[0]);
+      const int4 w1 = *reinterpret_cast<const int4*>(&wcount[4]);
+      const int wc[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      const int s01 = wc[0] + wc[1], s23 = wc[2] + wc[3], s45 = wc[4] + wc[5], s67 = wc[6] + wc[7];
+      total = (s01 + s23) + (s45 + s67);
+      int prefix = 0;
+#pragma unroll
+      for (int w = 0; w < SMP_NT / 32; ++w) prefix += (w < warp) ? wc[w] : 0;
+      c = prefix + __popc(bal & below);
+      const int ip = i - c;
+      bool again = false;
+      if (valid && ip >= 1) {
+        v = y & mask_for((uint32_t)ip);
+        again = v <= (uint32_t)ip;
+      }
+      const int changed = __syncthreads_or(again != acc_me);
+      acc_me = again;
+      if (!changed) break;
+    }
+    int consumed = min(SMP_NT, MT_N - cur);
+    if (total == i) {                 // the permutation completes inside this round
+      if (acc_me && c == total - 1) s_pos = tid;
+      __syncthreads();
+      consumed = s_pos + 1;
+    }
+    if (acc_me) jlist[(long long)job * n_max + (i - c)] = (int)v;
+    i -= total;
+    cur += consumed;
+    if (i <= 0) { ++job; fresh = true; }
   }
+  __syncthreads();
   for (int k = tid; k < MT_N; k += SMP_NT) np_state[k] = nkey[k];
-  if (tid == 0) { np_state[MT_N] = (uint32_t)cur; *status = s_flag & 0xFF; }
+  if (tid == 0) { np_state[MT_N] = (uint32_t)cur; *status = flag; }
 }
 
 // Value that ends at position p after the Fisher-Yates swaps (i = n-1..1, swap a[i], a[j_i]) applied
