@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define INDNET_ABI_VERSION 1
+#define INDNET_ABI_VERSION 2
 
 typedef void* indnet_stream; /* cudaStream_t */
 
@@ -49,6 +49,19 @@ int indnet_sgemm(indnet_stream st, int transA, int transB, int M, int N, int K, 
 int indnet_colsum(indnet_stream st, const float* A, int rows, int cols, int lda, float* out, int accumulate);
 /* out[d0][d2][d1] = in[d0][d1][d2]  - converts TF's M[H,H,S] (layer_module.py:16) to the internal M'[H,S,H]. */
 int indnet_permute021(indnet_stream st, const float* in, float* out, int d0, int d1, int d2);
+
+/* ---- dense building block, bf16 tensor-core mode (tcgen05 + TMEM + TMA) -------------------------
+ * C[M,N] = A*B (+ bias[n]) (act 0/1 tanh/2 relu) (accumulate: += C), bf16 operands, fp32 accumulation.
+ * a_mn = 0: A stored [M][K] row-major (lda); a_mn = 1: A stored [K][M].  b_mn = 0: B stored [N][K]
+ * (i.e. B transposed); b_mn = 1: B stored [K][N].  Leading dimensions in elements, multiples of 8.
+ * Output fp32 C and/or bf16 Cb (either may be NULL), same ldc.  batch > 1: operand strides sA/sB/sC
+ * (elements).  splitk <= 0: automatic split-K (fp32 atomics) when the output grid is small.
+ * Same call sites as indnet_sgemm. */
+int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
+                   const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act,
+                   int accumulate, int batch, long long sA, long long sB, long long sC, int splitk);
+/* out (bf16) = in (fp32), n elements. */
+int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
 
 /* cudaMemsetAsync on the stream (gradient regions that accumulate must start at zero). */
 int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);
@@ -78,6 +91,11 @@ int indnet_sample_gather(indnet_stream st, const int* scopes, const int* t_word,
 /* ---- a2: Base.get_embedding, model/base.py:76-86 --------------------------------------------- */
 int indnet_embed_fwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* word_table,
                      const float* pos1_table, const float* pos2_table, float* x /*[T][D]*/, long long T, int E, int P);
+/* bf16 tensor-core mode: same lookup written as bf16 rows padded with zeros to 64 columns (xb [T][64]),
+ * the K-major operand of the input-projection MMAs.  Requires E + 2P <= 64. */
+int indnet_embed_fwd_bf16(indnet_stream st, const int* word, const int* pos1, const int* pos2,
+                          const float* word_table, const float* pos1_table, const float* pos2_table, void* xb,
+                          long long T, int E, int P);
 /* Scatter-add dx into dpos1/dpos2 [pos_rows][P] (and dword_table [vocab][E] when not NULL, i.e. when
  * the word table is trainable, base.py:62-65).  Accumulates (+=). */
 int indnet_embed_bwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* dx,
@@ -147,10 +165,11 @@ int indnet_ntn_head_bwd(indnet_stream st, const float* V, const float* w, const 
 
 /* ---- a11: build_optimize, model/base.py:94-99 ---------------------------------------------------
  * One fused TF-form Adam update over a flat buffer.  global_step: device int64, read for the staircase
- * decay then incremented; hyper: device float[2] receiving {lr_t, lr}.  grad_scale multiplies g. */
+ * decay then incremented; hyper: device float[2] receiving {lr_t, lr}.  grad_scale multiplies g.
+ * shadow_bf16: optional bf16 copy of params (same indexing) refreshed by the update. */
 int indnet_adam_step(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
                      long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate, float beta1,
-                     float beta2, float eps, float grad_scale);
+                     float beta2, float eps, float grad_scale, void* shadow_bf16);
 
 #ifdef __cplusplus
 }

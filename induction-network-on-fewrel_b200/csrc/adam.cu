@@ -6,6 +6,7 @@
 //   m = b1 m + (1-b1) g ; v = b2 v + (1-b2) g^2 ; theta -= lr_t * m / (sqrt(v) + eps)   (SURVEY A.6:
 //   epsilon is outside the bias correction, unlike torch.optim.Adam)
 // global_step lives on the device so the whole train step can sit in one CUDA graph.
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "../../include/indnet.h"
@@ -25,7 +26,7 @@ __global__ void adam_prep_kernel(long long* global_step, float* hyper, float lr0
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, long long n, const float* __restrict__ hyper, float beta1,
-                            float beta2, float eps, float gscale) {
+                            float beta2, float eps, float gscale, __nv_bfloat16* __restrict__ shadow) {
   const float lr_t = hyper[0];
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float gi = g[i] * gscale;
@@ -33,7 +34,9 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
     m[i] = mi;
     v[i] = vi;
-    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+    const float pi = p[i] - lr_t * mi / (sqrtf(vi) + eps);
+    p[i] = pi;
+    if (shadow) shadow[i] = __float2bfloat16(pi);   // bf16 copy read by the tensor-core mode kernels
   }
 }
 
@@ -43,7 +46,7 @@ using namespace indnet;
 
 extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* grads, float* m, float* v, long long n,
                                 long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate,
-                                float beta1, float beta2, float eps, float grad_scale) {
+                                float beta1, float beta2, float eps, float grad_scale, void* shadow_bf16) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(n >= 0 && decay_steps > 0, "adam_step: bad sizes");
   IN_REQUIRE(global_step && hyper, "adam_step: null step/hyper pointer");
@@ -53,7 +56,8 @@ extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* g
   IN_REQUIRE(params && grads && m && v, "adam_step: null pointer");
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale);
+  adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
+                                           (__nv_bfloat16*)shadow_bf16);
   IN_LAUNCH_CHECK("adam_kernel");
   return INDNET_OK;
 }

@@ -1,6 +1,7 @@
 // a2: Base.get_embedding (model/base.py:76-86): three table lookups concatenated on the feature
 // axis, x[t, :] = [word_table[word[t]] (E) ; pos1_table[pos1[t]] (P) ; pos2_table[pos2[t]] (P)],
 // and its backward (scatter-add of dx into the trainable tables).
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "../../include/indnet.h"
@@ -21,6 +22,21 @@ __global__ void embed_fwd_kernel(const int* __restrict__ word, const int* __rest
   else if (d < E + P) v = p1t[(long long)pos1[t] * P + (d - E)];
   else v = p2t[(long long)pos2[t] * P + (d - E - P)];
   x[i] = v;
+}
+
+__global__ void embed_fwd_bf16_kernel(const int* __restrict__ word, const int* __restrict__ pos1,
+                                      const int* __restrict__ pos2, const float* __restrict__ wt,
+                                      const float* __restrict__ p1t, const float* __restrict__ p2t,
+                                      __nv_bfloat16* __restrict__ xb, long long T, int E, int P) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= T * 64) return;
+  long long t = i >> 6;
+  int d = (int)(i & 63);
+  float v = 0.f;
+  if (d < E) v = wt[(long long)word[t] * E + d];
+  else if (d < E + P) v = p1t[(long long)pos1[t] * P + (d - E)];
+  else if (d < E + 2 * P) v = p2t[(long long)pos2[t] * P + (d - E - P)];
+  xb[i] = __float2bfloat16(v);
 }
 
 // Position tables are tiny ([2L, P]) and every token hits them: accumulate in shared memory per
@@ -96,5 +112,18 @@ extern "C" int indnet_embed_bwd(indnet_stream st_, const int* word, const int* p
     embed_word_bwd_kernel<<<ceil_div(T * E, 256), 256, 0, st>>>(word, dx, dword_table, T, E, E + 2 * P);
     IN_LAUNCH_CHECK("embed_word_bwd_kernel");
   }
+  return INDNET_OK;
+}
+
+extern "C" int indnet_embed_fwd_bf16(indnet_stream st_, const int* word, const int* pos1, const int* pos2,
+                                     const float* word_table, const float* pos1_table, const float* pos2_table,
+                                     void* xb, long long T, int E, int P) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(T >= 0 && E > 0 && P > 0 && E + 2 * P <= 64, "embed_fwd_bf16: need E + 2P <= 64 (E=%d P=%d)", E, P);
+  if (T == 0) return INDNET_OK;
+  IN_REQUIRE(word && pos1 && pos2 && word_table && pos1_table && pos2_table && xb, "embed_fwd_bf16: null pointer");
+  embed_fwd_bf16_kernel<<<ceil_div(T * 64, 256), 256, 0, st>>>(word, pos1, pos2, word_table, pos1_table, pos2_table,
+                                                               (__nv_bfloat16*)xb, T, E, P);
+  IN_LAUNCH_CHECK("embed_fwd_bf16_kernel");
   return INDNET_OK;
 }

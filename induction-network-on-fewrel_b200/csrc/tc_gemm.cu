@@ -1,0 +1,279 @@
+// bf16 tensor-core mode GEMM: C[M,N] = A * B (+ bias, tanh/relu, += C) with bf16 operands staged by
+// TMA into 128-byte-swizzled shared memory, tcgen05.mma (M=128, N=128, K=16 per instruction)
+// accumulating fp32 in TMEM, and a tcgen05.ld epilogue.  Warp-specialised: warp 0 = TMA producer,
+// warp 1 = TMEM allocator + single-thread MMA issuer, warps 2-5 = epilogue (one TMEM lane quarter
+// each).  4-stage smem ring, mbarrier full/empty pairs, tcgen05.commit releases stages.
+//
+// Operand layouts (no transposes anywhere in the pipeline - every contraction of the path maps onto
+// one of these):
+//   A "K-major"  : stored [M][K] row-major          A "MN-major" : stored [K][M] row-major
+//   B "K-major"  : stored [N][K] row-major (B^T)    B "MN-major" : stored [K][N] row-major
+// Batched (grid.z) through 3-D tensor maps, or split-K (grid.z) with fp32 atomic accumulation.
+#include "common.cuh"
+#include "indnet_internal.h"
+#include "tc_common.cuh"
+#include "../../include/indnet.h"
+
+namespace indnet {
+
+using namespace tc;
+
+constexpr int G_BM = 128, G_BN = 128, G_BK = 64, G_STAGES = 4;
+constexpr int G_A_BYTES = G_BM * G_BK * 2, G_B_BYTES = G_BN * G_BK * 2;   // 16 KB each
+constexpr int G_SMEM = G_STAGES * (G_A_BYTES + G_B_BYTES) + 256 + 1024;   // + barriers + alignment slack
+constexpr int G_THREADS = 192;
+
+struct TcGemmP {
+  float* C; __nv_bfloat16* Cb; const float* bias;
+  int M, N, K, ldc;
+  long long sC;        // batch stride of C (elements)
+  int act, accumulate, splitk, kb_per_split, batch;
+};
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(G_THREADS, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcGemmP p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + G_STAGES * G_A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * (G_A_BYTES + G_B_BYTES));
+  uint64_t* empty = full + G_STAGES;
+  uint64_t* tmem_full = empty + G_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * G_BN;
+  const int z = blockIdx.z;
+  const int batch = z / p.splitk, ks = z % p.splitk;
+  const int total_kb = (p.K + G_BK - 1) / G_BK;
+  const int kb0 = ks * p.kb_per_split;
+  const int num_kb = min(total_kb, kb0 + p.kb_per_split) - kb0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < G_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, G_BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t taddr = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], G_A_BYTES + G_B_BYTES);
+        const int k = (kb0 + kb) * G_BK;
+        uint8_t* a = sA + s * G_A_BYTES;
+        uint8_t* b = sB + s * G_B_BYTES;
+        if (A_MN) {   // stored [K][M]: two boxes of 64 (M) x 64 (K rows), one per 128-byte M atom
+          tma_load_3d(a, &tmA, &full[s], m0, k, batch);
+          tma_load_3d(a + G_A_BYTES / 2, &tmA, &full[s], m0 + 64, k, batch);
+        } else {      // stored [M][K]: one box of 64 (K) x 128 (M rows)
+          tma_load_3d(a, &tmA, &full[s], k, m0, batch);
+        }
+        if (B_MN) {
+          tma_load_3d(b, &tmB, &full[s], n0, k, batch);
+          tma_load_3d(b + G_B_BYTES / 2, &tmB, &full[s], n0 + 64, k, batch);
+        } else {
+          tma_load_3d(b, &tmB, &full[s], k, n0, batch);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = idesc_bf16(G_BM, G_BN, A_MN, B_MN);
+      // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the 128 B row.
+      // MN-major: 8-k-row groups 1024 B apart (SBO), 64-wide MN atoms G_BK*128 B apart (LBO), k-step = 16 rows.
+      constexpr uint32_t a_lbo = A_MN ? G_BK * 128 : 0, b_lbo = B_MN ? G_BK * 128 : 0;
+      constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32, b_kstep = B_MN ? 16 * 128 : 32;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + s * G_A_BYTES), b_base = smem_u32(sB + s * G_B_BYTES);
+#pragma unroll
+        for (int k = 0; k < G_BK / 16; ++k) {
+          const uint64_t ad = smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
+          const uint64_t bd = smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
+          umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    // epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32)
+    const int q = warp & 3;
+    const int row = m0 + q * 32 + lane;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    float* Crow = p.C ? p.C + batch * p.sC + (long long)row * p.ldc : nullptr;
+    __nv_bfloat16* Cbrow = p.Cb ? p.Cb + batch * p.sC + (long long)row * p.ldc : nullptr;
+#pragma unroll 1
+    for (int c = 0; c < G_BN / 32; ++c) {
+      float v[32];
+      tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + c * 32, v);
+      tmem_ld_wait();
+      if (row < p.M) {
+        const int nb = n0 + c * 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = nb + j;
+          if (n < p.N) {
+            float x = v[j];
+            if (p.splitk > 1) {
+              if (p.bias && ks == 0) x += p.bias[n];
+              atomicAdd(Crow + n, x);
+            } else {
+              if (p.bias) x += p.bias[n];
+              if (p.accumulate) x += Crow[n];
+              if (p.act == 1) x = tanhf(x);
+              else if (p.act == 2) x = fmaxf(x, 0.f);
+              if (Crow) Crow[n] = x;
+              if (Cbrow) Cbrow[n] = __float2bfloat16(x);
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(taddr, G_BN);
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 tensor [batch][outer][inner] (inner contiguous, row stride ld elements), box = box_inner x box_outer x 1
+int make_tmap_bf16(CUtensorMap* tm, const void* base, long long inner, long long outer, long long ld,
+                   long long batch, long long batch_stride, int box_inner, int box_outer) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(INDNET_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  IN_REQUIRE((ld * 2) % 16 == 0, "tensor map: row stride %lld elements is not a multiple of 16 bytes", ld);
+  IN_REQUIRE(((uintptr_t)base & 15) == 0, "tensor map: base pointer not 16-byte aligned");
+  if (batch < 1) batch = 1;
+  if (batch_stride <= 0) batch_stride = outer * ld;
+  IN_REQUIRE((batch_stride * 2) % 16 == 0, "tensor map: batch stride is not a multiple of 16 bytes");
+  cuuint64_t dims[3] = {(cuuint64_t)inner, (cuuint64_t)outer, (cuuint64_t)batch};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)batch_stride * 2};
+  cuuint32_t box[3] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(INDNET_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
+  return INDNET_OK;
+}
+
+int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const void* A, long long lda,
+            const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act, int accumulate,
+            int batch, long long sA, long long sB, long long sC, int splitk) {
+  IN_REQUIRE(M > 0 && N > 0 && K > 0 && batch > 0, "tc_gemm: bad sizes M=%d N=%d K=%d batch=%d", M, N, K, batch);
+  IN_REQUIRE(A && B && (C || Cb), "tc_gemm: null operand");
+  const int total_kb = ceil_div(K, G_BK);
+  const int gx = ceil_div(N, G_BN), gy = ceil_div(M, G_BM);
+  if (splitk <= 0) {
+    splitk = 1;
+    long long ctas = (long long)gx * gy * batch;
+    if (batch == 1 && ctas < 148 && total_kb >= 16 && act == 0 && !Cb) {
+      splitk = (int)((296 + ctas - 1) / ctas);
+      if (splitk > total_kb / 4) splitk = total_kb / 4;
+      if (splitk < 1) splitk = 1;
+    }
+  }
+  IN_REQUIRE(splitk == 1 || (batch == 1 && act == 0 && !Cb && C), "tc_gemm: split-K needs fp32 output, no activation, no batch");
+  TcGemmP p;
+  p.C = C; p.Cb = (__nv_bfloat16*)Cb; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.sC = sC;
+  p.act = act; p.accumulate = accumulate; p.splitk = splitk; p.batch = batch;
+  p.kb_per_split = ceil_div(total_kb, splitk);
+  splitk = ceil_div(total_kb, p.kb_per_split);      // no empty K slices
+  p.splitk = splitk;
+  if (splitk > 1 && !accumulate) {
+    IN_REQUIRE(ldc == N, "tc_gemm: split-K zero-fill expects a dense C");
+    IN_CUDA(cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N, st));
+  }
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (a_mn) rc = make_tmap_bf16(&tmA, A, M, K, lda, batch, sA, 64, G_BK);
+  else rc = make_tmap_bf16(&tmA, A, K, M, lda, batch, sA, G_BK, G_BM);
+  if (rc) return rc;
+  if (b_mn) rc = make_tmap_bf16(&tmB, B, N, K, ldb, batch, sB, 64, G_BK);
+  else rc = make_tmap_bf16(&tmB, B, K, N, ldb, batch, sB, G_BK, G_BN);
+  if (rc) return rc;
+  dim3 grid(gx, gy, batch * splitk);
+  IN_REQUIRE(grid.z <= 65535, "tc_gemm: batch*splitk too large");
+#define LAUNCH_TC(AM, BM_)                                                                                      \
+  do {                                                                                                          \
+    static bool attr_set = false;                                                                               \
+    if (!attr_set) {                                                                                            \
+      IN_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<AM, BM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM)); \
+      attr_set = true;                                                                                          \
+    }                                                                                                           \
+    tc_gemm_kernel<AM, BM_><<<grid, G_THREADS, G_SMEM, st>>>(tmA, tmB, p);                                      \
+  } while (0)
+  if (a_mn && b_mn) LAUNCH_TC(true, true);
+  else if (a_mn) LAUNCH_TC(true, false);
+  else if (b_mn) LAUNCH_TC(false, true);
+  else LAUNCH_TC(false, false);
+#undef LAUNCH_TC
+  IN_LAUNCH_CHECK("tc_gemm_kernel");
+  return INDNET_OK;
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n) {
+  long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < n) {
+    const float4 v = *reinterpret_cast<const float4*>(in + i);
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&a);
+    o.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(out + i) = o;
+  } else {
+    for (; i < n; ++i) out[i] = __float2bfloat16(in[i]);
+  }
+}
+
+}  // namespace indnet
+
+using namespace indnet;
+
+extern "C" int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
+                              const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act,
+                              int accumulate, int batch, long long sA, long long sB, long long sC, int splitk) {
+  return tc_gemm((cudaStream_t)st, a_mn != 0, b_mn != 0, M, N, K, A, lda, B, ldb, C, Cb, ldc, bias, act, accumulate,
+                 batch, sA, sB, sC, splitk);
+}
+
+extern "C" int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n) {
+  IN_REQUIRE(n >= 0, "cast_bf16: negative size");
+  if (n == 0) return INDNET_OK;
+  IN_REQUIRE(in && out, "cast_bf16: null pointer");
+  IN_REQUIRE((((uintptr_t)in) & 15) == 0 && (((uintptr_t)out) & 7) == 0, "cast_bf16: unaligned pointers");
+  cast_bf16_kernel<<<ceil_div(ceil_div(n, 4), 256), 256, 0, (cudaStream_t)st>>>(in, (__nv_bfloat16*)out, n);
+  IN_LAUNCH_CHECK("cast_bf16_kernel");
+  return INDNET_OK;
+}

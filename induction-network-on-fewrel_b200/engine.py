@@ -144,6 +144,19 @@ class ParamStore:
         self.v = torch.zeros_like(self.params)
         self.global_step = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.hyper = torch.zeros(2, dtype=torch.float32, device=self.device)   # {lr_t, lr}
+        self.params_bf = None      # bf16 shadow of ``params`` (tensor-core mode), same indexing
+
+    def enable_bf16_shadow(self):
+        if self.params_bf is None:
+            self.params_bf = torch.zeros(self.numel, dtype=torch.bfloat16, device=self.device)
+        self.refresh_bf16()
+
+    def refresh_bf16(self):
+        if self.params_bf is not None:
+            LIB.call("indnet_cast_bf16", current_stream(), ptr(self.params), ptr(self.params_bf), self.numel)
+
+    def view_bf(self, name):
+        return self.view(name, self.params_bf)
 
     def internal_shape(self, name):
         s = self.tf_shapes[name]
@@ -166,6 +179,7 @@ class ParamStore:
             if name == "M":
                 t = t.permute(0, 2, 1)
             self.view(name).copy_(t.contiguous().to(self.device))
+        self.refresh_bf16()
 
     def _export(self, buf):
         out = {}
@@ -251,6 +265,17 @@ class EpisodePipeline:
         self.correct = i32(c.B * c.n_q)
         self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
         self._bwd_ready = False
+        self.bf16 = cfg.mode == "bf16"
+        if self.bf16:
+            if c.D > 64 or c.u % 8:
+                raise ValueError("bf16 tensor-core mode needs E + 10 <= 64 and hidden_size % 8 == 0 "
+                                 "(16-byte aligned bf16 rows for TMA)")
+            store.enable_bf16_shadow()
+            h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
+            self.x_bf = h(c.T, 64)
+            self.hout_bf = h(c.T, c.H)
+            self.es_bf = h(c.B * c.NK, c.H)
+            self.cvec_bf = h(c.B * c.N, c.H)
 
     # ------------------------------------------------------------------ helpers
     def _call(self, name, *args):
@@ -288,6 +313,25 @@ class EpisodePipeline:
                    ptr(bias) if isinstance(bias, torch.Tensor) else bias, act, batch, inner,
                    sA[0], sA[1], sB[0], sB[1], sC[0], sC[1], splitk)
 
+    def _tc(self, a_mn, b_mn, M, N, K, A, lda, Bm, ldb, C=None, Cb=None, ldc=None, bias=None, act=0,
+            accumulate=0, batch=1, sA=0, sB=0, sC=0, splitk=0, tag=None):
+        """tcgen05 GEMM (csrc/tc_gemm.cu).  A/Bm/C/Cb: tensors or raw device addresses."""
+        self._tag = ("tc_gemm:" + tag) if tag else None
+        ad = lambda t: t.data_ptr() if isinstance(t, torch.Tensor) else t  # noqa: E731
+        try:
+            self._call("indnet_tc_gemm", int(a_mn), int(b_mn), M, N, K, ad(A), lda, ad(Bm), ldb, ad(C), ad(Cb),
+                       ldc if ldc is not None else N, ptr(bias) if isinstance(bias, torch.Tensor) else bias, act,
+                       accumulate, batch, sA, sB, sC, splitk)
+        finally:
+            self._tag = None
+
+    def _cast(self, src, dst, tag=None):
+        self._tag = ("cast_bf16:" + tag) if tag else None
+        try:
+            self._call("indnet_cast_bf16", ptr(src), ptr(dst), src.numel())
+        finally:
+            self._tag = None
+
     def set_inputs(self, inputs, query_label):
         """Copies one batch into the static input buffers.  Accepts torch tensors (any device) or
         numpy arrays shaped [B, n_s, L] (or [n_s, L] when B == 1)."""
@@ -299,6 +343,8 @@ class EpisodePipeline:
 
     # ------------------------------------------------------------------ forward (model/graph.py:29-86)
     def forward(self, train: bool = False):
+        if self.bf16:
+            return self._forward_bf16(train)
         c, p = self.cfg, self.p
         keep = c.keep_prob if train else 1.0
         wt = p.view("word_embedding") if self.trainable_words else self.word_table
@@ -335,6 +381,44 @@ class EpisodePipeline:
                    c.B * c.n_q, c.N)
         self._last_keep = keep
 
+    def _forward_bf16(self, train: bool):
+        """bf16 tensor-core mode: every large contraction runs on tcgen05 (fp32 accumulation); the
+        reductions, softmaxes, routing and the loss stay in fp32."""
+        c, p = self.cfg, self.p
+        keep = c.keep_prob if train else 1.0
+        wt = p.view("word_embedding") if self.trainable_words else self.word_table
+        u4 = 4 * c.u
+        self._call("indnet_embed_fwd_bf16", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(wt),
+                   ptr(p.view("pos1_embedding")), ptr(p.view("pos2_embedding")), ptr(self.x_bf), c.T, c.E, POS_DIM)
+        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+            # K = 64: the zero-padded x columns 60..63 meet rows D..D+3 of the TF kernel (finite), product 0
+            self._tc(0, 1, c.T, u4, 64, self.x_bf, 64, p.view_bf(kn), u4, C=self.xproj[d], bias=p.view(bn),
+                     tag="inproj")
+        wh_fw = p.view(FW_K)[c.D:]
+        wh_bw = p.view(BW_K)[c.D:]
+        self._call("indnet_lstm_fwd", ptr(self.xproj), ptr(wh_fw), ptr(wh_bw), ptr(self.hout), ptr(self.gates),
+                   ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
+        self._cast(self.hout, self.hout_bf, "hout")
+        self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, C=self.proj, bias=p.view(ATT_B),
+                 act=1, tag="attn_dense")
+        self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
+                   ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
+        self._cast(self.es, self.es_bf, "es")
+        self._tc(0, 1, c.B * c.NK, c.H, c.H, self.es_bf, c.H, p.view_bf("W_s"), c.H, C=self.ehat,
+                 tag="routing_transform")
+        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
+        self._cast(self.cvec, self.cvec_bf, "cvec")
+        self._tc(0, 1, c.B * c.N, c.S * c.H, c.H, self.cvec_bf, c.H, p.view_bf("M"), c.S * c.H, C=self.Tp,
+                 tag="ntn_stage1")
+        NS = c.N * c.S
+        self._gemm(0, 1, c.n_q, NS, c.H, ptr(self.eq), c.H, ptr(self.Tp), c.H, ptr(self.V), NS,
+                   batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0), tag="ntn_stage2")
+        self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
+                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
+        self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
+                   c.B * c.n_q, c.N)
+        self._last_keep = keep
+
     # ------------------------------------------------------------------ backward
     def _alloc_bwd(self):
         c = self.cfg
@@ -352,12 +436,21 @@ class EpisodePipeline:
         self.dz = self.xproj                   # xproj is dead after the forward recurrence
         self.dx = f(c.T, c.D)
         self.whT = f(2, 4 * c.u, c.u)
+        if self.bf16:
+            h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
+            self.dTp_bf = h(c.B * c.N, c.S * c.H)
+            self.dehat_bf = h(c.B * c.NK, c.H)
+            self.dpre_bf = h(c.T, c.H)
+            self.dz_bf = h(2, c.T, 4 * c.u)
+            self.hprev_bf = h(2, c.T, c.u)
         self._bwd_ready = True
 
     def backward(self):
         """Hand-written backward of every forward op, in reverse order; fills ``self.p.grads``."""
         if not self._bwd_ready:
             self._alloc_bwd()
+        if self.bf16:
+            return self._backward_bf16()
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
@@ -412,12 +505,68 @@ class EpisodePipeline:
         self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
                    ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
 
+    def _backward_bf16(self):
+        c, p = self.cfg, self.p
+        u4, NS = 4 * c.u, c.N * c.S
+        rows = c.B * c.n_q
+        self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
+                   None, ptr(self.dlogit), ptr(self.dV), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
+                   1.0 / (rows * c.N))
+        # per-episode contractions with N*S columns stay on the FP32 path (N*S is not 16-byte aligned in bf16)
+        self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0), tag="ntn_dqe")
+        self._gemm(1, 0, NS, c.H, c.n_q, ptr(self.dV), NS, ptr(self.eq), c.H, ptr(self.dTp), c.H,
+                   batch=c.B, sA=(c.n_q * NS, 0), sB=(c.n_q * c.H, 0), sC=(NS * c.H, 0), tag="ntn_dT")
+        self._cast(self.dTp, self.dTp_bf, "dTp")
+        # dM' = cv^T dT' (both operands stored [K][.]) ; dcv = dT' M'^T (both K-major)
+        self._tc(1, 1, c.H, c.S * c.H, c.B * c.N, self.cvec_bf, c.H, self.dTp_bf, c.S * c.H, C=p.grad("M"),
+                 splitk=1, tag="ntn_dM")
+        self._tc(0, 0, c.B * c.N, c.H, c.S * c.H, self.dTp_bf, c.S * c.H, p.view_bf("M"), c.S * c.H, C=self.dcvec,
+                 tag="ntn_dcv")
+        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
+                   c.B * c.N, c.K, c.H, c.iters)
+        self._cast(self.dehat, self.dehat_bf, "dehat")
+        self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
+        self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
+        self._call("indnet_attn_pool_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout), ptr(self.proj),
+                   ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre), ptr(self.dw2_part),
+                   c.X, c.L, c.H, c.n_s, c.NK)
+        self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
+        self._cast(self.dpre, self.dpre_bf, "dpre")
+        self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
+        self._call("indnet_colsum", ptr(self.dpre), c.T, c.H, c.H, ptr(p.grad(ATT_B)), 0)
+        self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
+                 splitk=1, tag="attn_dh")
+        wh_fw = p.view(FW_K)[c.D:]
+        wh_bw = p.view(BW_K)[c.D:]
+        self._call("indnet_lstm_bwd", ptr(self.dhout), ptr(self.gates), ptr(self.cstate), ptr(wh_fw), ptr(wh_bw),
+                   ptr(self.whT), ptr(self.dz), c.X, c.L, c.u, self._last_keep, self.seed, ptr(p.global_step))
+        self._cast(self.dz, self.dz_bf, "dz")
+        self._cast(self.hprev, self.hprev_bf, "hprev")
+        n0 = 0 if self.trainable_words else c.E
+        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+            gk = p.grad(kn)
+            self._tc(1, 1, c.D, u4, c.T, self.x_bf, 64, self.dz_bf[d], u4, C=gk, tag="lstm_dWx")
+            self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
+            self._call("indnet_colsum", ptr(self.dz[d]), c.T, u4, u4, ptr(p.grad(bn)), 0)
+            self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
+                     C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
+        g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
+        self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
+        self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
+        gw = None
+        if self.trainable_words:
+            gw = p.grad("word_embedding")
+            self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
+        self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
+                   ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+
     # ------------------------------------------------------------------ update (model/base.py:94-99)
     def adam(self, grad_scale: float = 1.0):
         p = self.p
         self._call("indnet_adam_step", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), p.numel,
                    ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
-                   0.9, 0.999, 1e-8, grad_scale)
+                   0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf))
 
     def train_step(self):
         """fwd + bwd + Adam on the inputs currently in the static buffers (no host sync)."""

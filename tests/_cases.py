@@ -13,6 +13,7 @@ CASES = {
     "toy_train_py": dict(N=5, K=2, Q=5, B=2, L=37, E=5, u=20, S=100),     # train.py:24-36 constants
     "k1": dict(N=5, K=1, Q=5, B=3, L=12, E=8, u=16, S=12),                # degenerate K=1 routing
     "ragged": dict(N=4, K=3, Q=2, B=5, L=9, E=7, u=13, S=7),              # nothing a multiple of 32/16
+    "u24": dict(N=4, K=3, Q=5, B=3, L=11, E=20, u=24, S=16),                # smallest bf16-mode-legal widths
     "cfg0_5w5s": dict(N=5, K=5, Q=5, B=2, L=40, E=50, u=128, S=100),      # BASELINE configs[0] shape, B=2
 }
 

@@ -185,3 +185,49 @@ def test_large_batch_properties():
     cfg2 = EpisodeConfig(N=5, K=1, Q=5, B=2, L=40, E=50, u=128, S=100)
     ref = oracle_forward(cfg2, tables, sub, label[[5, 41]], params, dtype=torch.float64)
     assert rel_err(probs[[5, 41]], ref["probs"]) < FWD_TOL
+
+
+# ---------------------------------------------------------------------------------------------------
+# bf16 tensor-core mode (tcgen05, fp32 accumulation): north_star tolerance 2e-2 on probs / loss.
+BF16_TOL = 2e-2
+BF16_GRAD_TOL = 6e-2     # gradients: bf16-rounded activations AND bf16-rounded upstream gradients
+BF16_CASES = ["u24", "k1", "cfg0_5w5s"]
+
+
+@pytest.mark.parametrize("name", BF16_CASES)
+def test_bf16_mode_forward_and_backward_parity(name):
+    cfg, tables, inputs, label, params = make_case(name, seed=3, mode="bf16")
+    pipe = build_pipeline(cfg, tables, params)
+    pipe.set_inputs(inputs, label)
+    pipe.forward(train=True)
+    pipe.backward()
+    torch.cuda.synchronize()
+    ref, gref = oracle_grads(cfg, tables, inputs, label, params, dtype=torch.float64)
+    e_probs = rel_err(pipe.probs, ref["probs"])
+    e_loss = abs(pipe.loss() - float(ref["loss"])) / float(ref["loss"])
+    got = pipe.p.grad_dict()
+    errs = {k: rel_err(got[k], gref[k]) for k in gref}
+    print(name, "probs", e_probs, "loss", e_loss, {k: "%.1e" % v for k, v in errs.items()})
+    assert e_probs < BF16_TOL and e_loss < BF16_TOL
+    for k, e in errs.items():
+        assert e < BF16_GRAD_TOL, (name, k, e)
+
+
+def test_bf16_mode_train_steps_track_fp32_mode():
+    cfg, tables, inputs, label, params = make_case("u24", seed=6, mode="bf16")
+    cfg32, *_ = make_case("u24", seed=6)
+    pb, pf = build_pipeline(cfg, tables, params), build_pipeline(cfg32, tables, params)
+    for p in (pb, pf):
+        p.set_inputs(inputs, label)
+    lb, lf = [], []
+    for _ in range(5):
+        pb.train_step(); pf.train_step()
+        lb.append(pb.loss()); lf.append(pf.loss())
+    np.testing.assert_allclose(lb, lf, rtol=BF16_TOL)
+    assert lb[-1] < lb[0]      # the bf16 shadow weights are refreshed by Adam: the loss goes down
+
+
+def test_bf16_mode_rejects_unsupported_shapes():
+    cfg, tables, inputs, label, params = make_case("ragged", seed=3, mode="bf16")   # u = 13
+    with pytest.raises(ValueError, match="bf16 tensor-core mode needs"):
+        build_pipeline(cfg, tables, params)

@@ -12,9 +12,13 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 from _cases import CASES, make_case, oracle_forward, oracle_grads, rel_err  # noqa: E402
 from induction_b200.engine import EpisodePipeline, ParamStore, tf_param_shapes  # noqa: E402
 
-names = sys.argv[1:] or list(CASES)
+mode = "fp32"
+args = sys.argv[1:]
+if args and args[0] in ("fp32", "bf16"):
+    mode, args = args[0], args[1:]
+names = args or list(CASES)
 for name in names:
-    cfg, tables, inputs, label, params = make_case(name, seed=3)
+    cfg, tables, inputs, label, params = make_case(name, seed=3, mode=mode)
     store = ParamStore(tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S))
     store.load_state_dict(params)
     pipe = EpisodePipeline(cfg, store, torch.from_numpy(tables["word_vec_mat"]))
