@@ -116,6 +116,25 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
                     const float* Wh_bw, float* whT_scratch, float* dz, int X, int L, int u, float keep_prob,
                     unsigned long long seed, const long long* seed_step);
 
+/* bf16 tensor-core mode of indnet_lstm_fwd with the input projection fused in (hidden_size 128,
+ * E+10 <= 64): x_bf [X][L][64] bf16 zero-padded embeddings (indnet_embed_fwd_bf16), kernel_* the TF
+ * LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch: caller-provided bf16 [2][4u][192] (packed
+ * transposed weights, rebuilt every call).  Outputs as indnet_lstm_fwd, each optionally in fp32
+ * and/or bf16 (NULL = skip; cstate is always written). */
+int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_fw, const float* bias_fw,
+                       const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout, void* hout_bf,
+                       float* gates, void* gates_bf, float* cstate, float* hprev, void* hprev_bf, int X, int L, int D,
+                       int u, float keep_prob, unsigned long long seed, const long long* seed_step);
+
+/* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][4u] bf16 and cstate
+ * fp32 as saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h
+ * = rows D.., read in place by TMA, no scratch).  Writes dz_bf [2][X][L][4u] bf16. */
+int indnet_lstm_bwd_tc(indnet_stream st, const float* dhout, const void* gates_bf, const float* cstate,
+                       const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D, int u,
+                       float keep_prob, unsigned long long seed, const long long* seed_step);
+/* out[c] = sum_r A[r][c] for a dense bf16 matrix [rows][cols] (bias gradients from the bf16 dz stream). */
+int indnet_colsum_bf16(indnet_stream st, const void* A, long long rows, int cols, float* out);
+
 /* No counterpart in the reference.  Same computation as indnet_lstm_bwd for callers that must not
  * allocate device memory (custom-op / plugin callbacks that only get input and output buffers,
  * loops that cannot afford cudaMalloc's device synchronisation): the [2][4u][u] scratch is a fixed

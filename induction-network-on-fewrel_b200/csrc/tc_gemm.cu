@@ -18,7 +18,7 @@ namespace indnet {
 
 using namespace tc;
 
-constexpr int G_BM = 128, G_BN = 128, G_BK = 64, G_STAGES = 4;
+constexpr int G_BM = 128, G_BN = 128, G_BK = 64, G_STAGES = 3;   // 3 stages: 2 CTAs per SM
 constexpr int G_A_BYTES = G_BM * G_BK * 2, G_B_BYTES = G_BN * G_BK * 2;   // 16 KB each
 constexpr int G_SMEM = G_STAGES * (G_A_BYTES + G_B_BYTES) + 256 + 1024;   // + barriers + alignment slack
 constexpr int G_THREADS = 192;
@@ -31,7 +31,7 @@ struct TcGemmP {
 };
 
 template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(G_THREADS, 1)
+__global__ void __launch_bounds__(G_THREADS, 2)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcGemmP p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -114,34 +114,40 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int row = m0 + q * 32 + lane;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
-    float* Crow = p.C ? p.C + batch * p.sC + (long long)row * p.ldc : nullptr;
-    __nv_bfloat16* Cbrow = p.Cb ? p.Cb + batch * p.sC + (long long)row * p.ldc : nullptr;
+    // All loads of this tile have been consumed once tmem_full fires, so the operand ring is free:
+    // reuse it as a per-warp 32x33 fp32 transpose tile so that every global store instruction writes
+    // one contiguous 128-byte row segment (lane = column) instead of 32 scattered rows.
+    float* tile = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);
+    const int row0 = m0 + q * 32;
+    float* Cbase = p.C ? p.C + batch * p.sC : nullptr;
+    __nv_bfloat16* Cbbase = p.Cb ? p.Cb + batch * p.sC : nullptr;
 #pragma unroll 1
     for (int c = 0; c < G_BN / 32; ++c) {
       float v[32];
       tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + c * 32, v);
       tmem_ld_wait();
-      if (row < p.M) {
-        const int nb = n0 + c * 32;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = nb + j;
-          if (n < p.N) {
-            float x = v[j];
-            if (p.splitk > 1) {
-              if (p.bias && ks == 0) x += p.bias[n];
-              atomicAdd(Crow + n, x);
-            } else {
-              if (p.bias) x += p.bias[n];
-              if (p.accumulate) x += Crow[n];
-              if (p.act == 1) x = tanhf(x);
-              else if (p.act == 2) x = fmaxf(x, 0.f);
-              if (Crow) Crow[n] = x;
-              if (Cbrow) Cbrow[n] = __float2bfloat16(x);
-            }
+      for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+      __syncwarp();
+      const int n = n0 + c * 32 + lane;
+      if (n < p.N) {
+        const float bv = (p.bias && (p.splitk == 1 || ks == 0)) ? p.bias[n] : 0.f;
+        const int rmax = min(32, p.M - row0);
+        for (int rr = 0; rr < rmax; ++rr) {
+          float x = tile[rr * 33 + lane] + bv;
+          const long long o = (long long)(row0 + rr) * p.ldc + n;
+          if (p.splitk > 1) {
+            atomicAdd(Cbase + o, x);
+          } else {
+            if (p.accumulate) x += Cbase[o];
+            if (p.act == 1) x = tanhf(x);
+            else if (p.act == 2) x = fmaxf(x, 0.f);
+            if (Cbase) Cbase[o] = x;
+            if (Cbbase) Cbbase[o] = __float2bfloat16(x);
           }
         }
       }
+      __syncwarp();
     }
     tc_fence_before();
   }

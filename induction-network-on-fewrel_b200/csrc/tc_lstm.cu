@@ -1,0 +1,502 @@
+// a3, bf16 tensor-core mode: the BiLSTM of model/graph.py:34-49 as ONE persistent tcgen05 kernel with
+// the input projection fused in.
+//
+// Swap-AB formulation.  Per step t and direction, for a tile of NS sentences:
+//     Z^T[4u, NS] = [W_x^T | W_h^T][4u, 64+u] * [x_t ; h_{t-1}][64+u, NS]
+// * MMA-M = gate units: four M=128 tiles, one per gate (i, j, f, o - the TF kernel column order), so
+//   TMEM lane m of every tile is unit m and one thread reads all four gates of its unit from its own
+//   lane; MMA-N = sentences (NS = 32), so a step's accumulators are 4 x NS TMEM columns.
+// * The weights [W_x^T | W_h^T] (bf16, 192 KB for u = 128) are loaded ONCE by TMA into 128-byte-swizzled
+//   shared memory and stay resident for all L steps.  x_t tiles stream in by TMA (double buffered, one
+//   step ahead); h_{t-1} is written by the gate threads straight into the swizzled B-operand layout.
+// * Gate math (forget bias 1.0, no length masking - SURVEY A.1/A.2) runs on the accumulators right
+//   after tcgen05.ld; c stays in registers for the whole sequence.
+// Warps 0-7: gate threads (TMEM lane quarter = warp % 4, sentence half = warp / 4).
+// Warp 8: TMA + single-thread MMA issue.
+#include "common.cuh"
+#include "indnet_internal.h"
+#include "tc_common.cuh"
+#include "../../include/indnet.h"
+
+namespace indnet {
+
+using namespace tc;
+
+constexpr int LT_U = 128;            // units per direction this kernel is specialised for
+constexpr int LT_KX = 64;            // padded input width (D <= 64)
+constexpr int LT_K = LT_KX + LT_U;   // 192
+constexpr int LT_KB = LT_K / 64;     // 3 K-blocks of 64 (one 128-byte swizzle row each)
+constexpr int LT_NS = 32;            // sentences per CTA (MMA N)
+constexpr int LT_THREADS = 288;
+constexpr int LT_GATE_THREADS = 256;
+constexpr int LT_MMA_WARP = 8;
+constexpr int LT_SPT = LT_NS / 2;        // sentences per gate thread
+static_assert(LT_SPT == 16, "gate threads use 16-column TMEM loads");
+constexpr int LT_W_BYTES = 4 * LT_KB * 128 * 128;            // 196608
+constexpr int LT_XB_BYTES = LT_NS * 128;                     // one x tile
+constexpr int LT_HB_BYTES = 2 * LT_NS * 128;                 // h tile: 2 K-blocks
+constexpr int LT_SMEM = LT_W_BYTES + 2 * LT_XB_BYTES + LT_HB_BYTES + 256 + 1024;
+
+int make_tmap_bf16(CUtensorMap* tm, const void* base, long long inner, long long outer, long long ld,
+                   long long batch, long long batch_stride, int box_inner, int box_outer);
+
+// WT[dir][g*128 + m][k] (bf16, k-major, 192 wide): k < D -> W_x[k][g*128+m]; D <= k < 64 -> 0;
+// k >= 64 -> W_h[k-64][g*128+m].  kernel = TF BasicLSTMCell kernel [D+u][4u] (W_x rows then W_h rows).
+__global__ void lstm_pack_weights_kernel(const float* __restrict__ k_fw, const float* __restrict__ k_bw,
+                                         __nv_bfloat16* __restrict__ WT, int D) {
+  const int dir = blockIdx.y;
+  const float* __restrict__ kern = dir ? k_bw : k_fw;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;      // over 4u * K with the unit index fastest
+  if (idx >= 4 * LT_U * LT_K) return;
+  const int col = idx % (4 * LT_U), k = idx / (4 * LT_U);
+  float v = 0.f;
+  if (k < D) v = kern[(long long)k * (4 * LT_U) + col];
+  else if (k >= LT_KX) v = kern[(long long)(D + k - LT_KX) * (4 * LT_U) + col];
+  WT[((long long)dir * 4 * LT_U + col) * LT_K + k] = __float2bfloat16(v);
+}
+
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(tanh_fast(0.5f * x), 0.5f, 0.5f); }
+
+struct LstmTcP {
+  const float* bias_fw; const float* bias_bw;
+  float* hout; __nv_bfloat16* hout_bf;
+  float* gates; __nv_bfloat16* gates_bf;
+  float* cstate;
+  float* hprev; __nv_bfloat16* hprev_bf;
+  int X, L;
+  float keep_prob; unsigned long long seed; const long long* seed_step;
+};
+
+__global__ void __launch_bounds__(LT_THREADS, 1)
+tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, LstmTcP p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;                                   // [4 gates][3 kb][128 rows][128 B]
+  uint8_t* sX = smem + LT_W_BYTES;                      // [2][NS rows][128 B]
+  uint8_t* sH = sX + 2 * LT_XB_BYTES;                   // [2 kb][NS rows][128 B]
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(sH + LT_HB_BYTES);
+  uint64_t* x_full = w_full + 1;                        // [2]
+  uint64_t* mma_done = x_full + 2;
+  uint64_t* h_ready = mma_done + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dir = blockIdx.y;
+  const int x0 = blockIdx.x * LT_NS;
+  const int L = p.L;
+  unsigned long long seed = p.seed;
+  if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
+
+  // h_{-1} = 0
+  for (int i = threadIdx.x; i < LT_HB_BYTES / 16; i += LT_THREADS) reinterpret_cast<uint4*>(sH)[i] = make_uint4(0, 0, 0, 0);
+  if (warp == LT_MMA_WARP && lane == 0) {
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmX);
+    mbar_init(w_full, 1);
+    mbar_init(&x_full[0], 1);
+    mbar_init(&x_full[1], 1);
+    mbar_init(mma_done, 1);
+    mbar_init(h_ready, LT_GATE_THREADS);
+    fence_barrier_init();
+  }
+  if (warp == LT_MMA_WARP) tmem_alloc(tmem_slot, 4 * LT_NS);
+  fence_proxy_async();          // the zero-fill of sH must be visible to the tensor core's operand reads
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t taddr = *tmem_slot;
+
+  if (warp == LT_MMA_WARP) {
+    if (lane == 0) {
+      // resident weights: 12 boxes of 64 (k) x 128 (rows)
+      mbar_expect_tx(w_full, LT_W_BYTES);
+      for (int g = 0; g < 4; ++g)
+        for (int kb = 0; kb < LT_KB; ++kb)
+          tma_load_3d(sW + (g * LT_KB + kb) * 16384, &tmW, w_full, kb * 64, g * 128, dir);
+      // x of the first step
+      {
+        const int t = dir ? (L - 1) : 0;
+        mbar_expect_tx(&x_full[0], LT_XB_BYTES);
+        tma_load_3d(sX, &tmX, &x_full[0], 0, t, x0);
+      }
+      mbar_wait(w_full, 0);
+      constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
+      const uint32_t w_base = smem_u32(sW), x_base = smem_u32(sX), h_base = smem_u32(sH);
+      for (int s = 0; s < L; ++s) {
+        if (s > 0) mbar_wait(h_ready, (s - 1) & 1);      // h_{s-1} is in sH and TMEM has been drained
+        if (s + 1 < L) {                                  // prefetch x of the next step (its buffer is free)
+          const int tn = dir ? (L - 2 - s) : (s + 1);
+          mbar_expect_tx(&x_full[(s + 1) & 1], LT_XB_BYTES);
+          tma_load_3d(sX + ((s + 1) & 1) * LT_XB_BYTES, &tmX, &x_full[(s + 1) & 1], 0, tn, x0);
+        }
+        mbar_wait(&x_full[s & 1], (s >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+          for (int kb = 0; kb < LT_KB; ++kb) {
+            const uint32_t b_tile = (kb == 0) ? (x_base + (s & 1) * LT_XB_BYTES) : (h_base + (kb - 1) * (LT_NS * 128));
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+              const uint64_t ad = smem_desc_sw128(w_base + (g * LT_KB + kb) * 16384 + k4 * 32, 0, 1024);
+              const uint64_t bd = smem_desc_sw128(b_tile + k4 * 32, 0, 1024);
+              umma_bf16(taddr + g * LT_NS, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            }
+          }
+        }
+        umma_commit(mma_done);
+      }
+    }
+  } else {
+    // ---- gate threads: thread = (unit m = TMEM lane, sentence half hf), LT_SPT sentences each
+    const int m = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
+    const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
+    const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+    const float inv_keep = 1.0f / p.keep_prob;
+    float c[LT_SPT];
+    float hp[LT_SPT];     // h_{t-1} (fp32) of this unit, for the hprev save
+#pragma unroll
+    for (int s = 0; s < LT_SPT; ++s) { c[s] = 0.f; hp[s] = 0.f; }
+    // destination of this unit inside the swizzled h tile: K-block m/64, element k = m%64
+    const int hkb = m >> 6, hk = m & 63;
+    uint8_t* hdst = sH + hkb * (LT_NS * 128) + (hk & 7) * 2;
+    const uint32_t hchunk = (uint32_t)(hk >> 3);
+
+    for (int s = 0; s < L; ++s) {
+      const int t = dir ? (L - 1 - s) : s;
+      mbar_wait(mma_done, s & 1);
+      tc_fence_after();
+      {
+        float zi[16], zj[16], zf[16], zo[16];
+        tmem_ld16(lane_addr + 0 * LT_NS, zi);
+        tmem_ld16(lane_addr + 1 * LT_NS, zj);
+        tmem_ld16(lane_addr + 2 * LT_NS, zf);
+        tmem_ld16(lane_addr + 3 * LT_NS, zo);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          const int sl = hf * LT_SPT + q;
+          const int x = x0 + sl;
+          const float gi = sigmoid_fast(zi[q] + bi);
+          const float gj = tanh_fast(zj[q] + bj);
+          const float gf = sigmoid_fast(zf[q] + bf);
+          const float go = sigmoid_fast(zo[q] + bo);
+          const float cn = fmaf(c[q], gf, gi * gj);
+          const float h = tanh_fast(cn) * go;
+          c[q] = cn;
+          // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
+          *reinterpret_cast<__nv_bfloat16*>(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4)) = __float2bfloat16(h);
+          if (x < p.X) {
+            const long long tok = ((long long)dir * p.X + x) * L + t;
+            if (p.gates) {
+              float* gp = p.gates + tok * (4 * LT_U) + m;
+              gp[0] = gi; gp[LT_U] = gj; gp[2 * LT_U] = gf; gp[3 * LT_U] = go;
+            }
+            if (p.gates_bf) {
+              __nv_bfloat16* gp = p.gates_bf + tok * (4 * LT_U) + m;
+              gp[0] = __float2bfloat16(gi); gp[LT_U] = __float2bfloat16(gj);
+              gp[2 * LT_U] = __float2bfloat16(gf); gp[3 * LT_U] = __float2bfloat16(go);
+            }
+            p.cstate[tok * LT_U + m] = cn;
+            if (p.hprev) p.hprev[tok * LT_U + m] = hp[q];
+            if (p.hprev_bf) p.hprev_bf[tok * LT_U + m] = __float2bfloat16(hp[q]);
+            const long long oi = ((long long)x * L + t) * (2 * LT_U) + dir * LT_U + m;
+            float ho = h;
+            if (p.keep_prob < 1.0f) ho = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? h * inv_keep : 0.f;
+            if (p.hout) p.hout[oi] = ho;
+            if (p.hout_bf) p.hout_bf[oi] = __float2bfloat16(ho);
+          }
+          hp[q] = h;
+        }
+      }
+      fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
+      tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
+      mbar_arrive(h_ready);
+    }
+  }
+  __syncthreads();
+  if (warp == LT_MMA_WARP) tmem_dealloc(taddr, 4 * LT_NS);
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// BPTT, bf16 tensor-core mode.  Per step (reverse processing order) and tile of NS sentences:
+//     dh_rec^T[u, NS] = W_h[u, 4u] * dz^T[4u, NS]
+// A = W_h exactly as the TF kernel stores it (rows D.. of [D+u][4u], K-major over the 4u gate columns):
+// eight 64-wide K-blocks loaded once by TMA (128 KB resident).  B = dz of the step, written by the
+// gate-gradient threads (bf16, swizzled).  dh_rec comes back through TMEM (NS columns); dc_rec stays
+// in registers.  dz is also streamed to HBM in bf16 for the weight-gradient GEMMs.
+constexpr int LB_KB = 4 * LT_U / 64;                           // 8 K-blocks
+constexpr int LB_W_BYTES = LB_KB * 128 * 128;                  // 131072
+constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                // 32768
+constexpr int LB_SMEM = LB_W_BYTES + LB_Z_BYTES + 256 + 1024;
+
+struct LstmTcBwdP {
+  const float* dhout; const __nv_bfloat16* gates_bf; const float* cstate; __nv_bfloat16* dz_bf;
+  int X, L;
+  float keep_prob; unsigned long long seed; const long long* seed_step;
+};
+
+__global__ void __launch_bounds__(LT_THREADS, 1)
+tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_constant__ CUtensorMap tmWb, LstmTcBwdP p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;                                   // [8 kb][128 rows][128 B]
+  uint8_t* sZ = smem + LB_W_BYTES;                      // [8 kb][NS rows][128 B]
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(sZ + LB_Z_BYTES);
+  uint64_t* mma_done = w_full + 1;
+  uint64_t* z_ready = mma_done + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_ready + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int dir = blockIdx.y;
+  const int x0 = blockIdx.x * LT_NS;
+  const int L = p.L;
+  unsigned long long seed = p.seed;
+  if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
+
+  if (warp == LT_MMA_WARP && lane == 0) {
+    tma_prefetch_desc(dir ? &tmWb : &tmWf);
+    mbar_init(w_full, 1);
+    mbar_init(mma_done, 1);
+    mbar_init(z_ready, LT_GATE_THREADS);
+    fence_barrier_init();
+  }
+  if (warp == LT_MMA_WARP) tmem_alloc(tmem_slot, LT_NS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t taddr = *tmem_slot;
+
+  if (warp == LT_MMA_WARP) {
+    if (lane == 0) {
+      const CUtensorMap* tmW = dir ? &tmWb : &tmWf;
+      mbar_expect_tx(w_full, LB_W_BYTES);
+      for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sW + kb * 16384, tmW, w_full, kb * 64, 0, 0);
+      mbar_wait(w_full, 0);
+      constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
+      const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+      for (int step = 0; step + 1 < L; ++step) {          // the last step's dh_rec has no consumer
+        mbar_wait(z_ready, step & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kb = 0; kb < LB_KB; ++kb) {
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4) {
+            const uint64_t ad = smem_desc_sw128(w_base + kb * 16384 + k4 * 32, 0, 1024);
+            const uint64_t bd = smem_desc_sw128(z_base + kb * (LT_NS * 128) + k4 * 32, 0, 1024);
+            umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(mma_done);
+      }
+    }
+  } else {
+    const int m = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+    const float inv_keep = 1.0f / p.keep_prob;
+    float dcr[LT_SPT];
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) dcr[q] = 0.f;
+    // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
+    uint8_t* zdst = sZ + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
+    const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
+
+    for (int step = 0; step < L; ++step) {
+      const int pstep = L - 1 - step;
+      const int t = dir ? (L - 1 - pstep) : pstep;
+      const int tprev = dir ? (t + 1) : (t - 1);
+      // ---- saved activations of this step (independent of the MMA in flight: issued before the wait)
+      float dh[LT_SPT], gi[LT_SPT], gj[LT_SPT], gf[LT_SPT], go[LT_SPT], cc[LT_SPT], cp[LT_SPT];
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        const int x = x0 + hf * LT_SPT + q;
+        if (x < p.X) {
+          const long long tok = ((long long)dir * p.X + x) * L + t;
+          const long long oi = ((long long)x * L + t) * (2 * LT_U) + dir * LT_U + m;
+          float d = p.dhout[oi];
+          if (p.keep_prob < 1.0f) d = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? d * inv_keep : 0.f;
+          dh[q] = d;
+          const __nv_bfloat16* gp = p.gates_bf + tok * (4 * LT_U) + m;
+          gi[q] = __bfloat162float(gp[0]); gj[q] = __bfloat162float(gp[LT_U]);
+          gf[q] = __bfloat162float(gp[2 * LT_U]); go[q] = __bfloat162float(gp[3 * LT_U]);
+          cc[q] = p.cstate[tok * LT_U + m];
+          cp[q] = (pstep > 0) ? p.cstate[(((long long)dir * p.X + x) * L + tprev) * LT_U + m] : 0.f;
+        } else {
+          dh[q] = 0.f; gi[q] = 0.f; gj[q] = 0.f; gf[q] = 0.f; go[q] = 0.f; cc[q] = 0.f; cp[q] = 0.f;
+        }
+      }
+      if (step > 0) {
+        float dhr[LT_SPT];
+        mbar_wait(mma_done, (step - 1) & 1);
+        tc_fence_after();
+        tmem_ld16(lane_addr, dhr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < LT_SPT; ++q) dh[q] += dhr[q];
+      }
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        const int sl = hf * LT_SPT + q;
+        const int x = x0 + sl;
+        const float tc_ = tanh_fast(cc[q]);
+        const float dob = dh[q] * tc_ * go[q] * (1.f - go[q]);
+        const float dc = dcr[q] + dh[q] * go[q] * (1.f - tc_ * tc_);
+        const float di = dc * gj[q] * gi[q] * (1.f - gi[q]);
+        const float dj = dc * gi[q] * (1.f - gj[q] * gj[q]);
+        const float df = dc * cp[q] * gf[q] * (1.f - gf[q]);
+        dcr[q] = dc * gf[q];
+        const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
+                            bo = __float2bfloat16(dob);
+        uint8_t* zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
+        *reinterpret_cast<__nv_bfloat16*>(zp) = bi;
+        *reinterpret_cast<__nv_bfloat16*>(zp + 2 * (LT_NS * 128)) = bj;
+        *reinterpret_cast<__nv_bfloat16*>(zp + 4 * (LT_NS * 128)) = bf;
+        *reinterpret_cast<__nv_bfloat16*>(zp + 6 * (LT_NS * 128)) = bo;
+        if (x < p.X) {
+          __nv_bfloat16* gz = p.dz_bf + (((long long)dir * p.X + x) * L + t) * (4 * LT_U) + m;
+          gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
+        }
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      mbar_arrive(z_ready);
+    }
+  }
+  __syncthreads();
+  if (warp == LT_MMA_WARP) tmem_dealloc(taddr, LT_NS);
+}
+
+// out[c] = sum_r A[r][c] for a bf16 matrix (bias gradient from the bf16 dz stream)
+__global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ A, long long rows, int cols, float* out,
+                                   int rows_per_block) {
+  __shared__ float red[8][33];
+  int tx = threadIdx.x % 32, ty = threadIdx.x / 32;
+  int c = blockIdx.x * 32 + tx;
+  long long r0 = (long long)blockIdx.y * rows_per_block;
+  long long r1 = min(rows, r0 + rows_per_block);
+  float s = 0.f;
+  if (c < cols)
+    for (long long r = r0 + ty; r < r1; r += 8) s += __bfloat162float(A[r * cols + c]);
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][tx];
+    atomicAdd(out + c, t);
+  }
+}
+
+}  // namespace indnet
+
+using namespace indnet;
+
+extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
+                                  const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout,
+                                  void* hout_bf, float* gates, void* gates_bf, float* cstate, float* hprev,
+                                  void* hprev_bf, int X, int L, int D, int u, float keep_prob,
+                                  unsigned long long seed, const long long* seed_step) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(X >= 0 && L > 0, "lstm_fwd_tc: bad sizes X=%d L=%d", X, L);
+  IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_fwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
+  IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_fwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
+  if (X == 0) return INDNET_OK;
+  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && cstate && (hout || hout_bf),
+             "lstm_fwd_tc: null pointer");
+  lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw,
+                                                                                    (__nv_bfloat16*)wt_scratch, D);
+  IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
+  CUtensorMap tmW, tmX;
+  // WT as [dir][4u rows][192]: box 64 (k) x 128 (rows)
+  int rc = make_tmap_bf16(&tmW, wt_scratch, LT_K, 4 * LT_U, LT_K, 2, (long long)4 * LT_U * LT_K, 64, 128);
+  if (rc) return rc;
+  // x as [X][L][64]: box 64 x 1 (step) x NS (sentences) -> NS rows of 128 B
+  {
+    typedef CUresult (*Fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                           const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                           CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    IN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q));
+    IN_REQUIRE(fp && q == cudaDriverEntryPointSuccess, "lstm_fwd_tc: cuTensorMapEncodeTiled unavailable");
+    cuuint64_t dims[3] = {(cuuint64_t)LT_KX, (cuuint64_t)L, (cuuint64_t)X};
+    cuuint64_t strides[2] = {(cuuint64_t)LT_KX * 2, (cuuint64_t)L * LT_KX * 2};
+    cuuint32_t box[3] = {(cuuint32_t)LT_KX, 1, (cuuint32_t)LT_NS};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = ((Fn)fp)(&tmX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(x_bf), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    IN_REQUIRE(r == CUDA_SUCCESS, "lstm_fwd_tc: cuTensorMapEncodeTiled(x) failed with %d", (int)r);
+  }
+  LstmTcP p;
+  p.bias_fw = bias_fw; p.bias_bw = bias_bw;
+  p.hout = hout; p.hout_bf = (__nv_bfloat16*)hout_bf;
+  p.gates = gates; p.gates_bf = (__nv_bfloat16*)gates_bf;
+  p.cstate = cstate; p.hprev = hprev; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
+  p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LT_SMEM));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(X, LT_NS), 2);
+  tc_lstm_fwd_kernel<<<grid, LT_THREADS, LT_SMEM, st>>>(tmW, tmX, p);
+  IN_LAUNCH_CHECK("tc_lstm_fwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const float* dhout, const void* gates_bf, const float* cstate,
+                                  const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D,
+                                  int u, float keep_prob, unsigned long long seed, const long long* seed_step) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(X >= 0 && L > 0, "lstm_bwd_tc: bad sizes X=%d L=%d", X, L);
+  IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_bwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
+  IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_bwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
+  if (X == 0) return INDNET_OK;
+  IN_REQUIRE(dhout && gates_bf && cstate && kernel_fw_bf && kernel_bw_bf && dz_bf, "lstm_bwd_tc: null pointer");
+  // W_h = rows D.. of the bf16 TF kernel [D+u][4u]
+  CUtensorMap tmWf, tmWb;
+  const __nv_bfloat16* wf = (const __nv_bfloat16*)kernel_fw_bf + (long long)D * 4 * LT_U;
+  const __nv_bfloat16* wb = (const __nv_bfloat16*)kernel_bw_bf + (long long)D * 4 * LT_U;
+  int rc = make_tmap_bf16(&tmWf, wf, 4 * LT_U, LT_U, 4 * LT_U, 1, 0, 64, 128);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmWb, wb, 4 * LT_U, LT_U, 4 * LT_U, 1, 0, 64, 128);
+  if (rc) return rc;
+  LstmTcBwdP p;
+  p.dhout = dhout; p.gates_bf = (const __nv_bfloat16*)gates_bf; p.cstate = cstate; p.dz_bf = (__nv_bfloat16*)dz_bf;
+  p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(X, LT_NS), 2);
+  tc_lstm_bwd_kernel<<<grid, LT_THREADS, LB_SMEM, st>>>(tmWf, tmWb, p);
+  IN_LAUNCH_CHECK("tc_lstm_bwd_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_colsum_bf16(indnet_stream st_, const void* A, long long rows, int cols, float* out) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(rows >= 0 && cols >= 0, "colsum_bf16: bad sizes");
+  if (cols == 0) return INDNET_OK;
+  IN_REQUIRE(out != nullptr, "colsum_bf16: null output");
+  IN_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * cols, st));
+  if (rows == 0) return INDNET_OK;
+  IN_REQUIRE(A != nullptr, "colsum_bf16: null input");
+  int rpb = 256;
+  long long gy = (rows + rpb - 1) / rpb;
+  while (gy > 65535) { rpb *= 2; gy = (rows + rpb - 1) / rpb; }
+  colsum_bf16_kernel<<<dim3(ceil_div(cols, 32), (unsigned)gy), 256, 0, st>>>((const __nv_bfloat16*)A, rows, cols, out, rpb);
+  IN_LAUNCH_CHECK("colsum_bf16_kernel");
+  return INDNET_OK;
+}

@@ -276,6 +276,11 @@ class EpisodePipeline:
             self.hout_bf = h(c.T, c.H)
             self.es_bf = h(c.B * c.NK, c.H)
             self.cvec_bf = h(c.B * c.N, c.H)
+            self.hprev_bf = h(2, c.T, c.u)
+            self.tc_lstm = (c.u == 128)        # persistent tcgen05 recurrence is specialised for u = 128
+            if self.tc_lstm:
+                self.wt_bf = h(2, 4 * c.u, 64 + c.u)
+                self.gates_bf = h(2, c.T, 4 * c.u)
 
     # ------------------------------------------------------------------ helpers
     def _call(self, name, *args):
@@ -390,15 +395,23 @@ class EpisodePipeline:
         u4 = 4 * c.u
         self._call("indnet_embed_fwd_bf16", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(wt),
                    ptr(p.view("pos1_embedding")), ptr(p.view("pos2_embedding")), ptr(self.x_bf), c.T, c.E, POS_DIM)
-        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
-            # K = 64: the zero-padded x columns 60..63 meet rows D..D+3 of the TF kernel (finite), product 0
-            self._tc(0, 1, c.T, u4, 64, self.x_bf, 64, p.view_bf(kn), u4, C=self.xproj[d], bias=p.view(bn),
-                     tag="inproj")
-        wh_fw = p.view(FW_K)[c.D:]
-        wh_bw = p.view(BW_K)[c.D:]
-        self._call("indnet_lstm_fwd", ptr(self.xproj), ptr(wh_fw), ptr(wh_bw), ptr(self.hout), ptr(self.gates),
-                   ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
-        self._cast(self.hout, self.hout_bf, "hout")
+        if self.tc_lstm:
+            # input projection + recurrence + gates in one persistent tcgen05 kernel
+            self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
+                       ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), ptr(self.hout), ptr(self.hout_bf),
+                       None, ptr(self.gates_bf), ptr(self.cstate), None, ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
+                       keep, self.seed, ptr(p.global_step))
+        else:
+            for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+                # K = 64: the zero-padded x columns 60..63 meet rows D..D+3 of the TF kernel (finite), product 0
+                self._tc(0, 1, c.T, u4, 64, self.x_bf, 64, p.view_bf(kn), u4, C=self.xproj[d], bias=p.view(bn),
+                         tag="inproj")
+            wh_fw = p.view(FW_K)[c.D:]
+            wh_bw = p.view(BW_K)[c.D:]
+            self._call("indnet_lstm_fwd", ptr(self.xproj), ptr(wh_fw), ptr(wh_bw), ptr(self.hout), ptr(self.gates),
+                       ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
+            self._cast(self.hout, self.hout_bf, "hout")
+            self._cast(self.hprev, self.hprev_bf, "hprev")
         self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, C=self.proj, bias=p.view(ATT_B),
                  act=1, tag="attn_dense")
         self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
@@ -442,7 +455,6 @@ class EpisodePipeline:
             self.dehat_bf = h(c.B * c.NK, c.H)
             self.dpre_bf = h(c.T, c.H)
             self.dz_bf = h(2, c.T, 4 * c.u)
-            self.hprev_bf = h(2, c.T, c.u)
         self._bwd_ready = True
 
     def backward(self):
@@ -537,18 +549,22 @@ class EpisodePipeline:
         self._call("indnet_colsum", ptr(self.dpre), c.T, c.H, c.H, ptr(p.grad(ATT_B)), 0)
         self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
                  splitk=1, tag="attn_dh")
-        wh_fw = p.view(FW_K)[c.D:]
-        wh_bw = p.view(BW_K)[c.D:]
-        self._call("indnet_lstm_bwd", ptr(self.dhout), ptr(self.gates), ptr(self.cstate), ptr(wh_fw), ptr(wh_bw),
-                   ptr(self.whT), ptr(self.dz), c.X, c.L, c.u, self._last_keep, self.seed, ptr(p.global_step))
-        self._cast(self.dz, self.dz_bf, "dz")
-        self._cast(self.hprev, self.hprev_bf, "hprev")
+        if self.tc_lstm:
+            self._call("indnet_lstm_bwd_tc", ptr(self.dhout), ptr(self.gates_bf), ptr(self.cstate),
+                       ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), c.X, c.L, c.D, c.u,
+                       self._last_keep, self.seed, ptr(p.global_step))
+        else:
+            wh_fw = p.view(FW_K)[c.D:]
+            wh_bw = p.view(BW_K)[c.D:]
+            self._call("indnet_lstm_bwd", ptr(self.dhout), ptr(self.gates), ptr(self.cstate), ptr(wh_fw), ptr(wh_bw),
+                       ptr(self.whT), ptr(self.dz), c.X, c.L, c.u, self._last_keep, self.seed, ptr(p.global_step))
+            self._cast(self.dz, self.dz_bf, "dz")
         n0 = 0 if self.trainable_words else c.E
         for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
             gk = p.grad(kn)
             self._tc(1, 1, c.D, u4, c.T, self.x_bf, 64, self.dz_bf[d], u4, C=gk, tag="lstm_dWx")
             self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
-            self._call("indnet_colsum", ptr(self.dz[d]), c.T, u4, u4, ptr(p.grad(bn)), 0)
+            self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))
             self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
                      C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
         g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
