@@ -119,14 +119,15 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
 /* bf16 tensor-core mode of indnet_lstm_fwd with the input projection fused in (hidden_size 128,
  * E+10 <= 64): x_bf [X][L][64] bf16 zero-padded embeddings (indnet_embed_fwd_bf16), kernel_* the TF
  * LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch: caller-provided bf16 [2][4u][192] (packed
- * transposed weights, rebuilt every call).  Outputs as indnet_lstm_fwd, each optionally in fp32
- * and/or bf16 (NULL = skip; cstate is always written). */
+ * transposed weights, rebuilt every call).  Writes hout_bf [X][L][2u] bf16 (and hout fp32 when not
+ * NULL), and for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate
+ * [2][X][L][u] fp32, hprev_bf [2][X][L][u] bf16. */
 int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                        const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout, void* hout_bf,
-                       float* gates, void* gates_bf, float* cstate, float* hprev, void* hprev_bf, int X, int L, int D,
-                       int u, float keep_prob, unsigned long long seed, const long long* seed_step);
+                       void* gates_bf, float* cstate, void* hprev_bf, int X, int L, int D, int u, float keep_prob,
+                       unsigned long long seed, const long long* seed_step);
 
-/* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][4u] bf16 and cstate
+/* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] bf16 and cstate
  * fp32 as saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h
  * = rows D.., read in place by TMA, no scratch).  Writes dz_bf [2][X][L][4u] bf16. */
 int indnet_lstm_bwd_tc(indnet_stream st, const float* dhout, const void* gates_bf, const float* cstate,

@@ -176,31 +176,42 @@ sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_s
     const int idx = cur + tid;
     const bool valid = idx < MT_N;
     const uint32_t y = valid ? ntemp[idx] : 0u;
-    bool acc_me = valid && ((y & mask_for((uint32_t)i)) <= (uint32_t)i);
-    int c = 0, total = 0;
+    // Two-level fixed point.  Outer: each warp publishes how many of its 32 draws it accepts and
+    // reads its carry-in (accepted by the warps before it).  Inner: with that carry the warp settles
+    // its own 32 lanes exactly by ballot iteration (no block barrier).  Repeat until no warp's count
+    // moves.  First guess: the expected number of earlier accepts at the batch's acceptance rate.
+    const uint32_t m0 = mask_for((uint32_t)i);
+    int c = (int)(((long long)tid * (i + 1)) >> (32 - __clz(m0)));
     uint32_t v = 0;
+    bool acc_me = false;
+    {
+      const int ip = i - c;
+      if (valid && ip >= 1) { v = y & mask_for((uint32_t)ip); acc_me = v <= (uint32_t)ip; }
+    }
+    uint32_t bal = __ballot_sync(0xffffffffu, acc_me);
+    int total = 0;
     while (true) {
-      const uint32_t bal = __ballot_sync(0xffffffffu, acc_me);
-      if (lane == 0) wcount[warp] = __popc(bal);
+      const int published = __popc(bal);
+      if (lane == 0) wcount[warp] = published;
       __syncthreads();
       const int4 w0 = *reinterpret_cast<const int4*>(&wcount[0]);
       const int4 w1 = *reinterpret_cast<const int4*>(&wcount[4]);
       const int wc[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-      const int s01 = wc[0] + wc[1], s23 = wc[2] + wc[3], s45 = wc[4] + wc[5], s67 = wc[6] + wc[7];
-      total = (s01 + s23) + (s45 + s67);
+      total = ((wc[0] + wc[1]) + (wc[2] + wc[3])) + ((wc[4] + wc[5]) + (wc[6] + wc[7]));
       int prefix = 0;
 #pragma unroll
       for (int w = 0; w < SMP_NT / 32; ++w) prefix += (w < warp) ? wc[w] : 0;
-      c = prefix + __popc(bal & below);
-      const int ip = i - c;
-      bool again = false;
-      if (valid && ip >= 1) {
-        v = y & mask_for((uint32_t)ip);
-        again = v <= (uint32_t)ip;
+      while (true) {      // warp-local: exact for this carry-in
+        c = prefix + __popc(bal & below);
+        const int ip = i - c;
+        bool again = false;
+        if (valid && ip >= 1) { v = y & mask_for((uint32_t)ip); again = v <= (uint32_t)ip; }
+        const uint32_t bal2 = __ballot_sync(0xffffffffu, again);
+        acc_me = again;
+        if (bal2 == bal) break;
+        bal = bal2;
       }
-      const int changed = __syncthreads_or(again != acc_me);
-      acc_me = again;
-      if (!changed) break;
+      if (!__syncthreads_or(__popc(bal) != published)) break;
     }
     int consumed = min(SMP_NT, MT_N - cur);
     if (total == i) {                 // the permutation completes inside this round

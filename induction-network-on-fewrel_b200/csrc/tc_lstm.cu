@@ -11,8 +11,8 @@
 //   step ahead); h_{t-1} is written by the gate threads straight into the swizzled B-operand layout.
 // * Gate math (forget bias 1.0, no length masking - SURVEY A.1/A.2) runs on the accumulators right
 //   after tcgen05.ld; c stays in registers for the whole sequence.
-// Warps 0-7: gate threads (TMEM lane quarter = warp % 4, sentence half = warp / 4).
-// Warp 8: TMA + single-thread MMA issue.
+// Warps 0-7: gate threads (TMEM lane quarter = warp % 4, sentence half = warp / 4); thread 0 also
+// issues the TMA loads and the MMAs between its gate phases.
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "tc_common.cuh"
@@ -27,9 +27,7 @@ constexpr int LT_KX = 64;            // padded input width (D <= 64)
 constexpr int LT_K = LT_KX + LT_U;   // 192
 constexpr int LT_KB = LT_K / 64;     // 3 K-blocks of 64 (one 128-byte swizzle row each)
 constexpr int LT_NS = 32;            // sentences per CTA (MMA N)
-constexpr int LT_THREADS = 288;
-constexpr int LT_GATE_THREADS = 256;
-constexpr int LT_MMA_WARP = 8;
+constexpr int LT_THREADS = 256;
 constexpr int LT_SPT = LT_NS / 2;        // sentences per gate thread
 static_assert(LT_SPT == 16, "gate threads use 16-column TMEM loads");
 constexpr int LT_W_BYTES = 4 * LT_KB * 128 * 128;            // 196608
@@ -65,13 +63,23 @@ __device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(tanh_fast(0
 struct LstmTcP {
   const float* bias_fw; const float* bias_bw;
   float* hout; __nv_bfloat16* hout_bf;
-  float* gates; __nv_bfloat16* gates_bf;
-  float* cstate;
-  float* hprev; __nv_bfloat16* hprev_bf;
+  __nv_bfloat16* gates_bf;      // [2][X][L][u][4]  (i, j, f, o of a unit adjacent: one 8-byte store / load)
+  float* cstate;                // [2][X][L][u]
+  __nv_bfloat16* hprev_bf;      // [2][X][L][u]
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
 
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+// All 8 warps are gate warps (TMEM lane quarter = warp % 4, sentence half = warp / 4); thread 0 also
+// plays the TMA / MMA issuer between its own gate phases (it would be waiting on the MMA anyway), so
+// the CTA is exactly 256 threads and every thread may use up to 255 registers.
 __global__ void __launch_bounds__(LT_THREADS, 1)
 tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, LstmTcP p) {
   extern __shared__ uint8_t smem_raw[];
@@ -86,145 +94,134 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool issuer = threadIdx.x == 0;
   const int dir = blockIdx.y;
   const int x0 = blockIdx.x * LT_NS;
   const int L = p.L;
   unsigned long long seed = p.seed;
   if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
 
-  // h_{-1} = 0
-  for (int i = threadIdx.x; i < LT_HB_BYTES / 16; i += LT_THREADS) reinterpret_cast<uint4*>(sH)[i] = make_uint4(0, 0, 0, 0);
-  if (warp == LT_MMA_WARP && lane == 0) {
+  for (int i = threadIdx.x; i < LT_HB_BYTES / 16; i += LT_THREADS) reinterpret_cast<uint4*>(sH)[i] = make_uint4(0, 0, 0, 0);   // h_{-1} = 0
+  if (issuer) {
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmX);
     mbar_init(w_full, 1);
     mbar_init(&x_full[0], 1);
     mbar_init(&x_full[1], 1);
     mbar_init(mma_done, 1);
-    mbar_init(h_ready, LT_GATE_THREADS);
+    mbar_init(h_ready, LT_THREADS);
     fence_barrier_init();
   }
-  if (warp == LT_MMA_WARP) tmem_alloc(tmem_slot, 4 * LT_NS);
+  __syncwarp();
+  if (warp == 0) tmem_alloc(tmem_slot, 4 * LT_NS);
   fence_proxy_async();          // the zero-fill of sH must be visible to the tensor core's operand reads
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
+  constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
+  const uint32_t w_base = smem_u32(sW), x_base = smem_u32(sX), h_base = smem_u32(sH);
 
-  if (warp == LT_MMA_WARP) {
-    if (lane == 0) {
-      // resident weights: 12 boxes of 64 (k) x 128 (rows)
-      mbar_expect_tx(w_full, LT_W_BYTES);
-      for (int g = 0; g < 4; ++g)
-        for (int kb = 0; kb < LT_KB; ++kb)
-          tma_load_3d(sW + (g * LT_KB + kb) * 16384, &tmW, w_full, kb * 64, g * 128, dir);
-      // x of the first step
-      {
-        const int t = dir ? (L - 1) : 0;
-        mbar_expect_tx(&x_full[0], LT_XB_BYTES);
-        tma_load_3d(sX, &tmX, &x_full[0], 0, t, x0);
-      }
-      mbar_wait(w_full, 0);
-      constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
-      const uint32_t w_base = smem_u32(sW), x_base = smem_u32(sX), h_base = smem_u32(sH);
-      for (int s = 0; s < L; ++s) {
-        if (s > 0) mbar_wait(h_ready, (s - 1) & 1);      // h_{s-1} is in sH and TMEM has been drained
-        if (s + 1 < L) {                                  // prefetch x of the next step (its buffer is free)
-          const int tn = dir ? (L - 2 - s) : (s + 1);
-          mbar_expect_tx(&x_full[(s + 1) & 1], LT_XB_BYTES);
-          tma_load_3d(sX + ((s + 1) & 1) * LT_XB_BYTES, &tmX, &x_full[(s + 1) & 1], 0, tn, x0);
+  // issue the MMAs of processing step s (thread 0 only)
+  auto issue_step = [&](int s) {
+    if (s + 1 < L) {                                      // prefetch x of the step after (its buffer is free)
+      const int tn = dir ? (L - 2 - s) : (s + 1);
+      mbar_expect_tx(&x_full[(s + 1) & 1], LT_XB_BYTES);
+      tma_load_3d(sX + ((s + 1) & 1) * LT_XB_BYTES, &tmX, &x_full[(s + 1) & 1], 0, tn, x0);
+    }
+    mbar_wait(&x_full[s & 1], (s >> 1) & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+      for (int kb = 0; kb < LT_KB; ++kb) {
+        const uint32_t b_tile = (kb == 0) ? (x_base + (s & 1) * LT_XB_BYTES) : (h_base + (kb - 1) * (LT_NS * 128));
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const uint64_t ad = smem_desc_sw128(w_base + (g * LT_KB + kb) * 16384 + k4 * 32, 0, 1024);
+          const uint64_t bd = smem_desc_sw128(b_tile + k4 * 32, 0, 1024);
+          umma_bf16(taddr + g * LT_NS, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
         }
-        mbar_wait(&x_full[s & 1], (s >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-#pragma unroll
-          for (int kb = 0; kb < LT_KB; ++kb) {
-            const uint32_t b_tile = (kb == 0) ? (x_base + (s & 1) * LT_XB_BYTES) : (h_base + (kb - 1) * (LT_NS * 128));
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) {
-              const uint64_t ad = smem_desc_sw128(w_base + (g * LT_KB + kb) * 16384 + k4 * 32, 0, 1024);
-              const uint64_t bd = smem_desc_sw128(b_tile + k4 * 32, 0, 1024);
-              umma_bf16(taddr + g * LT_NS, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
-            }
-          }
-        }
-        umma_commit(mma_done);
       }
     }
-  } else {
-    // ---- gate threads: thread = (unit m = TMEM lane, sentence half hf), LT_SPT sentences each
-    const int m = (warp & 3) * 32 + lane;
-    const int hf = warp >> 2;
-    const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
-    const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
-    const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
-    const float inv_keep = 1.0f / p.keep_prob;
-    float c[LT_SPT];
-    float hp[LT_SPT];     // h_{t-1} (fp32) of this unit, for the hprev save
-#pragma unroll
-    for (int s = 0; s < LT_SPT; ++s) { c[s] = 0.f; hp[s] = 0.f; }
-    // destination of this unit inside the swizzled h tile: K-block m/64, element k = m%64
-    const int hkb = m >> 6, hk = m & 63;
-    uint8_t* hdst = sH + hkb * (LT_NS * 128) + (hk & 7) * 2;
-    const uint32_t hchunk = (uint32_t)(hk >> 3);
+    umma_commit(mma_done);
+  };
 
-    for (int s = 0; s < L; ++s) {
-      const int t = dir ? (L - 1 - s) : s;
-      mbar_wait(mma_done, s & 1);
-      tc_fence_after();
-      {
-        float zi[16], zj[16], zf[16], zo[16];
-        tmem_ld16(lane_addr + 0 * LT_NS, zi);
-        tmem_ld16(lane_addr + 1 * LT_NS, zj);
-        tmem_ld16(lane_addr + 2 * LT_NS, zf);
-        tmem_ld16(lane_addr + 3 * LT_NS, zo);
-        tmem_ld_wait();
+  if (issuer) {
+    mbar_expect_tx(w_full, LT_W_BYTES);                   // resident weights: 12 boxes of 64 (k) x 128 (rows)
+    for (int g = 0; g < 4; ++g)
+      for (int kb = 0; kb < LT_KB; ++kb)
+        tma_load_3d(sW + (g * LT_KB + kb) * 16384, &tmW, w_full, kb * 64, g * 128, dir);
+    mbar_expect_tx(&x_full[0], LT_XB_BYTES);              // x of the first step
+    tma_load_3d(sX, &tmX, &x_full[0], 0, dir ? (L - 1) : 0, x0);
+    mbar_wait(w_full, 0);
+    issue_step(0);
+  }
+
+  // ---- gate phase: thread = (unit m = TMEM lane, sentence half hf), LT_SPT sentences each
+  const int m = (warp & 3) * 32 + lane;
+  const int hf = warp >> 2;
+  const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
+  const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
+  const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+  const float inv_keep = 1.0f / p.keep_prob;
+  const bool drop = p.keep_prob < 1.0f;
+  float c[LT_SPT], hp[LT_SPT];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) {
-          const int sl = hf * LT_SPT + q;
-          const int x = x0 + sl;
-          const float gi = sigmoid_fast(zi[q] + bi);
-          const float gj = tanh_fast(zj[q] + bj);
-          const float gf = sigmoid_fast(zf[q] + bf);
-          const float go = sigmoid_fast(zo[q] + bo);
-          const float cn = fmaf(c[q], gf, gi * gj);
-          const float h = tanh_fast(cn) * go;
-          c[q] = cn;
-          // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
-          *reinterpret_cast<__nv_bfloat16*>(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4)) = __float2bfloat16(h);
-          if (x < p.X) {
-            const long long tok = ((long long)dir * p.X + x) * L + t;
-            if (p.gates) {
-              float* gp = p.gates + tok * (4 * LT_U) + m;
-              gp[0] = gi; gp[LT_U] = gj; gp[2 * LT_U] = gf; gp[3 * LT_U] = go;
-            }
-            if (p.gates_bf) {
-              __nv_bfloat16* gp = p.gates_bf + tok * (4 * LT_U) + m;
-              gp[0] = __float2bfloat16(gi); gp[LT_U] = __float2bfloat16(gj);
-              gp[2 * LT_U] = __float2bfloat16(gf); gp[3 * LT_U] = __float2bfloat16(go);
-            }
-            p.cstate[tok * LT_U + m] = cn;
-            if (p.hprev) p.hprev[tok * LT_U + m] = hp[q];
-            if (p.hprev_bf) p.hprev_bf[tok * LT_U + m] = __float2bfloat16(hp[q]);
-            const long long oi = ((long long)x * L + t) * (2 * LT_U) + dir * LT_U + m;
-            float ho = h;
-            if (p.keep_prob < 1.0f) ho = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? h * inv_keep : 0.f;
-            if (p.hout) p.hout[oi] = ho;
-            if (p.hout_bf) p.hout_bf[oi] = __float2bfloat16(ho);
-          }
-          hp[q] = h;
-        }
+  for (int q = 0; q < LT_SPT; ++q) { c[q] = 0.f; hp[q] = 0.f; }
+  const int hkb = m >> 6, hk = m & 63;                     // destination inside the swizzled h tile
+  uint8_t* hdst = sH + hkb * (LT_NS * 128) + (hk & 7) * 2;
+  const uint32_t hchunk = (uint32_t)(hk >> 3);
+  const int xs0 = x0 + hf * LT_SPT;                        // first sentence of this thread
+  const int tok_base = (dir * p.X + xs0) * L;              // token index of (sentence q, time t) = tok_base + q*L + t
+
+  for (int s = 0; s < L; ++s) {
+    const int t = dir ? (L - 1 - s) : s;
+    mbar_wait(mma_done, s & 1);
+    __syncwarp();
+    tc_fence_after();
+    float zi[16], zj[16], zf[16], zo[16];
+    tmem_ld16(lane_addr + 0 * LT_NS, zi);
+    tmem_ld16(lane_addr + 1 * LT_NS, zj);
+    tmem_ld16(lane_addr + 2 * LT_NS, zf);
+    tmem_ld16(lane_addr + 3 * LT_NS, zo);
+    tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) {
+      const int sl = hf * LT_SPT + q;
+      const float gi = sigmoid_fast(zi[q] + bi);
+      const float gj = tanh_fast(zj[q] + bj);
+      const float gf = sigmoid_fast(zf[q] + bf);
+      const float go = sigmoid_fast(zo[q] + bo);
+      const float cn = fmaf(c[q], gf, gi * gj);
+      const float h = tanh_fast(cn) * go;
+      c[q] = cn;
+      // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
+      *reinterpret_cast<__nv_bfloat16*>(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4)) = __float2bfloat16(h);
+      if (xs0 + q < p.X) {
+        const long long e = (long long)(tok_base + q * L + t) * LT_U + m;     // [tok][unit]
+        *reinterpret_cast<uint2*>(p.gates_bf + e * 4) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
+        p.cstate[e] = cn;
+        p.hprev_bf[e] = __float2bfloat16(hp[q]);
+        const long long oi = ((long long)(xs0 + q) * L + t) * (2 * LT_U) + dir * LT_U + m;
+        float ho = h;
+        if (drop) ho = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? h * inv_keep : 0.f;
+        if (p.hout) p.hout[oi] = ho;
+        p.hout_bf[oi] = __float2bfloat16(ho);
       }
-      fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
-      tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
-      mbar_arrive(h_ready);
+      hp[q] = h;
+    }
+    fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
+    tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
+    mbar_arrive(h_ready);
+    if (issuer && s + 1 < L) {
+      mbar_wait(h_ready, s & 1);        // every thread has published h_s and drained TMEM
+      issue_step(s + 1);
     }
   }
   __syncthreads();
-  if (warp == LT_MMA_WARP) tmem_dealloc(taddr, 4 * LT_NS);
+  if (warp == 0) tmem_dealloc(taddr, 4 * LT_NS);
 }
-
 
 // ------------------------------------------------------------------------------------------------
 // BPTT, bf16 tensor-core mode.  Per step (reverse processing order) and tile of NS sentences:
@@ -256,123 +253,149 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool issuer = threadIdx.x == 0;
   const int dir = blockIdx.y;
   const int x0 = blockIdx.x * LT_NS;
   const int L = p.L;
   unsigned long long seed = p.seed;
   if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
+  const CUtensorMap* tmW = dir ? &tmWb : &tmWf;
 
-  if (warp == LT_MMA_WARP && lane == 0) {
-    tma_prefetch_desc(dir ? &tmWb : &tmWf);
+  if (issuer) {
+    tma_prefetch_desc(tmW);
     mbar_init(w_full, 1);
     mbar_init(mma_done, 1);
-    mbar_init(z_ready, LT_GATE_THREADS);
+    mbar_init(z_ready, LT_THREADS);
     fence_barrier_init();
   }
-  if (warp == LT_MMA_WARP) tmem_alloc(tmem_slot, LT_NS);
+  __syncwarp();
+  if (warp == 0) tmem_alloc(tmem_slot, LT_NS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
+  constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
+  const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+  if (issuer) {
+    mbar_expect_tx(w_full, LB_W_BYTES);
+    for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sW + kb * 16384, tmW, w_full, kb * 64, 0, 0);
+  }
 
-  if (warp == LT_MMA_WARP) {
-    if (lane == 0) {
-      const CUtensorMap* tmW = dir ? &tmWb : &tmWf;
-      mbar_expect_tx(w_full, LB_W_BYTES);
-      for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sW + kb * 16384, tmW, w_full, kb * 64, 0, 0);
-      mbar_wait(w_full, 0);
-      constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
-      const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
-      for (int step = 0; step + 1 < L; ++step) {          // the last step's dh_rec has no consumer
-        mbar_wait(z_ready, step & 1);
-        tc_fence_after();
+  const int m = (warp & 3) * 32 + lane;
+  const int hf = warp >> 2;
+  const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+  const float inv_keep = 1.0f / p.keep_prob;
+  const bool drop = p.keep_prob < 1.0f;
+  // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
+  uint8_t* zdst = sZ + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
+  const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
+  const int xs0 = x0 + hf * LT_SPT;
+  const int tok_base = (dir * p.X + xs0) * L;
+  // out-of-range sentences of the last tile read sentence X-1 (any valid address) and are zeroed via dh
+  int qoff[LT_SPT];
+  float live[LT_SPT];
 #pragma unroll
-        for (int kb = 0; kb < LB_KB; ++kb) {
+  for (int q = 0; q < LT_SPT; ++q) {
+    const bool ok = xs0 + q < p.X;
+    qoff[q] = ok ? q : (p.X - 1 - xs0);
+    live[q] = ok ? 1.f : 0.f;
+  }
+  float dcr[LT_SPT], cc[LT_SPT];
+  {
+    const int t_first = dir ? 0 : (L - 1);      // time index of the first step processed here
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t ad = smem_desc_sw128(w_base + kb * 16384 + k4 * 32, 0, 1024);
-            const uint64_t bd = smem_desc_sw128(z_base + kb * (LT_NS * 128) + k4 * 32, 0, 1024);
-            umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
-          }
+    for (int q = 0; q < LT_SPT; ++q) {
+      dcr[q] = 0.f;
+      cc[q] = p.cstate[(long long)(tok_base + qoff[q] * L + t_first) * LT_U + m];
+    }
+  }
+
+  for (int step = 0; step < L; ++step) {
+    const int pstep = L - 1 - step;
+    const int t = dir ? (L - 1 - pstep) : pstep;
+    const int tprev = dir ? (t + 1) : (t - 1);
+    // ---- this step's saved activations: every load is issued before anything waits on them
+    uint2 gw[LT_SPT];
+    float dh[LT_SPT], cp[LT_SPT];
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) {
+      const int tokq = tok_base + qoff[q] * L;
+      const long long e = (long long)(tokq + t) * LT_U + m;
+      gw[q] = *reinterpret_cast<const uint2*>(p.gates_bf + e * 4);
+      dh[q] = p.dhout[((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m];
+      cp[q] = (pstep > 0) ? p.cstate[(long long)(tokq + tprev) * LT_U + m] : 0.f;
+    }
+    if (step > 0) {
+      float dhr[LT_SPT];
+      mbar_wait(mma_done, (step - 1) & 1);
+      __syncwarp();
+      tc_fence_after();
+      tmem_ld16(lane_addr, dhr);
+      tmem_ld_wait();
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        // dropout acts on the external gradient only; the recurrent part is added after it
+        if (drop) {
+          const long long oi = ((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m;
+          dh[q] = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? dh[q] * inv_keep : 0.f;
         }
-        umma_commit(mma_done);
+        dh[q] = (dh[q] + dhr[q]) * live[q];
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        if (drop) {
+          const long long oi = ((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m;
+          dh[q] = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? dh[q] * inv_keep : 0.f;
+        }
+        dh[q] *= live[q];
+      }
+      if (issuer) mbar_wait(w_full, 0);
+    }
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) {
+      const int sl = hf * LT_SPT + q;
+      const float gi = bf16_lo(gw[q].x), gj = bf16_hi(gw[q].x), gf = bf16_lo(gw[q].y), go = bf16_hi(gw[q].y);
+      const float tc_ = tanh_fast(cc[q]);
+      const float dob = dh[q] * tc_ * go * (1.f - go);
+      const float dc = dcr[q] + dh[q] * go * (1.f - tc_ * tc_);
+      const float di = dc * gj * gi * (1.f - gi);
+      const float dj = dc * gi * (1.f - gj * gj);
+      const float df = dc * cp[q] * gf * (1.f - gf);
+      dcr[q] = dc * gf;
+      cc[q] = cp[q];                        // c_{t_prev} is the cell state of the next step processed
+      const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
+                          bo = __float2bfloat16(dob);
+      uint8_t* zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
+      *reinterpret_cast<__nv_bfloat16*>(zp) = bi;
+      *reinterpret_cast<__nv_bfloat16*>(zp + 2 * (LT_NS * 128)) = bj;
+      *reinterpret_cast<__nv_bfloat16*>(zp + 4 * (LT_NS * 128)) = bf;
+      *reinterpret_cast<__nv_bfloat16*>(zp + 6 * (LT_NS * 128)) = bo;
+      if (xs0 + q < p.X) {
+        __nv_bfloat16* gz = p.dz_bf + (long long)(tok_base + q * L + t) * (4 * LT_U) + m;
+        gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
       }
     }
-  } else {
-    const int m = (warp & 3) * 32 + lane;
-    const int hf = warp >> 2;
-    const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
-    const float inv_keep = 1.0f / p.keep_prob;
-    float dcr[LT_SPT];
+    fence_proxy_async();
+    tc_fence_before();
+    mbar_arrive(z_ready);
+    if (issuer && step + 1 < L) {             // the last step's dh_rec has no consumer
+      mbar_wait(z_ready, step & 1);
+      tc_fence_after();
 #pragma unroll
-    for (int q = 0; q < LT_SPT; ++q) dcr[q] = 0.f;
-    // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
-    uint8_t* zdst = sZ + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
-    const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
-
-    for (int step = 0; step < L; ++step) {
-      const int pstep = L - 1 - step;
-      const int t = dir ? (L - 1 - pstep) : pstep;
-      const int tprev = dir ? (t + 1) : (t - 1);
-      // ---- saved activations of this step (independent of the MMA in flight: issued before the wait)
-      float dh[LT_SPT], gi[LT_SPT], gj[LT_SPT], gf[LT_SPT], go[LT_SPT], cc[LT_SPT], cp[LT_SPT];
+      for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
-      for (int q = 0; q < LT_SPT; ++q) {
-        const int x = x0 + hf * LT_SPT + q;
-        if (x < p.X) {
-          const long long tok = ((long long)dir * p.X + x) * L + t;
-          const long long oi = ((long long)x * L + t) * (2 * LT_U) + dir * LT_U + m;
-          float d = p.dhout[oi];
-          if (p.keep_prob < 1.0f) d = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? d * inv_keep : 0.f;
-          dh[q] = d;
-          const __nv_bfloat16* gp = p.gates_bf + tok * (4 * LT_U) + m;
-          gi[q] = __bfloat162float(gp[0]); gj[q] = __bfloat162float(gp[LT_U]);
-          gf[q] = __bfloat162float(gp[2 * LT_U]); go[q] = __bfloat162float(gp[3 * LT_U]);
-          cc[q] = p.cstate[tok * LT_U + m];
-          cp[q] = (pstep > 0) ? p.cstate[(((long long)dir * p.X + x) * L + tprev) * LT_U + m] : 0.f;
-        } else {
-          dh[q] = 0.f; gi[q] = 0.f; gj[q] = 0.f; gf[q] = 0.f; go[q] = 0.f; cc[q] = 0.f; cp[q] = 0.f;
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const uint64_t ad = smem_desc_sw128(w_base + kb * 16384 + k4 * 32, 0, 1024);
+          const uint64_t bd = smem_desc_sw128(z_base + kb * (LT_NS * 128) + k4 * 32, 0, 1024);
+          umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
         }
       }
-      if (step > 0) {
-        float dhr[LT_SPT];
-        mbar_wait(mma_done, (step - 1) & 1);
-        tc_fence_after();
-        tmem_ld16(lane_addr, dhr);
-        tmem_ld_wait();
-#pragma unroll
-        for (int q = 0; q < LT_SPT; ++q) dh[q] += dhr[q];
-      }
-#pragma unroll
-      for (int q = 0; q < LT_SPT; ++q) {
-        const int sl = hf * LT_SPT + q;
-        const int x = x0 + sl;
-        const float tc_ = tanh_fast(cc[q]);
-        const float dob = dh[q] * tc_ * go[q] * (1.f - go[q]);
-        const float dc = dcr[q] + dh[q] * go[q] * (1.f - tc_ * tc_);
-        const float di = dc * gj[q] * gi[q] * (1.f - gi[q]);
-        const float dj = dc * gi[q] * (1.f - gj[q] * gj[q]);
-        const float df = dc * cp[q] * gf[q] * (1.f - gf[q]);
-        dcr[q] = dc * gf[q];
-        const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
-                            bo = __float2bfloat16(dob);
-        uint8_t* zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
-        *reinterpret_cast<__nv_bfloat16*>(zp) = bi;
-        *reinterpret_cast<__nv_bfloat16*>(zp + 2 * (LT_NS * 128)) = bj;
-        *reinterpret_cast<__nv_bfloat16*>(zp + 4 * (LT_NS * 128)) = bf;
-        *reinterpret_cast<__nv_bfloat16*>(zp + 6 * (LT_NS * 128)) = bo;
-        if (x < p.X) {
-          __nv_bfloat16* gz = p.dz_bf + (((long long)dir * p.X + x) * L + t) * (4 * LT_U) + m;
-          gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
-        }
-      }
-      fence_proxy_async();
-      tc_fence_before();
-      mbar_arrive(z_ready);
+      umma_commit(mma_done);
     }
   }
   __syncthreads();
-  if (warp == LT_MMA_WARP) tmem_dealloc(taddr, LT_NS);
+  if (warp == 0) tmem_dealloc(taddr, LT_NS);
 }
 
 // out[c] = sum_r A[r][c] for a bf16 matrix (bias gradient from the bf16 dz stream)
@@ -402,16 +425,16 @@ using namespace indnet;
 
 extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                                   const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout,
-                                  void* hout_bf, float* gates, void* gates_bf, float* cstate, float* hprev,
-                                  void* hprev_bf, int X, int L, int D, int u, float keep_prob,
-                                  unsigned long long seed, const long long* seed_step) {
+                                  void* hout_bf, void* gates_bf, float* cstate, void* hprev_bf, int X, int L, int D,
+                                  int u, float keep_prob, unsigned long long seed, const long long* seed_step) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0, "lstm_fwd_tc: bad sizes X=%d L=%d", X, L);
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_fwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
   IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_fwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && cstate && (hout || hout_bf),
-             "lstm_fwd_tc: null pointer");
+  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && cstate && hout_bf && gates_bf &&
+             hprev_bf, "lstm_fwd_tc: null pointer");
+  IN_REQUIRE((long long)2 * X * L < 2147483647LL / 1, "lstm_fwd_tc: token count exceeds 32-bit indexing");
   lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw,
                                                                                     (__nv_bfloat16*)wt_scratch, D);
   IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
@@ -440,8 +463,8 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   LstmTcP p;
   p.bias_fw = bias_fw; p.bias_bw = bias_bw;
   p.hout = hout; p.hout_bf = (__nv_bfloat16*)hout_bf;
-  p.gates = gates; p.gates_bf = (__nv_bfloat16*)gates_bf;
-  p.cstate = cstate; p.hprev = hprev; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
+  p.gates_bf = (__nv_bfloat16*)gates_bf;
+  p.cstate = cstate; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
   static bool attr_set = false;
   if (!attr_set) {

@@ -399,7 +399,7 @@ class EpisodePipeline:
             # input projection + recurrence + gates in one persistent tcgen05 kernel
             self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
                        ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), ptr(self.hout), ptr(self.hout_bf),
-                       None, ptr(self.gates_bf), ptr(self.cstate), None, ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
+                       ptr(self.gates_bf), ptr(self.cstate), ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
                        keep, self.seed, ptr(p.global_step))
         else:
             for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
