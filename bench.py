@@ -281,6 +281,22 @@ def run_b200(args, w):
         total_ms = sum(a.elapsed_time(b) for a, b in evs)
         loss_after = pipe.loss()
 
+        # ---- same K steps without the sampler in the loop (episodes already resident in HBM)
+        evs2 = []
+        for i in range(args.steps):
+            flush.fill_(float(i))
+            pipe.set_inputs(*dev_pool[i % POOL])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            if graph_train is not None:
+                graph_train.replay()
+            else:
+                train_body()
+            e1.record(stream)
+            evs2.append((e0, e1))
+        stream.synchronize()
+        resident_ms = sum(a.elapsed_time(b) for a, b in evs2)
+
         # ---- roofline leg: per-call CUDA-event timing of the same step, eager launches
         pipe.profile = []
         smp_ev = []
@@ -316,10 +332,10 @@ def run_b200(args, w):
         torch.cuda.synchronize()
         e2e_ms = (time.perf_counter() - t0) * 1000.0
 
-    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    t = torch.tensor([total_ms, e2e_ms, resident_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(t[0]), float(t[1])
+    total_ms, e2e_ms, resident_ms = float(t[0]), float(t[1]), float(t[2])
     ms_per_step = total_ms / args.steps
     value = world * cfg.B * args.steps / (total_ms / 1000.0)
     e2e_value = world * cfg.B * e2e_steps / (e2e_ms / 1000.0)
@@ -334,6 +350,15 @@ def run_b200(args, w):
         flops_tab = {   # algorithmic FLOPs per launch of the calls that can dominate
             "indnet_lstm_fwd": 2 * T * cfg.u * 4 * cfg.u * 2,
             "indnet_lstm_bwd": 2 * T * cfg.u * 4 * cfg.u * 2,
+            # tcgen05 recurrence: input projection (K = 64 padded) + recurrent part, both directions
+            "indnet_lstm_fwd_tc": 2 * T * (64 + cfg.u) * 4 * cfg.u * 2,
+            "indnet_lstm_bwd_tc": 2 * T * cfg.u * 4 * cfg.u * 2,
+            "tc_gemm:attn_dense": 2 * T * cfg.H * cfg.H, "tc_gemm:attn_dW": 2 * T * cfg.H * cfg.H,
+            "tc_gemm:attn_dh": 2 * T * cfg.H * cfg.H, "tc_gemm:lstm_dWx": 2 * T * cfg.D * 4 * cfg.u,
+            "tc_gemm:lstm_dWh": 2 * T * cfg.u * 4 * cfg.u, "tc_gemm:lstm_dx": 2 * T * 10 * 4 * cfg.u,
+            "tc_gemm:ntn_stage1": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S,
+            "tc_gemm:ntn_dM": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S,
+            "tc_gemm:ntn_dcv": 2 * cfg.B * cfg.N * cfg.H * cfg.H * cfg.S,
             "sgemm:attn_dense": 2 * T * cfg.H * cfg.H, "sgemm:attn_dW": 2 * T * cfg.H * cfg.H,
             "sgemm:attn_dh": 2 * T * cfg.H * cfg.H,
             "sgemm:inproj": 2 * T * cfg.D * 4 * cfg.u, "sgemm:lstm_dWx": 2 * T * cfg.D * 4 * cfg.u,
@@ -353,8 +378,18 @@ def run_b200(args, w):
                     "note": "FP32 parity-mode kernels run on FFMA, reported against the bf16 tensor peak"
                     if args.mode == "fp32" else "bf16 tcgen05 mode"}
         else:
-            roof = {"bound": "hbm", "kernel": dom[0], "achieved": None, "peak": peaks.get("hbm_gbs", 6650.0),
-                    "unit": "GB/s", "frac": None, "traffic": None, "avg_launch_ms": dom_ms}
+            # HBM-bound kernels: algorithmic bytes per launch
+            bytes_tab = {
+                "indnet_attn_pool_bwd": cfg.X * (cfg.L * cfg.H * 4 * 4 + cfg.H * 8),   # h, proj in; dh, dpre out
+                "indnet_attn_pool_fwd": cfg.X * 42304,
+                "indnet_embed_bwd": T * 40, "indnet_adam_step": store.numel * 28,
+                "sgemm:ntn_dqe": cfg.B * (cfg.n_q * cfg.N * cfg.S + cfg.N * cfg.S * cfg.H + cfg.n_q * cfg.H) * 4,
+                "sgemm:ntn_stage2": cfg.B * (cfg.n_q * cfg.N * cfg.S + cfg.N * cfg.S * cfg.H + cfg.n_q * cfg.H) * 4,
+            }
+            pk = peaks.get("hbm_gbs", 6650.0)
+            ach = bytes_tab[dom[0]] / (dom_ms * 1e-3) / 1e9 if dom[0] in bytes_tab else None
+            roof = {"bound": "hbm", "kernel": dom[0], "achieved": ach, "peak": pk, "unit": "GB/s",
+                    "frac": (ach / pk) if ach else None, "traffic": None, "avg_launch_ms": dom_ms}
         roof["step_share"] = share
         # whole-step achieved TFLOP/s (train = 3 x forward)
         step_tflops = value * 3 * fwd_flops_per_episode(cfg.N, cfg.K, cfg.L, cfg.u) / 1e12
@@ -386,6 +421,9 @@ def run_b200(args, w):
             "clocks": sampler.summary(),
             "roofline": roof,
             "step_tflops": step_tflops,
+            "train_only": {"value": world * cfg.B * args.steps / (resident_ms / 1000.0), "unit": "episodes/s",
+                           "ms_per_step": resident_ms / args.steps,
+                           "note": "fwd+bwd+all-reduce+Adam on episodes already resident in HBM (sampler not in the loop)"},
             "sampler": {"where": "device, bit-exact MT19937 x2 (csrc/sampler.cu), walk for step t+1 overlapped on a "
                                  "side stream inside the step graph", "walk_ms_serial": sampler_walk_ms},
             "cpu_baseline": cpu,
@@ -402,7 +440,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (0-3)")
-    ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--mode", default="bf16", choices=["fp32", "bf16"],
+                    help="bf16 = tcgen05 tensor-core mode (default); fp32 = FFMA parity mode")
     ap.add_argument("--keep-prob", type=float, default=1.0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

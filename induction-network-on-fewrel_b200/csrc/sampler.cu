@@ -84,6 +84,8 @@ struct SerialMT {
 // NumPy random_interval mask: smallest 2^k - 1 >= mx (mx >= 1): all ones below the top set bit.
 __device__ __forceinline__ uint32_t mask_for(uint32_t mx) { return 0xFFFFFFFFu >> __clz(mx); }
 
+__device__ __forceinline__ bool warp_id_is_zero(int tid) { return tid < 32; }
+
 // status codes written to *status
 enum { SMP_OK = 0, SMP_SCOPE_TOO_SMALL = 1, SMP_SCOPE_TOO_LARGE = 2 };
 
@@ -133,100 +135,149 @@ sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_s
   __syncthreads();
 
   // ---- phase B: the NumPy stream.  jobs: for each episode, N class permutations then the query one.
-  // The whole CTA consumes up to 256 draws per round.  Lane p (stream order) needs c_p = number of
-  // draws accepted before it: then its Fisher-Yates index is i_p = i - c_p, its mask is mask(i_p),
-  // and it is accepted iff (y_p & mask(i_p)) <= i_p.  That is a triangular system (lane p depends
-  // only on lanes before it), so iterating "recount, re-decide" from any start reaches the exact
-  // sequential answer; it settles in a few rounds because only draws near a threshold ever flip.
-  // Every thread keeps the same (job, i, cur) in registers - all updates derive from shared counts.
-  __shared__ uint32_t ntemp[MT_N];
-  __shared__ __align__(16) int wcount[SMP_NT / 32];
-  __shared__ int s_pos;
-  const int warp = tid >> 5;
+  // Warp 0 walks the stream in rows of 32 draws.  With c = draws accepted so far in the row before
+  // lane l, lane l's Fisher-Yates index is i - c, its mask follows from that index, and it is accepted
+  // iff (y & mask) <= index.  That is a triangular system over the lanes, settled exactly by ballot
+  // iteration from the expected-rate guess (it normally confirms on the second ballot, and it crosses
+  // the mask changes inside the row); the carry into the next row is then exact, so there is no
+  // iteration across rows.  Meanwhile the whole CTA keeps a ring of untempered MT19937 blocks ahead of
+  // the consumer (3-phase parallel twist); the state handed back is the block the consumer stopped in.
+  constexpr int RING = 4;      // power of two
+  __shared__ uint32_t ring[RING][MT_N];
+  __shared__ int s_blk, s_off, s_done;
   const uint32_t below = (1u << lane) - 1u;
   const int jobs = B * (N + 1);
-  int cur = (int)np_state[MT_N];
-  for (int k = tid; k < MT_N; k += SMP_NT) ntemp[k] = mt_temper(nkey[k]);
+  for (int k = tid; k < MT_N; k += SMP_NT) ring[0][k] = nkey[k];
   __syncthreads();
-  int job = 0, i = 0, flag = SMP_OK;
+  int gen = 1;                               // blocks generated so far (block b lives in ring[b % RING])
+  int blk = 0, off = (int)np_state[MT_N];    // next draw to consume = block blk, offset off (off may be 624)
+  int done = 0, flag = SMP_OK;
+  // warp-0 job state
+  int job = 0, i = 0;
   bool fresh = true;
-  while (true) {
-    if (fresh) {
-      if (job >= jobs) break;
-      const int b = job / (N + 1), ci = job % (N + 1);
-      int n;
-      if (ci < N) {
-        const int c = classes[(long long)b * N + ci];
-        n = scopes[2 * c + 1] - scopes[2 * c];
-        if (n < K + Q) { flag = SMP_SCOPE_TOO_SMALL; break; }
-        if (n > n_max) { flag = SMP_SCOPE_TOO_LARGE; break; }
-      } else {
-        n = N * Q;
+  int* jrow = jlist;
+  // permutation length of job j (>= 0), or -(error code); jobs past the end report 0
+  auto job_size = [&](int j) -> int {
+    if (j >= jobs) return 0;
+    const int b = j / (N + 1), ci = j % (N + 1);
+    if (ci == N) return N * Q;
+    const int c = classes[(long long)b * N + ci];
+    const int n = scopes[2 * c + 1] - scopes[2 * c];
+    if (n < K + Q) return -SMP_SCOPE_TOO_SMALL;
+    if (n > n_max) return -SMP_SCOPE_TOO_LARGE;
+    return n;
+  };
+  int n_next = job_size(0);
+  const long long clk0 = clock64();
+  int n_pass = 0, n_round = 0;
+  while (!done) {
+    // ---- keep at least one full block (plus a row) generated beyond the consumer
+    while ((gen - 1 - blk) * MT_N - off < MT_N + 32 && gen - blk < RING) {
+      const uint32_t* o = ring[(gen - 1) % RING];
+      uint32_t* w = ring[gen % RING];
+      if (tid < 227) w[tid] = mt_mix(o[tid], o[tid + 1], o[tid + MT_M]);
+      __syncthreads();
+      if (tid < 227) w[tid + 227] = mt_mix(o[tid + 227], o[tid + 228], w[tid]);
+      __syncthreads();
+      if (tid < 170) {
+        const int k = tid + 454;
+        w[k] = mt_mix(o[k], (k + 1 < MT_N) ? o[k + 1] : w[0], w[k - 227]);
       }
-      i = n - 1;
-      fresh = false;
-      if (i <= 0) { ++job; fresh = true; continue; }   // permutation(1): no draws
-    }
-    if (cur >= MT_N) {
-      mt_twist_block(nkey);
-      for (int k = tid; k < MT_N; k += SMP_NT) ntemp[k] = mt_temper(nkey[k]);
       __syncthreads();
-      cur = 0;
+      ++gen;
     }
-    const int idx = cur + tid;
-    const bool valid = idx < MT_N;
-    const uint32_t y = valid ? ntemp[idx] : 0u;
-    // Two-level fixed point.  Outer: each warp publishes how many of its 32 draws it accepts and
-    // reads its carry-in (accepted by the warps before it).  Inner: with that carry the warp settles
-    // its own 32 lanes exactly by ballot iteration (no block barrier).  Repeat until no warp's count
-    // moves.  First guess: the expected number of earlier accepts at the batch's acceptance rate.
-    const uint32_t m0 = mask_for((uint32_t)i);
-    int c = (int)(((long long)tid * (i + 1)) >> (32 - __clz(m0)));
-    uint32_t v = 0;
-    bool acc_me = false;
-    {
-      const int ip = i - c;
-      if (valid && ip >= 1) { v = y & mask_for((uint32_t)ip); acc_me = v <= (uint32_t)ip; }
-    }
-    uint32_t bal = __ballot_sync(0xffffffffu, acc_me);
-    int total = 0;
-    while (true) {
-      const int published = __popc(bal);
-      if (lane == 0) wcount[warp] = published;
-      __syncthreads();
-      const int4 w0 = *reinterpret_cast<const int4*>(&wcount[0]);
-      const int4 w1 = *reinterpret_cast<const int4*>(&wcount[4]);
-      const int wc[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-      total = ((wc[0] + wc[1]) + (wc[2] + wc[3])) + ((wc[4] + wc[5]) + (wc[6] + wc[7]));
-      int prefix = 0;
+    if (warp_id_is_zero(tid)) {
+      // Groups of GR rows (32 draws each) are consumed while a whole group is available in the ring.
+      // Everything that does not depend on the carry (ring reads, tempering) is done for the whole
+      // group up front so those instruction streams overlap; only the accept chain is serial.
+      constexpr int GR = 4;
+      while (true) {
+        if (fresh) {
+          if (job >= jobs) { done = 1; break; }
+          i = n_next - 1;
+          if (n_next < 0) { flag = -n_next; done = 1; break; }
+          jrow = jlist + (long long)job * n_max;
+          n_next = job_size(job + 1);          // prefetch: its global-load latency hides behind this job's rows
+          fresh = false;
+          if (i <= 0) { ++job; fresh = true; continue; }   // permutation(1): no draws
+        }
+        if ((gen - blk) * MT_N - off < 32 * GR) break;     // need more blocks
+        uint32_t y[GR];
 #pragma unroll
-      for (int w = 0; w < SMP_NT / 32; ++w) prefix += (w < warp) ? wc[w] : 0;
-      while (true) {      // warp-local: exact for this carry-in
-        c = prefix + __popc(bal & below);
-        const int ip = i - c;
-        bool again = false;
-        if (valid && ip >= 1) { v = y & mask_for((uint32_t)ip); again = v <= (uint32_t)ip; }
-        const uint32_t bal2 = __ballot_sync(0xffffffffu, again);
-        acc_me = again;
-        if (bal2 == bal) break;
-        bal = bal2;
+        for (int r = 0; r < GR; ++r) {
+          int pb = blk, po = off + r * 32 + lane;
+          if (po >= MT_N) { po -= MT_N; ++pb; }
+          y[r] = mt_temper(ring[pb & (RING - 1)][po]);
+        }
+        int used = 32 * GR;
+#pragma unroll
+        for (int r = 0; r < GR; ++r) {
+          const uint32_t m0 = mask_for((uint32_t)i);
+          const int sh = 32 - __clz(m0);
+          int c = (lane * (i + 1)) >> sh;                  // expected accepts before this lane
+          uint32_t bal, v;
+          int ip;
+          if (i - 31 > (int)(m0 >> 1)) {
+            // common case: every index this row can reach shares the mask -> accept iff c <= i - v
+            v = y[r] & m0;
+            const int t = i - (int)v;
+            bal = __ballot_sync(0xffffffffu, c <= t);
+            while (true) {
+              c = __popc(bal & below);
+              const uint32_t bal2 = __ballot_sync(0xffffffffu, c <= t);
+              ++n_pass;
+              if (bal2 == bal) break;
+              bal = bal2;
+            }
+            ip = i - c;
+          } else {
+            ip = i - c;
+            v = y[r] & mask_for((uint32_t)max(ip, 1));
+            bal = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
+            while (true) {
+              c = __popc(bal & below);
+              ip = i - c;
+              v = y[r] & mask_for((uint32_t)max(ip, 1));
+              const uint32_t bal2 = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
+              ++n_pass;
+              if (bal2 == bal) break;
+              bal = bal2;
+            }
+          }
+          const int acc = __popc(bal);
+          if ((bal >> lane) & 1u) jrow[ip] = (int)v;
+          ++n_round;
+          if (acc >= i) {                                  // the permutation ends at its last accepted draw
+            used = r * 32 + (32 - __clz(bal));
+            ++job;
+            fresh = true;
+            break;
+          }
+          i -= acc;
+        }
+        off += used;
+        if (off > MT_N) { off -= MT_N; ++blk; }            // off == 624 stays: "end of block blk"
       }
-      if (!__syncthreads_or(__popc(bal) != published)) break;
+      if (lane == 0) { s_blk = blk; s_off = off; s_done = done; }
     }
-    int consumed = min(SMP_NT, MT_N - cur);
-    if (total == i) {                 // the permutation completes inside this round
-      if (acc_me && c == total - 1) s_pos = tid;
-      __syncthreads();
-      consumed = s_pos + 1;
-    }
-    if (acc_me) jlist[(long long)job * n_max + (i - c)] = (int)v;
-    i -= total;
-    cur += consumed;
-    if (i <= 0) { ++job; fresh = true; }
+    __syncthreads();
+    blk = s_blk; off = s_off; done = s_done;
+    __syncthreads();
   }
-  __syncthreads();
-  for (int k = tid; k < MT_N; k += SMP_NT) np_state[k] = nkey[k];
-  if (tid == 0) { np_state[MT_N] = (uint32_t)cur; *status = flag; }
+  {
+    // hand back the block the consumer stopped in (an offset of 624 = "block exhausted", which is
+    // also what the host generators hold at a block boundary)
+    const uint32_t* fin = ring[blk % RING];
+    for (int k = tid; k < MT_N; k += SMP_NT) np_state[k] = fin[k];
+    if (tid == 0) {
+      np_state[MT_N] = (uint32_t)off;
+      status[0] = flag;
+      // diagnostics: SM cycles spent in the stream walk, ballot passes, rows
+      status[1] = (int)((clock64() - clk0) >> 4);
+      status[2] = n_pass;
+      status[3] = n_round;
+    }
+  }
 }
 
 // Value that ends at position p after the Fisher-Yates swaps (i = n-1..1, swap a[i], a[j_i]) applied

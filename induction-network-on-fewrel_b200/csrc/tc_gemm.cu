@@ -23,6 +23,12 @@ constexpr int G_A_BYTES = G_BM * G_BK * 2, G_B_BYTES = G_BN * G_BK * 2;   // 16 
 constexpr int G_SMEM = G_STAGES * (G_A_BYTES + G_B_BYTES) + 256 + 1024;   // + barriers + alignment slack
 constexpr int G_THREADS = 192;
 
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct TcGemmP {
   float* C; __nv_bfloat16* Cb; const float* bias;
   int M, N, K, ldc;
@@ -133,17 +139,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (n < p.N) {
         const float bv = (p.bias && (p.splitk == 1 || ks == 0)) ? p.bias[n] : 0.f;
         const int rmax = min(32, p.M - row0);
-        for (int rr = 0; rr < rmax; ++rr) {
-          float x = tile[rr * 33 + lane] + bv;
-          const long long o = (long long)(row0 + rr) * p.ldc + n;
-          if (p.splitk > 1) {
-            atomicAdd(Cbase + o, x);
-          } else {
-            if (p.accumulate) x += Cbase[o];
-            if (p.act == 1) x = tanhf(x);
-            else if (p.act == 2) x = fmaxf(x, 0.f);
-            if (Cbase) Cbase[o] = x;
-            if (Cbbase) Cbbase[o] = __float2bfloat16(x);
+        const long long o0 = (long long)row0 * p.ldc + n;
+        if (p.splitk > 1) {
+          for (int rr = 0; rr < rmax; ++rr) atomicAdd(Cbase + o0 + (long long)rr * p.ldc, tile[rr * 33 + lane] + bv);
+        } else {
+          // "+= C": fetch the whole column strip first so the 32 loads are in flight together
+          // (interleaved with the stores they would each wait a full memory round trip)
+          float old[32];
+          if (p.accumulate) {
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) old[rr] = (rr < rmax) ? Cbase[o0 + (long long)rr * p.ldc] : 0.f;
+          }
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) {
+            if (rr < rmax) {
+              float x = tile[rr * 33 + lane] + bv;
+              if (p.accumulate) x += old[rr];
+              if (p.act == 1) x = tanh_approx(x);       // bf16 mode: MUFU.TANH is well inside the 2e-2 budget
+              else if (p.act == 2) x = fmaxf(x, 0.f);
+              const long long o = o0 + (long long)rr * p.ldc;
+              if (Cbase) Cbase[o] = x;
+              if (Cbbase) Cbbase[o] = __float2bfloat16(x);
+            }
           }
         }
       }

@@ -33,7 +33,7 @@ class DeviceEpisodeSampler:
                        .to(self.device) for k in KEYS}
         self.py_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.np_state = torch.zeros(625, dtype=torch.int32, device=self.device)
-        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.status = torch.zeros(4, dtype=torch.int32, device=self.device)   # {status, cycles/16, passes, rounds}
         self._bufs = {}
         self.load_host_streams()
 
@@ -107,7 +107,7 @@ class DeviceEpisodeSampler:
 
     def check(self):
         """Synchronising status check (mirrors the ValueError np.random.choice raises on the host)."""
-        s = int(self.status.item())
+        s = int(self.status[0].item())
         if s == 1:
             raise ValueError("Cannot take a larger sample than population when 'replace=False'")
         if s != 0:

@@ -51,7 +51,7 @@ def test_tc_gemm_batched_bias_act_bf16_out_and_accumulate():
     bias = torch.randn(256, device="cuda")
     C, _ = _tc(0, 1, 300, 256, 256, A, B, bias=bias, act=1)
     ref = torch.tanh(want / 1.0 + bias.double())
-    assert float((C.double() - ref).abs().max()) < 2e-5
+    assert float((C.double() - ref).abs().max()) < 2e-3      # epilogue tanh is MUFU tanh.approx
     base = torch.randn(1, 300, 256, device="cuda")
     C, _ = _tc(0, 1, 300, 256, 256, A, B, accumulate=base)
     assert float((C.double() - (want + base.double())).abs().max() / want.abs().max()) < 2e-5
