@@ -430,7 +430,14 @@ def run_b200(args, w):
             "loss_after": loss_after,
         }))
     if world > 1:
-        dist.destroy_process_group()
+        # tearing down a communicator that captured CUDA graphs still reference can hang at exit:
+        # drop the graphs, drain the device, line the ranks up, then leave without NCCL destructors
+        graph = graph_train = None
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
