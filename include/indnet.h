@@ -62,6 +62,9 @@ int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, co
                    int accumulate, int batch, long long sA, long long sB, long long sC, int splitk);
 /* out (bf16) = in (fp32), n elements. */
 int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
+/* Row-wise cast with a padded output row stride: out[r][0..ldo) = in[r][0..cols), zeros beyond cols
+ * (makes rows 16-byte aligned for TMA when cols*2 is not a multiple of 16). */
+int indnet_cast_bf16_rows(indnet_stream st, const float* in, void* out, long long rows, int cols, int ldo);
 
 /* cudaMemsetAsync on the stream (gradient regions that accumulate must start at zero). */
 int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);

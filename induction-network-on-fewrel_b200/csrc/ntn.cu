@@ -15,6 +15,9 @@ namespace indnet {
 
 constexpr int NTN_NT = 128;
 
+// tf.nn.relu propagates NaN (fmaxf would silently turn it into 0 and hide an upstream fault)
+__device__ __forceinline__ float relu_nan(float v) { return v < 0.f ? 0.f : v; }
+
 __global__ void __launch_bounds__(NTN_NT)
 ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, const float* __restrict__ bias,
                     const int* __restrict__ labels, float* __restrict__ probs, float* __restrict__ loss_part,
@@ -28,7 +31,7 @@ ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
     float acc = 0.f;
     for (int r = lane; r < NS; r += 32) {
       const int c = r / S, k = r % S;
-      acc = fmaf(fmaxf(v[r], 0.f), w[(long long)(k * N + c) * N + cp], acc);
+      acc = fmaf(relu_nan(v[r]), w[(long long)(k * N + c) * N + cp], acc);
     }
     acc = warp_sum(acc);
     if (lane == 0) {
@@ -115,7 +118,7 @@ __global__ void ntn_dw_kernel(const float* __restrict__ V, const float* __restri
   const int r0 = blockIdx.y * rows_per_block, r1 = min(rows, r0 + rows_per_block);
   float acc = 0.f;
   for (int row = r0; row < r1; ++row)
-    acc = fmaf(fmaxf(V[(long long)row * NS + r], 0.f), dlogit[(long long)row * N + cp], acc);
+    acc = fmaf(relu_nan(V[(long long)row * NS + r]), dlogit[(long long)row * N + cp], acc);
   const int c = r / S, k = r % S;
   atomicAdd(dw + (long long)(k * N + c) * N + cp, acc);
 }

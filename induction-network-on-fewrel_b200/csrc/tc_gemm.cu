@@ -280,6 +280,16 @@ __global__ void cast_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __
   }
 }
 
+// out[r][0..ldo) (bf16) = in[r][0..cols) (fp32), zero in the padding columns [cols, ldo)
+__global__ void cast_bf16_rows_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, long long rows,
+                                      int cols, int ldo) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= rows * ldo) return;
+  const long long r = i / ldo;
+  const int c = (int)(i % ldo);
+  out[i] = __float2bfloat16(c < cols ? in[r * cols + c] : 0.f);
+}
+
 }  // namespace indnet
 
 using namespace indnet;
@@ -298,5 +308,14 @@ extern "C" int indnet_cast_bf16(indnet_stream st, const float* in, void* out, lo
   IN_REQUIRE((((uintptr_t)in) & 15) == 0 && (((uintptr_t)out) & 7) == 0, "cast_bf16: unaligned pointers");
   cast_bf16_kernel<<<ceil_div(ceil_div(n, 4), 256), 256, 0, (cudaStream_t)st>>>(in, (__nv_bfloat16*)out, n);
   IN_LAUNCH_CHECK("cast_bf16_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_cast_bf16_rows(indnet_stream st, const float* in, void* out, long long rows, int cols, int ldo) {
+  IN_REQUIRE(rows >= 0 && cols >= 0 && ldo >= cols, "cast_bf16_rows: bad sizes");
+  if (rows == 0 || ldo == 0) return INDNET_OK;
+  IN_REQUIRE(in && out, "cast_bf16_rows: null pointer");
+  cast_bf16_rows_kernel<<<ceil_div(rows * ldo, 256), 256, 0, (cudaStream_t)st>>>(in, (__nv_bfloat16*)out, rows, cols, ldo);
+  IN_LAUNCH_CHECK("cast_bf16_rows_kernel");
   return INDNET_OK;
 }

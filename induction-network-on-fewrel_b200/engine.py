@@ -277,6 +277,9 @@ class EpisodePipeline:
             self.es_bf = h(c.B * c.NK, c.H)
             self.cvec_bf = h(c.B * c.N, c.H)
             self.hprev_bf = h(2, c.T, c.u)
+            self.eq_bf = h(c.B * c.n_q, c.H)
+            self.Tp_bf = h(c.B * c.N, c.S * c.H)
+            self.NSp = (c.N * c.S + 7) // 8 * 8          # dV rows padded to 16 bytes for TMA
             self.tc_lstm = (c.u == 128)        # persistent tcgen05 recurrence is specialised for u = 128
             if self.tc_lstm:
                 self.wt_bf = h(2, 4 * c.u, 64 + c.u)
@@ -403,8 +406,8 @@ class EpisodePipeline:
                        keep, self.seed, ptr(p.global_step))
         else:
             for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
-                # K = 64: the zero-padded x columns 60..63 meet rows D..D+3 of the TF kernel (finite), product 0
-                self._tc(0, 1, c.T, u4, 64, self.x_bf, 64, p.view_bf(kn), u4, C=self.xproj[d], bias=p.view(bn),
+                # K = D exactly: TMA zero-fills the padded x columns and never reads kernel rows past W_x
+                self._tc(0, 1, c.T, u4, c.D, self.x_bf, 64, p.view_bf(kn), u4, C=self.xproj[d], bias=p.view(bn),
                          tag="inproj")
             wh_fw = p.view(FW_K)[c.D:]
             wh_bw = p.view(BW_K)[c.D:]
@@ -421,11 +424,13 @@ class EpisodePipeline:
                  tag="routing_transform")
         self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
         self._cast(self.cvec, self.cvec_bf, "cvec")
-        self._tc(0, 1, c.B * c.N, c.S * c.H, c.H, self.cvec_bf, c.H, p.view_bf("M"), c.S * c.H, C=self.Tp,
+        self._tc(0, 1, c.B * c.N, c.S * c.H, c.H, self.cvec_bf, c.H, p.view_bf("M"), c.S * c.H, Cb=self.Tp_bf,
                  tag="ntn_stage1")
         NS = c.N * c.S
-        self._gemm(0, 1, c.n_q, NS, c.H, ptr(self.eq), c.H, ptr(self.Tp), c.H, ptr(self.V), NS,
-                   batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0), tag="ntn_stage2")
+        self._cast(self.eq, self.eq_bf, "eq")
+        # V_b[n_q, N*S] = qe_b [n_q, H] * T'_b^T (T'_b stored [N*S][H]: K-major) - one batch entry per episode
+        self._tc(0, 0, c.n_q, NS, c.H, self.eq_bf, c.H, self.Tp_bf, c.H, C=self.V, ldc=NS, batch=c.B,
+                 sA=c.n_q * c.H, sB=NS * c.H, sC=c.n_q * NS, tag="ntn_stage2")
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
         self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
@@ -452,6 +457,7 @@ class EpisodePipeline:
         if self.bf16:
             h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
             self.dTp_bf = h(c.B * c.N, c.S * c.H)
+            self.dV_bf = h(c.B * c.n_q, self.NSp)
             self.dehat_bf = h(c.B * c.NK, c.H)
             self.dpre_bf = h(c.T, c.H)
             self.dz_bf = h(2, c.T, 4 * c.u)
@@ -524,12 +530,15 @@ class EpisodePipeline:
         self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
                    None, ptr(self.dlogit), ptr(self.dV), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
                    1.0 / (rows * c.N))
-        # per-episode contractions with N*S columns stay on the FP32 path (N*S is not 16-byte aligned in bf16)
-        self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
-                   batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0), tag="ntn_dqe")
-        self._gemm(1, 0, NS, c.H, c.n_q, ptr(self.dV), NS, ptr(self.eq), c.H, ptr(self.dTp), c.H,
-                   batch=c.B, sA=(c.n_q * NS, 0), sB=(c.n_q * c.H, 0), sC=(NS * c.H, 0), tag="ntn_dT")
-        self._cast(self.dTp, self.dTp_bf, "dTp")
+        # dV rows are N*S wide (1000 B in bf16): cast into rows padded to a 16-byte multiple for TMA
+        self._tag = "cast_bf16:dV"
+        self._call("indnet_cast_bf16_rows", ptr(self.dV), ptr(self.dV_bf), rows, NS, self.NSp)
+        self._tag = None
+        # dqe_b = dV_b [n_q, N*S] * T'_b [N*S, H] ; dT'_b = dV_b^T [N*S, n_q] * qe_b [n_q, H]
+        self._tc(0, 1, c.n_q, c.H, NS, self.dV_bf, self.NSp, self.Tp_bf, c.H, C=self.deq, ldc=c.H, batch=c.B,
+                 sA=c.n_q * self.NSp, sB=NS * c.H, sC=c.n_q * c.H, splitk=1, tag="ntn_dqe")
+        self._tc(1, 1, NS, c.H, c.n_q, self.dV_bf, self.NSp, self.eq_bf, c.H, Cb=self.dTp_bf, ldc=c.H, batch=c.B,
+                 sA=c.n_q * self.NSp, sB=c.n_q * c.H, sC=NS * c.H, splitk=1, tag="ntn_dT")
         # dM' = cv^T dT' (both operands stored [K][.]) ; dcv = dT' M'^T (both K-major)
         self._tc(1, 1, c.H, c.S * c.H, c.B * c.N, self.cvec_bf, c.H, self.dTp_bf, c.S * c.H, C=p.grad("M"),
                  splitk=1, tag="ntn_dM")
