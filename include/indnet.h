@@ -164,6 +164,17 @@ int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* den
                          const float* proj, const float* alphas, const float* w_a2, float* dhout, float* dpre,
                          float* dw2_part, int X, int L, int H, int group, int split);
 
+/* bf16 tensor-core mode variants: hout_bf / proj_bf are the bf16 copies [X][L][H]; dpre_bf is written in
+ * bf16 (the operand format of the Dense-gradient GEMMs); dsum_part [X][H] (optional) receives the
+ * per-sentence fp32 sums of dpre over time (Dense-bias gradient partials).  Everything else as above. */
+int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
+                              const float* w_a2, float* enc_a, float* enc_b, float* alphas, int X, int L, int H,
+                              int group, int split);
+int indnet_attn_pool_bwd_bf16(indnet_stream st, const float* denc_a, const float* denc_b, const void* hout_bf,
+                              const void* proj_bf, const float* alphas, const float* w_a2, float* dhout,
+                              void* dpre_bf, float* dw2_part, float* dsum_part, int X, int L, int H, int group,
+                              int split);
+
 /* ---- a6/a7: dynamic_routing + squash, model/layer_module.py:101-162 ---------------------------
  * ehat [BC][K][H] = e_s*W_s; b_in [BC][K] or NULL (zeros, model/graph.py:71); cvec [BC][H]. K <= 32. */
 int indnet_routing_fwd(indnet_stream st, const float* ehat, const float* b_in, float* cvec, int BC, int K, int H,

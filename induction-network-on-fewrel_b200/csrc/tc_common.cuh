@@ -113,6 +113,13 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo
   return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
          ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46) | (2ull << 61);
 }
+// Same descriptor from a pre-shifted base (addr >> 4) plus a byte offset that is a multiple of 16, for
+// K-major SWIZZLE_128B tiles (LBO unused, SBO = 1024): the 64-bit value is a constant high word and
+// one integer add, which keeps the single MMA-issuing thread short.
+__device__ __forceinline__ uint64_t smem_desc_sw128_k(uint32_t base16, uint32_t off_bytes) {
+  constexpr uint64_t HI = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+  return HI | (uint64_t)(base16 + (off_bytes >> 4));
+}
 // Instruction descriptor, kind::f16: D = F32 (bits [4,6) = 1), A = B = BF16 (bits [7,10) = [10,13) = 1),
 // bit 15 / 16: A / B is MN-major, bits [17,23) N >> 3, bits [24,29) M >> 4.
 __host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, bool a_mn, bool b_mn) {

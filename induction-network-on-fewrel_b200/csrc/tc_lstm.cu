@@ -120,7 +120,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
-  const uint32_t w_base = smem_u32(sW), x_base = smem_u32(sX), h_base = smem_u32(sH);
+  const uint32_t w16 = smem_u32(sW) >> 4, x16 = smem_u32(sX) >> 4, h16 = smem_u32(sH) >> 4;
 
   // issue the MMAs of processing step s (thread 0 only)
   auto issue_step = [&](int s) {
@@ -135,11 +135,11 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     for (int g = 0; g < 4; ++g) {
 #pragma unroll
       for (int kb = 0; kb < LT_KB; ++kb) {
-        const uint32_t b_tile = (kb == 0) ? (x_base + (s & 1) * LT_XB_BYTES) : (h_base + (kb - 1) * (LT_NS * 128));
+        const uint32_t b16 = (kb == 0) ? (x16 + (s & 1) * (LT_XB_BYTES >> 4)) : (h16 + (kb - 1) * ((LT_NS * 128) >> 4));
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
-          const uint64_t ad = smem_desc_sw128(w_base + (g * LT_KB + kb) * 16384 + k4 * 32, 0, 1024);
-          const uint64_t bd = smem_desc_sw128(b_tile + k4 * 32, 0, 1024);
+          const uint64_t ad = smem_desc_sw128_k(w16, (g * LT_KB + kb) * 16384 + k4 * 32);
+          const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
           umma_bf16(taddr + g * LT_NS, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
         }
       }
@@ -275,7 +275,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
-  const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+  const uint32_t w16 = smem_u32(sW) >> 4, z16 = smem_u32(sZ) >> 4;
   if (issuer) {
     mbar_expect_tx(w_full, LB_W_BYTES);
     for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sW + kb * 16384, tmW, w_full, kb * 64, 0, 0);
@@ -386,8 +386,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
-          const uint64_t ad = smem_desc_sw128(w_base + kb * 16384 + k4 * 32, 0, 1024);
-          const uint64_t bd = smem_desc_sw128(z_base + kb * (LT_NS * 128) + k4 * 32, 0, 1024);
+          const uint64_t ad = smem_desc_sw128_k(w16, kb * 16384 + k4 * 32);
+          const uint64_t bd = smem_desc_sw128_k(z16, kb * (LT_NS * 128) + k4 * 32);
           umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
         }
       }

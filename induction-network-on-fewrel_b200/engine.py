@@ -274,6 +274,7 @@ class EpisodePipeline:
             h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
             self.x_bf = h(c.T, 64)
             self.hout_bf = h(c.T, c.H)
+            self.proj_bf = h(c.T, c.H)
             self.es_bf = h(c.B * c.NK, c.H)
             self.cvec_bf = h(c.B * c.N, c.H)
             self.hprev_bf = h(2, c.T, c.u)
@@ -401,7 +402,7 @@ class EpisodePipeline:
         if self.tc_lstm:
             # input projection + recurrence + gates in one persistent tcgen05 kernel
             self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
-                       ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), ptr(self.hout), ptr(self.hout_bf),
+                       ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), None, ptr(self.hout_bf),
                        ptr(self.gates_bf), ptr(self.cstate), ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
                        keep, self.seed, ptr(p.global_step))
         else:
@@ -415,10 +416,10 @@ class EpisodePipeline:
                        ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
             self._cast(self.hout, self.hout_bf, "hout")
             self._cast(self.hprev, self.hprev_bf, "hprev")
-        self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, C=self.proj, bias=p.view(ATT_B),
+        self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, Cb=self.proj_bf, bias=p.view(ATT_B),
                  act=1, tag="attn_dense")
-        self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
-                   ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
+        self._call("indnet_attn_pool_fwd_bf16", ptr(self.hout_bf), ptr(self.proj_bf), ptr(self.mask),
+                   ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
         self._cast(self.es, self.es_bf, "es")
         self._tc(0, 1, c.B * c.NK, c.H, c.H, self.es_bf, c.H, p.view_bf("W_s"), c.H, C=self.ehat,
                  tag="routing_transform")
@@ -458,6 +459,7 @@ class EpisodePipeline:
             h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
             self.dTp_bf = h(c.B * c.N, c.S * c.H)
             self.dV_bf = h(c.B * c.n_q, self.NSp)
+            self.dba_part = f(c.X, c.H)
             self.dehat_bf = h(c.B * c.NK, c.H)
             self.dpre_bf = h(c.T, c.H)
             self.dz_bf = h(2, c.T, 4 * c.u)
@@ -549,13 +551,12 @@ class EpisodePipeline:
         self._cast(self.dehat, self.dehat_bf, "dehat")
         self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
         self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
-        self._call("indnet_attn_pool_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout), ptr(self.proj),
-                   ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre), ptr(self.dw2_part),
-                   c.X, c.L, c.H, c.n_s, c.NK)
+        self._call("indnet_attn_pool_bwd_bf16", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
+                   ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre_bf), ptr(self.dw2_part),
+                   ptr(self.dba_part), c.X, c.L, c.H, c.n_s, c.NK)
         self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
-        self._cast(self.dpre, self.dpre_bf, "dpre")
         self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
-        self._call("indnet_colsum", ptr(self.dpre), c.T, c.H, c.H, ptr(p.grad(ATT_B)), 0)
+        self._call("indnet_colsum", ptr(self.dba_part), c.X, c.H, c.H, ptr(p.grad(ATT_B)), 0)
         self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
                  splitk=1, tag="attn_dh")
         if self.tc_lstm:

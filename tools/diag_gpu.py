@@ -32,7 +32,7 @@ for name in names:
         print("== %s  (oracle %.1fs)" % (name, time.time() - t0))
         print("  fwd: x %.2e hout %.2e alphas %.2e enc %.2e cvec %.2e probs %.2e loss %.8f/%.8f acc %.4f/%.4f" % (
             rel_err(pipe.x.view(cfg.X, cfg.L, cfg.D), ref["x"]),
-            rel_err(pipe.hout.view(cfg.X, cfg.L, cfg.H), ref["hout"]),
+            rel_err((pipe.hout_bf.float() if pipe.bf16 else pipe.hout).view(cfg.X, cfg.L, cfg.H), ref["hout"]),
             rel_err(pipe.alphas.view(cfg.B, cfg.n_s, cfg.L, 1), ref["alphas"]),
             rel_err(enc, ref["encoder"]), rel_err(pipe.cvec.view(cfg.B, cfg.N, cfg.H), ref["class_vector"]),
             rel_err(pipe.probs, ref["probs"]), pipe.loss(), float(ref["loss"]), pipe.accuracy(), float(ref["accuracy"])))
