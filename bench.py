@@ -390,6 +390,16 @@ def run_b200(args, w):
             ach = bytes_tab[dom[0]] / (dom_ms * 1e-3) / 1e9 if dom[0] in bytes_tab else None
             roof = {"bound": "hbm", "kernel": dom[0], "achieved": ach, "peak": pk, "unit": "GB/s",
                     "frac": (ach / pk) if ach else None, "traffic": None, "avg_launch_ms": dom_ms}
+        # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture (profiles/), same workload
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tr = json.load(f)
+            key = {"indnet_lstm_fwd_tc": "tc_lstm_fwd_kernel", "indnet_lstm_bwd_tc": "tc_lstm_bwd_kernel"}.get(dom[0])
+            if key in tr and tr[key]["workload"] == "cfg%d" % args.config and args.mode == "bf16":
+                roof["traffic"] = tr[key]["dram_bytes_per_launch"]
+                roof["traffic_source"] = "profiles/r1_tc_lstm_ncu.md (dram__bytes_read.sum + dram__bytes_write.sum)"
+        except Exception:
+            pass
         roof["step_share"] = share
         # whole-step achieved TFLOP/s (train = 3 x forward)
         step_tflops = value * 3 * fwd_flops_per_episode(cfg.N, cfg.K, cfg.L, cfg.u) / 1e12
