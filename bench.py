@@ -168,6 +168,8 @@ def run_b200(args, w):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL prints its version banner on stdout at NCCL_DEBUG=VERSION/INFO; stdout carries the JSON line only
+        os.environ["NCCL_DEBUG"] = os.environ.get("INDNET_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     peaks = {}
     try:
