@@ -238,6 +238,8 @@ class EpisodePipeline:
         self.seed = int(seed)
         self.launches = 0
         self.profile = None      # set to [] to collect per-call CUDA-event timings
+        self.grad_ready_hook = None   # callable(name): fired when a gradient slot is final ("M" is 95 % of the bytes
+                                      # and is produced first, so its all-reduce can hide under the encoder BPTT)
         self._tag = None
         c = cfg
         f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
@@ -486,6 +488,8 @@ class EpisodePipeline:
         # dM' = cv^T dT' ; dcv = dT' M'^T
         self._gemm(1, 0, c.H, c.S * c.H, c.B * c.N, ptr(self.cvec), c.H, ptr(self.dTp), c.S * c.H,
                    ptr(p.grad("M")), c.S * c.H, tag="ntn_dM")
+        if self.grad_ready_hook is not None:
+            self.grad_ready_hook("M")
         self._gemm(0, 1, c.B * c.N, c.H, c.S * c.H, ptr(self.dTp), c.S * c.H, ptr(p.view("M")), c.S * c.H,
                    ptr(self.dcvec), c.H, tag="ntn_dcv")
         # routing
@@ -544,6 +548,8 @@ class EpisodePipeline:
         # dM' = cv^T dT' (both operands stored [K][.]) ; dcv = dT' M'^T (both K-major)
         self._tc(1, 1, c.H, c.S * c.H, c.B * c.N, self.cvec_bf, c.H, self.dTp_bf, c.S * c.H, C=p.grad("M"),
                  splitk=1, tag="ntn_dM")
+        if self.grad_ready_hook is not None:
+            self.grad_ready_hook("M")
         self._tc(0, 0, c.B * c.N, c.H, c.S * c.H, self.dTp_bf, c.S * c.H, p.view_bf("M"), c.S * c.H, C=self.dcvec,
                  tag="ntn_dcv")
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
