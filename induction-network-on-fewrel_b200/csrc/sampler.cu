@@ -22,6 +22,7 @@
 // host can hand its streams in and take them back.
 #include "common.cuh"
 #include "indnet_internal.h"
+#include "tc_common.cuh"
 #include "../../include/indnet.h"
 
 namespace indnet {
@@ -84,25 +85,20 @@ struct SerialMT {
 // NumPy random_interval mask: smallest 2^k - 1 >= mx (mx >= 1): all ones below the top set bit.
 __device__ __forceinline__ uint32_t mask_for(uint32_t mx) { return 0xFFFFFFFFu >> __clz(mx); }
 
-__device__ __forceinline__ bool warp_id_is_zero(int tid) { return tid < 32; }
+// status codes written to status[0]
+enum { SMP_OK = 0, SMP_SCOPE_TOO_SMALL = 1, SMP_SCOPE_TOO_LARGE = 2, SMP_STREAM_BUDGET = 3 };
 
-// status codes written to *status
-enum { SMP_OK = 0, SMP_SCOPE_TOO_SMALL = 1, SMP_SCOPE_TOO_LARGE = 2 };
+constexpr int TB = 64;     // draws per transition-table block
 
-__global__ void __launch_bounds__(SMP_NT)
-sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_state,
-                    const int* __restrict__ scopes, int R, int B, int N, int K, int Q, int n_max,
-                    int* __restrict__ classes, int* __restrict__ jlist, int* __restrict__ status) {
+// ---- kernel P: the Python stream (random.sample(range(R), N) per episode), one thread ------------
+__global__ void smp_python_kernel(uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
+                                  const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
   __shared__ uint32_t pkey[MT_N];
-  __shared__ uint32_t nkey[MT_N];
   __shared__ int pool[1024];
   __shared__ uint32_t seen[32];
-  const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < MT_N; i += SMP_NT) { pkey[i] = py_state[i]; nkey[i] = np_state[i]; }
+  for (int i = threadIdx.x; i < MT_N; i += blockDim.x) pkey[i] = py_state[i];
   __syncthreads();
-
-  // ---- phase A: the Python stream, random.sample(range(R), N) per episode (thread 0)
-  if (tid == 0) {
+  if (threadIdx.x == 0) {
     SerialMT mt{pkey, (int)py_state[MT_N]};
     int setsize = 21;
     if (N > 5) {   // setsize += 4 ** ceil(log(N*3, 4))
@@ -129,154 +125,288 @@ sampler_walk_kernel(uint32_t* __restrict__ py_state, uint32_t* __restrict__ np_s
         }
       }
     }
-    for (int i = 0; i < MT_N; ++i) py_state[i] = pkey[i];
     py_state[MT_N] = (uint32_t)mt.pos;
   }
   __syncthreads();
-
-  // ---- phase B: the NumPy stream.  jobs: for each episode, N class permutations then the query one.
-  // Warp 0 walks the stream in rows of 32 draws.  With c = draws accepted so far in the row before
-  // lane l, lane l's Fisher-Yates index is i - c, its mask follows from that index, and it is accepted
-  // iff (y & mask) <= index.  That is a triangular system over the lanes, settled exactly by ballot
-  // iteration from the expected-rate guess (it normally confirms on the second ballot, and it crosses
-  // the mask changes inside the row); the carry into the next row is then exact, so there is no
-  // iteration across rows.  Meanwhile the whole CTA keeps a ring of untempered MT19937 blocks ahead of
-  // the consumer (3-phase parallel twist); the state handed back is the block the consumer stopped in.
-  constexpr int RING = 4;      // power of two
-  __shared__ uint32_t ring[RING][MT_N];
-  __shared__ int s_blk, s_off, s_done;
-  const uint32_t below = (1u << lane) - 1u;
-  const int jobs = B * (N + 1);
-  for (int k = tid; k < MT_N; k += SMP_NT) ring[0][k] = nkey[k];
-  __syncthreads();
-  int gen = 1;                               // blocks generated so far (block b lives in ring[b % RING])
-  int blk = 0, off = (int)np_state[MT_N];    // next draw to consume = block blk, offset off (off may be 624)
-  int done = 0, flag = SMP_OK;
-  // warp-0 job state
-  int job = 0, i = 0;
-  bool fresh = true;
-  int* jrow = jlist;
-  // permutation length of job j (>= 0), or -(error code); jobs past the end report 0
-  auto job_size = [&](int j) -> int {
-    if (j >= jobs) return 0;
+  for (int i = threadIdx.x; i < MT_N; i += blockDim.x) py_state[i] = pkey[i];
+  // permutation length of every job of the walk (episode-major: N class scopes, then the N*Q query
+  // permutation); negative = the error the walker reports when it reaches that job
+  for (int j = threadIdx.x; j < B * (N + 1); j += blockDim.x) {
     const int b = j / (N + 1), ci = j % (N + 1);
-    if (ci == N) return N * Q;
-    const int c = classes[(long long)b * N + ci];
-    const int n = scopes[2 * c + 1] - scopes[2 * c];
-    if (n < K + Q) return -SMP_SCOPE_TOO_SMALL;
-    if (n > n_max) return -SMP_SCOPE_TOO_LARGE;
-    return n;
-  };
-  int n_next = job_size(0);
-  const long long clk0 = clock64();
-  int n_pass = 0, n_round = 0;
-  while (!done) {
-    // ---- keep at least one full block (plus a row) generated beyond the consumer
-    while ((gen - 1 - blk) * MT_N - off < MT_N + 32 && gen - blk < RING) {
-      const uint32_t* o = ring[(gen - 1) % RING];
-      uint32_t* w = ring[gen % RING];
-      if (tid < 227) w[tid] = mt_mix(o[tid], o[tid + 1], o[tid + MT_M]);
-      __syncthreads();
-      if (tid < 227) w[tid + 227] = mt_mix(o[tid + 227], o[tid + 228], w[tid]);
-      __syncthreads();
-      if (tid < 170) {
-        const int k = tid + 454;
-        w[k] = mt_mix(o[k], (k + 1 < MT_N) ? o[k + 1] : w[0], w[k - 227]);
-      }
-      __syncthreads();
-      ++gen;
+    int n = N * Q;
+    if (ci < N) {
+      const int c = classes[(long long)b * N + ci];
+      n = scopes[2 * c + 1] - scopes[2 * c];
+      if (n < K + Q) n = -SMP_SCOPE_TOO_SMALL;
+      else if (n > n_max) n = -SMP_SCOPE_TOO_LARGE;
     }
-    if (warp_id_is_zero(tid)) {
-      // Groups of GR rows (32 draws each) are consumed while a whole group is available in the ring.
-      // Everything that does not depend on the carry (ring reads, tempering) is done for the whole
-      // group up front so those instruction streams overlap; only the accept chain is serial.
-      constexpr int GR = 4;
-      while (true) {
-        if (fresh) {
-          if (job >= jobs) { done = 1; break; }
-          i = n_next - 1;
-          if (n_next < 0) { flag = -n_next; done = 1; break; }
-          jrow = jlist + (long long)job * n_max;
-          n_next = job_size(job + 1);          // prefetch: its global-load latency hides behind this job's rows
-          fresh = false;
-          if (i <= 0) { ++job; fresh = true; continue; }   // permutation(1): no draws
-        }
-        if ((gen - blk) * MT_N - off < 32 * GR) break;     // need more blocks
-        uint32_t y[GR];
-#pragma unroll
-        for (int r = 0; r < GR; ++r) {
-          int pb = blk, po = off + r * 32 + lane;
-          if (po >= MT_N) { po -= MT_N; ++pb; }
-          y[r] = mt_temper(ring[pb & (RING - 1)][po]);
-        }
-        int used = 32 * GR;
-#pragma unroll
-        for (int r = 0; r < GR; ++r) {
-          const uint32_t m0 = mask_for((uint32_t)i);
-          const int sh = 32 - __clz(m0);
-          int c = (lane * (i + 1)) >> sh;                  // expected accepts before this lane
-          uint32_t bal, v;
-          int ip;
-          if (i - 31 > (int)(m0 >> 1)) {
-            // common case: every index this row can reach shares the mask -> accept iff c <= i - v
-            v = y[r] & m0;
-            const int t = i - (int)v;
-            bal = __ballot_sync(0xffffffffu, c <= t);
-            while (true) {
-              c = __popc(bal & below);
-              const uint32_t bal2 = __ballot_sync(0xffffffffu, c <= t);
-              ++n_pass;
-              if (bal2 == bal) break;
-              bal = bal2;
-            }
-            ip = i - c;
-          } else {
-            ip = i - c;
-            v = y[r] & mask_for((uint32_t)max(ip, 1));
-            bal = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
-            while (true) {
-              c = __popc(bal & below);
-              ip = i - c;
-              v = y[r] & mask_for((uint32_t)max(ip, 1));
-              const uint32_t bal2 = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
-              ++n_pass;
-              if (bal2 == bal) break;
-              bal = bal2;
-            }
-          }
-          const int acc = __popc(bal);
-          if ((bal >> lane) & 1u) jrow[ip] = (int)v;
-          ++n_round;
-          if (acc >= i) {                                  // the permutation ends at its last accepted draw
-            used = r * 32 + (32 - __clz(bal));
-            ++job;
-            fresh = true;
-            break;
-          }
-          i -= acc;
-        }
-        off += used;
-        if (off > MT_N) { off -= MT_N; ++blk; }            // off == 624 stays: "end of block blk"
-      }
-      if (lane == 0) { s_blk = blk; s_off = off; s_done = done; }
-    }
-    __syncthreads();
-    blk = s_blk; off = s_off; done = s_done;
-    __syncthreads();
+    jsize[j] = n;
   }
+}
+
+// ---- kernel G: nb consecutive untempered MT19937 blocks of the NumPy stream ---------------------
+// keys[0] = the state handed in; keys[b] = twist(keys[b-1]).  One CTA: the twist is sequential across
+// blocks, 3-phase parallel inside one; blocks are twisted in shared memory and streamed out.
+__global__ void __launch_bounds__(SMP_NT)
+smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ keys, int nb) {
+  __shared__ uint32_t ring[2][MT_N];
+  const int tid = threadIdx.x;
+  for (int k = tid; k < MT_N; k += SMP_NT) { const uint32_t v = np_state[k]; ring[0][k] = v; keys[k] = v; }
+  __syncthreads();
+  for (int b = 1; b < nb; ++b) {
+    const uint32_t* o = ring[(b - 1) & 1];
+    uint32_t* w = ring[b & 1];
+    if (tid < 227) w[tid] = mt_mix(o[tid], o[tid + 1], o[tid + MT_M]);
+    __syncthreads();
+    if (tid < 227) w[tid + 227] = mt_mix(o[tid + 227], o[tid + 228], w[tid]);
+    __syncthreads();
+    if (tid < 170) {
+      const int k = tid + 454;
+      w[k] = mt_mix(o[k], (k + 1 < MT_N) ? o[k + 1] : w[0], w[k - 227]);
+    }
+    __syncthreads();
+    uint32_t* dst = keys + (long long)b * MT_N;
+    for (int k = tid; k < MT_N; k += SMP_NT) dst[k] = w[k];
+  }
+}
+
+// ---- kernel T: transition tables ----------------------------------------------------------------
+// For every 64-draw block b of the stream and every Fisher-Yates index s in [1, n_states):
+// F[b][s] = index after the block's draws are offered to a permutation currently at index s
+// (accept iff (y & mask(s)) <= s, then s -= 1), saturating at 0 = "the permutation ends inside this
+// block"; for s <= 64 the end table E[b][s] holds how many of the block's draws that permutation
+// consumes (0xFF: it does not end here).  Both are independent of which job meets the block, so the
+// whole GPU builds them in parallel and the serial walker only chains one lookup per 64 draws.  The
+// tempered draws are stored too (ytemp) for the walker's exact rows and the fill kernel.
+constexpr int E_STRIDE = 80;   // bytes per block of E (65 used; keeps the record 16-byte granular)
+// One record per block, contiguous in memory so that a run of blocks is ONE bulk copy for the walker:
+//   [ F row: n_states x u16 | the block's 64 tempered draws: u32 | E row: 80 x u8 ]
+__host__ __device__ inline long long rec_bytes(long long n_states) { return n_states * 2 + TB * 4 + E_STRIDE; }
+
+__global__ void __launch_bounds__(256)
+smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ tab, int n_states) {
+  __shared__ uint32_t y[TB];
+  const long long b = blockIdx.x;
+  unsigned char* rec = tab + b * rec_bytes(n_states);
+  unsigned short* F = reinterpret_cast<unsigned short*>(rec);
+  uint32_t* Y = reinterpret_cast<uint32_t*>(rec + n_states * 2);
+  unsigned char* E = rec + n_states * 2 + TB * 4;
+  if (threadIdx.x < TB) {
+    const uint32_t v = mt_temper(keys[b * TB + threadIdx.x]);
+    y[threadIdx.x] = v;
+    Y[threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int s0 = threadIdx.x; s0 < n_states; s0 += 256) {
+    int s = s0, e = 0xFF;
+    if (s >= 1) {
+      uint32_t m = mask_for((uint32_t)s);
+      int thr = (int)(m >> 1);
+      if (s0 <= TB) {
+        for (int k = 0; k < TB; ++k) {
+          if (s <= thr) { m >>= 1; thr >>= 1; }
+          const uint32_t v = y[k] & m;
+          if (s >= 1 && v <= (uint32_t)s) { if (--s == 0) e = k + 1; }
+        }
+      } else {
+#pragma unroll 8
+        for (int k = 0; k < TB; ++k) {
+          if (s <= thr) { m >>= 1; thr >>= 1; }       // the index shrinks by at most one per draw
+          const uint32_t v = y[k] & m;
+          s -= (v <= (uint32_t)s) ? 1 : 0;            // s0 > 64 cannot reach 0 inside the block
+        }
+      }
+    }
+    F[s0] = (unsigned short)s;
+    if (s0 < E_STRIDE) E[s0] = (unsigned char)((s0 >= 1 && s0 <= TB) ? e : 0xFF);
+  }
+}
+
+// ---- kernel W: the serial walk (one warp) --------------------------------------------------------
+// Jobs: for each episode its N class permutations, then the query permutation.  At a 64-aligned stream
+// position the walker jumps a whole block through F (and records (index, job) for the fill kernel); a
+// permutation that ends inside the block it entered aligned takes its end offset from E; everything
+// else (the stretch from a permutation's first draw to the next block boundary, and permutations that
+// start and end inside one block) is walked exactly in rows of up to 32 draws (ballot fixed point over
+// the lanes).
+// The lookups form one dependent chain, so their latency is the walk time.  The tables of the next
+// blocks are therefore staged in shared memory ahead of the walker: the stream is cut into chunks of
+// 2^cb_log blocks whose F rows / draws / E rows are contiguous in global memory, and a ring of 2^rc_log
+// chunk slots is kept full with bulk async copies (one mbarrier per slot, complete_tx), issued when
+// the walker leaves a chunk.  A lookup is then one LDS.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// Shared-memory loads by 32-bit shared address.  Written as asm so the walker's loop-carried index
+// stays in ordinary registers: left to itself the compiler proves the whole walk warp-uniform and moves
+// it to the uniform datapath, whose longer dependent-issue latency is the wrong trade for this chain.
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+  unsigned short v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(32)
+smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restrict__ tab, int n_states,
+                long long nblk, int cb_log, int rc_log, uint32_t* __restrict__ np_state,
+                const int* __restrict__ jsize, int jobs, int n_max, int* __restrict__ jlist,
+                int2* __restrict__ blk_rec, int* __restrict__ status) {
+  extern __shared__ __align__(128) unsigned char ring[];
+  const int lane = threadIdx.x;
+  const uint32_t below = (1u << lane) - 1u;
+  const int CB = 1 << cb_log, RC = 1 << rc_log;
+  const uint32_t f_bytes = (uint32_t)n_states * 2u, y_bytes = TB * 4u;
+  const uint32_t blk_bytes = (uint32_t)rec_bytes(n_states), slot_bytes = blk_bytes << cb_log;
+  const uint32_t ring_s = tc::smem_u32(ring);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)RC * slot_bytes);
+  const uint32_t bars_s = tc::smem_u32(bars);
+  const long long nchunks = nblk >> cb_log;
+  if (lane == 0) {
+    for (int r = 0; r < RC; ++r) tc::mbar_init(&bars[r], 1);
+    tc::fence_barrier_init();
+  }
+  // A zero the compiler cannot see through, one per lane: adding it to the walk index keeps the chain
+  // in ordinary registers (see lds_u16 above).
+  volatile uint32_t* zeros = reinterpret_cast<volatile uint32_t*>(bars + RC);
+  zeros[lane] = 0u;
+  __syncwarp();
+  const int lane_zero = (int)zeros[lane];
+  auto issue = [&](long long c) {                  // one bulk copy: the chunk's records are contiguous
+    if (lane == 0 && c < nchunks) {
+      const uint32_t r = (uint32_t)c & (uint32_t)(RC - 1);
+      const uint32_t bar = bars_s + 8u * r;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(slot_bytes) : "memory");
+      bulk_g2s(ring_s + r * slot_bytes, tab + c * (long long)slot_bytes, slot_bytes, bar);
+    }
+  };
+  const long long clk0 = clock64();
+  long long pos = (long long)np_state[MT_N];      // absolute draw index; keys[0] is the state handed in
+  const long long c0 = pos >> (6 + cb_log);
+  for (int k = 0; k < RC - 1; ++k) issue(c0 + k);
+  long long ready = c0 - 1;                       // last chunk whose slot has been waited for
+  int flag = SMP_OK, n_jump = 0, n_row = 0;
+  int n_next = jobs > 0 ? jsize[0] : 0;
+  for (int job = 0; job < jobs && flag == SMP_OK; ++job) {
+    const int n = n_next;
+    if (n < 0) { flag = -n; break; }
+    n_next = (job + 1 < jobs) ? jsize[job + 1] : 0;   // in flight while this job is walked
+    int i = n - 1 + lane_zero;
+    int* jrow = jlist + (long long)job * n_max;
+    while (i > 0) {
+      const long long b = pos >> 6;
+      const int off = (int)(pos & (TB - 1));
+      if (b >= nblk) { flag = SMP_STREAM_BUDGET; break; }
+      const long long c = b >> cb_log;
+      while (ready < c) {                          // entering a new chunk: its slot must have landed;
+        ++ready;                                   // the slot of the chunk just left is refilled
+        tc::mbar_wait(&bars[ready & (RC - 1)], (uint32_t)(((ready - c0) >> rc_log) & 1));
+        issue(ready + RC - 1);
+      }
+      const int lb = (int)(b & (CB - 1));
+      const uint32_t blk_s = ring_s + ((uint32_t)c & (uint32_t)(RC - 1)) * slot_bytes + (uint32_t)lb * blk_bytes;
+      if (off == 0) {
+        // chain of table jumps through the rest of this chunk: one LDS + a few ALU ops per 64 draws
+        uint32_t a = blk_s;
+        int2* rec = blk_rec + b;
+        int left = CB - lb, inext;
+        do {
+          inext = (int)lds_u16(a + 2u * (uint32_t)i);
+          if (inext == 0) break;
+          if (lane == 0) *rec = make_int2(i, job);
+          i = inext;
+          a += blk_bytes;
+          ++rec;
+        } while (--left > 0);
+        const int done = (CB - lb) - left;
+        n_jump += done;
+        pos += (long long)done * TB;
+        if (inext == 0) {                                   // ends inside block b + done; then i <= 64
+          const int e = (int)lds_u8(a + f_bytes + y_bytes + (uint32_t)i);
+          if (lane == 0) *rec = make_int2(i, job);
+          i = 0;
+          pos += e;
+          ++n_jump;
+        }
+        continue;
+      }
+      // exact row: up to 32 draws, not crossing the next block boundary
+      const int limit = min(32, TB - off);
+      const bool valid = lane < limit;
+      const uint32_t y = valid ? lds_u32(blk_s + f_bytes + 4u * (uint32_t)(off + lane)) : 0u;
+      const uint32_t m0 = mask_for((uint32_t)i);
+      int cn = (lane * (i + 1)) >> (32 - __clz(m0));       // expected accepts before this lane
+      int ip = i - cn;
+      uint32_t v = y & mask_for((uint32_t)max(ip, 1));
+      uint32_t bal = __ballot_sync(0xffffffffu, valid && ip >= 1 && v <= (uint32_t)ip);
+      while (true) {
+        cn = __popc(bal & below);
+        ip = i - cn;
+        v = y & mask_for((uint32_t)max(ip, 1));
+        const uint32_t bal2 = __ballot_sync(0xffffffffu, valid && ip >= 1 && v <= (uint32_t)ip);
+        if (bal2 == bal) break;
+        bal = bal2;
+      }
+      const int acc = __popc(bal);
+      if ((bal >> lane) & 1u) jrow[ip] = (int)v;
+      int used = limit;
+      if (acc >= i) used = 32 - __clz(bal);                // the permutation ends at its last accepted draw
+      i -= acc;
+      pos += used;
+      ++n_row;
+    }
+  }
+  // hand the stream back: the block the walk stopped in (offset 624 = "block exhausted")
   {
-    // hand back the block the consumer stopped in (an offset of 624 = "block exhausted", which is
-    // also what the host generators hold at a block boundary)
-    const uint32_t* fin = ring[blk % RING];
-    for (int k = tid; k < MT_N; k += SMP_NT) np_state[k] = fin[k];
-    if (tid == 0) {
+    long long blk = pos / MT_N;
+    int off = (int)(pos % MT_N);
+    if (off == 0 && blk > 0) { blk -= 1; off = MT_N; }
+    const uint32_t* fin = keys + blk * MT_N;
+    uint32_t tmp[MT_N / 32 + 1];
+    int cnt = 0;
+    for (int k = lane; k < MT_N; k += 32) tmp[cnt++] = fin[k];
+    cnt = 0;
+    for (int k = lane; k < MT_N; k += 32) np_state[k] = tmp[cnt++];
+    if (lane == 0) {
       np_state[MT_N] = (uint32_t)off;
       status[0] = flag;
-      // diagnostics: SM cycles spent in the stream walk, ballot passes, rows
-      status[1] = (int)((clock64() - clk0) >> 4);
-      status[2] = n_pass;
-      status[3] = n_round;
+      status[1] = (int)((clock64() - clk0) >> 4);     // diagnostics: walk cycles / 16, table jumps, exact rows
+      status[2] = n_jump;
+      status[3] = n_row;
     }
+  }
+  // copies still in flight target this CTA's shared memory: drain them before the CTA retires
+  for (long long c = ready + 1; c < ready + RC && c < nchunks; ++c)
+    tc::mbar_wait(&bars[c & (RC - 1)], (uint32_t)(((c - c0) >> rc_log) & 1));
+}
+
+// ---- kernel F: accepted (index, j) pairs of the blocks the walker jumped over --------------------
+__global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int n_states, const int2* __restrict__ blk_rec,
+                                long long nblk, int n_max, int* __restrict__ jlist) {
+  const long long b = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (b >= nblk) return;
+  const int2 rec = blk_rec[b];
+  if (rec.y < 0) return;
+  int s = rec.x;
+  int* jrow = jlist + (long long)rec.y * n_max;
+  uint32_t m = mask_for((uint32_t)s);
+  int thr = (int)(m >> 1);
+  const uint32_t* yp = reinterpret_cast<const uint32_t*>(tab + b * rec_bytes(n_states) + (long long)n_states * 2);
+  for (int k = 0; k < TB && s >= 1; ++k) {
+    if (s <= thr) { m >>= 1; thr >>= 1; }
+    const uint32_t v = yp[k] & m;
+    if (v <= (uint32_t)s) { jrow[s] = (int)v; --s; }
   }
 }
 
@@ -343,12 +473,61 @@ __global__ void sampler_gather_kernel(const int* __restrict__ scopes, const int*
 
 using namespace indnet;
 
+namespace {
+// Scratch layout shared by the walk and gather halves (all offsets in bytes, 256-byte aligned).
+struct SmpLayout {
+  long long jobs, stride, pick_max, n_states, nb, nblk;
+  int cb_log, rc_log;              // walker staging: 2^cb_log blocks per chunk, 2^rc_log chunk slots (-1: does not fit)
+  long long smem_bytes;
+  long long o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_blk_rec, bytes;
+};
+static double expected_draws(long long n) {      // E[draws] of NumPy's permutation(n) (rejection sampling)
+  double e = 0.0;
+  for (long long i = 1; i < n; ++i) {
+    unsigned long long m = (unsigned long long)i;
+    m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16; m |= m >> 32;
+    e += (double)(m + 1) / (double)(i + 1);
+  }
+  return e;
+}
+static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
+  SmpLayout L;
+  L.jobs = (long long)B * (N + 1);
+  L.pick_max = (K + Q > N * Q) ? (K + Q) : (N * Q);
+  L.stride = (n_max > N * Q) ? n_max : (N * Q);      // j-list stride also holds the N*Q-entry query permutation
+  L.n_states = (L.stride + 7) / 8 * 8;
+  // stream budget: expectation + 3 % + slack (std of one 700-permutation is ~21 draws; this is > 10 sigma)
+  const double e = (double)B * ((double)N * expected_draws(n_max) + expected_draws((long long)N * Q));
+  const long long budget = (long long)(e * 1.03) + 8192 + MT_N;
+  L.nblk = (budget + TB - 1) / TB;
+  L.nblk = (L.nblk + 7) / 8 * 8;                      // whole chunks for every chunk size the walker may pick
+  L.nb = (L.nblk * TB + MT_N - 1) / MT_N + 1;
+  // walker staging ring: the largest chunk / ring that fits in 200 KB of shared memory
+  const long long per_block = rec_bytes(L.n_states);
+  static const int opts[5][2] = {{3, 3}, {2, 3}, {1, 3}, {0, 3}, {0, 2}};
+  L.cb_log = L.rc_log = -1;
+  L.smem_bytes = 0;
+  for (int k = 0; k < 5; ++k) {
+    const long long need = (((per_block << opts[k][0]) + 8) << opts[k][1]) + 128;
+    if (need <= 200 * 1024) { L.cb_log = opts[k][0]; L.rc_log = opts[k][1]; L.smem_bytes = need; break; }
+  }
+  auto al = [](long long x) { return (x + 255) / 256 * 256; };
+  long long o = 0;
+  L.o_classes = o; o = al(o + 4LL * B * N);
+  L.o_jsize = o;   o = al(o + 4LL * L.jobs);
+  L.o_jlist = o;   o = al(o + 4LL * L.jobs * L.stride);
+  L.o_picks = o;   o = al(o + 4LL * L.jobs * L.pick_max);
+  L.o_keys = o;    o = al(o + 4LL * L.nb * MT_N);
+  L.o_tab = o;     o = al(o + rec_bytes(L.n_states) * L.nblk);
+  L.o_blk_rec = o; o = al(o + 8LL * L.nblk);
+  L.bytes = o;
+  return L;
+}
+}  // namespace
+
 extern "C" long long indnet_sampler_scratch_bytes(int B, int N, int K, int Q, int n_max) {
   if (B < 0 || N <= 0 || K < 0 || Q < 0 || n_max <= 0) return -1;
-  const long long jobs = (long long)B * (N + 1);
-  const long long pick_max = (K + Q > N * Q) ? (K + Q) : (N * Q);
-  const long long stride = (n_max > N * Q) ? n_max : (N * Q);   // the query permutation has N*Q entries
-  return 4 * ((long long)B * N + jobs * stride + jobs * pick_max + 64);
+  return smp_layout(B, N, K, Q, n_max).bytes;
 }
 
 static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np_state, const int* scopes, int R,
@@ -356,18 +535,41 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   IN_REQUIRE(B >= 0 && N > 0 && K > 0 && Q > 0 && R > 0 && n_max > 0, "sample_episodes: bad sizes");
   IN_REQUIRE(N <= R, "sample_episodes: Sample larger than population (N=%d classes of %d relations)", N, R);
   IN_REQUIRE(R <= 1024, "sample_episodes: at most 1024 relations supported, got %d", R);
+  IN_REQUIRE(n_max < 65536 && N * Q < 65536, "sample_episodes: scopes above 65535 instances are not supported");
   if (B == 0) return INDNET_OK;
   IN_REQUIRE(py_state && np_state && scopes && scratch && status, "sample_episodes: null pointer");
-  const long long jobs = (long long)B * (N + 1);
-  const int pick_max = (K + Q > N * Q) ? (K + Q) : (N * Q);
-  if (n_max < N * Q) n_max = N * Q;   // j-list stride must also hold the N*Q-entry query permutation
-  int* classes = (int*)scratch;
-  int* jlist = classes + (((long long)B * N + 15) / 16) * 16;
-  int* picks = jlist + jobs * n_max;
-  sampler_walk_kernel<<<1, SMP_NT, 0, st>>>(py_state, np_state, scopes, R, B, N, K, Q, n_max, classes, jlist, status);
-  IN_LAUNCH_CHECK("sampler_walk_kernel");
-  sampler_trace_kernel<<<ceil_div(jobs * pick_max, 128), 128, 0, st>>>(scopes, classes, jlist, B, N, K, Q, n_max,
-                                                                       pick_max, picks);
+  const SmpLayout L = smp_layout(B, N, K, Q, n_max);
+  char* base = (char*)scratch;
+  int* classes = (int*)(base + L.o_classes);
+  int* jlist = (int*)(base + L.o_jlist);
+  int* picks = (int*)(base + L.o_picks);
+  uint32_t* keys = (uint32_t*)(base + L.o_keys);
+  unsigned char* tab = (unsigned char*)(base + L.o_tab);
+  int* jsize = (int*)(base + L.o_jsize);
+  int2* blk_rec = (int2*)(base + L.o_blk_rec);
+  IN_REQUIRE(L.cb_log >= 0, "sample_episodes: n_max=%d is too large for the walker's shared-memory table ring", n_max);
+  IN_REQUIRE(L.nblk <= 2147483647LL, "sample_episodes: stream too long");
+  static bool smem_set[64] = {};
+  int dev = 0;
+  IN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !smem_set[dev]) {
+    IN_CUDA(cudaFuncSetAttribute(smp_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    if (dev >= 0 && dev < 64) smem_set[dev] = true;
+  }
+  smp_python_kernel<<<1, 128, 0, st>>>(py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
+  IN_LAUNCH_CHECK("smp_python_kernel");
+  smp_gen_kernel<<<1, SMP_NT, 0, st>>>(np_state, keys, (int)L.nb);
+  IN_LAUNCH_CHECK("smp_gen_kernel");
+  smp_table_kernel<<<(unsigned)L.nblk, 256, 0, st>>>(keys, tab, (int)L.n_states);
+  IN_LAUNCH_CHECK("smp_table_kernel");
+  IN_CUDA(cudaMemsetAsync(blk_rec, 0xFF, 8 * L.nblk, st));
+  smp_walk_kernel<<<1, 32, (size_t)L.smem_bytes, st>>>(keys, tab, (int)L.n_states, L.nblk, L.cb_log, L.rc_log, np_state,
+                                                      jsize, (int)L.jobs, (int)L.stride, jlist, blk_rec, status);
+  IN_LAUNCH_CHECK("smp_walk_kernel");
+  smp_fill_kernel<<<ceil_div(L.nblk, 128), 128, 0, st>>>(tab, (int)L.n_states, blk_rec, L.nblk, (int)L.stride, jlist);
+  IN_LAUNCH_CHECK("smp_fill_kernel");
+  sampler_trace_kernel<<<ceil_div(L.jobs * L.pick_max, 128), 128, 0, st>>>(scopes, classes, jlist, B, N, K, Q,
+                                                                           (int)L.stride, (int)L.pick_max, picks);
   IN_LAUNCH_CHECK("sampler_trace_kernel");
   return INDNET_OK;
 }
@@ -379,12 +581,11 @@ static int sample_gather(cudaStream_t st, const int* scopes, const int* t_word, 
   if (B == 0) return INDNET_OK;
   IN_REQUIRE(scopes && t_word && t_pos1 && t_pos2 && t_mask && scratch && rows && labels && o_word && o_pos1 &&
              o_pos2 && o_mask, "sample_gather: null pointer");
-  const long long jobs = (long long)B * (N + 1);
-  const int pick_max = (K + Q > N * Q) ? (K + Q) : (N * Q);
-  if (n_max < N * Q) n_max = N * Q;
-  const int* classes = (const int*)scratch;
-  const int* jlist = classes + (((long long)B * N + 15) / 16) * 16;
-  const int* picks = jlist + jobs * n_max;
+  const SmpLayout lay = smp_layout(B, N, K, Q, n_max);
+  const char* base = (const char*)scratch;
+  const int* classes = (const int*)(base + lay.o_classes);
+  const int* picks = (const int*)(base + lay.o_picks);
+  const int pick_max = (int)lay.pick_max;
   sampler_gather_kernel<<<B * N * (K + Q), 64, 0, st>>>(scopes, classes, picks, pick_max, B, N, K, Q, L, t_word,
                                                        t_pos1, t_pos2, t_mask, rows, labels, o_word, o_pos1, o_pos2,
                                                        o_mask);
