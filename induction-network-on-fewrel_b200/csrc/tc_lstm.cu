@@ -27,13 +27,17 @@ constexpr int LT_KX = 64;            // padded input width (D <= 64)
 constexpr int LT_K = LT_KX + LT_U;   // 192
 constexpr int LT_KB = LT_K / 64;     // 3 K-blocks of 64 (one 128-byte swizzle row each)
 constexpr int LT_NS = 32;            // sentences per CTA (MMA N)
-constexpr int LT_THREADS = 256;
-constexpr int LT_SPT = LT_NS / 2;        // sentences per gate thread
-static_assert(LT_SPT == 16, "gate threads use 16-column TMEM loads");
+constexpr int LT_THREADS = 512;
+constexpr int LT_SPT = LT_NS / (LT_THREADS / 128);   // sentences per gate thread
+static_assert(LT_SPT == 8 || LT_SPT == 16, "gate threads use 8- or 16-column TMEM loads");
+__device__ __forceinline__ void tmem_ld_spt(uint32_t taddr, float* v) {
+  if constexpr (LT_SPT == 16) tmem_ld16(taddr, v); else tmem_ld8(taddr, v);
+}
 constexpr int LT_W_BYTES = 4 * LT_KB * 128 * 128;            // 196608
 constexpr int LT_XB_BYTES = LT_NS * 128;                     // one x tile
 constexpr int LT_HB_BYTES = 2 * LT_NS * 128;                 // h tile: 2 K-blocks
-constexpr int LT_SMEM = LT_W_BYTES + 2 * LT_XB_BYTES + LT_HB_BYTES + 256 + 1024;
+constexpr int LT_XBUFS = 3;                                 // x tiles in flight (see issue_x / issue_h)
+constexpr int LT_SMEM = LT_W_BYTES + LT_XBUFS * LT_XB_BYTES + LT_HB_BYTES + 256 + 1024;
 
 int make_tmap_bf16(CUtensorMap* tm, const void* base, long long inner, long long outer, long long ld,
                    long long batch, long long batch_stride, int box_inner, int box_outer);
@@ -74,6 +78,9 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ void sts_bf16(uint32_t saddr, __nv_bfloat16 v) {
+  asm volatile("st.shared.b16 [%0], %1;" ::"r"(saddr), "h"(*reinterpret_cast<unsigned short*>(&v)) : "memory");
+}
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
 
@@ -85,11 +92,11 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = smem;                                   // [4 gates][3 kb][128 rows][128 B]
-  uint8_t* sX = smem + LT_W_BYTES;                      // [2][NS rows][128 B]
-  uint8_t* sH = sX + 2 * LT_XB_BYTES;                   // [2 kb][NS rows][128 B]
+  uint8_t* sX = smem + LT_W_BYTES;                      // [3][NS rows][128 B]
+  uint8_t* sH = sX + LT_XBUFS * LT_XB_BYTES;            // [2 kb][NS rows][128 B]
   uint64_t* w_full = reinterpret_cast<uint64_t*>(sH + LT_HB_BYTES);
-  uint64_t* x_full = w_full + 1;                        // [2]
-  uint64_t* mma_done = x_full + 2;
+  uint64_t* x_full = w_full + 1;                        // [3]
+  uint64_t* mma_done = x_full + LT_XBUFS;
   uint64_t* h_ready = mma_done + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
 
@@ -106,14 +113,13 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmX);
     mbar_init(w_full, 1);
-    mbar_init(&x_full[0], 1);
-    mbar_init(&x_full[1], 1);
+    for (int b = 0; b < LT_XBUFS; ++b) mbar_init(&x_full[b], 1);
     mbar_init(mma_done, 1);
     mbar_init(h_ready, LT_THREADS);
     fence_barrier_init();
   }
   __syncwarp();
-  if (warp == 0) tmem_alloc(tmem_slot, 4 * LT_NS);
+  if (warp == 0) tmem_alloc(tmem_slot, 8 * LT_NS);      // two accumulator buffers of 4 gates x NS columns
   fence_proxy_async();          // the zero-fill of sH must be visible to the tensor core's operand reads
   tc_fence_before();
   __syncthreads();
@@ -122,25 +128,41 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
   const uint32_t w16 = smem_u32(sW) >> 4, x16 = smem_u32(sX) >> 4, h16 = smem_u32(sH) >> 4;
 
-  // issue the MMAs of processing step s (thread 0 only)
-  auto issue_step = [&](int s) {
-    if (s + 1 < L) {                                      // prefetch x of the step after (its buffer is free)
-      const int tn = dir ? (L - 2 - s) : (s + 1);
-      mbar_expect_tx(&x_full[(s + 1) & 1], LT_XB_BYTES);
-      tma_load_3d(sX + ((s + 1) & 1) * LT_XB_BYTES, &tmX, &x_full[(s + 1) & 1], 0, tn, x0);
-    }
-    mbar_wait(&x_full[s & 1], (s >> 1) & 1);
+  // MMAs of processing step s, thread 0 only.  The x part does not depend on the recurrence, so it is
+  // issued a step early into the other accumulator buffer (buffer = s & 1) and only the h part sits on
+  // the serial path between two gate phases.  x tiles: three buffers, tile of step s in buffer s % 3.
+  auto load_x = [&](int s) {
+    const int tn = dir ? (L - 1 - s) : s;
+    mbar_expect_tx(&x_full[s % LT_XBUFS], LT_XB_BYTES);
+    tma_load_3d(sX + (s % LT_XBUFS) * LT_XB_BYTES, &tmX, &x_full[s % LT_XBUFS], 0, tn, x0);
+  };
+  auto issue_x = [&](int s) {
+    mbar_wait(&x_full[s % LT_XBUFS], (s / LT_XBUFS) & 1);
     tc_fence_after();
+    const uint32_t b16 = x16 + (s % LT_XBUFS) * (LT_XB_BYTES >> 4);
+    const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
 #pragma unroll
-      for (int kb = 0; kb < LT_KB; ++kb) {
-        const uint32_t b16 = (kb == 0) ? (x16 + (s & 1) * (LT_XB_BYTES >> 4)) : (h16 + (kb - 1) * ((LT_NS * 128) >> 4));
+      for (int k4 = 0; k4 < 4; ++k4) {
+        const uint64_t ad = smem_desc_sw128_k(w16, (g * LT_KB) * 16384 + k4 * 32);
+        const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
+        umma_bf16(acc + g * LT_NS, ad, bd, idesc, k4 > 0 ? 1u : 0u);
+      }
+    }
+  };
+  auto issue_h = [&](int s) {
+    const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+      for (int kb = 1; kb < LT_KB; ++kb) {
+        const uint32_t b16 = h16 + (kb - 1) * ((LT_NS * 128) >> 4);
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
           const uint64_t ad = smem_desc_sw128_k(w16, (g * LT_KB + kb) * 16384 + k4 * 32);
           const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
-          umma_bf16(taddr + g * LT_NS, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+          umma_bf16(acc + g * LT_NS, ad, bd, idesc, 1u);
         }
       }
     }
@@ -152,10 +174,11 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     for (int g = 0; g < 4; ++g)
       for (int kb = 0; kb < LT_KB; ++kb)
         tma_load_3d(sW + (g * LT_KB + kb) * 16384, &tmW, w_full, kb * 64, g * 128, dir);
-    mbar_expect_tx(&x_full[0], LT_XB_BYTES);              // x of the first step
-    tma_load_3d(sX, &tmX, &x_full[0], 0, dir ? (L - 1) : 0, x0);
+    for (int s = 0; s < LT_XBUFS && s < L; ++s) load_x(s);
     mbar_wait(w_full, 0);
-    issue_step(0);
+    issue_x(0);
+    issue_h(0);
+    if (L > 1) issue_x(1);
   }
 
   // ---- gate phase: thread = (unit m = TMEM lane, sentence half hf), LT_SPT sentences each
@@ -163,14 +186,14 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   const int hf = warp >> 2;
   const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
   const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
-  const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+  const uint32_t lane_addr0 = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
   const float inv_keep = 1.0f / p.keep_prob;
   const bool drop = p.keep_prob < 1.0f;
   float c[LT_SPT], hp[LT_SPT];
 #pragma unroll
   for (int q = 0; q < LT_SPT; ++q) { c[q] = 0.f; hp[q] = 0.f; }
   const int hkb = m >> 6, hk = m & 63;                     // destination inside the swizzled h tile
-  uint8_t* hdst = sH + hkb * (LT_NS * 128) + (hk & 7) * 2;
+  const uint32_t hdst = smem_u32(sH) + hkb * (LT_NS * 128) + (hk & 7) * 2;
   const uint32_t hchunk = (uint32_t)(hk >> 3);
   const int xs0 = x0 + hf * LT_SPT;                        // first sentence of this thread
   const int tok_base = (dir * p.X + xs0) * L;              // token index of (sentence q, time t) = tok_base + q*L + t
@@ -180,11 +203,12 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     mbar_wait(mma_done, s & 1);
     __syncwarp();
     tc_fence_after();
-    float zi[16], zj[16], zf[16], zo[16];
-    tmem_ld16(lane_addr + 0 * LT_NS, zi);
-    tmem_ld16(lane_addr + 1 * LT_NS, zj);
-    tmem_ld16(lane_addr + 2 * LT_NS, zf);
-    tmem_ld16(lane_addr + 3 * LT_NS, zo);
+    float zi[LT_SPT], zj[LT_SPT], zf[LT_SPT], zo[LT_SPT];
+    const uint32_t lane_addr = lane_addr0 + (s & 1) * (4 * LT_NS);
+    tmem_ld_spt(lane_addr + 0 * LT_NS, zi);
+    tmem_ld_spt(lane_addr + 1 * LT_NS, zj);
+    tmem_ld_spt(lane_addr + 2 * LT_NS, zf);
+    tmem_ld_spt(lane_addr + 3 * LT_NS, zo);
     tmem_ld_wait();
 #pragma unroll
     for (int q = 0; q < LT_SPT; ++q) {
@@ -197,7 +221,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       const float h = tanh_fast(cn) * go;
       c[q] = cn;
       // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
-      *reinterpret_cast<__nv_bfloat16*>(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4)) = __float2bfloat16(h);
+      sts_bf16(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4), __float2bfloat16(h));
       if (xs0 + q < p.X) {
         const long long e = (long long)(tok_base + q * L + t) * LT_U + m;     // [tok][unit]
         *reinterpret_cast<uint2*>(p.gates_bf + e * 4) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
@@ -216,11 +240,14 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     mbar_arrive(h_ready);
     if (issuer && s + 1 < L) {
       mbar_wait(h_ready, s & 1);        // every thread has published h_s and drained TMEM
-      issue_step(s + 1);
+      tc_fence_after();
+      issue_h(s + 1);
+      if (s + 2 < L) issue_x(s + 2);    // accumulator buffer s & 1 was drained by the gate phase just finished
+      if (s + 3 < L) load_x(s + 3);     // into the buffer of x_s, whose MMAs are known complete (mma_done of step s)
     }
   }
   __syncthreads();
-  if (warp == 0) tmem_dealloc(taddr, 4 * LT_NS);
+  if (warp == 0) tmem_dealloc(taddr, 8 * LT_NS);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -287,7 +314,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
   const float inv_keep = 1.0f / p.keep_prob;
   const bool drop = p.keep_prob < 1.0f;
   // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
-  uint8_t* zdst = sZ + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
+  const uint32_t zdst = smem_u32(sZ) + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
   const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
   const int xs0 = x0 + hf * LT_SPT;
   const int tok_base = (dir * p.X + xs0) * L;
@@ -330,7 +357,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       mbar_wait(mma_done, (step - 1) & 1);
       __syncwarp();
       tc_fence_after();
-      tmem_ld16(lane_addr, dhr);
+      tmem_ld_spt(lane_addr, dhr);
       tmem_ld_wait();
 #pragma unroll
       for (int q = 0; q < LT_SPT; ++q) {
@@ -366,11 +393,11 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       cc[q] = cp[q];                        // c_{t_prev} is the cell state of the next step processed
       const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
                           bo = __float2bfloat16(dob);
-      uint8_t* zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
-      *reinterpret_cast<__nv_bfloat16*>(zp) = bi;
-      *reinterpret_cast<__nv_bfloat16*>(zp + 2 * (LT_NS * 128)) = bj;
-      *reinterpret_cast<__nv_bfloat16*>(zp + 4 * (LT_NS * 128)) = bf;
-      *reinterpret_cast<__nv_bfloat16*>(zp + 6 * (LT_NS * 128)) = bo;
+      const uint32_t zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
+      sts_bf16(zp, bi);
+      sts_bf16(zp + 2 * (LT_NS * 128), bj);
+      sts_bf16(zp + 4 * (LT_NS * 128), bf);
+      sts_bf16(zp + 6 * (LT_NS * 128), bo);
       if (xs0 + q < p.X) {
         __nv_bfloat16* gz = p.dz_bf + (long long)(tok_base + q * L + t) * (4 * LT_U) + m;
         gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
