@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define INDNET_ABI_VERSION 2
+#define INDNET_ABI_VERSION 3
 
 typedef void* indnet_stream; /* cudaStream_t */
 
@@ -60,6 +60,15 @@ int indnet_permute021(indnet_stream st, const float* in, float* out, int d0, int
 int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
                    const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act,
                    int accumulate, int batch, long long sA, long long sB, long long sC, int splitk);
+/* Same GEMM (batch 1, no split-K) with a rank-1 term in the epilogue:
+ *   C[m][n] = sum_k A*B + rs[m] * v(m / rv_rows)[n]
+ * where v(x) is row x of the pair (rv_a, rv_b), N wide, in the support/query split layout of
+ * indnet_attn_pool_bwd (group, split).  This is d(loss)/d(h) of the self-attention block in one pass:
+ * the Dense path dpre * W_a1^T plus the pooling path alpha_t * denc (autodiff of
+ * model/layer_module.py:44-54), written once (fp32 C and/or bf16 Cb) instead of accumulated in HBM. */
+int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
+                         const void* B, long long ldb, float* C, void* Cb, int ldc, const float* rs,
+                         const float* rv_a, const float* rv_b, int rv_rows, int group, int split);
 /* out (bf16) = in (fp32), n elements. */
 int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
 /* Row-wise cast with a padded output row stride: out[r][0..ldo) = in[r][0..cols), zeros beyond cols
@@ -133,8 +142,9 @@ int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_f
 
 /* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] bf16 and cstate
  * fp32 as saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h
- * = rows D.., read in place by TMA, no scratch).  Writes dz_bf [2][X][L][4u] bf16. */
-int indnet_lstm_bwd_tc(indnet_stream st, const float* dhout, const void* gates_bf, const float* cstate,
+ * = rows D.., read in place by TMA, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
+ * Writes dz_bf [2][X][L][4u] bf16. */
+int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const float* cstate,
                        const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D, int u,
                        float keep_prob, unsigned long long seed, const long long* seed_step);
 /* out[c] = sum_r A[r][c] for a dense bf16 matrix [rows][cols] (bias gradients from the bf16 dz stream). */
@@ -159,7 +169,8 @@ int indnet_lstm_bwd_static(indnet_stream st, const float* dhout, const float* ga
 int indnet_attn_pool_fwd(indnet_stream st, const float* hout, const float* proj, const int* mask, const float* w_a2,
                          float* enc_a, float* enc_b, float* alphas, int X, int L, int H, int group, int split);
 /* Reads denc_a/denc_b in the same split layout.  Writes dhout = alpha_t*denc (caller adds
- * dpre*Wa1^T), dpre [X][L][H], dw2_part [X][H]. */
+ * dpre*Wa1^T; the bf16 variant accepts dhout = NULL when that term is fused into
+ * indnet_tc_gemm_rank1), dpre [X][L][H], dw2_part [X][H]. */
 int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* denc_b, const float* hout,
                          const float* proj, const float* alphas, const float* w_a2, float* dhout, float* dpre,
                          float* dw2_part, int X, int L, int H, int group, int split);

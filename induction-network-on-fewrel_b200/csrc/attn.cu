@@ -119,7 +119,7 @@ attn_pool_bwd_kernel(const float* __restrict__ denc_a, const float* __restrict__
       const long long o = ((long long)x * L + t) * H + h;
       const float p = ldf(pj + (long long)t * H + h);
       const float dp = dsc[t] * w * (1.0f - p * p);
-      dhout[o] = al[t] * g;
+      if (dhout) dhout[o] = al[t] * g;
       stf(dpre + o, dp);
       dw = fmaf(dsc[t], p, dw);
       dsum += dp;
@@ -187,7 +187,7 @@ extern "C" int indnet_attn_pool_bwd_bf16(indnet_stream st_, const float* denc_a,
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0 && H > 0 && L <= 4096, "attn_pool_bwd_bf16: bad sizes X=%d L=%d H=%d", X, L, H);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && dhout && dpre_bf && dw2_part, "attn_pool_bwd_bf16: null pointer");
+  IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && dpre_bf && dw2_part, "attn_pool_bwd_bf16: null pointer");
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_pool_bwd_bf16: bad group/split %d/%d", group, split);
   IN_REQUIRE(split == group || denc_b, "attn_pool_bwd_bf16: second gradient input missing");
   attn_pool_bwd_kernel<__nv_bfloat16><<<X, ATT_NT, sizeof(float) * 2 * L, st>>>(

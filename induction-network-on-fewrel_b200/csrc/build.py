@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "libindnet.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-shared", "--threads", "0"]
+         "-Xcompiler", "-fPIC", "-shared", "--threads", "0"] + os.environ.get("INDNET_NVCC_DEFINES", "").split()
 
 
 def sources():

@@ -29,11 +29,17 @@ __device__ __forceinline__ float tanh_approx(float x) {
   return y;
 }
 
+struct TcGemmRank1 { const float* rs; const float* rv_a; const float* rv_b; int rv_rows, group, split; };
+
 struct TcGemmP {
   float* C; __nv_bfloat16* Cb; const float* bias;
+  // optional rank-1 term of the epilogue: C[m][n] += rs[m] * v(m / rv_rows)[n], v(x) = row x of the pair of
+  // matrices (rv_a, rv_b) in the split layout of the attention kernels (group / split), N wide
+  const float* rs; const float* rv_a; const float* rv_b; int rv_rows, rv_group, rv_split;
   int M, N, K, ldc;
   long long sC;        // batch stride of C (elements)
   int act, accumulate, splitk, kb_per_split, batch;
+  int vec;        // 1: outputs / bias / rank-1 vectors are 16-byte aligned -> row-path epilogue
 };
 
 template <bool A_MN, bool B_MN>
@@ -132,8 +138,70 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       float v[32];
       tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + c * 32, v);
       tmem_ld_wait();
+      const int nc = n0 + c * 32;
+      if (p.vec && nc + 32 <= p.N) {
+        // Row path (everything 16-byte aligned, full 32-column chunk): the lane keeps its own row, i.e. 32
+        // consecutive output columns, and moves them with 16-byte loads / stores - no shared-memory
+        // transpose, 4 (bf16) or 8 (fp32) store instructions per chunk instead of 32.
+        if (row < p.M) {
+          const long long o = (long long)row * p.ldc + nc;
+          if (p.bias) {
+            const float4* b4 = reinterpret_cast<const float4*>(p.bias + nc);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = __ldg(b4 + j);
+              v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+            }
+          }
+          if (p.accumulate) {
+            const float4* c4 = reinterpret_cast<const float4*>(Cbase + o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = c4[j];
+              v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+            }
+          } else if (p.rs) {
+            const float rs = p.rs[row];
+            const int xr = row / p.rv_rows;
+            const int g = xr / p.rv_group, r = xr - g * p.rv_group;
+            const float* vp = (r < p.rv_split) ? p.rv_a + ((long long)g * p.rv_split + r) * p.N
+                                               : p.rv_b + ((long long)g * (p.rv_group - p.rv_split) + (r - p.rv_split)) * p.N;
+            const float4* v4 = reinterpret_cast<const float4*>(vp + nc);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = __ldg(v4 + j);
+              v[4 * j] = fmaf(rs, b.x, v[4 * j]); v[4 * j + 1] = fmaf(rs, b.y, v[4 * j + 1]);
+              v[4 * j + 2] = fmaf(rs, b.z, v[4 * j + 2]); v[4 * j + 3] = fmaf(rs, b.w, v[4 * j + 3]);
+            }
+          }
+          if (p.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = tanh_approx(v[j]);
+          } else if (p.act == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (Cbase) {
+            float4* c4 = reinterpret_cast<float4*>(Cbase + o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) c4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+          if (Cbbase) {
+            uint4* c4 = reinterpret_cast<uint4*>(Cbbase + o);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              __nv_bfloat162 a = __floats2bfloat162_rn(v[8 * j], v[8 * j + 1]), b = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+              __nv_bfloat162 cc = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]), d = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
+              c4[j] = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b),
+                                 *reinterpret_cast<uint32_t*>(&cc), *reinterpret_cast<uint32_t*>(&d));
+            }
+          }
+        }
+        continue;
+      }
 #pragma unroll
       for (int j = 0; j < 32; ++j) tile[lane * 33 + j] = v[j];
+      if (p.rs) tile[lane * 33 + 32] = (row0 + lane < p.M) ? p.rs[row0 + lane] : 0.f;   // padding column: rs of row `lane`
       __syncwarp();
       const int n = n0 + c * 32 + lane;
       if (n < p.N) {
@@ -149,12 +217,30 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (p.accumulate) {
 #pragma unroll
             for (int rr = 0; rr < 32; ++rr) old[rr] = (rr < rmax) ? Cbase[o0 + (long long)rr * p.ldc] : 0.f;
+          } else if (p.rs) {
+            // rank-1 term: rs of the strip's rows sits in the tile's padding column; a 32-row strip touches
+            // at most a few vectors, each fetched once; the row -> vector index advances incrementally
+            int xr = row0 / p.rv_rows, rem = row0 - xr * p.rv_rows;
+            float vv = 0.f;
+            bool fresh = true;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) {
+              if (rr < rmax && fresh) {
+                const int g = xr / p.rv_group, r = xr - g * p.rv_group;
+                const float* vp = (r < p.rv_split) ? p.rv_a + ((long long)g * p.rv_split + r) * p.N
+                                                   : p.rv_b + ((long long)g * (p.rv_group - p.rv_split) + (r - p.rv_split)) * p.N;
+                vv = vp[n];
+              }
+              old[rr] = tile[rr * 33 + 32] * vv;
+              fresh = (++rem == p.rv_rows);
+              if (fresh) { rem = 0; ++xr; }
+            }
           }
 #pragma unroll
           for (int rr = 0; rr < 32; ++rr) {
             if (rr < rmax) {
               float x = tile[rr * 33 + lane] + bv;
-              if (p.accumulate) x += old[rr];
+              if (p.accumulate || p.rs) x += old[rr];
               if (p.act == 1) x = tanh_approx(x);       // bf16 mode: MUFU.TANH is well inside the 2e-2 budget
               else if (p.act == 2) x = fmaxf(x, 0.f);
               const long long o = o0 + (long long)rr * p.ldc;
@@ -212,7 +298,7 @@ int make_tmap_bf16(CUtensorMap* tm, const void* base, long long inner, long long
 
 int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const void* A, long long lda,
             const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act, int accumulate,
-            int batch, long long sA, long long sB, long long sC, int splitk) {
+            int batch, long long sA, long long sB, long long sC, int splitk, const TcGemmRank1* r1 = nullptr) {
   IN_REQUIRE(M > 0 && N > 0 && K > 0 && batch > 0, "tc_gemm: bad sizes M=%d N=%d K=%d batch=%d", M, N, K, batch);
   IN_REQUIRE(A && B && (C || Cb), "tc_gemm: null operand");
   const int total_kb = ceil_div(K, G_BK);
@@ -229,11 +315,27 @@ int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const vo
   IN_REQUIRE(splitk == 1 || (batch == 1 && act == 0 && !Cb && C), "tc_gemm: split-K needs fp32 output, no activation, no batch");
   TcGemmP p;
   p.C = C; p.Cb = (__nv_bfloat16*)Cb; p.bias = bias;
+  p.rs = nullptr; p.rv_a = p.rv_b = nullptr; p.rv_rows = p.rv_group = 1; p.rv_split = 0;
+  if (r1) {
+    IN_REQUIRE(splitk == 1 && batch == 1 && !accumulate, "tc_gemm: the rank-1 epilogue needs splitk = batch = 1 and no accumulate");
+    IN_REQUIRE(r1->rs && r1->rv_a && r1->rv_rows > 0 && r1->group > 0 && r1->split >= 0 && r1->split <= r1->group &&
+               (r1->split == r1->group || r1->rv_b), "tc_gemm: bad rank-1 epilogue arguments");
+    p.rs = r1->rs; p.rv_a = r1->rv_a; p.rv_b = r1->rv_b; p.rv_rows = r1->rv_rows; p.rv_group = r1->group; p.rv_split = r1->split;
+  }
   p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.sC = sC;
   p.act = act; p.accumulate = accumulate; p.splitk = splitk; p.batch = batch;
   p.kb_per_split = ceil_div(total_kb, splitk);
   splitk = ceil_div(total_kb, p.kb_per_split);      // no empty K slices
   p.splitk = splitk;
+  {
+    auto al16 = [](const void* q) { return ((uintptr_t)q & 15) == 0; };
+    bool v = splitk == 1;
+    if (C) v = v && al16(C) && ldc % 4 == 0 && (batch == 1 || sC % 4 == 0);
+    if (Cb) v = v && al16(Cb) && ldc % 8 == 0 && (batch == 1 || sC % 8 == 0);
+    if (bias) v = v && al16(bias);
+    if (p.rs) v = v && al16(p.rv_a) && (!p.rv_b || al16(p.rv_b)) && N % 4 == 0;
+    p.vec = v ? 1 : 0;
+  }
   if (splitk > 1 && !accumulate) {
     IN_REQUIRE(ldc == N, "tc_gemm: split-K zero-fill expects a dense C");
     IN_CUDA(cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N, st));
@@ -318,4 +420,13 @@ extern "C" int indnet_cast_bf16_rows(indnet_stream st, const float* in, void* ou
   cast_bf16_rows_kernel<<<ceil_div(rows * ldo, 256), 256, 0, (cudaStream_t)st>>>(in, (__nv_bfloat16*)out, rows, cols, ldo);
   IN_LAUNCH_CHECK("cast_bf16_rows_kernel");
   return INDNET_OK;
+}
+
+extern "C" int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A,
+                                    long long lda, const void* B, long long ldb, float* C, void* Cb, int ldc,
+                                    const float* rs, const float* rv_a, const float* rv_b, int rv_rows, int group,
+                                    int split) {
+  TcGemmRank1 r1{rs, rv_a, rv_b, rv_rows, group, split};
+  return tc_gemm((cudaStream_t)st, a_mn != 0, b_mn != 0, M, N, K, A, lda, B, ldb, C, Cb, ldc, nullptr, 0, 0, 1, 0, 0, 0,
+                 1, &r1);
 }

@@ -33,7 +33,7 @@ static_assert(LT_SPT == 8 || LT_SPT == 16, "gate threads use 8- or 16-column TME
 __device__ __forceinline__ void tmem_ld_spt(uint32_t taddr, float* v) {
   if constexpr (LT_SPT == 16) tmem_ld16(taddr, v); else tmem_ld8(taddr, v);
 }
-constexpr int LT_W_BYTES = 4 * LT_KB * 128 * 128;            // 196608
+constexpr int LT_W_BYTES = 4 * 128 * 128;                    // W_x only (4 gate tiles x 64 k): 65536; W_h lives in TMEM
 constexpr int LT_XB_BYTES = LT_NS * 128;                     // one x tile
 constexpr int LT_HB_BYTES = 2 * LT_NS * 128;                 // h tile: 2 K-blocks
 constexpr int LT_XBUFS = 3;                                 // x tiles in flight (see issue_x / issue_h)
@@ -57,6 +57,14 @@ __global__ void lstm_pack_weights_kernel(const float* __restrict__ k_fw, const f
   WT[((long long)dir * 4 * LT_U + col) * LT_K + k] = __float2bfloat16(v);
 }
 
+// Optional per-step timeline of CTA (0,0) (build with INDNET_NVCC_DEFINES=-DINDNET_LSTM_TIMELINE, read with
+// tools/lstm_dbg.py); compiled out of the product build.
+#ifdef INDNET_LSTM_TIMELINE
+__device__ long long g_lstm_dbg[64 * 8];
+#define LT_MARK(cond, s, k) do { if ((cond) && blockIdx.x == 0 && blockIdx.y == 0 && (s) < 64) g_lstm_dbg[(s) * 8 + (k)] = clock64(); } while (0)
+#else
+#define LT_MARK(cond, s, k) do { } while (0)
+#endif
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -70,6 +78,7 @@ struct LstmTcP {
   __nv_bfloat16* gates_bf;      // [2][X][L][u][4]  (i, j, f, o of a unit adjacent: one 8-byte store / load)
   float* cstate;                // [2][X][L][u]
   __nv_bfloat16* hprev_bf;      // [2][X][L][u]
+  const __nv_bfloat16* wt;      // packed weights WT[dir][4u][192] (lstm_pack_weights_kernel)
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
@@ -84,14 +93,18 @@ __device__ __forceinline__ void sts_bf16(uint32_t saddr, __nv_bfloat16 v) {
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
 
-// All 8 warps are gate warps (TMEM lane quarter = warp % 4, sentence half = warp / 4); thread 0 also
-// plays the TMA / MMA issuer between its own gate phases (it would be waiting on the MMA anyway), so
-// the CTA is exactly 256 threads and every thread may use up to 255 registers.
-__global__ void __launch_bounds__(LT_THREADS, 1)
+// Warps 0-15 are gate warps (TMEM lane quarter = warp % 4, sentence quarter = warp / 4); warp 16 issues the
+// TMA loads and the MMAs (one elected lane, operands in uniform registers).  DROP / HOUT32 are
+// compile-time so the per-element code carries no uniform branches.
+constexpr int LT_GATE_THREADS = LT_THREADS;
+constexpr int LT_FWD_THREADS = LT_THREADS + 32;
+
+template <bool DROP, bool HOUT32>
+__global__ void __launch_bounds__(LT_FWD_THREADS, 1)
 tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, LstmTcP p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sW = smem;                                   // [4 gates][3 kb][128 rows][128 B]
+  uint8_t* sW = smem;                                   // W_x^T: [4 gates][128 rows][128 B]
   uint8_t* sX = smem + LT_W_BYTES;                      // [3][NS rows][128 B]
   uint8_t* sH = sX + LT_XBUFS * LT_XB_BYTES;            // [2 kb][NS rows][128 B]
   uint64_t* w_full = reinterpret_cast<uint64_t*>(sH + LT_HB_BYTES);
@@ -100,26 +113,24 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   uint64_t* h_ready = mma_done + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool issuer = threadIdx.x == 0;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
+  const bool gate_warp = warp < LT_GATE_THREADS / 32;
   const int dir = blockIdx.y;
   const int x0 = blockIdx.x * LT_NS;
   const int L = p.L;
-  unsigned long long seed = p.seed;
-  if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
 
-  for (int i = threadIdx.x; i < LT_HB_BYTES / 16; i += LT_THREADS) reinterpret_cast<uint4*>(sH)[i] = make_uint4(0, 0, 0, 0);   // h_{-1} = 0
-  if (issuer) {
+  for (int i = threadIdx.x; i < LT_HB_BYTES / 16; i += LT_FWD_THREADS) reinterpret_cast<uint4*>(sH)[i] = make_uint4(0, 0, 0, 0);   // h_{-1} = 0
+  if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmX);
     mbar_init(w_full, 1);
     for (int b = 0; b < LT_XBUFS; ++b) mbar_init(&x_full[b], 1);
     mbar_init(mma_done, 1);
-    mbar_init(h_ready, LT_THREADS);
+    mbar_init(h_ready, LT_GATE_THREADS);
     fence_barrier_init();
   }
   __syncwarp();
-  if (warp == 0) tmem_alloc(tmem_slot, 8 * LT_NS);      // two accumulator buffers of 4 gates x NS columns
+  if (warp == 0) tmem_alloc(tmem_slot, 512);            // two accumulator buffers (2 x 4 gates x NS columns) + W_h^T (256)
   fence_proxy_async();          // the zero-fill of sH must be visible to the tensor core's operand reads
   tc_fence_before();
   __syncthreads();
@@ -127,127 +138,184 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   const uint32_t taddr = *tmem_slot;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
   const uint32_t w16 = smem_u32(sW) >> 4, x16 = smem_u32(sX) >> 4, h16 = smem_u32(sH) >> 4;
-
-  // MMAs of processing step s, thread 0 only.  The x part does not depend on the recurrence, so it is
-  // issued a step early into the other accumulator buffer (buffer = s & 1) and only the h part sits on
-  // the serial path between two gate phases.  x tiles: three buffers, tile of step s in buffer s % 3.
-  auto load_x = [&](int s) {
-    const int tn = dir ? (L - 1 - s) : s;
-    mbar_expect_tx(&x_full[s % LT_XBUFS], LT_XB_BYTES);
-    tma_load_3d(sX + (s % LT_XBUFS) * LT_XB_BYTES, &tmX, &x_full[s % LT_XBUFS], 0, tn, x0);
-  };
-  auto issue_x = [&](int s) {
-    mbar_wait(&x_full[s % LT_XBUFS], (s / LT_XBUFS) & 1);
-    tc_fence_after();
-    const uint32_t b16 = x16 + (s % LT_XBUFS) * (LT_XB_BYTES >> 4);
-    const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
+  const uint32_t wh_t = taddr + 8 * LT_NS;                 // W_h^T: gate g at columns g*64, lane = unit
+  if (gate_warp) {
+    // The recurrent weights are the A operand of every step's serial MMAs.  Read from shared memory
+    // they cost 4 KB per 128x32x16 MMA and the tensor pipe runs at that read rate; resident in tensor
+    // memory the MMA is bounded by its math.  Warp w stages gate w / 4, lane quarter w % 4: thread =
+    // one row (unit) of W_h^T, 128 k values = 64 packed columns.
+    const int g = warp >> 2, row = (warp & 3) * 32 + lane;
+    const uint4* src = reinterpret_cast<const uint4*>(p.wt + ((long long)(dir * 4 + g) * LT_U + row) * LT_K + LT_KX);
+    const uint32_t dst = wh_t + ((uint32_t)((warp & 3) * 32) << 16) + g * (LT_U / 2);
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[16];
 #pragma unroll
-      for (int k4 = 0; k4 < 4; ++k4) {
-        const uint64_t ad = smem_desc_sw128_k(w16, (g * LT_KB) * 16384 + k4 * 32);
-        const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
-        umma_bf16(acc + g * LT_NS, ad, bd, idesc, k4 > 0 ? 1u : 0u);
+      for (int v = 0; v < 4; ++v) {
+        const uint4 q = src[c * 4 + v];
+        r[v * 4 + 0] = q.x; r[v * 4 + 1] = q.y; r[v * 4 + 2] = q.z; r[v * 4 + 3] = q.w;
       }
+      tmem_st16(dst + c * 16, r);
     }
-  };
-  auto issue_h = [&](int s) {
-    const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  if (!gate_warp) {
+    // ---- issuer warp.  The x part of a step does not depend on the recurrence, so it is issued a step
+    // early into the other accumulator buffer (buffer = s & 1) and only the h part sits on the serial
+    // path between two gate phases.  x tiles: three buffers, tile of step s in buffer s % 3.
+    auto load_x = [&](int s) {
+      if (elect_one()) {
+        const int tn = dir ? (L - 1 - s) : s;
+        mbar_expect_tx(&x_full[s % LT_XBUFS], LT_XB_BYTES);
+        tma_load_3d(sX + (s % LT_XBUFS) * LT_XB_BYTES, &tmX, &x_full[s % LT_XBUFS], 0, tn, x0);
+      }
+      __syncwarp();
+    };
+    auto issue_x = [&](int s) {
+      mbar_wait(&x_full[s % LT_XBUFS], (s / LT_XBUFS) & 1);
+      tc_fence_after();
+      const uint32_t b16 = x16 + (s % LT_XBUFS) * (LT_XB_BYTES >> 4);
+      const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
+      if (elect_one()) {
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 4; ++g) {
 #pragma unroll
-      for (int kb = 1; kb < LT_KB; ++kb) {
-        const uint32_t b16 = h16 + (kb - 1) * ((LT_NS * 128) >> 4);
-#pragma unroll
-        for (int k4 = 0; k4 < 4; ++k4) {
-          const uint64_t ad = smem_desc_sw128_k(w16, (g * LT_KB + kb) * 16384 + k4 * 32);
-          const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
-          umma_bf16(acc + g * LT_NS, ad, bd, idesc, 1u);
+          for (int k4 = 0; k4 < 4; ++k4) {
+            const uint64_t ad = smem_desc_sw128_k(w16, g * 16384 + k4 * 32);
+            const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
+            umma_bf16(acc + g * LT_NS, ad, bd, idesc, k4 > 0 ? 1u : 0u);
+          }
         }
       }
+      __syncwarp();
+    };
+    auto issue_h = [&](int s) {
+      const uint32_t acc = taddr + (s & 1) * (4 * LT_NS);
+      if (elect_one()) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+#pragma unroll
+          for (int kb = 0; kb < 2; ++kb) {
+            const uint32_t b16 = h16 + kb * ((LT_NS * 128) >> 4);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+              // A = W_h^T of gate g from tensor memory: 8 columns (16 k) per MMA
+              const uint64_t bd = smem_desc_sw128_k(b16, k4 * 32);
+              umma_bf16_ts(acc + g * LT_NS, wh_t + g * (LT_U / 2) + kb * 32 + k4 * 8, bd, idesc, 1u);
+            }
+          }
+        }
+        umma_commit(mma_done);
+      }
+      __syncwarp();
+    };
+    if (elect_one()) {
+      mbar_expect_tx(w_full, LT_W_BYTES);                 // resident W_x^T: 4 boxes of 64 (k) x 128 (rows)
+      for (int g = 0; g < 4; ++g) tma_load_3d(sW + g * 16384, &tmW, w_full, 0, g * 128, dir);
     }
-    umma_commit(mma_done);
-  };
-
-  if (issuer) {
-    mbar_expect_tx(w_full, LT_W_BYTES);                   // resident weights: 12 boxes of 64 (k) x 128 (rows)
-    for (int g = 0; g < 4; ++g)
-      for (int kb = 0; kb < LT_KB; ++kb)
-        tma_load_3d(sW + (g * LT_KB + kb) * 16384, &tmW, w_full, kb * 64, g * 128, dir);
+    __syncwarp();
     for (int s = 0; s < LT_XBUFS && s < L; ++s) load_x(s);
     mbar_wait(w_full, 0);
     issue_x(0);
     issue_h(0);
     if (L > 1) issue_x(1);
-  }
-
-  // ---- gate phase: thread = (unit m = TMEM lane, sentence half hf), LT_SPT sentences each
-  const int m = (warp & 3) * 32 + lane;
-  const int hf = warp >> 2;
-  const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
-  const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
-  const uint32_t lane_addr0 = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
-  const float inv_keep = 1.0f / p.keep_prob;
-  const bool drop = p.keep_prob < 1.0f;
-  float c[LT_SPT], hp[LT_SPT];
-#pragma unroll
-  for (int q = 0; q < LT_SPT; ++q) { c[q] = 0.f; hp[q] = 0.f; }
-  const int hkb = m >> 6, hk = m & 63;                     // destination inside the swizzled h tile
-  const uint32_t hdst = smem_u32(sH) + hkb * (LT_NS * 128) + (hk & 7) * 2;
-  const uint32_t hchunk = (uint32_t)(hk >> 3);
-  const int xs0 = x0 + hf * LT_SPT;                        // first sentence of this thread
-  const int tok_base = (dir * p.X + xs0) * L;              // token index of (sentence q, time t) = tok_base + q*L + t
-
-  for (int s = 0; s < L; ++s) {
-    const int t = dir ? (L - 1 - s) : s;
-    mbar_wait(mma_done, s & 1);
-    __syncwarp();
-    tc_fence_after();
-    float zi[LT_SPT], zj[LT_SPT], zf[LT_SPT], zo[LT_SPT];
-    const uint32_t lane_addr = lane_addr0 + (s & 1) * (4 * LT_NS);
-    tmem_ld_spt(lane_addr + 0 * LT_NS, zi);
-    tmem_ld_spt(lane_addr + 1 * LT_NS, zj);
-    tmem_ld_spt(lane_addr + 2 * LT_NS, zf);
-    tmem_ld_spt(lane_addr + 3 * LT_NS, zo);
-    tmem_ld_wait();
-#pragma unroll
-    for (int q = 0; q < LT_SPT; ++q) {
-      const int sl = hf * LT_SPT + q;
-      const float gi = sigmoid_fast(zi[q] + bi);
-      const float gj = tanh_fast(zj[q] + bj);
-      const float gf = sigmoid_fast(zf[q] + bf);
-      const float go = sigmoid_fast(zo[q] + bo);
-      const float cn = fmaf(c[q], gf, gi * gj);
-      const float h = tanh_fast(cn) * go;
-      c[q] = cn;
-      // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
-      sts_bf16(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4), __float2bfloat16(h));
-      if (xs0 + q < p.X) {
-        const long long e = (long long)(tok_base + q * L + t) * LT_U + m;     // [tok][unit]
-        *reinterpret_cast<uint2*>(p.gates_bf + e * 4) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
-        p.cstate[e] = cn;
-        p.hprev_bf[e] = __float2bfloat16(hp[q]);
-        const long long oi = ((long long)(xs0 + q) * L + t) * (2 * LT_U) + dir * LT_U + m;
-        float ho = h;
-        if (drop) ho = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? h * inv_keep : 0.f;
-        if (p.hout) p.hout[oi] = ho;
-        p.hout_bf[oi] = __float2bfloat16(ho);
-      }
-      hp[q] = h;
-    }
-    fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
-    tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
-    mbar_arrive(h_ready);
-    if (issuer && s + 1 < L) {
-      mbar_wait(h_ready, s & 1);        // every thread has published h_s and drained TMEM
+    for (int s = 0; s + 1 < L; ++s) {
+      mbar_wait(h_ready, s & 1);        // every gate thread has published h_s and drained accumulator buffer s & 1
       tc_fence_after();
+      LT_MARK(lane == 0, s, 5);
       issue_h(s + 1);
-      if (s + 2 < L) issue_x(s + 2);    // accumulator buffer s & 1 was drained by the gate phase just finished
-      if (s + 3 < L) load_x(s + 3);     // into the buffer of x_s, whose MMAs are known complete (mma_done of step s)
+      LT_MARK(lane == 0, s, 6);
+      if (s + 2 < L) issue_x(s + 2);
+      if (s + 3 < L) load_x(s + 3);     // into the buffer of x_s: its MMAs completed before h_s could exist
+      LT_MARK(lane == 0, s, 7);
+    }
+  } else {
+    // ---- gate warps: thread = (unit m = TMEM lane, sentence quarter hf), LT_SPT sentences each
+    unsigned long long seed = p.seed;
+    if (DROP && p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
+    const int m = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const float* __restrict__ bias = dir ? p.bias_bw : p.bias_fw;
+    const float bi = bias[m], bj = bias[LT_U + m], bf = bias[2 * LT_U + m] + 1.0f, bo = bias[3 * LT_U + m];
+    const uint32_t lane_addr0 = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+    const float inv_keep = 1.0f / p.keep_prob;
+    float c[LT_SPT], hp[LT_SPT];
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) { c[q] = 0.f; hp[q] = 0.f; }
+    const int hkb = m >> 6, hk = m & 63;                     // destination inside the swizzled h tile
+    const uint32_t hdst = smem_u32(sH) + hkb * (LT_NS * 128) + (hk & 7) * 2;
+    const uint32_t hchunk = (uint32_t)(hk >> 3);
+    const int xs0 = x0 + hf * LT_SPT;                        // first sentence of this thread
+    uint32_t valid = 0;
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) valid |= (xs0 + q < p.X) ? (1u << q) : 0u;
+    // Running byte pointers of sentence q = 0 at the current time step; sentence q adds q * (a
+    // per-array stride), one wide multiply-add per access.
+    const int t0 = dir ? (L - 1) : 0;
+    const long long e0 = ((long long)(dir * p.X + xs0) * L + t0) * LT_U + m;            // [dir][X][L][u] element
+    const long long o0 = ((long long)xs0 * L + t0) * (2 * LT_U) + dir * LT_U + m;       // [X][L][2u] element
+    const long long estep = dir ? -(long long)LT_U : (long long)LT_U;
+    const long long ostep = dir ? -(long long)(2 * LT_U) : (long long)(2 * LT_U);
+    const uint32_t qe = (uint32_t)L * LT_U, qo = (uint32_t)L * 2 * LT_U;                // elements between sentences
+    char* g_ptr = reinterpret_cast<char*>(p.gates_bf) + e0 * 8;
+    char* c_ptr = reinterpret_cast<char*>(p.cstate) + e0 * 4;
+    char* hp_ptr = reinterpret_cast<char*>(p.hprev_bf) + e0 * 2;
+    char* ob_ptr = reinterpret_cast<char*>(p.hout_bf) + o0 * 2;
+    char* of_ptr = reinterpret_cast<char*>(p.hout) + o0 * 4;
+    long long oi = o0;
+
+    for (int s = 0; s < L; ++s) {
+      LT_MARK(threadIdx.x == 0, s, 0);
+      mbar_wait(mma_done, s & 1);
+      __syncwarp();
+      tc_fence_after();
+      LT_MARK(threadIdx.x == 0, s, 1);
+      float zi[LT_SPT], zj[LT_SPT], zf[LT_SPT], zo[LT_SPT];
+      const uint32_t lane_addr = lane_addr0 + (s & 1) * (4 * LT_NS);
+      tmem_ld_spt(lane_addr + 0 * LT_NS, zi);
+      tmem_ld_spt(lane_addr + 1 * LT_NS, zj);
+      tmem_ld_spt(lane_addr + 2 * LT_NS, zf);
+      tmem_ld_spt(lane_addr + 3 * LT_NS, zo);
+      tmem_ld_wait();
+      LT_MARK(threadIdx.x == 0, s, 2);
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        const int sl = hf * LT_SPT + q;
+        const float gi = sigmoid_fast(zi[q] + bi);
+        const float gj = tanh_fast(zj[q] + bj);
+        const float gf = sigmoid_fast(zf[q] + bf);
+        const float go = sigmoid_fast(zo[q] + bo);
+        const float cn = fmaf(c[q], gf, gi * gj);
+        const float h = tanh_fast(cn) * go;
+        c[q] = cn;
+        // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
+        sts_bf16(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4), __float2bfloat16(h));
+        if (valid & (1u << q)) {
+          const unsigned long long eq = (unsigned long long)qe * (uint32_t)q, oq = (unsigned long long)qo * (uint32_t)q;
+          *reinterpret_cast<uint2*>(g_ptr + eq * 8) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
+          *reinterpret_cast<float*>(c_ptr + eq * 4) = cn;
+          *reinterpret_cast<__nv_bfloat16*>(hp_ptr + eq * 2) = __float2bfloat16(hp[q]);
+          float ho = h;
+          if (DROP) ho = dropout_keep(seed, (unsigned long long)(oi + (long long)oq), p.keep_prob) ? h * inv_keep : 0.f;
+          if (HOUT32) *reinterpret_cast<float*>(of_ptr + oq * 4) = ho;
+          *reinterpret_cast<__nv_bfloat16*>(ob_ptr + oq * 2) = __float2bfloat16(ho);
+        }
+        hp[q] = h;
+      }
+      LT_MARK(threadIdx.x == 0, s, 3);
+      fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
+      tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
+      mbar_arrive(h_ready);
+      LT_MARK(threadIdx.x == 0, s, 4);
+      g_ptr += estep * 8; c_ptr += estep * 4; hp_ptr += estep * 2; ob_ptr += ostep * 2; of_ptr += ostep * 4; oi += ostep;
     }
   }
   __syncthreads();
-  if (warp == 0) tmem_dealloc(taddr, 8 * LT_NS);
+  if (warp == 0) tmem_dealloc(taddr, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -263,7 +331,7 @@ constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                // 32768
 constexpr int LB_SMEM = LB_W_BYTES + LB_Z_BYTES + 256 + 1024;
 
 struct LstmTcBwdP {
-  const float* dhout; const __nv_bfloat16* gates_bf; const float* cstate; __nv_bfloat16* dz_bf;
+  const __nv_bfloat16* dhout; const __nv_bfloat16* gates_bf; const float* cstate; __nv_bfloat16* dz_bf;
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
@@ -279,7 +347,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
   uint64_t* z_ready = mma_done + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_ready + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
+  const bool issuer_warp = warp == 0;       // converged warp 0 issues the MMAs, one elected lane (see the forward kernel)
   const bool issuer = threadIdx.x == 0;
   const int dir = blockIdx.y;
   const int x0 = blockIdx.x * LT_NS;
@@ -349,7 +418,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       const int tokq = tok_base + qoff[q] * L;
       const long long e = (long long)(tokq + t) * LT_U + m;
       gw[q] = *reinterpret_cast<const uint2*>(p.gates_bf + e * 4);
-      dh[q] = p.dhout[((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m];
+      dh[q] = __bfloat162float(p.dhout[((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m]);
       cp[q] = (pstep > 0) ? p.cstate[(long long)(tokq + tprev) * LT_U + m] : 0.f;
     }
     if (step > 0) {
@@ -377,7 +446,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
         }
         dh[q] *= live[q];
       }
-      if (issuer) mbar_wait(w_full, 0);
+      if (issuer_warp) mbar_wait(w_full, 0);
     }
 #pragma unroll
     for (int q = 0; q < LT_SPT; ++q) {
@@ -406,19 +475,22 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
     fence_proxy_async();
     tc_fence_before();
     mbar_arrive(z_ready);
-    if (issuer && step + 1 < L) {             // the last step's dh_rec has no consumer
+    if (issuer_warp && step + 1 < L) {        // the last step's dh_rec has no consumer
       mbar_wait(z_ready, step & 1);
       tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
-      for (int kb = 0; kb < LB_KB; ++kb) {
+        for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
-        for (int k4 = 0; k4 < 4; ++k4) {
-          const uint64_t ad = smem_desc_sw128_k(w16, kb * 16384 + k4 * 32);
-          const uint64_t bd = smem_desc_sw128_k(z16, kb * (LT_NS * 128) + k4 * 32);
-          umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+          for (int k4 = 0; k4 < 4; ++k4) {
+            const uint64_t ad = smem_desc_sw128_k(w16, kb * 16384 + k4 * 32);
+            const uint64_t bd = smem_desc_sw128_k(z16, kb * (LT_NS * 128) + k4 * 32);
+            umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+          }
         }
+        umma_commit(mma_done);
       }
-      umma_commit(mma_done);
+      __syncwarp();
     }
   }
   __syncthreads();
@@ -450,6 +522,11 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ A, long lon
 
 using namespace indnet;
 
+#ifdef INDNET_LSTM_TIMELINE
+extern "C" int indnet_debug_lstm(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, g_lstm_dbg, sizeof(long long) * 512);
+}
+#endif
 extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                                   const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout,
                                   void* hout_bf, void* gates_bf, float* cstate, void* hprev_bf, int X, int L, int D,
@@ -492,19 +569,30 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   p.hout = hout; p.hout_bf = (__nv_bfloat16*)hout_bf;
   p.gates_bf = (__nv_bfloat16*)gates_bf;
   p.cstate = cstate; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
+  p.wt = (const __nv_bfloat16*)wt_scratch;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
-  static bool attr_set = false;
-  if (!attr_set) {
-    IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LT_SMEM));
-    attr_set = true;
-  }
   dim3 grid(ceil_div(X, LT_NS), 2);
-  tc_lstm_fwd_kernel<<<grid, LT_THREADS, LT_SMEM, st>>>(tmW, tmX, p);
+  const bool drop = keep_prob < 1.0f, h32 = hout != nullptr;
+#define LT_FWD_LAUNCH(DROP_, H32_)                                                                              \
+  do {                                                                                                          \
+    static bool attr_set = false;                                                                               \
+    if (!attr_set) {                                                                                            \
+      IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel<DROP_, H32_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   LT_SMEM));                                                                   \
+      attr_set = true;                                                                                          \
+    }                                                                                                           \
+    tc_lstm_fwd_kernel<DROP_, H32_><<<grid, LT_FWD_THREADS, LT_SMEM, st>>>(tmW, tmX, p);                          \
+  } while (0)
+  if (drop && h32) LT_FWD_LAUNCH(true, true);
+  else if (drop) LT_FWD_LAUNCH(true, false);
+  else if (h32) LT_FWD_LAUNCH(false, true);
+  else LT_FWD_LAUNCH(false, false);
+#undef LT_FWD_LAUNCH
   IN_LAUNCH_CHECK("tc_lstm_fwd_kernel");
   return INDNET_OK;
 }
 
-extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const float* dhout, const void* gates_bf, const float* cstate,
+extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const void* gates_bf, const float* cstate,
                                   const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D,
                                   int u, float keep_prob, unsigned long long seed, const long long* seed_step) {
   cudaStream_t st = (cudaStream_t)st_;
@@ -512,7 +600,7 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const float* dhout, const v
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_bwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
   IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_bwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(dhout && gates_bf && cstate && kernel_fw_bf && kernel_bw_bf && dz_bf, "lstm_bwd_tc: null pointer");
+  IN_REQUIRE(dhout_bf && gates_bf && cstate && kernel_fw_bf && kernel_bw_bf && dz_bf, "lstm_bwd_tc: null pointer");
   // W_h = rows D.. of the bf16 TF kernel [D+u][4u]
   CUtensorMap tmWf, tmWb;
   const __nv_bfloat16* wf = (const __nv_bfloat16*)kernel_fw_bf + (long long)D * 4 * LT_U;
@@ -522,7 +610,7 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const float* dhout, const v
   rc = make_tmap_bf16(&tmWb, wb, 4 * LT_U, LT_U, 4 * LT_U, 1, 0, 64, 128);
   if (rc) return rc;
   LstmTcBwdP p;
-  p.dhout = dhout; p.gates_bf = (const __nv_bfloat16*)gates_bf; p.cstate = cstate; p.dz_bf = (__nv_bfloat16*)dz_bf;
+  p.dhout = (const __nv_bfloat16*)dhout_bf; p.gates_bf = (const __nv_bfloat16*)gates_bf; p.cstate = cstate; p.dz_bf = (__nv_bfloat16*)dz_bf;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
   static bool attr_set = false;
   if (!attr_set) {

@@ -465,6 +465,7 @@ class EpisodePipeline:
             self.dehat_bf = h(c.B * c.NK, c.H)
             self.dpre_bf = h(c.T, c.H)
             self.dz_bf = h(2, c.T, 4 * c.u)
+            self.dhout_bf = h(c.T, c.H) if self.tc_lstm else None
         self._bwd_ready = True
 
     def backward(self):
@@ -557,16 +558,28 @@ class EpisodePipeline:
         self._cast(self.dehat, self.dehat_bf, "dehat")
         self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
         self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
+        # d(loss)/d(h): pooling path alpha_t * denc + Dense path dpre * W_a1^T.  With the tensor-core LSTM the
+        # sum is formed once in the GEMM epilogue and written in bf16; otherwise it is accumulated in fp32.
+        fused = self.tc_lstm
         self._call("indnet_attn_pool_bwd_bf16", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
-                   ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(self.dhout), ptr(self.dpre_bf), ptr(self.dw2_part),
-                   ptr(self.dba_part), c.X, c.L, c.H, c.n_s, c.NK)
+                   ptr(self.alphas), ptr(p.view(ATT_W2)), None if fused else ptr(self.dhout), ptr(self.dpre_bf),
+                   ptr(self.dw2_part), ptr(self.dba_part), c.X, c.L, c.H, c.n_s, c.NK)
         self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
         self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
         self._call("indnet_colsum", ptr(self.dba_part), c.X, c.H, c.H, ptr(p.grad(ATT_B)), 0)
-        self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
-                 splitk=1, tag="attn_dh")
+        if fused:
+            self._tag = "tc_gemm:attn_dh"
+            try:
+                self._call("indnet_tc_gemm_rank1", 0, 0, c.T, c.H, c.H, ptr(self.dpre_bf), c.H, ptr(p.view_bf(ATT_K)),
+                           c.H, None, ptr(self.dhout_bf), c.H, ptr(self.alphas), ptr(self.des), ptr(self.deq), c.L,
+                           c.n_s, c.NK)
+            finally:
+                self._tag = None
+        else:
+            self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
+                     splitk=1, tag="attn_dh")
         if self.tc_lstm:
-            self._call("indnet_lstm_bwd_tc", ptr(self.dhout), ptr(self.gates_bf), ptr(self.cstate),
+            self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate),
                        ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), c.X, c.L, c.D, c.u,
                        self._last_keep, self.seed, ptr(p.global_step))
         else:
