@@ -90,15 +90,43 @@ enum { SMP_OK = 0, SMP_SCOPE_TOO_SMALL = 1, SMP_SCOPE_TOO_LARGE = 2, SMP_STREAM_
 
 constexpr int TB = 64;     // draws per transition-table block
 
-// ---- kernel P: the Python stream (random.sample(range(R), N) per episode), one thread ------------
-__global__ void smp_python_kernel(uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
-                                  const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
-  __shared__ uint32_t pkey[MT_N];
+// ---- kernel G: both host streams, two CTAs ------------------------------------------------------
+// CTA 0: nb consecutive untempered MT19937 blocks of the NumPy stream.  keys[0..624) = the state handed
+// in; beyond that the flat recurrence x[n] = mix(x[n-624], x[n-623], x[n-227]) lets 224 consecutive words
+// be produced per round (one barrier each) out of a 1024-word shared ring.
+// CTA 1: the Python stream - random.sample(range(R), N) per episode, restated literally (pool / set
+// variants of CPython's Random.sample), one thread; then the permutation length of every job.
+constexpr int GEN_NT = 224;
+
+__global__ void __launch_bounds__(GEN_NT)
+smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ keys, int nb,
+               uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
+               const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
+  __shared__ uint32_t ring[1024];
+  const int tid = threadIdx.x;
+  if (blockIdx.x == 0) {
+    for (int k = tid; k < MT_N; k += GEN_NT) { const uint32_t v = np_state[k]; ring[k] = v; keys[k] = v; }
+    __syncthreads();
+    const long long total = (long long)nb * MT_N;
+    for (long long base = MT_N; base < total; base += GEN_NT) {
+      const long long n = base + tid;
+      if (n < total) {
+        const uint32_t v = mt_mix(ring[(n - MT_N) & 1023], ring[(n - MT_N + 1) & 1023], ring[(n - (MT_N - MT_M)) & 1023]);
+        ring[n & 1023] = v;
+        keys[n] = v;
+      }
+      __syncthreads();
+    }
+    return;
+  }
+  // ---- CTA 1
+  uint32_t* pkey = ring;                     // 624 words
   __shared__ int pool[1024];
   __shared__ uint32_t seen[32];
-  for (int i = threadIdx.x; i < MT_N; i += blockDim.x) pkey[i] = py_state[i];
+  for (int i = tid; i < MT_N; i += GEN_NT) pkey[i] = py_state[i];
+  for (int i = tid; i < R; i += GEN_NT) pool[i] = i;
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     SerialMT mt{pkey, (int)py_state[MT_N]};
     int setsize = 21;
     if (N > 5) {   // setsize += 4 ** ceil(log(N*3, 4))
@@ -109,12 +137,18 @@ __global__ void smp_python_kernel(uint32_t* __restrict__ py_state, int R, int B,
     for (int b = 0; b < B; ++b) {
       int* out = classes + (long long)b * N;
       if (R <= setsize) {
-        for (int i = 0; i < R; ++i) pool[i] = i;
+        // pool variant; the pool is restored after each episode instead of rebuilt (only the <= 2N
+        // entries the draws touched differ from the identity)
+        int touched[64];
+        int nt = 0;
         for (int i = 0; i < N; ++i) {
           const int j = mt.randbelow(R - i);
           out[i] = pool[j];
           pool[j] = pool[R - i - 1];
+          if (nt < 64) touched[nt++] = j;
         }
+        if (N <= 64) { for (int i = 0; i < nt; ++i) pool[touched[i]] = touched[i]; }
+        else { for (int i = 0; i < R; ++i) pool[i] = i; }
       } else {
         for (int i = 0; i < 32; ++i) seen[i] = 0u;
         for (int i = 0; i < N; ++i) {
@@ -128,10 +162,10 @@ __global__ void smp_python_kernel(uint32_t* __restrict__ py_state, int R, int B,
     py_state[MT_N] = (uint32_t)mt.pos;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < MT_N; i += blockDim.x) py_state[i] = pkey[i];
+  for (int i = tid; i < MT_N; i += GEN_NT) py_state[i] = pkey[i];
   // permutation length of every job of the walk (episode-major: N class scopes, then the N*Q query
   // permutation); negative = the error the walker reports when it reaches that job
-  for (int j = threadIdx.x; j < B * (N + 1); j += blockDim.x) {
+  for (int j = tid; j < B * (N + 1); j += GEN_NT) {
     const int b = j / (N + 1), ci = j % (N + 1);
     int n = N * Q;
     if (ci < N) {
@@ -141,32 +175,6 @@ __global__ void smp_python_kernel(uint32_t* __restrict__ py_state, int R, int B,
       else if (n > n_max) n = -SMP_SCOPE_TOO_LARGE;
     }
     jsize[j] = n;
-  }
-}
-
-// ---- kernel G: nb consecutive untempered MT19937 blocks of the NumPy stream ---------------------
-// keys[0] = the state handed in; keys[b] = twist(keys[b-1]).  One CTA: the twist is sequential across
-// blocks, 3-phase parallel inside one; blocks are twisted in shared memory and streamed out.
-__global__ void __launch_bounds__(SMP_NT)
-smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ keys, int nb) {
-  __shared__ uint32_t ring[2][MT_N];
-  const int tid = threadIdx.x;
-  for (int k = tid; k < MT_N; k += SMP_NT) { const uint32_t v = np_state[k]; ring[0][k] = v; keys[k] = v; }
-  __syncthreads();
-  for (int b = 1; b < nb; ++b) {
-    const uint32_t* o = ring[(b - 1) & 1];
-    uint32_t* w = ring[b & 1];
-    if (tid < 227) w[tid] = mt_mix(o[tid], o[tid + 1], o[tid + MT_M]);
-    __syncthreads();
-    if (tid < 227) w[tid + 227] = mt_mix(o[tid + 227], o[tid + 228], w[tid]);
-    __syncthreads();
-    if (tid < 170) {
-      const int k = tid + 454;
-      w[k] = mt_mix(o[k], (k + 1 < MT_N) ? o[k + 1] : w[0], w[k - 227]);
-    }
-    __syncthreads();
-    uint32_t* dst = keys + (long long)b * MT_N;
-    for (int k = tid; k < MT_N; k += SMP_NT) dst[k] = w[k];
   }
 }
 
@@ -500,14 +508,14 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   const double e = (double)B * ((double)N * expected_draws(n_max) + expected_draws((long long)N * Q));
   const long long budget = (long long)(e * 1.03) + 8192 + MT_N;
   L.nblk = (budget + TB - 1) / TB;
-  L.nblk = (L.nblk + 7) / 8 * 8;                      // whole chunks for every chunk size the walker may pick
+  L.nblk = (L.nblk + 15) / 16 * 16;                      // whole chunks for every chunk size the walker may pick
   L.nb = (L.nblk * TB + MT_N - 1) / MT_N + 1;
   // walker staging ring: the largest chunk / ring that fits in 200 KB of shared memory
   const long long per_block = rec_bytes(L.n_states);
-  static const int opts[5][2] = {{3, 3}, {2, 3}, {1, 3}, {0, 3}, {0, 2}};
+  static const int opts[6][2] = {{4, 2}, {3, 2}, {2, 3}, {1, 3}, {0, 3}, {0, 2}};
   L.cb_log = L.rc_log = -1;
   L.smem_bytes = 0;
-  for (int k = 0; k < 5; ++k) {
+  for (int k = 0; k < 6; ++k) {
     const long long need = (((per_block << opts[k][0]) + 8) << opts[k][1]) + 128;
     if (need <= 200 * 1024) { L.cb_log = opts[k][0]; L.rc_log = opts[k][1]; L.smem_bytes = need; break; }
   }
@@ -556,9 +564,7 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
     IN_CUDA(cudaFuncSetAttribute(smp_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     if (dev >= 0 && dev < 64) smem_set[dev] = true;
   }
-  smp_python_kernel<<<1, 128, 0, st>>>(py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
-  IN_LAUNCH_CHECK("smp_python_kernel");
-  smp_gen_kernel<<<1, SMP_NT, 0, st>>>(np_state, keys, (int)L.nb);
+  smp_gen_kernel<<<2, GEN_NT, 0, st>>>(np_state, keys, (int)L.nb, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
   IN_LAUNCH_CHECK("smp_gen_kernel");
   smp_table_kernel<<<(unsigned)L.nblk, 256, 0, st>>>(keys, tab, (int)L.n_states);
   IN_LAUNCH_CHECK("smp_table_kernel");
