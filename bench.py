@@ -360,6 +360,10 @@ def run_b200(args, w):
     if rank == 0:
         # dominant call of the step and its roofline
         dom = max(prof.items(), key=lambda kv: kv[1][1])
+        if os.environ.get("INDNET_SHARES_OUT"):        # full per-call table of the eager profile leg (tuning aid)
+            with open(os.environ["INDNET_SHARES_OUT"], "w") as f:
+                json.dump({k: {"calls": v[0], "ms_total": v[1], "ms_per_call": v[1] / v[0], "ms_per_step": v[1] / prof_steps}
+                           for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}, f, indent=1)
         share = {k: round(v[1] / sum(x[1] for x in prof.values()), 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])[:8]}
         dom_ms = dom[1][1] / dom[1][0]
         calls_per_step = dom[1][0] / prof_steps

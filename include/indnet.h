@@ -143,10 +143,12 @@ int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_f
 /* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] bf16 and cstate
  * fp32 as saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h
  * = rows D.., read in place by TMA, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
- * Writes dz_bf [2][X][L][4u] bf16. */
+ * Writes dz_bf [2][X][L][4u] bf16 and, when dbias_fw / dbias_bw [4u] are given, the two LSTM bias
+ * gradients (fp32 column sums of dz, formed in registers before the bf16 rounding). */
 int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const float* cstate,
-                       const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D, int u,
-                       float keep_prob, unsigned long long seed, const long long* seed_step);
+                       const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
+                       float* dbias_bw, int X, int L, int D, int u, float keep_prob, unsigned long long seed,
+                       const long long* seed_step);
 /* out[c] = sum_r A[r][c] for a dense bf16 matrix [rows][cols] (bias gradients from the bf16 dz stream). */
 int indnet_colsum_bf16(indnet_stream st, const void* A, long long rows, int cols, float* out);
 

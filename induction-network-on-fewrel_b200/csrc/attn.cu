@@ -129,6 +129,163 @@ attn_pool_bwd_kernel(const float* __restrict__ denc_a, const float* __restrict__
   }
 }
 
+
+// ---- bf16 tensor-core mode, H a multiple of 8: the same math with 16-byte accesses.  A warp reads a whole
+// row of 256 features with one load instruction (8 bf16 per lane); the sums over time run as 8 groups of
+// time steps in parallel (thread = (time group, 8-feature chunk)) and meet in shared memory.
+__device__ __forceinline__ void unpack8(const uint4& q, float* f) {
+  f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xFFFF0000u);
+  f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xFFFF0000u);
+  f[4] = __uint_as_float(q.z << 16); f[5] = __uint_as_float(q.z & 0xFFFF0000u);
+  f[6] = __uint_as_float(q.w << 16); f[7] = __uint_as_float(q.w & 0xFFFF0000u);
+}
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+constexpr int ATT_TG = ATT_NT / 32;      // time groups
+
+__global__ void __launch_bounds__(ATT_NT)
+attn_pool_fwd_v8_kernel(const __nv_bfloat16* __restrict__ hout, const __nv_bfloat16* __restrict__ proj,
+                        const int* __restrict__ mask, const float* __restrict__ w2, float* __restrict__ enc_a,
+                        float* __restrict__ enc_b, float* __restrict__ alphas, int L, int H, int group, int split) {
+  extern __shared__ float sm[];   // sc[L] | red[ATT_TG][H]
+  float* sc = sm;
+  float* red = sm + L;
+  const int x = blockIdx.x;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int chunks = H / 8;
+  const uint4* pj = reinterpret_cast<const uint4*>(proj + (long long)x * L * H);
+  const uint4* hp = reinterpret_cast<const uint4*>(hout + (long long)x * L * H);
+  for (int t = warp; t < L; t += ATT_TG) {
+    float s = 0.f;
+    for (int c = lane; c < chunks; c += 32) {
+      float f[8];
+      unpack8(pj[(long long)t * chunks + c], f);
+      const float* w = w2 + c * 8;          // parameter views are only 4-byte aligned
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s = fmaf(f[j], w[j], s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) {
+      const float m = mask[(long long)x * L + t] > 0 ? 1.0f : 0.0f;
+      sc[t] = s + (1.0f - m) * (-2147483648.0f);
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float mx = -INFINITY;
+    for (int t = lane; t < L; t += 32) mx = fmaxf(mx, sc[t]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int t = lane; t < L; t += 32) {
+      float e = expf(sc[t] - mx);
+      sc[t] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+    for (int t = lane; t < L; t += 32) {
+      float a = sc[t] * inv;
+      sc[t] = a;
+      alphas[(long long)x * L + t] = a;
+    }
+  }
+  __syncthreads();
+  for (int c = lane; c < chunks; c += 32) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int t = warp; t < L; t += ATT_TG) {
+      float f[8];
+      unpack8(hp[(long long)t * chunks + c], f);
+      const float a = sc[t];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaf(a, f[j], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp * H + c * 8 + j] = acc[j];
+  }
+  __syncthreads();
+  float* enc = split_row(enc_a, enc_b, x, group, split, H);
+  for (int h = threadIdx.x; h < H; h += ATT_NT) {
+    float acc = 0.f;
+#pragma unroll
+    for (int g = 0; g < ATT_TG; ++g) acc += red[g * H + h];
+    enc[h] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(ATT_NT)
+attn_pool_bwd_v8_kernel(const float* __restrict__ denc_a, const float* __restrict__ denc_b,
+                        const __nv_bfloat16* __restrict__ hout, const __nv_bfloat16* proj /* may alias dpre */,
+                        const float* __restrict__ alphas, const float* __restrict__ w2, float* __restrict__ dhout,
+                        __nv_bfloat16* dpre, float* __restrict__ dw2_part, float* __restrict__ dsum_part, int L, int H,
+                        int group, int split) {
+  extern __shared__ float sm[];   // dsc[L] | al[L] | red_w[ATT_TG][H] | red_s[ATT_TG][H]
+  float* dsc = sm;
+  float* al = sm + L;
+  float* red_w = sm + 2 * L;
+  float* red_s = red_w + ATT_TG * H;
+  const int x = blockIdx.x;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int chunks = H / 8;
+  const uint4* hp = reinterpret_cast<const uint4*>(hout + (long long)x * L * H);
+  const uint4* pj = reinterpret_cast<const uint4*>(proj + (long long)x * L * H);
+  uint4* dp4 = reinterpret_cast<uint4*>(dpre + (long long)x * L * H);
+  const float* de = split_row(denc_a, denc_b, x, group, split, H);
+  for (int t = warp; t < L; t += ATT_TG) {
+    float s = 0.f;
+    for (int c = lane; c < chunks; c += 32) {
+      float f[8];
+      unpack8(hp[(long long)t * chunks + c], f);
+      const float4 da = *reinterpret_cast<const float4*>(de + c * 8), db = *reinterpret_cast<const float4*>(de + c * 8 + 4);
+      s += f[0] * da.x + f[1] * da.y + f[2] * da.z + f[3] * da.w + f[4] * db.x + f[5] * db.y + f[6] * db.z + f[7] * db.w;
+    }
+    s = warp_sum(s);
+    if (lane == 0) { dsc[t] = s; al[t] = alphas[(long long)x * L + t]; }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float dot = 0.f;
+    for (int t = lane; t < L; t += 32) dot = fmaf(al[t], dsc[t], dot);
+    dot = warp_sum(dot);
+    for (int t = lane; t < L; t += 32) dsc[t] = al[t] * (dsc[t] - dot);
+  }
+  __syncthreads();
+  for (int c = lane; c < chunks; c += 32) {
+    float w[8], g[8], dw[8], ds[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { w[j] = w2[c * 8 + j]; g[j] = de[c * 8 + j]; dw[j] = 0.f; ds[j] = 0.f; }
+    for (int t = warp; t < L; t += ATT_TG) {
+      float pr[8], dp[8];
+      unpack8(pj[(long long)t * chunks + c], pr);
+      const float d = dsc[t];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        dp[j] = d * w[j] * (1.0f - pr[j] * pr[j]);
+        dw[j] = fmaf(d, pr[j], dw[j]);
+        ds[j] += dp[j];
+      }
+      dp4[(long long)t * chunks + c] = make_uint4(pack2(dp[0], dp[1]), pack2(dp[2], dp[3]), pack2(dp[4], dp[5]), pack2(dp[6], dp[7]));
+      if (dhout) {
+        const float a = al[t];
+        float4* o = reinterpret_cast<float4*>(dhout + ((long long)x * L + t) * H + c * 8);
+        o[0] = make_float4(a * g[0], a * g[1], a * g[2], a * g[3]);
+        o[1] = make_float4(a * g[4], a * g[5], a * g[6], a * g[7]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { red_w[warp * H + c * 8 + j] = dw[j]; red_s[warp * H + c * 8 + j] = ds[j]; }
+  }
+  __syncthreads();
+  for (int h = threadIdx.x; h < H; h += ATT_NT) {
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int g = 0; g < ATT_TG; ++g) { a += red_w[g * H + h]; b += red_s[g * H + h]; }
+    dw2_part[(long long)x * H + h] = a;
+    if (dsum_part) dsum_part[(long long)x * H + h] = b;   // Dense-bias gradient partial, summed in fp32
+  }
+}
+
 }  // namespace indnet
 
 using namespace indnet;
@@ -174,6 +331,14 @@ extern "C" int indnet_attn_pool_fwd_bf16(indnet_stream st_, const void* hout_bf,
   IN_REQUIRE(hout_bf && proj_bf && mask && w_a2 && enc_a && alphas, "attn_pool_fwd_bf16: null pointer");
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_pool_fwd_bf16: bad group/split %d/%d", group, split);
   IN_REQUIRE(split == group || enc_b, "attn_pool_fwd_bf16: second output missing");
+  const bool v8 = H % 8 == 0 && (((uintptr_t)hout_bf | (uintptr_t)proj_bf) & 15) == 0 &&
+                  sizeof(float) * (L + ATT_TG * H) <= 48 * 1024;
+  if (v8) {
+    attn_pool_fwd_v8_kernel<<<X, ATT_NT, sizeof(float) * (L + ATT_TG * H), st>>>(
+        (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, mask, w_a2, enc_a, enc_b, alphas, L, H, group, split);
+    IN_LAUNCH_CHECK("attn_pool_fwd_v8_kernel");
+    return INDNET_OK;
+  }
   attn_pool_fwd_kernel<__nv_bfloat16><<<X, ATT_NT, sizeof(float) * L, st>>>(
       (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, mask, w_a2, enc_a, enc_b, alphas, L, H, group, split);
   IN_LAUNCH_CHECK("attn_pool_fwd_kernel<bf16>");
@@ -190,6 +355,17 @@ extern "C" int indnet_attn_pool_bwd_bf16(indnet_stream st_, const float* denc_a,
   IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && dpre_bf && dw2_part, "attn_pool_bwd_bf16: null pointer");
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_pool_bwd_bf16: bad group/split %d/%d", group, split);
   IN_REQUIRE(split == group || denc_b, "attn_pool_bwd_bf16: second gradient input missing");
+  const size_t v8_smem = sizeof(float) * (2 * L + 2 * ATT_TG * H);
+  const bool v8 = H % 8 == 0 && v8_smem <= 48 * 1024 &&
+                  (((uintptr_t)hout_bf | (uintptr_t)proj_bf | (uintptr_t)dpre_bf | (uintptr_t)denc_a |
+                    (uintptr_t)denc_b | (uintptr_t)dhout) & 15) == 0;
+  if (v8) {
+    attn_pool_bwd_v8_kernel<<<X, ATT_NT, v8_smem, st>>>(denc_a, denc_b, (const __nv_bfloat16*)hout_bf,
+                                                        (const __nv_bfloat16*)proj_bf, alphas, w_a2, dhout,
+                                                        (__nv_bfloat16*)dpre_bf, dw2_part, dsum_part, L, H, group, split);
+    IN_LAUNCH_CHECK("attn_pool_bwd_v8_kernel");
+    return INDNET_OK;
+  }
   attn_pool_bwd_kernel<__nv_bfloat16><<<X, ATT_NT, sizeof(float) * 2 * L, st>>>(
       denc_a, denc_b, (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, alphas, w_a2, dhout,
       (__nv_bfloat16*)dpre_bf, dw2_part, dsum_part, L, H, group, split);

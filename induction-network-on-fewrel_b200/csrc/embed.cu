@@ -103,7 +103,7 @@ extern "C" int indnet_embed_bwd(indnet_stream st_, const int* word, const int* p
   IN_REQUIRE(pos1 && pos2 && dx && dpos1 && dpos2, "embed_bwd: null pointer");
   size_t smem = sizeof(float) * 2 * pos_rows * P;
   IN_REQUIRE(smem <= 48 * 1024, "embed_bwd: position tables too large for the shared-memory accumulator (%zu B)", smem);
-  long long tpb = 2048;
+  long long tpb = 512;        // ~150 CTAs at 77k tokens; each flushes its shared-memory tables once
   int blocks = ceil_div(T, tpb);
   embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx, dpos1, dpos2, T, E, P, pos_rows, tpb);
   IN_LAUNCH_CHECK("embed_pos_bwd_kernel");

@@ -332,6 +332,7 @@ constexpr int LB_SMEM = LB_W_BYTES + LB_Z_BYTES + 256 + 1024;
 
 struct LstmTcBwdP {
   const __nv_bfloat16* dhout; const __nv_bfloat16* gates_bf; const float* cstate; __nv_bfloat16* dz_bf;
+  float* dbias_fw; float* dbias_bw;     // optional: bias gradients (column sums of dz), accumulated with atomics
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
@@ -396,6 +397,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
     qoff[q] = ok ? q : (p.X - 1 - xs0);
     live[q] = ok ? 1.f : 0.f;
   }
+  float sb_i = 0.f, sb_j = 0.f, sb_f = 0.f, sb_o = 0.f;     // this unit's bias-gradient partial sums
   float dcr[LT_SPT], cc[LT_SPT];
   {
     const int t_first = dir ? 0 : (L - 1);      // time index of the first step processed here
@@ -460,6 +462,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       const float df = dc * cp[q] * gf * (1.f - gf);
       dcr[q] = dc * gf;
       cc[q] = cp[q];                        // c_{t_prev} is the cell state of the next step processed
+      sb_i += di; sb_j += dj; sb_f += df; sb_o += dob;
       const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
                           bo = __float2bfloat16(dob);
       const uint32_t zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
@@ -492,6 +495,10 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
       }
       __syncwarp();
     }
+  }
+  if (p.dbias_fw) {
+    float* db = dir ? p.dbias_bw : p.dbias_fw;
+    atomicAdd(db + m, sb_i); atomicAdd(db + LT_U + m, sb_j); atomicAdd(db + 2 * LT_U + m, sb_f); atomicAdd(db + 3 * LT_U + m, sb_o);
   }
   __syncthreads();
   if (warp == 0) tmem_dealloc(taddr, LT_NS);
@@ -593,8 +600,9 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
 }
 
 extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const void* gates_bf, const float* cstate,
-                                  const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, int X, int L, int D,
-                                  int u, float keep_prob, unsigned long long seed, const long long* seed_step) {
+                                  const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
+                                  float* dbias_bw, int X, int L, int D, int u, float keep_prob,
+                                  unsigned long long seed, const long long* seed_step) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0, "lstm_bwd_tc: bad sizes X=%d L=%d", X, L);
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_bwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
@@ -612,6 +620,12 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   LstmTcBwdP p;
   p.dhout = (const __nv_bfloat16*)dhout_bf; p.gates_bf = (const __nv_bfloat16*)gates_bf; p.cstate = cstate; p.dz_bf = (__nv_bfloat16*)dz_bf;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
+  IN_REQUIRE((dbias_fw == nullptr) == (dbias_bw == nullptr), "lstm_bwd_tc: pass both bias gradients or neither");
+  p.dbias_fw = dbias_fw; p.dbias_bw = dbias_bw;
+  if (dbias_fw) {
+    IN_CUDA(cudaMemsetAsync(dbias_fw, 0, sizeof(float) * 4 * LT_U, st));
+    IN_CUDA(cudaMemsetAsync(dbias_bw, 0, sizeof(float) * 4 * LT_U, st));
+  }
   static bool attr_set = false;
   if (!attr_set) {
     IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));

@@ -580,8 +580,8 @@ class EpisodePipeline:
                      splitk=1, tag="attn_dh")
         if self.tc_lstm:
             self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate),
-                       ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), c.X, c.L, c.D, c.u,
-                       self._last_keep, self.seed, ptr(p.global_step))
+                       ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), ptr(p.grad(FW_B)),
+                       ptr(p.grad(BW_B)), c.X, c.L, c.D, c.u, self._last_keep, self.seed, ptr(p.global_step))
         else:
             wh_fw = p.view(FW_K)[c.D:]
             wh_bw = p.view(BW_K)[c.D:]
@@ -593,7 +593,8 @@ class EpisodePipeline:
             gk = p.grad(kn)
             self._tc(1, 1, c.D, u4, c.T, self.x_bf, 64, self.dz_bf[d], u4, C=gk, tag="lstm_dWx")
             self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
-            self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))
+            if not self.tc_lstm:
+                self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))
             self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
                      C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
         g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
