@@ -133,19 +133,19 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
  * E+10 <= 64): x_bf [X][L][64] bf16 zero-padded embeddings (indnet_embed_fwd_bf16), kernel_* the TF
  * LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch: caller-provided bf16 [2][4u][192] (packed
  * transposed weights, rebuilt every call).  Writes hout_bf [X][L][2u] bf16 (and hout fp32 when not
- * NULL), and for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate
- * [2][X][L][u] fp32, hprev_bf [2][X][L][u] bf16. */
+ * NULL), and for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate_bf
+ * [2][X][L][u] bf16 (the recurrence itself carries c in fp32 registers), hprev_bf [2][X][L][u] bf16. */
 int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                        const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout, void* hout_bf,
-                       void* gates_bf, float* cstate, void* hprev_bf, int X, int L, int D, int u, float keep_prob,
+                       void* gates_bf, void* cstate_bf, void* hprev_bf, int X, int L, int D, int u, float keep_prob,
                        unsigned long long seed, const long long* seed_step);
 
-/* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] bf16 and cstate
- * fp32 as saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h
- * = rows D.., read in place by TMA, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
+/* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] and cstate_bf as
+ * saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h = rows
+ * D.., staged into tensor memory, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
  * Writes dz_bf [2][X][L][4u] bf16 and, when dbias_fw / dbias_bw [4u] are given, the two LSTM bias
  * gradients (fp32 column sums of dz, formed in registers before the bf16 rounding). */
-int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const float* cstate,
+int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const void* cstate_bf,
                        const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
                        float* dbias_bw, int X, int L, int D, int u, float keep_prob, unsigned long long seed,
                        const long long* seed_step);

@@ -76,7 +76,7 @@ struct LstmTcP {
   const float* bias_fw; const float* bias_bw;
   float* hout; __nv_bfloat16* hout_bf;
   __nv_bfloat16* gates_bf;      // [2][X][L][u][4]  (i, j, f, o of a unit adjacent: one 8-byte store / load)
-  float* cstate;                // [2][X][L][u]
+  __nv_bfloat16* cstate;        // [2][X][L][u]
   __nv_bfloat16* hprev_bf;      // [2][X][L][u]
   const __nv_bfloat16* wt;      // packed weights WT[dir][4u][192] (lstm_pack_weights_kernel)
   int X, L;
@@ -262,7 +262,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const long long ostep = dir ? -(long long)(2 * LT_U) : (long long)(2 * LT_U);
     const uint32_t qe = (uint32_t)L * LT_U, qo = (uint32_t)L * 2 * LT_U;                // elements between sentences
     char* g_ptr = reinterpret_cast<char*>(p.gates_bf) + e0 * 8;
-    char* c_ptr = reinterpret_cast<char*>(p.cstate) + e0 * 4;
+    char* c_ptr = reinterpret_cast<char*>(p.cstate) + e0 * 2;
     char* hp_ptr = reinterpret_cast<char*>(p.hprev_bf) + e0 * 2;
     char* ob_ptr = reinterpret_cast<char*>(p.hout_bf) + o0 * 2;
     char* of_ptr = reinterpret_cast<char*>(p.hout) + o0 * 4;
@@ -274,44 +274,47 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       __syncwarp();
       tc_fence_after();
       LT_MARK(threadIdx.x == 0, s, 1);
-      float zi[LT_SPT], zj[LT_SPT], zf[LT_SPT], zo[LT_SPT];
       const uint32_t lane_addr = lane_addr0 + (s & 1) * (4 * LT_NS);
-      tmem_ld_spt(lane_addr + 0 * LT_NS, zi);
-      tmem_ld_spt(lane_addr + 1 * LT_NS, zj);
-      tmem_ld_spt(lane_addr + 2 * LT_NS, zf);
-      tmem_ld_spt(lane_addr + 3 * LT_NS, zo);
-      tmem_ld_wait();
-      LT_MARK(threadIdx.x == 0, s, 2);
+      // two halves of 4 sentences: halves the live accumulator registers of the gate math
 #pragma unroll
-      for (int q = 0; q < LT_SPT; ++q) {
-        const int sl = hf * LT_SPT + q;
-        const float gi = sigmoid_fast(zi[q] + bi);
-        const float gj = tanh_fast(zj[q] + bj);
-        const float gf = sigmoid_fast(zf[q] + bf);
-        const float go = sigmoid_fast(zo[q] + bo);
-        const float cn = fmaf(c[q], gf, gi * gj);
-        const float h = tanh_fast(cn) * go;
-        c[q] = cn;
-        // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
-        sts_bf16(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4), __float2bfloat16(h));
-        if (valid & (1u << q)) {
-          const unsigned long long eq = (unsigned long long)qe * (uint32_t)q, oq = (unsigned long long)qo * (uint32_t)q;
-          *reinterpret_cast<uint2*>(g_ptr + eq * 8) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
-          *reinterpret_cast<float*>(c_ptr + eq * 4) = cn;
-          *reinterpret_cast<__nv_bfloat16*>(hp_ptr + eq * 2) = __float2bfloat16(hp[q]);
-          float ho = h;
-          if (DROP) ho = dropout_keep(seed, (unsigned long long)(oi + (long long)oq), p.keep_prob) ? h * inv_keep : 0.f;
-          if (HOUT32) *reinterpret_cast<float*>(of_ptr + oq * 4) = ho;
-          *reinterpret_cast<__nv_bfloat16*>(ob_ptr + oq * 2) = __float2bfloat16(ho);
+      for (int half = 0; half < LT_SPT / 4; ++half) {
+        float zi[4], zj[4], zf[4], zo[4];
+        tmem_ld4(lane_addr + 0 * LT_NS + half * 4, zi);
+        tmem_ld4(lane_addr + 1 * LT_NS + half * 4, zj);
+        tmem_ld4(lane_addr + 2 * LT_NS + half * 4, zf);
+        tmem_ld4(lane_addr + 3 * LT_NS + half * 4, zo);
+        tmem_ld_wait();
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          const int q = half * 4 + qq;
+          const int sl = hf * LT_SPT + q;
+          const float gi = sigmoid_fast(zi[qq] + bi);
+          const float gj = tanh_fast(zj[qq] + bj);
+          const float gf = sigmoid_fast(zf[qq] + bf);
+          const float go = sigmoid_fast(zo[qq] + bo);
+          const float cn = fmaf(c[q], gf, gi * gj);
+          const float h = tanh_fast(cn) * go;
+          c[q] = cn;
+          // next step's B operand: row = sentence, 16-byte chunk XOR (row & 7)
+          sts_bf16(hdst + sl * 128 + ((hchunk ^ (uint32_t)(sl & 7)) << 4), __float2bfloat16(h));
+          if (valid & (1u << q)) {
+            const unsigned long long eq = (unsigned long long)qe * (uint32_t)q, oq = (unsigned long long)qo * (uint32_t)q;
+            *reinterpret_cast<uint2*>(g_ptr + eq * 8) = make_uint2(pack_bf16x2(gi, gj), pack_bf16x2(gf, go));
+            *reinterpret_cast<__nv_bfloat16*>(c_ptr + eq * 2) = __float2bfloat16(cn);
+            *reinterpret_cast<__nv_bfloat16*>(hp_ptr + eq * 2) = __float2bfloat16(hp[q]);
+            float ho = h;
+            if (DROP) ho = dropout_keep(seed, (unsigned long long)(oi + (long long)oq), p.keep_prob) ? h * inv_keep : 0.f;
+            if (HOUT32) *reinterpret_cast<float*>(of_ptr + oq * 4) = ho;
+            *reinterpret_cast<__nv_bfloat16*>(ob_ptr + oq * 2) = __float2bfloat16(ho);
+          }
+          hp[q] = h;
         }
-        hp[q] = h;
       }
-      LT_MARK(threadIdx.x == 0, s, 3);
       fence_proxy_async();      // h stores -> visible to the MMA's shared-memory reads
       tc_fence_before();        // TMEM loads ordered before the next step's MMAs overwrite the columns
       mbar_arrive(h_ready);
       LT_MARK(threadIdx.x == 0, s, 4);
-      g_ptr += estep * 8; c_ptr += estep * 4; hp_ptr += estep * 2; ob_ptr += ostep * 2; of_ptr += ostep * 4; oi += ostep;
+      g_ptr += estep * 8; c_ptr += estep * 2; hp_ptr += estep * 2; ob_ptr += ostep * 2; of_ptr += ostep * 4; oi += ostep;
     }
   }
   __syncthreads();
@@ -321,164 +324,78 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 // ------------------------------------------------------------------------------------------------
 // BPTT, bf16 tensor-core mode.  Per step (reverse processing order) and tile of NS sentences:
 //     dh_rec^T[u, NS] = W_h[u, 4u] * dz^T[4u, NS]
-// A = W_h exactly as the TF kernel stores it (rows D.. of [D+u][4u], K-major over the 4u gate columns):
-// eight 64-wide K-blocks loaded once by TMA (128 KB resident).  B = dz of the step, written by the
-// gate-gradient threads (bf16, swizzled).  dh_rec comes back through TMEM (NS columns); dc_rec stays
-// in registers.  dz is also streamed to HBM in bf16 for the weight-gradient GEMMs.
+// A = W_h exactly as the TF kernel stores it (rows D.. of [D+u][4u], K-major over the 4u gate columns),
+// staged ONCE into tensor memory (lane = hidden unit, 256 packed columns), so the step's 32 MMAs run at
+// the math rate.  B = dz of the step, written by the gate-gradient threads (bf16, swizzled shared
+// memory).  dh_rec comes back through TMEM (NS columns); dc_rec stays in registers.  dz is also streamed
+// to HBM in bf16 for the weight-gradient GEMMs, and its column sums (bias gradients) are formed here.
+// Warps 0-15: gate-gradient threads; warp 16: MMA issuer.
 constexpr int LB_KB = 4 * LT_U / 64;                           // 8 K-blocks
-constexpr int LB_W_BYTES = LB_KB * 128 * 128;                  // 131072
 constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                // 32768
-constexpr int LB_SMEM = LB_W_BYTES + LB_Z_BYTES + 256 + 1024;
+constexpr int LB_SMEM = LB_Z_BYTES + 256 + 1024;
+constexpr int LB_THREADS = LT_THREADS + 32;
 
 struct LstmTcBwdP {
-  const __nv_bfloat16* dhout; const __nv_bfloat16* gates_bf; const float* cstate; __nv_bfloat16* dz_bf;
+  const __nv_bfloat16* dhout; const __nv_bfloat16* gates_bf; const __nv_bfloat16* cstate; __nv_bfloat16* dz_bf;
+  const __nv_bfloat16* wh_fw; const __nv_bfloat16* wh_bw;     // W_h = rows D.. of the bf16 TF kernels, [u][4u]
   float* dbias_fw; float* dbias_bw;     // optional: bias gradients (column sums of dz), accumulated with atomics
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
 
-__global__ void __launch_bounds__(LT_THREADS, 1)
-tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_constant__ CUtensorMap tmWb, LstmTcBwdP p) {
+template <bool DROP>
+__global__ void __launch_bounds__(LB_THREADS, 1)
+tc_lstm_bwd_kernel(LstmTcBwdP p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sW = smem;                                   // [8 kb][128 rows][128 B]
-  uint8_t* sZ = smem + LB_W_BYTES;                      // [8 kb][NS rows][128 B]
-  uint64_t* w_full = reinterpret_cast<uint64_t*>(sZ + LB_Z_BYTES);
-  uint64_t* mma_done = w_full + 1;
+  uint8_t* sZ = smem;                                   // [8 kb][NS rows][128 B]
+  uint64_t* mma_done = reinterpret_cast<uint64_t*>(sZ + LB_Z_BYTES);
   uint64_t* z_ready = mma_done + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_ready + 1);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const bool issuer_warp = warp == 0;       // converged warp 0 issues the MMAs, one elected lane (see the forward kernel)
-  const bool issuer = threadIdx.x == 0;
+  const bool gate_warp = warp < LT_THREADS / 32;
   const int dir = blockIdx.y;
   const int x0 = blockIdx.x * LT_NS;
   const int L = p.L;
-  unsigned long long seed = p.seed;
-  if (p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
-  const CUtensorMap* tmW = dir ? &tmWb : &tmWf;
 
-  if (issuer) {
-    tma_prefetch_desc(tmW);
-    mbar_init(w_full, 1);
+  if (threadIdx.x == 0) {
     mbar_init(mma_done, 1);
     mbar_init(z_ready, LT_THREADS);
     fence_barrier_init();
   }
   __syncwarp();
-  if (warp == 0) tmem_alloc(tmem_slot, LT_NS);
+  if (warp == 0) tmem_alloc(tmem_slot, 512);            // W_h: 256 columns, dh_rec accumulator: NS columns
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
+  const uint32_t wh_t = taddr, acc_t = taddr + 2 * LT_U;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
-  const uint32_t w16 = smem_u32(sW) >> 4, z16 = smem_u32(sZ) >> 4;
-  if (issuer) {
-    mbar_expect_tx(w_full, LB_W_BYTES);
-    for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sW + kb * 16384, tmW, w_full, kb * 64, 0, 0);
+  const uint32_t z16 = smem_u32(sZ) >> 4;
+  if (gate_warp) {
+    // stage W_h: warp w writes lane quarter w % 4, k range [(w / 4) * 128, +128) = 64 packed columns
+    const int kq = warp >> 2, row = (warp & 3) * 32 + lane;
+    const uint4* src = reinterpret_cast<const uint4*>((dir ? p.wh_bw : p.wh_fw) + (long long)row * (4 * LT_U) + kq * LT_U);
+    const uint32_t dst = wh_t + ((uint32_t)((warp & 3) * 32) << 16) + kq * (LT_U / 2);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[16];
+#pragma unroll
+      for (int v = 0; v < 4; ++v) {
+        const uint4 q = src[c * 4 + v];
+        r[v * 4 + 0] = q.x; r[v * 4 + 1] = q.y; r[v * 4 + 2] = q.z; r[v * 4 + 3] = q.w;
+      }
+      tmem_st16(dst + c * 16, r);
+    }
+    tmem_st_wait();
   }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
-  const int m = (warp & 3) * 32 + lane;
-  const int hf = warp >> 2;
-  const uint32_t lane_addr = taddr + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
-  const float inv_keep = 1.0f / p.keep_prob;
-  const bool drop = p.keep_prob < 1.0f;
-  // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
-  const uint32_t zdst = smem_u32(sZ) + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
-  const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
-  const int xs0 = x0 + hf * LT_SPT;
-  const int tok_base = (dir * p.X + xs0) * L;
-  // out-of-range sentences of the last tile read sentence X-1 (any valid address) and are zeroed via dh
-  int qoff[LT_SPT];
-  float live[LT_SPT];
-#pragma unroll
-  for (int q = 0; q < LT_SPT; ++q) {
-    const bool ok = xs0 + q < p.X;
-    qoff[q] = ok ? q : (p.X - 1 - xs0);
-    live[q] = ok ? 1.f : 0.f;
-  }
-  float sb_i = 0.f, sb_j = 0.f, sb_f = 0.f, sb_o = 0.f;     // this unit's bias-gradient partial sums
-  float dcr[LT_SPT], cc[LT_SPT];
-  {
-    const int t_first = dir ? 0 : (L - 1);      // time index of the first step processed here
-#pragma unroll
-    for (int q = 0; q < LT_SPT; ++q) {
-      dcr[q] = 0.f;
-      cc[q] = p.cstate[(long long)(tok_base + qoff[q] * L + t_first) * LT_U + m];
-    }
-  }
-
-  for (int step = 0; step < L; ++step) {
-    const int pstep = L - 1 - step;
-    const int t = dir ? (L - 1 - pstep) : pstep;
-    const int tprev = dir ? (t + 1) : (t - 1);
-    // ---- this step's saved activations: every load is issued before anything waits on them
-    uint2 gw[LT_SPT];
-    float dh[LT_SPT], cp[LT_SPT];
-#pragma unroll
-    for (int q = 0; q < LT_SPT; ++q) {
-      const int tokq = tok_base + qoff[q] * L;
-      const long long e = (long long)(tokq + t) * LT_U + m;
-      gw[q] = *reinterpret_cast<const uint2*>(p.gates_bf + e * 4);
-      dh[q] = __bfloat162float(p.dhout[((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m]);
-      cp[q] = (pstep > 0) ? p.cstate[(long long)(tokq + tprev) * LT_U + m] : 0.f;
-    }
-    if (step > 0) {
-      float dhr[LT_SPT];
-      mbar_wait(mma_done, (step - 1) & 1);
-      __syncwarp();
-      tc_fence_after();
-      tmem_ld_spt(lane_addr, dhr);
-      tmem_ld_wait();
-#pragma unroll
-      for (int q = 0; q < LT_SPT; ++q) {
-        // dropout acts on the external gradient only; the recurrent part is added after it
-        if (drop) {
-          const long long oi = ((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m;
-          dh[q] = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? dh[q] * inv_keep : 0.f;
-        }
-        dh[q] = (dh[q] + dhr[q]) * live[q];
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < LT_SPT; ++q) {
-        if (drop) {
-          const long long oi = ((long long)(xs0 + qoff[q]) * L + t) * (2 * LT_U) + dir * LT_U + m;
-          dh[q] = dropout_keep(seed, (unsigned long long)oi, p.keep_prob) ? dh[q] * inv_keep : 0.f;
-        }
-        dh[q] *= live[q];
-      }
-      if (issuer_warp) mbar_wait(w_full, 0);
-    }
-#pragma unroll
-    for (int q = 0; q < LT_SPT; ++q) {
-      const int sl = hf * LT_SPT + q;
-      const float gi = bf16_lo(gw[q].x), gj = bf16_hi(gw[q].x), gf = bf16_lo(gw[q].y), go = bf16_hi(gw[q].y);
-      const float tc_ = tanh_fast(cc[q]);
-      const float dob = dh[q] * tc_ * go * (1.f - go);
-      const float dc = dcr[q] + dh[q] * go * (1.f - tc_ * tc_);
-      const float di = dc * gj * gi * (1.f - gi);
-      const float dj = dc * gi * (1.f - gj * gj);
-      const float df = dc * cp[q] * gf * (1.f - gf);
-      dcr[q] = dc * gf;
-      cc[q] = cp[q];                        // c_{t_prev} is the cell state of the next step processed
-      sb_i += di; sb_j += dj; sb_f += df; sb_o += dob;
-      const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
-                          bo = __float2bfloat16(dob);
-      const uint32_t zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
-      sts_bf16(zp, bi);
-      sts_bf16(zp + 2 * (LT_NS * 128), bj);
-      sts_bf16(zp + 4 * (LT_NS * 128), bf);
-      sts_bf16(zp + 6 * (LT_NS * 128), bo);
-      if (xs0 + q < p.X) {
-        __nv_bfloat16* gz = p.dz_bf + (long long)(tok_base + q * L + t) * (4 * LT_U) + m;
-        gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
-      }
-    }
-    fence_proxy_async();
-    tc_fence_before();
-    mbar_arrive(z_ready);
-    if (issuer_warp && step + 1 < L) {        // the last step's dh_rec has no consumer
+  if (!gate_warp) {
+    for (int step = 0; step + 1 < L; ++step) {          // the last step's dh_rec has no consumer
       mbar_wait(z_ready, step & 1);
       tc_fence_after();
       if (elect_one()) {
@@ -486,22 +403,114 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmWf, const __grid_consta
         for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t ad = smem_desc_sw128_k(w16, kb * 16384 + k4 * 32);
             const uint64_t bd = smem_desc_sw128_k(z16, kb * (LT_NS * 128) + k4 * 32);
-            umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            umma_bf16_ts(acc_t, wh_t + kb * 32 + k4 * 8, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
           }
         }
         umma_commit(mma_done);
       }
       __syncwarp();
     }
-  }
-  if (p.dbias_fw) {
-    float* db = dir ? p.dbias_bw : p.dbias_fw;
-    atomicAdd(db + m, sb_i); atomicAdd(db + LT_U + m, sb_j); atomicAdd(db + 2 * LT_U + m, sb_f); atomicAdd(db + 3 * LT_U + m, sb_o);
+  } else {
+    unsigned long long seed = p.seed;
+    if (DROP && p.seed_step) seed += (unsigned long long)(*p.seed_step) * 1000003ull;
+    const int m = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const uint32_t lane_addr = acc_t + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+    const float inv_keep = 1.0f / p.keep_prob;
+    // dz element (sentence row sl, k = g*128 + m) inside the swizzled tile: K-block g*2 + m/64
+    const uint32_t zdst = smem_u32(sZ) + (m >> 6) * (LT_NS * 128) + (m & 7) * 2;
+    const uint32_t zchunk = (uint32_t)((m & 63) >> 3);
+    const int xs0 = x0 + hf * LT_SPT;
+    // out-of-range sentences of the last tile read sentence X-1 (any valid address) and are zeroed via dh
+    uint32_t valid = 0;
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) valid |= (xs0 + q < p.X) ? (1u << q) : 0u;
+    const int xs_c = min(xs0, p.X - 1);                  // clamped first sentence (whole thread out of range)
+    const uint32_t qmax = (uint32_t)max(0, min(LT_SPT - 1, p.X - 1 - xs_c));   // clamp for q offsets
+    // running byte pointers of (clamped) sentence q = 0 at the current time step; sentence q adds q * stride
+    const int t0 = dir ? 0 : (L - 1);                    // time index of the first step processed here
+    const long long e0 = ((long long)(dir * p.X + xs_c) * L + t0) * LT_U + m;
+    const long long o0 = ((long long)xs_c * L + t0) * (2 * LT_U) + dir * LT_U + m;
+    const long long estep = dir ? (long long)LT_U : -(long long)LT_U;           // BPTT walks time backwards
+    const long long ostep = dir ? (long long)(2 * LT_U) : -(long long)(2 * LT_U);
+    const uint32_t qe = (uint32_t)L * LT_U, qo = (uint32_t)L * 2 * LT_U;
+    const char* g_ptr = reinterpret_cast<const char*>(p.gates_bf) + e0 * 8;
+    const char* c_ptr = reinterpret_cast<const char*>(p.cstate) + e0 * 2;
+    const char* do_ptr = reinterpret_cast<const char*>(p.dhout) + o0 * 2;
+    char* z_ptr = reinterpret_cast<char*>(p.dz_bf) + (e0 - m) * 8 + m * 2;       // [tok][4u] bf16, column m
+    long long oi = o0;
+    float sb_i = 0.f, sb_j = 0.f, sb_f = 0.f, sb_o = 0.f;     // this unit's bias-gradient partial sums
+    float dcr[LT_SPT], cc[LT_SPT];
+#pragma unroll
+    for (int q = 0; q < LT_SPT; ++q) {
+      dcr[q] = 0.f;
+      const unsigned long long eq = (unsigned long long)qe * min((uint32_t)q, qmax);
+      cc[q] = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(c_ptr + eq * 2));
+    }
+
+    for (int step = 0; step < L; ++step) {
+      // ---- this step's saved activations: every load is issued before anything waits on them
+      uint2 gw[LT_SPT];
+      float dh[LT_SPT], cp[LT_SPT];
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        const uint32_t qq = min((uint32_t)q, qmax);
+        const unsigned long long eq = (unsigned long long)qe * qq, oq = (unsigned long long)qo * qq;
+        gw[q] = *reinterpret_cast<const uint2*>(g_ptr + eq * 8);
+        dh[q] = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(do_ptr + oq * 2));
+        cp[q] = (step + 1 < L) ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(c_ptr + estep * 2 + eq * 2)) : 0.f;
+        if (DROP) dh[q] = dropout_keep(seed, (unsigned long long)(oi + (long long)oq), p.keep_prob) ? dh[q] * inv_keep : 0.f;
+      }
+      if (step > 0) {
+        float dhr[LT_SPT];
+        mbar_wait(mma_done, (step - 1) & 1);
+        __syncwarp();
+        tc_fence_after();
+        tmem_ld_spt(lane_addr, dhr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < LT_SPT; ++q) dh[q] += dhr[q];      // the recurrent part is added after the dropout mask
+      }
+#pragma unroll
+      for (int q = 0; q < LT_SPT; ++q) {
+        const int sl = hf * LT_SPT + q;
+        const bool ok = (valid >> q) & 1u;
+        const float dhq = ok ? dh[q] : 0.f;
+        const float gi = bf16_lo(gw[q].x), gj = bf16_hi(gw[q].x), gf = bf16_lo(gw[q].y), go = bf16_hi(gw[q].y);
+        const float tc_ = tanh_fast(cc[q]);
+        const float dob = dhq * tc_ * go * (1.f - go);
+        const float dc = dcr[q] + dhq * go * (1.f - tc_ * tc_);
+        const float di = dc * gj * gi * (1.f - gi);
+        const float dj = dc * gi * (1.f - gj * gj);
+        const float df = dc * cp[q] * gf * (1.f - gf);
+        dcr[q] = dc * gf;
+        cc[q] = cp[q];                        // c_{t_prev} is the cell state of the next step processed
+        sb_i += di; sb_j += dj; sb_f += df; sb_o += dob;
+        const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
+                            bo = __float2bfloat16(dob);
+        const uint32_t zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
+        sts_bf16(zp, bi);
+        sts_bf16(zp + 2 * (LT_NS * 128), bj);
+        sts_bf16(zp + 4 * (LT_NS * 128), bf);
+        sts_bf16(zp + 6 * (LT_NS * 128), bo);
+        if (ok) {
+          __nv_bfloat16* gz = reinterpret_cast<__nv_bfloat16*>(z_ptr + (unsigned long long)qe * (uint32_t)q * 8);
+          gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
+        }
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      mbar_arrive(z_ready);
+      g_ptr += estep * 8; c_ptr += estep * 2; do_ptr += ostep * 2; z_ptr += estep * 8; oi += ostep;
+    }
+    if (p.dbias_fw) {
+      float* db = dir ? p.dbias_bw : p.dbias_fw;
+      atomicAdd(db + m, sb_i); atomicAdd(db + LT_U + m, sb_j); atomicAdd(db + 2 * LT_U + m, sb_f); atomicAdd(db + 3 * LT_U + m, sb_o);
+    }
   }
   __syncthreads();
-  if (warp == 0) tmem_dealloc(taddr, LT_NS);
+  if (warp == 0) tmem_dealloc(taddr, 512);
 }
 
 // out[c] = sum_r A[r][c] for a bf16 matrix (bias gradient from the bf16 dz stream)
@@ -536,14 +545,14 @@ extern "C" int indnet_debug_lstm(long long* out) {
 #endif
 extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                                   const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout,
-                                  void* hout_bf, void* gates_bf, float* cstate, void* hprev_bf, int X, int L, int D,
+                                  void* hout_bf, void* gates_bf, void* cstate_bf, void* hprev_bf, int X, int L, int D,
                                   int u, float keep_prob, unsigned long long seed, const long long* seed_step) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0, "lstm_fwd_tc: bad sizes X=%d L=%d", X, L);
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_fwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
   IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_fwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && cstate && hout_bf && gates_bf &&
+  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && cstate_bf && hout_bf && gates_bf &&
              hprev_bf, "lstm_fwd_tc: null pointer");
   IN_REQUIRE((long long)2 * X * L < 2147483647LL / 1, "lstm_fwd_tc: token count exceeds 32-bit indexing");
   lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw,
@@ -575,7 +584,7 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   p.bias_fw = bias_fw; p.bias_bw = bias_bw;
   p.hout = hout; p.hout_bf = (__nv_bfloat16*)hout_bf;
   p.gates_bf = (__nv_bfloat16*)gates_bf;
-  p.cstate = cstate; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
+  p.cstate = (__nv_bfloat16*)cstate_bf; p.hprev_bf = (__nv_bfloat16*)hprev_bf;
   p.wt = (const __nv_bfloat16*)wt_scratch;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
   dim3 grid(ceil_div(X, LT_NS), 2);
@@ -599,7 +608,7 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   return INDNET_OK;
 }
 
-extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const void* gates_bf, const float* cstate,
+extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const void* gates_bf, const void* cstate_bf,
                                   const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
                                   float* dbias_bw, int X, int L, int D, int u, float keep_prob,
                                   unsigned long long seed, const long long* seed_step) {
@@ -608,17 +617,14 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_bwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
   IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_bwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(dhout_bf && gates_bf && cstate && kernel_fw_bf && kernel_bw_bf && dz_bf, "lstm_bwd_tc: null pointer");
-  // W_h = rows D.. of the bf16 TF kernel [D+u][4u]
-  CUtensorMap tmWf, tmWb;
-  const __nv_bfloat16* wf = (const __nv_bfloat16*)kernel_fw_bf + (long long)D * 4 * LT_U;
-  const __nv_bfloat16* wb = (const __nv_bfloat16*)kernel_bw_bf + (long long)D * 4 * LT_U;
-  int rc = make_tmap_bf16(&tmWf, wf, 4 * LT_U, LT_U, 4 * LT_U, 1, 0, 64, 128);
-  if (rc) return rc;
-  rc = make_tmap_bf16(&tmWb, wb, 4 * LT_U, LT_U, 4 * LT_U, 1, 0, 64, 128);
-  if (rc) return rc;
+  IN_REQUIRE(dhout_bf && gates_bf && cstate_bf && kernel_fw_bf && kernel_bw_bf && dz_bf, "lstm_bwd_tc: null pointer");
   LstmTcBwdP p;
-  p.dhout = (const __nv_bfloat16*)dhout_bf; p.gates_bf = (const __nv_bfloat16*)gates_bf; p.cstate = cstate; p.dz_bf = (__nv_bfloat16*)dz_bf;
+  // W_h = rows D.. of the bf16 TF kernel [D+u][4u]; D*4u*2 bytes is a multiple of 16 for every D
+  p.wh_fw = (const __nv_bfloat16*)kernel_fw_bf + (long long)D * 4 * LT_U;
+  p.wh_bw = (const __nv_bfloat16*)kernel_bw_bf + (long long)D * 4 * LT_U;
+  IN_REQUIRE((((uintptr_t)p.wh_fw | (uintptr_t)p.wh_bw) & 15) == 0, "lstm_bwd_tc: bf16 kernels must be 16-byte aligned");
+  p.dhout = (const __nv_bfloat16*)dhout_bf; p.gates_bf = (const __nv_bfloat16*)gates_bf;
+  p.cstate = (const __nv_bfloat16*)cstate_bf; p.dz_bf = (__nv_bfloat16*)dz_bf;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
   IN_REQUIRE((dbias_fw == nullptr) == (dbias_bw == nullptr), "lstm_bwd_tc: pass both bias gradients or neither");
   p.dbias_fw = dbias_fw; p.dbias_bw = dbias_bw;
@@ -626,13 +632,22 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
     IN_CUDA(cudaMemsetAsync(dbias_fw, 0, sizeof(float) * 4 * LT_U, st));
     IN_CUDA(cudaMemsetAsync(dbias_bw, 0, sizeof(float) * 4 * LT_U, st));
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
-    attr_set = true;
-  }
   dim3 grid(ceil_div(X, LT_NS), 2);
-  tc_lstm_bwd_kernel<<<grid, LT_THREADS, LB_SMEM, st>>>(tmWf, tmWb, p);
+  if (keep_prob < 1.0f) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
+      attr_set = true;
+    }
+    tc_lstm_bwd_kernel<true><<<grid, LB_THREADS, LB_SMEM, st>>>(p);
+  } else {
+    static bool attr_set = false;
+    if (!attr_set) {
+      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
+      attr_set = true;
+    }
+    tc_lstm_bwd_kernel<false><<<grid, LB_THREADS, LB_SMEM, st>>>(p);
+  }
   IN_LAUNCH_CHECK("tc_lstm_bwd_kernel");
   return INDNET_OK;
 }

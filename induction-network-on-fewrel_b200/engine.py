@@ -287,6 +287,7 @@ class EpisodePipeline:
             if self.tc_lstm:
                 self.wt_bf = h(2, 4 * c.u, 64 + c.u)
                 self.gates_bf = h(2, c.T, 4 * c.u)
+                self.cstate_bf = h(2, c.T, c.u)
 
     # ------------------------------------------------------------------ helpers
     def _call(self, name, *args):
@@ -405,7 +406,7 @@ class EpisodePipeline:
             # input projection + recurrence + gates in one persistent tcgen05 kernel
             self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
                        ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), None, ptr(self.hout_bf),
-                       ptr(self.gates_bf), ptr(self.cstate), ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
+                       ptr(self.gates_bf), ptr(self.cstate_bf), ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
                        keep, self.seed, ptr(p.global_step))
         else:
             for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
@@ -579,7 +580,7 @@ class EpisodePipeline:
             self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
                      splitk=1, tag="attn_dh")
         if self.tc_lstm:
-            self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate),
+            self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate_bf),
                        ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), ptr(p.grad(FW_B)),
                        ptr(p.grad(BW_B)), c.X, c.L, c.D, c.u, self._last_keep, self.seed, ptr(p.global_step))
         else:
