@@ -183,65 +183,102 @@ smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ key
 // F[b][s] = index after the block's draws are offered to a permutation currently at index s
 // (accept iff (y & mask(s)) <= s, then s -= 1), saturating at 0 = "the permutation ends inside this
 // block"; for s <= 64 the end table E[b][s] holds how many of the block's draws that permutation
-// consumes (0xFF: it does not end here).  Both are independent of which job meets the block, so the
-// whole GPU builds them in parallel and the serial walker only chains one lookup per 64 draws.  The
-// tempered draws are stored too (ytemp) for the walker's exact rows and the fill kernel.
+// consumes (0xFF: it does not end here).  Even blocks also carry F2[b][s] = F[b+1][F[b][s]], the
+// index after the PAIR of blocks (0 if the permutation ends inside either).  All of it is independent of
+// which job meets the block, so the whole GPU builds the tables in parallel and the serial walker only
+// chains one lookup per 128 (or 64) draws.  The tempered draws are stored too, for the walker's exact
+// rows and the fill kernel.
 constexpr int E_STRIDE = 80;   // bytes per block of E (65 used; keeps the record 16-byte granular)
 // One record per block, contiguous in memory so that a run of blocks is ONE bulk copy for the walker:
-//   [ F row: n_states x u16 | the block's 64 tempered draws: u32 | E row: 80 x u8 ]
-__host__ __device__ inline long long rec_bytes(long long n_states) { return n_states * 2 + TB * 4 + E_STRIDE; }
+//   [ F row: n_states x u16 | F2 row (even blocks): n_states x u16 | 64 tempered draws: u32 | E row: 80 x u8 |
+//     E2 row (even blocks): 144 x u8 ]
+// E2[b][s], s <= 128: draws of the PAIR (b, b+1) consumed by a permutation entering at index s that ends
+// inside the pair (0xFF otherwise).
+constexpr int E2_STRIDE = 144;
+__host__ __device__ inline long long rec_bytes(long long n_states) { return n_states * 4 + TB * 4 + E_STRIDE + E2_STRIDE; }
 
+// index after the 64 draws y[0..64) starting from s0 >= 1; e = draws consumed if it reaches 0 (s0 <= 64)
+__device__ __forceinline__ int walk_block(const uint32_t* y, int s0, int& e) {
+  int s = s0;
+  uint32_t m = mask_for((uint32_t)s);
+  int thr = (int)(m >> 1);
+  e = 0xFF;
+  if (s0 <= TB) {
+    for (int k = 0; k < TB; ++k) {
+      if (s <= thr) { m >>= 1; thr >>= 1; }
+      const uint32_t v = y[k] & m;
+      if (s >= 1 && v <= (uint32_t)s) { if (--s == 0) e = k + 1; }
+    }
+  } else {
+#pragma unroll 8
+    for (int k = 0; k < TB; ++k) {
+      if (s <= thr) { m >>= 1; thr >>= 1; }       // the index shrinks by at most one per draw
+      const uint32_t v = y[k] & m;
+      s -= (v <= (uint32_t)s) ? 1 : 0;            // s0 > 64 cannot reach 0 inside the block
+    }
+  }
+  return s;
+}
+
+// one CTA per pair of blocks (2p, 2p+1)
 __global__ void __launch_bounds__(256)
 smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ tab, int n_states) {
-  __shared__ uint32_t y[TB];
-  const long long b = blockIdx.x;
-  unsigned char* rec = tab + b * rec_bytes(n_states);
-  unsigned short* F = reinterpret_cast<unsigned short*>(rec);
-  uint32_t* Y = reinterpret_cast<uint32_t*>(rec + n_states * 2);
-  unsigned char* E = rec + n_states * 2 + TB * 4;
-  if (threadIdx.x < TB) {
-    const uint32_t v = mt_temper(keys[b * TB + threadIdx.x]);
-    y[threadIdx.x] = v;
-    Y[threadIdx.x] = v;
+  extern __shared__ unsigned short fs[];          // [2][n_states]: F of the even / odd block
+  __shared__ uint32_t y[2][TB];
+  __shared__ unsigned char es[2][TB + 1];         // E of the even / odd block
+  const long long b0 = 2LL * blockIdx.x;
+  const long long rb = rec_bytes(n_states);
+  if (threadIdx.x < 2 * TB) {
+    const int h = threadIdx.x / TB, k = threadIdx.x % TB;
+    const uint32_t v = mt_temper(keys[(b0 + h) * TB + k]);
+    y[h][k] = v;
+    reinterpret_cast<uint32_t*>(tab + (b0 + h) * rb + (long long)n_states * 4)[k] = v;
   }
   __syncthreads();
   for (int s0 = threadIdx.x; s0 < n_states; s0 += 256) {
-    int s = s0, e = 0xFF;
-    if (s >= 1) {
-      uint32_t m = mask_for((uint32_t)s);
-      int thr = (int)(m >> 1);
-      if (s0 <= TB) {
-        for (int k = 0; k < TB; ++k) {
-          if (s <= thr) { m >>= 1; thr >>= 1; }
-          const uint32_t v = y[k] & m;
-          if (s >= 1 && v <= (uint32_t)s) { if (--s == 0) e = k + 1; }
-        }
-      } else {
-#pragma unroll 8
-        for (int k = 0; k < TB; ++k) {
-          if (s <= thr) { m >>= 1; thr >>= 1; }       // the index shrinks by at most one per draw
-          const uint32_t v = y[k] & m;
-          s -= (v <= (uint32_t)s) ? 1 : 0;            // s0 > 64 cannot reach 0 inside the block
-        }
-      }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      int e = 0xFF;
+      const int s = (s0 >= 1) ? walk_block(y[h], s0, e) : 0;
+      fs[h * n_states + s0] = (unsigned short)s;
+      unsigned char* rec = tab + (b0 + h) * rb;
+      reinterpret_cast<unsigned short*>(rec)[s0] = (unsigned short)s;
+      if (s0 < E_STRIDE) rec[(long long)n_states * 4 + TB * 4 + s0] = (unsigned char)((s0 >= 1 && s0 <= TB) ? e : 0xFF);
+      if (s0 <= TB) es[h][s0] = (unsigned char)((s0 >= 1) ? e : 0xFF);
     }
-    F[s0] = (unsigned short)s;
-    if (s0 < E_STRIDE) E[s0] = (unsigned char)((s0 >= 1 && s0 <= TB) ? e : 0xFF);
+  }
+  __syncthreads();
+  unsigned short* F2 = reinterpret_cast<unsigned short*>(tab + b0 * rb + (long long)n_states * 2);
+  for (int s0 = threadIdx.x; s0 < n_states; s0 += 256) {
+    const int s1 = fs[s0];
+    F2[s0] = s1 > 0 ? fs[n_states + s1] : (unsigned short)0;
+  }
+  unsigned char* E2 = tab + b0 * rb + (long long)n_states * 4 + TB * 4 + E_STRIDE;
+  for (int s0 = threadIdx.x; s0 < E2_STRIDE; s0 += 256) {
+    int e2 = 0xFF;
+    if (s0 >= 1 && s0 <= 2 * TB && s0 < n_states) {
+      const int s1 = fs[s0];
+      if (s1 == 0) e2 = (s0 <= TB) ? es[0][s0] : 0xFF;           // ends in the even block (then s0 <= 64)
+      else if (fs[n_states + s1] == 0 && s1 <= TB) e2 = TB + es[1][s1];   // ends in the odd block (then s1 <= 64)
+    }
+    E2[s0] = (unsigned char)e2;
   }
 }
 
-// ---- kernel W: the serial walk (one warp) --------------------------------------------------------
+// ---- kernel W: the serial walk ------------------------------------------------------------------
 // Jobs: for each episode its N class permutations, then the query permutation.  At a 64-aligned stream
-// position the walker jumps a whole block through F (and records (index, job) for the fill kernel); a
-// permutation that ends inside the block it entered aligned takes its end offset from E; everything
-// else (the stretch from a permutation's first draw to the next block boundary, and permutations that
-// start and end inside one block) is walked exactly in rows of up to 32 draws (ballot fixed point over
-// the lanes).
+// position the walker jumps a pair of blocks through F2 or one block through F (and records (index, job)
+// per block for the fill kernel); a permutation that ends inside the block it entered aligned takes its
+// end offset from E; everything else (the stretch from a permutation's first draw to the next block
+// boundary, and permutations that start and end inside one block) is walked exactly in rows of up to 32
+// draws (ballot fixed point over the lanes).
 // The lookups form one dependent chain, so their latency is the walk time.  The tables of the next
 // blocks are therefore staged in shared memory ahead of the walker: the stream is cut into chunks of
-// 2^cb_log blocks whose F rows / draws / E rows are contiguous in global memory, and a ring of 2^rc_log
-// chunk slots is kept full with bulk async copies (one mbarrier per slot, complete_tx), issued when
-// the walker leaves a chunk.  A lookup is then one LDS.
+// 2^cb_log blocks whose records are contiguous in global memory, and a ring of rc chunk slots is kept
+// full with bulk async copies (one mbarrier per slot, complete_tx).  Warp 0 walks; warp 1 is the
+// producer: it watches the walker's chunk counter in shared memory and refills the slots the walker
+// has left, so a chunk transition costs the walker one counter store and one (already complete)
+// barrier test.  A lookup is one LDS.
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
@@ -266,93 +303,204 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
   return v;
 }
 
-__global__ void __launch_bounds__(32)
+#ifdef INDNET_SMP_TIMELINE
+#define SMP_T(var) const long long var = clock64()
+#define SMP_ACC(acc, a, b) acc += (b) - (a)
+#else
+#define SMP_T(var) do { } while (0)
+#define SMP_ACC(acc, a, b) do { } while (0)
+#endif
+
+__device__ __forceinline__ int lds_acquire_s32(uint32_t a) {
+  int v;
+  asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_release_s32(uint32_t a, int v) {
+  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+
+// The walker is one warp on an otherwise idle SM: every instruction costs its full dependent latency, so
+// the walk time is (instructions on its path) x (a few cycles).  It therefore keeps nothing but the
+// chain: for every run of table jumps it logs ONE record {first block, entry index, job}; the fill kernel
+// replays those runs in parallel from the same tables to recover the per-block indices and the j-lists.
+__global__ void __launch_bounds__(64)
 smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restrict__ tab, int n_states,
-                long long nblk, int cb_log, int rc_log, uint32_t* __restrict__ np_state,
+                long long nblk, int cb_log, int rc, uint32_t* __restrict__ np_state,
                 const int* __restrict__ jsize, int jobs, int n_max, int* __restrict__ jlist,
-                int2* __restrict__ blk_rec, int* __restrict__ status) {
+                int4* __restrict__ seclog, int* __restrict__ nsec_out, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char ring[];
-  const int lane = threadIdx.x;
-  const uint32_t below = (1u << lane) - 1u;
-  const int CB = 1 << cb_log, RC = 1 << rc_log;
-  const uint32_t f_bytes = (uint32_t)n_states * 2u, y_bytes = TB * 4u;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int CB = 1 << cb_log;
+  const uint32_t f_bytes = (uint32_t)n_states * 2u, y_off = 2u * f_bytes, e_off = y_off + TB * 4u, e2_off = e_off + E_STRIDE;
   const uint32_t blk_bytes = (uint32_t)rec_bytes(n_states), slot_bytes = blk_bytes << cb_log;
   const uint32_t ring_s = tc::smem_u32(ring);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)RC * slot_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)rc * slot_bytes);
   const uint32_t bars_s = tc::smem_u32(bars);
-  const long long nchunks = nblk >> cb_log;
-  if (lane == 0) {
-    for (int r = 0; r < RC; ++r) tc::mbar_init(&bars[r], 1);
+  volatile uint32_t* zeros = reinterpret_cast<volatile uint32_t*>(bars + rc);   // [32]
+  volatile int* ctl = reinterpret_cast<volatile int*>(bars + rc) + 32;          // [0] walker's chunk - c0, [1] done, [2] landed chunks
+  const uint32_t ctl_s = tc::smem_u32(const_cast<int*>(ctl));
+  const int nchunks = (int)(nblk >> cb_log);
+  if (threadIdx.x == 0) {
+    for (int r = 0; r < rc; ++r) tc::mbar_init(&bars[r], 1);
     tc::fence_barrier_init();
+    ctl[0] = 0;
+    ctl[1] = 0;
+    ctl[2] = 0;
   }
   // A zero the compiler cannot see through, one per lane: adding it to the walk index keeps the chain
   // in ordinary registers (see lds_u16 above).
-  volatile uint32_t* zeros = reinterpret_cast<volatile uint32_t*>(bars + RC);
-  zeros[lane] = 0u;
-  __syncwarp();
-  const int lane_zero = (int)zeros[lane];
-  auto issue = [&](long long c) {                  // one bulk copy: the chunk's records are contiguous
-    if (lane == 0 && c < nchunks) {
-      const uint32_t r = (uint32_t)c & (uint32_t)(RC - 1);
-      const uint32_t bar = bars_s + 8u * r;
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(slot_bytes) : "memory");
-      bulk_g2s(ring_s + r * slot_bytes, tab + c * (long long)slot_bytes, slot_bytes, bar);
-    }
-  };
-  const long long clk0 = clock64();
+  if (warp == 0) zeros[lane] = 0u;
+  __syncthreads();
   long long pos = (long long)np_state[MT_N];      // absolute draw index; keys[0] is the state handed in
-  const long long c0 = pos >> (6 + cb_log);
-  for (int k = 0; k < RC - 1; ++k) issue(c0 + k);
-  long long ready = c0 - 1;                       // last chunk whose slot has been waited for
-  int flag = SMP_OK, n_jump = 0, n_row = 0;
+  const int c0 = (int)(pos >> (6 + cb_log));
+
+  if (warp == 1) {
+    // ---- producer (one lane): keep chunks [walker's chunk, +rc) resident.  It also does the waiting on
+    // the copies' mbarriers and publishes the number of landed chunks (ctl[2], release), so the walker's
+    // chunk transition is one counter store and one counter load.  It sleeps between polls: a spinning
+    // neighbour warp would sit in the same shared-memory pipeline as the walker's lookups.
+    if (lane == 0) {
+      int issued = c0, landed = c0;
+      while (true) {
+        const int cur = ctl[0], dn = ctl[1];
+        const int hi = min(c0 + cur + rc, nchunks);
+        while (issued < hi) {
+          const uint32_t r = (uint32_t)(issued - c0) % (uint32_t)rc;
+          const uint32_t bar = bars_s + 8u * r;
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(slot_bytes) : "memory");
+          bulk_g2s(ring_s + r * slot_bytes, tab + (long long)issued * slot_bytes, slot_bytes, bar);
+          ++issued;
+        }
+        while (landed < issued) {                  // in issue order; blocks only while a copy is in flight
+          const uint32_t rel = (uint32_t)(landed - c0);
+          tc::mbar_wait(&bars[rel % (uint32_t)rc], (rel / (uint32_t)rc) & 1u);
+          ++landed;
+          sts_release_s32(ctl_s + 8u, landed - c0);
+        }
+        if (dn) break;
+        __nanosleep(200);
+      }
+    }
+    return;
+  }
+
+  // ---- walker (warp 0)
+  const uint32_t below = (1u << lane) - 1u;
+  const int lane_zero = (int)zeros[lane];
+  const uint32_t fb = f_bytes, pair_bytes = 2u * blk_bytes;
+  const long long clk0 = clock64();
+  // the shared window base as a value the compiler has to keep (it would otherwise be re-derived from a
+  // special register, at that read's latency, at every chunk transition)
+  const uint32_t ring_w = ring_s + (uint32_t)lane_zero, ctl_w = ctl_s + (uint32_t)lane_zero;
+  int ready = c0 - 1;                             // last chunk whose slot has been waited for
+  int slot_i = -1;                                // its slot: (ready - c0) % rc, advanced incrementally
+  uint32_t slot_s = ring_w;                       // shared address of that slot
+  int flag = SMP_OK, n_sec = 0, n_row = 0;
+#ifdef INDNET_SMP_TIMELINE
+  long long a_job = 0, a_head = 0, a_wait = 0, a_jump = 0, a_row = 0, n_iter = 0;
+#endif
   int n_next = jobs > 0 ? jsize[0] : 0;
   for (int job = 0; job < jobs && flag == SMP_OK; ++job) {
+    SMP_T(tj0);
     const int n = n_next;
     if (n < 0) { flag = -n; break; }
     n_next = (job + 1 < jobs) ? jsize[job + 1] : 0;   // in flight while this job is walked
     int i = n - 1 + lane_zero;
     int* jrow = jlist + (long long)job * n_max;
+    SMP_T(tj1);
+    SMP_ACC(a_job, tj0, tj1);
     while (i > 0) {
       const long long b = pos >> 6;
       const int off = (int)(pos & (TB - 1));
       if (b >= nblk) { flag = SMP_STREAM_BUDGET; break; }
-      const long long c = b >> cb_log;
-      while (ready < c) {                          // entering a new chunk: its slot must have landed;
-        ++ready;                                   // the slot of the chunk just left is refilled
-        tc::mbar_wait(&bars[ready & (RC - 1)], (uint32_t)(((ready - c0) >> rc_log) & 1));
-        issue(ready + RC - 1);
+      const int c = (int)(b >> cb_log);
+      SMP_T(tw0);
+      while (ready < c) {                          // entering a new chunk: tell the producer, then make sure it landed
+        ++ready;
+        const int rel = ready - c0;
+        if (lane == 0) asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"(ctl_w), "r"(rel) : "memory");
+        while (lds_acquire_s32(ctl_w + 8u) <= rel) { }   // chunks [c0, c0 + ctl[2]) have landed
+        if (++slot_i == rc) slot_i = 0;
+        slot_s = ring_w + (uint32_t)slot_i * slot_bytes;
       }
+      SMP_T(tw1);
+      SMP_ACC(a_wait, tw0, tw1);
+#ifdef INDNET_SMP_TIMELINE
+      ++n_iter;
+#endif
       const int lb = (int)(b & (CB - 1));
-      const uint32_t blk_s = ring_s + ((uint32_t)c & (uint32_t)(RC - 1)) * slot_bytes + (uint32_t)lb * blk_bytes;
       if (off == 0) {
-        // chain of table jumps through the rest of this chunk: one LDS + a few ALU ops per 64 draws
-        uint32_t a = blk_s;
-        int2* rec = blk_rec + b;
-        int left = CB - lb, inext;
-        do {
-          inext = (int)lds_u16(a + 2u * (uint32_t)i);
-          if (inext == 0) break;
-          if (lane == 0) *rec = make_int2(i, job);
-          i = inext;
-          a += blk_bytes;
-          ++rec;
-        } while (--left > 0);
-        const int done = (CB - lb) - left;
-        n_jump += done;
-        pos += (long long)done * TB;
-        if (inext == 0) {                                   // ends inside block b + done; then i <= 64
-          const int e = (int)lds_u8(a + f_bytes + y_bytes + (uint32_t)i);
-          if (lane == 0) *rec = make_int2(i, job);
-          i = 0;
-          pos += e;
-          ++n_jump;
+        // ---- run of table jumps from block b to the end of this chunk (or of the permutation)
+        if (lane == 0) seclog[n_sec] = make_int4((int)b, i, job, 0);
+        ++n_sec;
+        const uint32_t cbase = slot_s;                     // block 0 of this chunk
+        uint32_t v = (uint32_t)i;
+        int lbb = lb;
+        uint32_t eaddr = 0;                                // where the end offset sits if the permutation ends in this run
+        int eblk = 0;                                      // ... and the block (within the chunk) it is relative to
+        if ((lb & 1) || CB == 1) {                         // odd block (or no pairs): one single-block jump first
+          const uint32_t ba = cbase + (uint32_t)lb * blk_bytes;
+          const uint32_t nx = lds_u16(ba + 2u * v);
+          if (nx == 0) { eaddr = ba + e_off + v; eblk = lb; }
+          else { v = nx; ++lbb; }
         }
+        SMP_T(tc0);
+        if (eaddr == 0 && lbb < CB) {
+          if (cb_log == 3) {
+            // the remaining pairs as one straight-line chain of F2 lookups entered at the current pair;
+            // index 0 is absorbing (F2[b][0] = 0), so an ending permutation arrives as 0 and is located after
+            uint32_t v0 = 1, v1 = 1, v2 = 1, v3 = 1, v4;
+            const uint32_t t0 = cbase + fb;
+            switch (lbb >> 1) {
+              case 0: v0 = v;
+                      v1 = lds_u16(t0 + 2u * v0);
+                      if (false) {
+              case 1:   v1 = v; }
+                      v2 = lds_u16(t0 + pair_bytes + 2u * v1);
+                      if (false) {
+              case 2:   v2 = v; }
+                      v3 = lds_u16(t0 + 2u * pair_bytes + 2u * v2);
+                      if (false) {
+              default:  v3 = v; }
+                      v4 = lds_u16(t0 + 3u * pair_bytes + 2u * v3);
+            }
+            const int passed = (v1 != 0) + (v2 != 0) + (v3 != 0) + (v4 != 0);   // = index of the pair it ends in, or 4
+            if (passed == 4) { v = v4; lbb = CB; }
+            else {
+              const uint32_t ve = passed == 0 ? v0 : passed == 1 ? v1 : passed == 2 ? v2 : v3;
+              eaddr = cbase + (uint32_t)passed * pair_bytes + e2_off + ve;
+              eblk = 2 * passed;
+            }
+          } else {
+            while (lbb < CB) {                             // generic chunk size: the same chain as a loop
+              const uint32_t ba = cbase + (uint32_t)lbb * blk_bytes;
+              const uint32_t nx = lds_u16(ba + fb + 2u * v);
+              if (nx == 0) { eaddr = ba + e2_off + v; eblk = lbb; break; }
+              v = nx;
+              lbb += 2;
+            }
+          }
+        }
+        SMP_T(tc1);
+        SMP_ACC(a_head, tc0, tc1);
+        const long long chunk_pos = (b - lb) << 6;
+        if (eaddr != 0) {                                  // the permutation ends inside this run
+          pos = chunk_pos + (long long)(eblk * TB + (int)lds_u8(eaddr));
+          i = 0;
+        } else {
+          pos = chunk_pos + (long long)lbb * TB;
+          i = (int)v;
+        }
+        SMP_T(tx1);
+        SMP_ACC(a_jump, tw1, tx1);
         continue;
       }
-      // exact row: up to 32 draws, not crossing the next block boundary
+      // ---- exact row: up to 32 draws, not crossing the next block boundary
+      const uint32_t blk_s = slot_s + (uint32_t)lb * blk_bytes;
       const int limit = min(32, TB - off);
       const bool valid = lane < limit;
-      const uint32_t y = valid ? lds_u32(blk_s + f_bytes + 4u * (uint32_t)(off + lane)) : 0u;
+      const uint32_t y = valid ? lds_u32(blk_s + y_off + 4u * (uint32_t)(off + lane)) : 0u;
       const uint32_t m0 = mask_for((uint32_t)i);
       int cn = (lane * (i + 1)) >> (32 - __clz(m0));       // expected accepts before this lane
       int ip = i - cn;
@@ -373,8 +521,11 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
       i -= acc;
       pos += used;
       ++n_row;
+      SMP_T(tr1);
+      SMP_ACC(a_row, tw1, tr1);
     }
   }
+  if (lane == 0) ctl[1] = 1;                               // the producer drains its copies and leaves
   // hand the stream back: the block the walk stopped in (offset 624 = "block exhausted")
   {
     long long blk = pos / MT_N;
@@ -388,32 +539,64 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
     for (int k = lane; k < MT_N; k += 32) np_state[k] = tmp[cnt++];
     if (lane == 0) {
       np_state[MT_N] = (uint32_t)off;
+      *nsec_out = n_sec;
       status[0] = flag;
-      status[1] = (int)((clock64() - clk0) >> 4);     // diagnostics: walk cycles / 16, table jumps, exact rows
-      status[2] = n_jump;
+      status[1] = (int)((clock64() - clk0) >> 4);     // diagnostics: walk cycles / 16, jump runs, exact rows
+      status[2] = n_sec;
       status[3] = n_row;
+#ifdef INDNET_SMP_TIMELINE
+      status[4] = (int)(a_job >> 4); status[5] = (int)(a_head >> 4); status[6] = (int)(a_wait >> 4);
+      status[7] = (int)(a_jump >> 4); status[8] = (int)(a_row >> 4); status[9] = (int)n_iter;
+#endif
     }
   }
-  // copies still in flight target this CTA's shared memory: drain them before the CTA retires
-  for (long long c = ready + 1; c < ready + RC && c < nchunks; ++c)
-    tc::mbar_wait(&bars[c & (RC - 1)], (uint32_t)(((c - c0) >> rc_log) & 1));
 }
 
 // ---- kernel F: accepted (index, j) pairs of the blocks the walker jumped over --------------------
-__global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int n_states, const int2* __restrict__ blk_rec,
-                                long long nblk, int n_max, int* __restrict__ jlist) {
-  const long long b = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (b >= nblk) return;
-  const int2 rec = blk_rec[b];
-  if (rec.y < 0) return;
-  int s = rec.x;
-  int* jrow = jlist + (long long)rec.y * n_max;
+// One thread per (logged run, block of its chunk): replay the run's chain through F / F2 in global memory
+// up to that block (at most CB / 2 + 1 dependent lookups), then offer the block's 64 draws.
+__global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int n_states, const int4* __restrict__ seclog,
+                                const int* __restrict__ nsec, int cb_log, int n_max, int* __restrict__ jlist) {
+  const int CB = 1 << cb_log;
+  const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int sec = (int)(id >> cb_log), k = (int)(id & (CB - 1));
+  if (sec >= *nsec) return;
+  const int4 lg = seclog[sec];
+  const long long b_start = lg.x, chunk0 = b_start & ~(long long)(CB - 1), mine = chunk0 + k;
+  if (mine < b_start) return;
+  const long long rb = rec_bytes(n_states);
+  auto F = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + blk * rb)[s]; };
+  auto F2 = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + blk * rb + (long long)n_states * 2)[s]; };
+  int s = lg.y;
+  long long bb = b_start;
+  bool found = false;
+  if ((bb & 1) || CB == 1) {
+    if (bb == mine) found = true;
+    else {
+      s = F(bb, s);
+      if (s == 0) return;                       // the permutation ended before this thread's block
+      ++bb;
+    }
+  }
+  while (!found) {                              // bb even, bb <= mine < chunk end
+    if (bb == mine) { found = true; break; }
+    if (bb + 1 == mine) {
+      s = F(bb, s);
+      if (s == 0) return;
+      found = true;
+      break;
+    }
+    s = F2(bb, s);
+    if (s == 0) return;
+    bb += 2;
+  }
+  int* jrow = jlist + (long long)lg.z * n_max;
   uint32_t m = mask_for((uint32_t)s);
   int thr = (int)(m >> 1);
-  const uint32_t* yp = reinterpret_cast<const uint32_t*>(tab + b * rec_bytes(n_states) + (long long)n_states * 2);
-  for (int k = 0; k < TB && s >= 1; ++k) {
+  const uint32_t* yp = reinterpret_cast<const uint32_t*>(tab + mine * rb + (long long)n_states * 4);
+  for (int q = 0; q < TB && s >= 1; ++q) {
     if (s <= thr) { m >>= 1; thr >>= 1; }
-    const uint32_t v = yp[k] & m;
+    const uint32_t v = yp[q] & m;
     if (v <= (uint32_t)s) { jrow[s] = (int)v; --s; }
   }
 }
@@ -485,9 +668,9 @@ namespace {
 // Scratch layout shared by the walk and gather halves (all offsets in bytes, 256-byte aligned).
 struct SmpLayout {
   long long jobs, stride, pick_max, n_states, nb, nblk;
-  int cb_log, rc_log;              // walker staging: 2^cb_log blocks per chunk, 2^rc_log chunk slots (-1: does not fit)
+  int cb_log, rc;                  // walker staging: 2^cb_log blocks per chunk, rc chunk slots (-1: does not fit)
   long long smem_bytes;
-  long long o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_blk_rec, bytes;
+  long long o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, o_nsec, sec_cap, bytes;
 };
 static double expected_draws(long long n) {      // E[draws] of NumPy's permutation(n) (rejection sampling)
   double e = 0.0;
@@ -512,12 +695,15 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   L.nb = (L.nblk * TB + MT_N - 1) / MT_N + 1;
   // walker staging ring: the largest chunk / ring that fits in 200 KB of shared memory
   const long long per_block = rec_bytes(L.n_states);
-  static const int opts[6][2] = {{4, 2}, {3, 2}, {2, 3}, {1, 3}, {0, 3}, {0, 2}};
-  L.cb_log = L.rc_log = -1;
+  // chunk = 8 blocks (or fewer for very wide tables), as many slots as fit (<= 8): a deep ring of small chunks
+  // keeps the copies well ahead of a walker that may pass a chunk in a few hundred cycles
+  L.cb_log = L.rc = -1;
   L.smem_bytes = 0;
-  for (int k = 0; k < 6; ++k) {
-    const long long need = (((per_block << opts[k][0]) + 8) << opts[k][1]) + 128;
-    if (need <= 200 * 1024) { L.cb_log = opts[k][0]; L.rc_log = opts[k][1]; L.smem_bytes = need; break; }
+  for (int cb = 3; cb >= 0 && L.cb_log < 0; --cb) {
+    for (int rc = 8; rc >= 3; --rc) {
+      const long long need = (per_block << cb) * rc + 8 * rc + 128 + 64;
+      if (need <= 200 * 1024) { L.cb_log = cb; L.rc = rc; L.smem_bytes = need; break; }
+    }
   }
   auto al = [](long long x) { return (x + 255) / 256 * 256; };
   long long o = 0;
@@ -527,7 +713,9 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   L.o_picks = o;   o = al(o + 4LL * L.jobs * L.pick_max);
   L.o_keys = o;    o = al(o + 4LL * L.nb * MT_N);
   L.o_tab = o;     o = al(o + rec_bytes(L.n_states) * L.nblk);
-  L.o_blk_rec = o; o = al(o + 8LL * L.nblk);
+  L.sec_cap = (L.nblk >> (L.cb_log < 0 ? 0 : L.cb_log)) + L.jobs + 2;   // one run per chunk entered aligned + one per job
+  L.o_seclog = o;  o = al(o + 16LL * L.sec_cap);
+  L.o_nsec = o;    o = al(o + 4);
   L.bytes = o;
   return L;
 }
@@ -554,7 +742,8 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   uint32_t* keys = (uint32_t*)(base + L.o_keys);
   unsigned char* tab = (unsigned char*)(base + L.o_tab);
   int* jsize = (int*)(base + L.o_jsize);
-  int2* blk_rec = (int2*)(base + L.o_blk_rec);
+  int4* seclog = (int4*)(base + L.o_seclog);
+  int* nsec = (int*)(base + L.o_nsec);
   IN_REQUIRE(L.cb_log >= 0, "sample_episodes: n_max=%d is too large for the walker's shared-memory table ring", n_max);
   IN_REQUIRE(L.nblk <= 2147483647LL, "sample_episodes: stream too long");
   static bool smem_set[64] = {};
@@ -562,17 +751,18 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   IN_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !smem_set[dev]) {
     IN_CUDA(cudaFuncSetAttribute(smp_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    IN_CUDA(cudaFuncSetAttribute(smp_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     if (dev >= 0 && dev < 64) smem_set[dev] = true;
   }
   smp_gen_kernel<<<2, GEN_NT, 0, st>>>(np_state, keys, (int)L.nb, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
   IN_LAUNCH_CHECK("smp_gen_kernel");
-  smp_table_kernel<<<(unsigned)L.nblk, 256, 0, st>>>(keys, tab, (int)L.n_states);
+  smp_table_kernel<<<(unsigned)(L.nblk / 2), 256, 4 * (size_t)L.n_states, st>>>(keys, tab, (int)L.n_states);
   IN_LAUNCH_CHECK("smp_table_kernel");
-  IN_CUDA(cudaMemsetAsync(blk_rec, 0xFF, 8 * L.nblk, st));
-  smp_walk_kernel<<<1, 32, (size_t)L.smem_bytes, st>>>(keys, tab, (int)L.n_states, L.nblk, L.cb_log, L.rc_log, np_state,
-                                                      jsize, (int)L.jobs, (int)L.stride, jlist, blk_rec, status);
+  smp_walk_kernel<<<1, 64, (size_t)L.smem_bytes, st>>>(keys, tab, (int)L.n_states, L.nblk, L.cb_log, L.rc, np_state,
+                                                      jsize, (int)L.jobs, (int)L.stride, jlist, seclog, nsec, status);
   IN_LAUNCH_CHECK("smp_walk_kernel");
-  smp_fill_kernel<<<ceil_div(L.nblk, 128), 128, 0, st>>>(tab, (int)L.n_states, blk_rec, L.nblk, (int)L.stride, jlist);
+  smp_fill_kernel<<<ceil_div(L.sec_cap << L.cb_log, 128), 128, 0, st>>>(tab, (int)L.n_states, seclog, nsec, L.cb_log,
+                                                                        (int)L.stride, jlist);
   IN_LAUNCH_CHECK("smp_fill_kernel");
   sampler_trace_kernel<<<ceil_div(L.jobs * L.pick_max, 128), 128, 0, st>>>(scopes, classes, jlist, B, N, K, Q,
                                                                            (int)L.stride, (int)L.pick_max, picks);

@@ -33,7 +33,7 @@ class DeviceEpisodeSampler:
                        .to(self.device) for k in KEYS}
         self.py_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.np_state = torch.zeros(625, dtype=torch.int32, device=self.device)
-        self.status = torch.zeros(4, dtype=torch.int32, device=self.device)   # {status, cycles/16, passes, rounds}
+        self.status = torch.zeros(16, dtype=torch.int32, device=self.device)  # {status, cycles/16, jumps, rows, timeline build: 6 more}
         self._bufs = {}
         self.load_host_streams()
 

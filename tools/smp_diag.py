@@ -16,3 +16,6 @@ for (B,N,K,Q) in [(64,5,1,5)]:
         st = smp.status.cpu().numpy()
         print("walk+trace %.3f ms gather %.3f ms | cycles %d passes %d rounds %d -> %.1f cyc/pass, clock %.0f MHz if walk=all" % (
             e0.elapsed_time(e1), e1.elapsed_time(e2), st[1]*16, st[2], st[3], st[1]*16/max(st[2],1), st[1]*16/(e0.elapsed_time(e1)*1e3)))
+        if st[9]:   # timeline build (INDNET_NVCC_DEFINES=-DINDNET_SMP_TIMELINE)
+            print("   cycles: job setup %d | loop head %d | chunk wait+issue %d | jumps %d | rows %d | iterations %d" % (
+                st[4]*16, st[5]*16, st[6]*16, st[7]*16, st[8]*16, st[9]))
