@@ -92,28 +92,41 @@ constexpr int TB = 64;     // draws per transition-table block
 
 // ---- kernel G: both host streams, two CTAs ------------------------------------------------------
 // CTA 0: nb consecutive untempered MT19937 blocks of the NumPy stream.  keys[0..624) = the state handed
-// in; beyond that the flat recurrence x[n] = mix(x[n-624], x[n-623], x[n-227]) lets 224 consecutive words
-// be produced per round (one barrier each) out of a 1024-word shared ring.
+// in; beyond that the recurrence runs in rounds of 227 words, two rounds per barrier, out of a 2048-word
+// shared ring.
 // CTA 1: the Python stream - random.sample(range(R), N) per episode, restated literally (pool / set
 // variants of CPython's Random.sample), one thread; then the permutation length of every job.
-constexpr int GEN_NT = 224;
+constexpr int GEN_NT = 256;
+
+// the part of the MT19937 recurrence that mixes two consecutive words: x[n] = x[n-227] ^ mt_g(x[n-624], x[n-623])
+__device__ __forceinline__ uint32_t mt_g(uint32_t a, uint32_t b) {
+  const uint32_t y = (a & 0x80000000u) | (b & 0x7FFFFFFFu);
+  return (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
+}
 
 __global__ void __launch_bounds__(GEN_NT)
 smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ keys, int nb,
                uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
                const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
-  __shared__ uint32_t ring[1024];
+  __shared__ uint32_t ring[2048];
   const int tid = threadIdx.x;
   if (blockIdx.x == 0) {
     for (int k = tid; k < MT_N; k += GEN_NT) { const uint32_t v = np_state[k]; ring[k] = v; keys[k] = v; }
     __syncthreads();
     const long long total = (long long)nb * MT_N;
-    for (long long base = MT_N; base < total; base += GEN_NT) {
-      const long long n = base + tid;
-      if (n < total) {
-        const uint32_t v = mt_mix(ring[(n - MT_N) & 1023], ring[(n - MT_N + 1) & 1023], ring[(n - (MT_N - MT_M)) & 1023]);
-        ring[n & 1023] = v;
-        keys[n] = v;
+    // Rounds of exactly 227 words: x[n-227] is then the word this thread produced one round earlier (kept in
+    // a register), and the two mixed words lie 397..624 back, i.e. at least one whole round behind even for
+    // the second of two consecutive rounds - so two rounds are produced per barrier.
+    const bool act = tid < 227;                              // every thread runs the loop: the barrier stays converged
+    uint32_t prev = act ? ring[MT_M + tid] : 0u;
+    for (long long base = MT_N; base < total; base += 2 * 227) {
+      if (act) {
+        const long long nA = base + tid, nB = nA + 227;
+        const uint32_t vA = prev ^ mt_g(ring[(nA - MT_N) & 2047], ring[(nA - MT_N + 1) & 2047]);
+        const uint32_t vB = vA ^ mt_g(ring[(nB - MT_N) & 2047], ring[(nB - MT_N + 1) & 2047]);
+        if (nA < total) { ring[nA & 2047] = vA; keys[nA] = vA; }
+        if (nB < total) { ring[nB & 2047] = vB; keys[nB] = vB; }
+        prev = vB;
       }
       __syncthreads();
     }
@@ -197,13 +210,19 @@ constexpr int E_STRIDE = 80;   // bytes per block of E (65 used; keeps the recor
 constexpr int E2_STRIDE = 144;
 __host__ __device__ inline long long rec_bytes(long long n_states) { return n_states * 4 + TB * 4 + E_STRIDE + E2_STRIDE; }
 
-// index after the 64 draws y[0..64) starting from s0 >= 1; e = draws consumed if it reaches 0 (s0 <= 64)
-__device__ __forceinline__ int walk_block(const uint32_t* y, int s0, int& e) {
+// index after the 64 draws y[0..64) starting from s0 >= 1; e = draws consumed if it reaches 0 (s0 <= 64).
+// ym = the same draws already masked with mask_for(s0): valid for the whole block when the index cannot
+// drop to the next smaller mask within 64 draws (s0 > (mask >> 1) + 64), which is most states - their
+// step is then a compare and a predicated decrement.
+__device__ __forceinline__ int walk_block(const uint32_t* y, const uint32_t* ym, int s0, int& e) {
   int s = s0;
   uint32_t m = mask_for((uint32_t)s);
   int thr = (int)(m >> 1);
   e = 0xFF;
-  if (s0 <= TB) {
+  if (s0 > thr + TB) {
+#pragma unroll 16
+    for (int k = 0; k < TB; ++k) s -= (ym[k] <= (uint32_t)s) ? 1 : 0;
+  } else if (s0 <= TB) {
     for (int k = 0; k < TB; ++k) {
       if (s <= thr) { m >>= 1; thr >>= 1; }
       const uint32_t v = y[k] & m;
@@ -226,6 +245,7 @@ smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ 
   extern __shared__ unsigned short fs[];          // [2][n_states]: F of the even / odd block
   __shared__ uint32_t y[2][TB];
   __shared__ unsigned char es[2][TB + 1];         // E of the even / odd block
+  __shared__ uint32_t yms[2][17][TB];             // the draws masked to b bits, b = 0..16
   const long long b0 = 2LL * blockIdx.x;
   const long long rb = rec_bytes(n_states);
   if (threadIdx.x < 2 * TB) {
@@ -235,11 +255,16 @@ smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ 
     reinterpret_cast<uint32_t*>(tab + (b0 + h) * rb + (long long)n_states * 4)[k] = v;
   }
   __syncthreads();
+  for (int q = threadIdx.x; q < 2 * 17 * TB; q += 256) {      // draws masked to 0..16 bits
+    const int h = q / (17 * TB), bits = (q / TB) % 17, k = q % TB;
+    yms[h][bits][k] = y[h][k] & ((1u << bits) - 1u);
+  }
+  __syncthreads();
   for (int s0 = threadIdx.x; s0 < n_states; s0 += 256) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       int e = 0xFF;
-      const int s = (s0 >= 1) ? walk_block(y[h], s0, e) : 0;
+      const int s = (s0 >= 1) ? walk_block(y[h], yms[h][32 - __clz(s0)], s0, e) : 0;
       fs[h * n_states + s0] = (unsigned short)s;
       unsigned char* rec = tab + (b0 + h) * rb;
       reinterpret_cast<unsigned short*>(rec)[s0] = (unsigned short)s;
