@@ -84,9 +84,13 @@ int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);
  * and np.random.get_state(); advanced in place.  scopes [R][2] = rel2scope values in dict order;
  * t_* the four [instances][L] int32 tables; n_max >= the largest scope.  scratch: caller-provided,
  * indnet_sampler_scratch_bytes(...) bytes.  Outputs: rows [B][n_s] (row ids, support class-major then
- * permuted queries), labels [B][N*Q], o_* [B][n_s][L].  status (device int[4]): [0] = 0 ok, 1 = a
- * sampled relation has fewer than K+Q instances, 2 = a scope exceeds n_max; [1..3] diagnostics (SM
- * cycles / 16 of the stream walk, carry passes, rounds). */
+ * permuted queries), labels [B][N*Q], o_* [B][n_s][L].  status (device int[16]): [0] = 0 ok, 1 = a
+ * sampled relation has fewer than K+Q instances, 2 = a scope exceeds n_max, 3 = the pre-generated
+ * stream budget (expected draws + 3 % + 8192) was exceeded; [1..3] diagnostics (SM cycles / 16 of the
+ * stream walk, table-jump runs, exact rows); [4..9] are written only by the timeline build.
+ * The NumPy stream is consumed through per-block transition tables (csrc/sampler.cu);
+ * n_max bounds the table width (at most ~12k instances per relation fit the walker's shared-memory
+ * ring, larger values are refused). */
 long long indnet_sampler_scratch_bytes(int B, int N, int K, int Q, int n_max);
 int indnet_sample_episodes(indnet_stream st, unsigned int* py_state, unsigned int* np_state, const int* scopes, int R,
                            const int* t_word, const int* t_pos1, const int* t_pos2, const int* t_mask, int L, int B,
