@@ -5,19 +5,24 @@
 //   * NumPy legacy global RandomState: np.random.choice(range(lo,hi), K+Q, False)   (:267, one per class)
 //     == lo + permutation(hi-lo)[:K+Q], then np.random.permutation(N*Q)            (:296)
 // Both are rejection samplers, so the stream position after an episode is data dependent and the
-// draws cannot be partitioned ahead of time.  Kernel 1 (one CTA) walks the streams:
-//   - MT19937 blocks of 624 words are regenerated cooperatively (3-phase parallel twist);
-//   - the Python draws (few) are taken by one thread; the pool / set algorithms of random.sample are
-//     restated literally;
-//   - the NumPy Fisher-Yates draws (~1000 per class) are consumed up to 256 at a time by the CTA:
-//     lane p's index is i - (#accepted before p), its mask follows from that index, and "accepted iff
-//     masked draw <= index" is a triangular system solved by a ballot/prefix-count fixed-point
-//     iteration (exact, and it crosses the mask changes inside a batch); accepted (i, j) pairs go to
-//     a j-list.
-// Kernel 2 turns each j-list into the first K+Q entries of its permutation WITHOUT simulating the
-// swaps: the value that ends at position p is found by tracing p backwards through the swap list
-// (identity start), one thread per output.  Kernel 3 assembles support||permuted-query row ids,
-// labels, and gathers the four [instances, L] int32 tables (:268-271, :286-307).
+// NumPy draws (~1000 per class) form one serial chain.  The chain is made cheap instead of parallel:
+//   G  smp_gen_kernel    the NumPy MT19937 stream for the whole batch (CTA 0) and, concurrently, the few
+//                        Python draws - random.sample's pool / set algorithms restated literally - plus
+//                        every job's permutation length (CTA 1);
+//   T  smp_table_kernel  for every 64-draw block and EVERY Fisher-Yates index the index after the block
+//                        (and after the pair of blocks) and the end offsets: job independent, built by
+//                        the whole GPU;
+//   W  smp_walk_kernel   one warp chains lookups through those tables (staged in shared memory by a
+//                        producer warp) and walks the unaligned stretches exactly, 32 draws per row:
+//                        lane p's index is i - (#accepted before p), its mask follows from that index,
+//                        and "accepted iff masked draw <= index" is a triangular system solved by a
+//                        ballot/prefix-count fixed-point iteration (exact across mask changes);
+//   F  smp_fill_kernel   replays the walker's logged runs in parallel -> accepted (i, j) pairs (j-lists).
+// sampler_trace_kernel turns each j-list into the first K+Q entries of its permutation WITHOUT
+// simulating the swaps: the value that ends at position p is found by tracing p backwards through the
+// swap list (identity start), one thread per output.  sampler_gather_kernel assembles
+// support||permuted-query row ids, labels, and gathers the four [instances, L] int32 tables (:268-271,
+// :286-307).
 // Stream states use the (key[624], pos) layout of random.getstate() / np.random.get_state(), so the
 // host can hand its streams in and take them back.
 #include "common.cuh"

@@ -110,6 +110,11 @@ class DeviceEpisodeSampler:
         s = int(self.status[0].item())
         if s == 1:
             raise ValueError("Cannot take a larger sample than population when 'replace=False'")
+        if s == 2:
+            raise IndnetError("device sampler: a relation has more instances than n_max=%d" % self.n_max)
+        if s == 3:
+            raise IndnetError("device sampler: the batch consumed more NumPy draws than the pre-generated stream "
+                              "budget (expected draws + 3 % + 8192); the streams were not advanced consistently")
         if s != 0:
             raise IndnetError("device sampler failed with status %d" % s)
 
