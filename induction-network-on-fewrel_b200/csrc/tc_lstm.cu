@@ -6,13 +6,16 @@
 // * MMA-M = gate units: four M=128 tiles, one per gate (i, j, f, o - the TF kernel column order), so
 //   TMEM lane m of every tile is unit m and one thread reads all four gates of its unit from its own
 //   lane; MMA-N = sentences (NS = 32), so a step's accumulators are 4 x NS TMEM columns.
-// * The weights [W_x^T | W_h^T] (bf16, 192 KB for u = 128) are loaded ONCE by TMA into 128-byte-swizzled
-//   shared memory and stay resident for all L steps.  x_t tiles stream in by TMA (double buffered, one
-//   step ahead); h_{t-1} is written by the gate threads straight into the swizzled B-operand layout.
+// * The weights are loaded ONCE and stay resident for all L steps: W_x^T (64 KB) by TMA into
+//   128-byte-swizzled shared memory, W_h^T - the operand of the serial, recurrent MMAs - into tensor
+//   memory (A-from-TMEM MMAs run at the math rate, not at the shared-memory read rate).  x_t tiles
+//   stream in by TMA (three buffers); h_{t-1} is written by the gate threads straight into the swizzled
+//   B-operand layout.  Two accumulator buffers let the x part of step s+1 be issued while the gate
+//   threads still read step s.
 // * Gate math (forget bias 1.0, no length masking - SURVEY A.1/A.2) runs on the accumulators right
 //   after tcgen05.ld; c stays in registers for the whole sequence.
-// Warps 0-7: gate threads (TMEM lane quarter = warp % 4, sentence half = warp / 4); thread 0 also
-// issues the TMA loads and the MMAs between its gate phases.
+// Warps 0-15: gate threads (TMEM lane quarter = warp % 4, sentence quarter = warp / 4); warp 16 issues the
+// TMA loads and the MMAs through one elected lane.
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "tc_common.cuh"
