@@ -191,7 +191,9 @@ def run_b200(args, w):
     smp = loader._device()
     smp.seed(rank)
     pipe_inputs = dict(word=pipe.word, pos1=pipe.pos1, pos2=pipe.pos2, mask=pipe.mask, label=pipe.label)
-    side = torch.cuda.Stream()
+    # the sampler of step t+1 runs at the lower priority: its table kernel fills the GPU and would otherwise take
+    # SMs from the training kernels of step t, which are the critical path
+    side = torch.cuda.Stream(priority=0)
     # resident input pool in HBM + pinned host copies for the e2e leg
     dev_pool, host_pool = [], []
     for inp, lab in batches:
@@ -202,7 +204,7 @@ def run_b200(args, w):
     # Gradient all-reduce in two pieces: M (first slot of the flat buffer, 95 % of the bytes) is final right
     # after the relation-module backward, so its all-reduce is issued then on a side stream and hides under
     # the attention / BPTT backward; the remaining slots go in one trailing all-reduce.
-    comm = torch.cuda.Stream()
+    comm = torch.cuda.Stream(priority=-1)
     m_end = store.offsets["w"]          # slots are laid out M, w, b, ... (engine.ParamStore)
 
     def on_grad_ready(name):
@@ -235,7 +237,7 @@ def run_b200(args, w):
         train_body()
         cur.wait_stream(side)
 
-    stream = torch.cuda.Stream()
+    stream = torch.cuda.Stream(priority=-1)
     graph = None
     with torch.cuda.stream(stream):
         pipe.set_inputs(*dev_pool[0])
