@@ -117,6 +117,10 @@ int indnet_embed_fwd_bf16(indnet_stream st, const int* word, const int* pos1, co
  * the word table is trainable, base.py:62-65).  Accumulates (+=). */
 int indnet_embed_bwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* dx,
                      float* dword_table, float* dpos1, float* dpos2, long long T, int E, int P, int pos_rows);
+/* Position-table gradients from a split input gradient: g[t][j] = dx_a[t*ld + col0 + j] (+ dx_b[...] when
+ * given), j < 2P (pos1 columns then pos2 columns).  Same scatter as indnet_embed_bwd. */
+int indnet_embed_pos_bwd2(indnet_stream st, const int* pos1, const int* pos2, const float* dx_a, const float* dx_b,
+                          int ld, int col0, float* dpos1, float* dpos2, long long T, int P, int pos_rows);
 
 /* ---- a3: rnn.BasicLSTMCell x2 + bidirectional_dynamic_rnn, model/graph.py:34-49 ---------------
  * xproj [2][X][L][4u] = x*W_x + bias per direction (gate order i,j,f,o); Wh_* [u][4u] (row stride 4u:
@@ -148,11 +152,15 @@ int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_f
  * saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h = rows
  * D.., staged into tensor memory, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
  * Writes dz_bf [2][X][L][4u] bf16 and, when dbias_fw / dbias_bw [4u] are given, the two LSTM bias
- * gradients (fp32 column sums of dz, formed in registers before the bf16 rounding). */
+ * gradients (fp32 column sums of dz, formed in registers before the bf16 rounding).  When dx2 is given
+ * (fp32 [2][X][L][16]) the kernel also forms the input gradient of features dx_first..D-1 (at most 16:
+ * the 2 x 5 position-embedding columns when the word table is frozen) per direction,
+ * dx2[dir][tok][f - dx_first] = sum_k dz[dir][tok][k] * kernel[f][k]; the caller adds the two directions
+ * (indnet_embed_pos_bwd2). */
 int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const void* cstate_bf,
                        const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
-                       float* dbias_bw, int X, int L, int D, int u, float keep_prob, unsigned long long seed,
-                       const long long* seed_step);
+                       float* dbias_bw, float* dx2, int dx_first, int X, int L, int D, int u, float keep_prob,
+                       unsigned long long seed, const long long* seed_step);
 /* out[c] = sum_r A[r][c] for a dense bf16 matrix [rows][cols] (bias gradients from the bf16 dz stream). */
 int indnet_colsum_bf16(indnet_stream st, const void* A, long long rows, int cols, float* out);
 

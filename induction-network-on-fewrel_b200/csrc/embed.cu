@@ -42,14 +42,14 @@ __global__ void embed_fwd_bf16_kernel(const int* __restrict__ word, const int* _
 // Position tables are tiny ([2L, P]) and every token hits them: accumulate in shared memory per
 // block, then one atomic per table entry per block.
 __global__ void embed_pos_bwd_kernel(const int* __restrict__ pos1, const int* __restrict__ pos2,
-                                     const float* __restrict__ dx, float* __restrict__ dp1,
-                                     float* __restrict__ dp2, long long T, int E, int P, int pos_rows,
-                                     long long tokens_per_block) {
+                                     const float* __restrict__ dx, const float* __restrict__ dx_b, int ld,
+                                     float* __restrict__ dp1, float* __restrict__ dp2, long long T, int E, int P,
+                                     int pos_rows, long long tokens_per_block) {
   extern __shared__ float sm[];  // [2][pos_rows*P]
   const int n = pos_rows * P;
   for (int i = threadIdx.x; i < 2 * n; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
-  const int D = E + 2 * P;
+  const int D = ld;                    // row stride of dx; E = first position column
   long long t0 = blockIdx.x * tokens_per_block;
   long long t1 = min(T, t0 + tokens_per_block);
   long long work = (t1 - t0) * (2 * P);
@@ -57,6 +57,7 @@ __global__ void embed_pos_bwd_kernel(const int* __restrict__ pos1, const int* __
     long long t = t0 + w / (2 * P);
     int j = (int)(w % (2 * P));
     float g = dx[t * D + E + j];
+    if (dx_b) g += dx_b[t * D + E + j];
     if (j < P) atomicAdd(&sm[pos1[t] * P + j], g);
     else atomicAdd(&sm[n + pos2[t] * P + (j - P)], g);
   }
@@ -105,13 +106,29 @@ extern "C" int indnet_embed_bwd(indnet_stream st_, const int* word, const int* p
   IN_REQUIRE(smem <= 48 * 1024, "embed_bwd: position tables too large for the shared-memory accumulator (%zu B)", smem);
   long long tpb = 512;        // ~150 CTAs at 77k tokens; each flushes its shared-memory tables once
   int blocks = ceil_div(T, tpb);
-  embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx, dpos1, dpos2, T, E, P, pos_rows, tpb);
+  embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx, nullptr, E + 2 * P, dpos1, dpos2, T, E, P, pos_rows, tpb);
   IN_LAUNCH_CHECK("embed_pos_bwd_kernel");
   if (dword_table) {
     IN_REQUIRE(word != nullptr, "embed_bwd: word ids needed for the trainable word table");
     embed_word_bwd_kernel<<<ceil_div(T * E, 256), 256, 0, st>>>(word, dx, dword_table, T, E, E + 2 * P);
     IN_LAUNCH_CHECK("embed_word_bwd_kernel");
   }
+  return INDNET_OK;
+}
+
+extern "C" int indnet_embed_pos_bwd2(indnet_stream st_, const int* pos1, const int* pos2, const float* dx_a,
+                                     const float* dx_b, int ld, int col0, float* dpos1, float* dpos2, long long T,
+                                     int P, int pos_rows) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(T >= 0 && P > 0 && pos_rows > 0 && ld >= col0 + 2 * P && col0 >= 0, "embed_pos_bwd2: bad sizes");
+  if (T == 0) return INDNET_OK;
+  IN_REQUIRE(pos1 && pos2 && dx_a && dpos1 && dpos2, "embed_pos_bwd2: null pointer");
+  size_t smem = sizeof(float) * 2 * pos_rows * P;
+  IN_REQUIRE(smem <= 48 * 1024, "embed_pos_bwd2: position tables too large for the shared-memory accumulator (%zu B)", smem);
+  long long tpb = 512;
+  int blocks = ceil_div(T, tpb);
+  embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx_a, dx_b, ld, dpos1, dpos2, T, col0, P, pos_rows, tpb);
+  IN_LAUNCH_CHECK("embed_pos_bwd_kernel");
   return INDNET_OK;
 }
 

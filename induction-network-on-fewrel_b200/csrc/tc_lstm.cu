@@ -16,6 +16,7 @@
 //   after tcgen05.ld; c stays in registers for the whole sequence.
 // Warps 0-15: gate threads (TMEM lane quarter = warp % 4, sentence quarter = warp / 4); warp 16 issues the
 // TMA loads and the MMAs through one elected lane.
+#include <cstring>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "tc_common.cuh"
@@ -335,26 +336,39 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 // Warps 0-15: gate-gradient threads; warp 16: MMA issuer.
 constexpr int LB_KB = 4 * LT_U / 64;                           // 8 K-blocks
 constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                // 32768
+constexpr int LB_WX_BYTES = LB_KB * 128 * 128;                 // 131072: W_x rows as a second A operand (dx path)
 constexpr int LB_SMEM = LB_Z_BYTES + 256 + 1024;
+constexpr int LB_SMEM_DX = 2 * LB_Z_BYTES + LB_WX_BYTES + 256 + 1024;   // dz double-buffered: dx MMAs outlive the step
+constexpr int LB_DX_LD = 16;                                   // dx2 row stride in floats (64-byte rows)
 constexpr int LB_THREADS = LT_THREADS + 32;
 
 struct LstmTcBwdP {
   const __nv_bfloat16* dhout; const __nv_bfloat16* gates_bf; const __nv_bfloat16* cstate; __nv_bfloat16* dz_bf;
   const __nv_bfloat16* wh_fw; const __nv_bfloat16* wh_bw;     // W_h = rows D.. of the bf16 TF kernels, [u][4u]
   float* dbias_fw; float* dbias_bw;     // optional: bias gradients (column sums of dz), accumulated with atomics
+  float* dx2; int dxn;                  // optional: dx2[dir][tok][16], the first dxn (<= 16) input-gradient features
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
 
-template <bool DROP>
+// DX: also form the input gradient dx^T[f, NS] = W_x[f, 4u] * dz^T of the step (rows n0.. of the TF kernel as a
+// second A operand, 128 KB in shared memory, its own accumulator and barrier): the MMAs run behind the
+// recurrent ones on an otherwise idle tensor pipe and replace a GEMM launch that re-read all of dz.
+template <bool DROP, bool DX>
 __global__ void __launch_bounds__(LB_THREADS, 1)
-tc_lstm_bwd_kernel(LstmTcBwdP p) {
+tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_constant__ CUtensorMap tmXb, LstmTcBwdP p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sZ = smem;                                   // [8 kb][NS rows][128 B]
-  uint64_t* mma_done = reinterpret_cast<uint64_t*>(sZ + LB_Z_BYTES);
+  // dz tile [8 kb][NS rows][128 B]; with DX two of them (step s uses buffer s & 1): the dx MMAs of step s
+  // still read dz(s) while the gate threads already write dz(s+1)
+  uint8_t* sZ = smem;
+  constexpr int ZBUFS = DX ? 2 : 1;
+  uint8_t* sWx = smem + ZBUFS * LB_Z_BYTES;             // DX only: [8 kb][128 rows][128 B]
+  uint64_t* mma_done = reinterpret_cast<uint64_t*>(sZ + ZBUFS * LB_Z_BYTES + (DX ? LB_WX_BYTES : 0));
   uint64_t* z_ready = mma_done + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_ready + 1);
+  uint64_t* dx_done = mma_done + 2;
+  uint64_t* wx_full = mma_done + 3;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_done + 4);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const bool gate_warp = warp < LT_THREADS / 32;
@@ -365,15 +379,23 @@ tc_lstm_bwd_kernel(LstmTcBwdP p) {
   if (threadIdx.x == 0) {
     mbar_init(mma_done, 1);
     mbar_init(z_ready, LT_THREADS);
+    mbar_init(dx_done, 1);
+    mbar_init(wx_full, 1);
     fence_barrier_init();
+    if (DX) {
+      const CUtensorMap* tmX = dir ? &tmXb : &tmXf;
+      tma_prefetch_desc(tmX);
+      mbar_expect_tx(wx_full, LB_WX_BYTES);
+      for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sWx + kb * 16384, tmX, wx_full, kb * 64, 0, 0);
+    }
   }
   __syncwarp();
-  if (warp == 0) tmem_alloc(tmem_slot, 512);            // W_h: 256 columns, dh_rec accumulator: NS columns
+  if (warp == 0) tmem_alloc(tmem_slot, 512);            // W_h: 256 columns, dh_rec accumulator: NS columns, dx accumulator: NS
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
-  const uint32_t wh_t = taddr, acc_t = taddr + 2 * LT_U;
+  const uint32_t wh_t = taddr, acc_t = taddr + 2 * LT_U, accx_t = acc_t + LT_NS;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
   const uint32_t z16 = smem_u32(sZ) >> 4;
   if (gate_warp) {
@@ -398,19 +420,45 @@ tc_lstm_bwd_kernel(LstmTcBwdP p) {
   tc_fence_after();
 
   if (!gate_warp) {
-    for (int step = 0; step + 1 < L; ++step) {          // the last step's dh_rec has no consumer
+    const uint32_t wx16 = smem_u32(sWx) >> 4;
+    if (DX) mbar_wait(wx_full, 0);
+    for (int step = 0; step < (DX ? L : L - 1); ++step) {
       mbar_wait(z_ready, step & 1);
       tc_fence_after();
+      const uint32_t zb16 = z16 + (DX ? (uint32_t)(step & 1) * (LB_Z_BYTES >> 4) : 0u);
       if (elect_one()) {
+        if (step + 1 < L) {                             // the last step's dh_rec has no consumer
 #pragma unroll
-        for (int kb = 0; kb < LB_KB; ++kb) {
+          for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t bd = smem_desc_sw128_k(z16, kb * (LT_NS * 128) + k4 * 32);
-            umma_bf16_ts(acc_t, wh_t + kb * 32 + k4 * 8, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            for (int k4 = 0; k4 < 4; ++k4) {
+              const uint64_t bd = smem_desc_sw128_k(zb16, kb * (LT_NS * 128) + k4 * 32);
+              umma_bf16_ts(acc_t, wh_t + kb * 32 + k4 * 8, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            }
           }
+          umma_commit(mma_done);
         }
-        umma_commit(mma_done);
+      }
+      __syncwarp();
+      if (DX) {
+        // Off the recurrence's critical path, own barrier - and issued only once the recurrent MMAs are done
+        // and the gate warps have had time to pull dh_rec out of tensor memory: shared-memory-operand MMAs
+        // keep the tensor pipe busy for ~1300 cycles and TMEM loads issued meanwhile wait behind them.
+        if (step + 1 < L) { mbar_wait(mma_done, step & 1); __nanosleep(256); }
+      }
+      if (elect_one()) {
+        if (DX) {
+#pragma unroll
+          for (int kb = 0; kb < LB_KB; ++kb) {
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4) {
+              const uint64_t ad = smem_desc_sw128_k(wx16, kb * 16384 + k4 * 32);
+              const uint64_t bd = smem_desc_sw128_k(zb16, kb * (LT_NS * 128) + k4 * 32);
+              umma_bf16(accx_t, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(dx_done);
+        }
       }
       __syncwarp();
     }
@@ -442,6 +490,25 @@ tc_lstm_bwd_kernel(LstmTcBwdP p) {
     const char* c_ptr = reinterpret_cast<const char*>(p.cstate) + e0 * 2;
     const char* do_ptr = reinterpret_cast<const char*>(p.dhout) + o0 * 2;
     char* z_ptr = reinterpret_cast<char*>(p.dz_bf) + (e0 - m) * 8 + m * 2;       // [tok][4u] bf16, column m
+    // dx2[dir][tok][16]: this thread's feature = its TMEM lane m (only lanes < dxn store), sentence q adds L rows
+    const bool dx_lane = DX && m < p.dxn;
+    char* x_ptr = DX ? reinterpret_cast<char*>(p.dx2) + ((e0 - m) / LT_U) * (LB_DX_LD * 4) + m * 4 : nullptr;
+    const uint32_t lanex_addr = accx_t + ((uint32_t)((warp & 3) * 32) << 16) + hf * LT_SPT;
+    auto store_dx = [&](int step_done) {                 // dx of processing step `step_done` (x_ptr still points at it)
+      if ((warp & 3) * 32 < p.dxn) {                     // warp-uniform: this lane quarter holds needed features
+        float dxv[LT_SPT];
+        mbar_wait(dx_done, step_done & 1);
+        __syncwarp();
+        tc_fence_after();
+        tmem_ld_spt(lanex_addr, dxv);
+        tmem_ld_wait();
+        if (dx_lane) {
+#pragma unroll
+          for (int q = 0; q < LT_SPT; ++q)
+            if ((valid >> q) & 1u) *reinterpret_cast<float*>(x_ptr + (unsigned long long)((uint32_t)L * (uint32_t)q) * (LB_DX_LD * 4)) = dxv[q];
+        }
+      }
+    };
     long long oi = o0;
     float sb_i = 0.f, sb_j = 0.f, sb_f = 0.f, sb_o = 0.f;     // this unit's bias-gradient partial sums
     float dcr[LT_SPT], cc[LT_SPT];
@@ -492,7 +559,7 @@ tc_lstm_bwd_kernel(LstmTcBwdP p) {
         sb_i += di; sb_j += dj; sb_f += df; sb_o += dob;
         const __nv_bfloat16 bi = __float2bfloat16(di), bj = __float2bfloat16(dj), bf = __float2bfloat16(df),
                             bo = __float2bfloat16(dob);
-        const uint32_t zp = zdst + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
+        const uint32_t zp = zdst + (DX ? (uint32_t)(step & 1) * LB_Z_BYTES : 0u) + sl * 128 + ((zchunk ^ (uint32_t)(sl & 7)) << 4);
         sts_bf16(zp, bi);
         sts_bf16(zp + 2 * (LT_NS * 128), bj);
         sts_bf16(zp + 4 * (LT_NS * 128), bf);
@@ -502,11 +569,14 @@ tc_lstm_bwd_kernel(LstmTcBwdP p) {
           gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
         }
       }
+      if (DX && step > 0) store_dx(step - 1);           // long complete by now; must precede this step's arrival
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(z_ready);
       g_ptr += estep * 8; c_ptr += estep * 2; do_ptr += ostep * 2; z_ptr += estep * 8; oi += ostep;
+      if (DX && step > 0) x_ptr += (estep / LT_U) * (LB_DX_LD * 4);
     }
+    if (DX) store_dx(L - 1);
     if (p.dbias_fw) {
       float* db = dir ? p.dbias_bw : p.dbias_fw;
       atomicAdd(db + m, sb_i); atomicAdd(db + LT_U + m, sb_j); atomicAdd(db + 2 * LT_U + m, sb_f); atomicAdd(db + 3 * LT_U + m, sb_o);
@@ -613,8 +683,8 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
 
 extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const void* gates_bf, const void* cstate_bf,
                                   const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
-                                  float* dbias_bw, int X, int L, int D, int u, float keep_prob,
-                                  unsigned long long seed, const long long* seed_step) {
+                                  float* dbias_bw, float* dx2, int dx_first, int X, int L, int D, int u,
+                                  float keep_prob, unsigned long long seed, const long long* seed_step) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0, "lstm_bwd_tc: bad sizes X=%d L=%d", X, L);
   IN_REQUIRE(u == LT_U && D > 0 && D <= LT_KX, "lstm_bwd_tc: specialised for hidden_size 128 and E+10 <= 64 (got u=%d D=%d)", u, D);
@@ -635,22 +705,39 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
     IN_CUDA(cudaMemsetAsync(dbias_fw, 0, sizeof(float) * 4 * LT_U, st));
     IN_CUDA(cudaMemsetAsync(dbias_bw, 0, sizeof(float) * 4 * LT_U, st));
   }
-  dim3 grid(ceil_div(X, LT_NS), 2);
-  if (keep_prob < 1.0f) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
-      attr_set = true;
-    }
-    tc_lstm_bwd_kernel<true><<<grid, LB_THREADS, LB_SMEM, st>>>(p);
-  } else {
-    static bool attr_set = false;
-    if (!attr_set) {
-      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB_SMEM));
-      attr_set = true;
-    }
-    tc_lstm_bwd_kernel<false><<<grid, LB_THREADS, LB_SMEM, st>>>(p);
+  p.dx2 = dx2; p.dxn = 0;
+  CUtensorMap tmXf, tmXb;
+  memset(&tmXf, 0, sizeof(tmXf));
+  memset(&tmXb, 0, sizeof(tmXb));
+  if (dx2) {
+    IN_REQUIRE(dx_first >= 0 && dx_first < D && D - dx_first <= LB_DX_LD,
+               "lstm_bwd_tc: the fused input gradient covers at most %d features (got first=%d of D=%d)", LB_DX_LD, dx_first, D);
+    p.dxn = D - dx_first;
+    // rows dx_first.. of the TF kernel [D+u][4u] as the A operand: box 64 (k) x 128 rows (rows past the matrix: zero fill)
+    const __nv_bfloat16* xf = (const __nv_bfloat16*)kernel_fw_bf + (long long)dx_first * 4 * LT_U;
+    const __nv_bfloat16* xb = (const __nv_bfloat16*)kernel_bw_bf + (long long)dx_first * 4 * LT_U;
+    int rc = make_tmap_bf16(&tmXf, xf, 4 * LT_U, D + LT_U - dx_first, 4 * LT_U, 1, 0, 64, 128);
+    if (rc) return rc;
+    rc = make_tmap_bf16(&tmXb, xb, 4 * LT_U, D + LT_U - dx_first, 4 * LT_U, 1, 0, 64, 128);
+    if (rc) return rc;
   }
+  dim3 grid(ceil_div(X, LT_NS), 2);
+  const bool drop = keep_prob < 1.0f;
+#define LB_LAUNCH(DROP_, DX_)                                                                                   \
+  do {                                                                                                          \
+    static bool attr_set = false;                                                                               \
+    const int smem = DX_ ? LB_SMEM_DX : LB_SMEM;                                                                \
+    if (!attr_set) {                                                                                            \
+      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+      attr_set = true;                                                                                          \
+    }                                                                                                           \
+    tc_lstm_bwd_kernel<DROP_, DX_><<<grid, LB_THREADS, smem, st>>>(tmXf, tmXb, p);                                \
+  } while (0)
+  if (drop && dx2) LB_LAUNCH(true, true);
+  else if (drop) LB_LAUNCH(true, false);
+  else if (dx2) LB_LAUNCH(false, true);
+  else LB_LAUNCH(false, false);
+#undef LB_LAUNCH
   IN_LAUNCH_CHECK("tc_lstm_bwd_kernel");
   return INDNET_OK;
 }

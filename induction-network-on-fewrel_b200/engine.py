@@ -467,6 +467,7 @@ class EpisodePipeline:
             self.dpre_bf = h(c.T, c.H)
             self.dz_bf = h(2, c.T, 4 * c.u)
             self.dhout_bf = h(c.T, c.H) if self.tc_lstm else None
+            self.dx2 = f(2, c.T, 16) if self.tc_lstm else None
         self._bwd_ready = True
 
     def backward(self):
@@ -579,10 +580,14 @@ class EpisodePipeline:
         else:
             self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
                      splitk=1, tag="attn_dh")
+        # with a frozen word table only the 2 x 5 position columns of dx are needed: the BPTT kernel forms
+        # them itself (per direction) instead of two GEMM launches that would re-read all of dz
+        fused_dx = self.tc_lstm and not self.trainable_words and c.D - c.E <= 16
         if self.tc_lstm:
             self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate_bf),
                        ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), ptr(p.grad(FW_B)),
-                       ptr(p.grad(BW_B)), c.X, c.L, c.D, c.u, self._last_keep, self.seed, ptr(p.global_step))
+                       ptr(p.grad(BW_B)), ptr(self.dx2) if fused_dx else None, c.E if fused_dx else 0,
+                       c.X, c.L, c.D, c.u, self._last_keep, self.seed, ptr(p.global_step))
         else:
             wh_fw = p.view(FW_K)[c.D:]
             wh_bw = p.view(BW_K)[c.D:]
@@ -596,8 +601,9 @@ class EpisodePipeline:
             self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
             if not self.tc_lstm:
                 self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))
-            self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
-                     C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
+            if not fused_dx:
+                self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
+                         C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
         g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
         self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
         self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
@@ -605,8 +611,12 @@ class EpisodePipeline:
         if self.trainable_words:
             gw = p.grad("word_embedding")
             self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
-        self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
-                   ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+        if fused_dx:
+            self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
+                       ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
+        else:
+            self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
+                       ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
 
     # ------------------------------------------------------------------ update (model/base.py:94-99)
     def adam(self, grad_scale: float = 1.0):
