@@ -191,21 +191,24 @@ int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* den
 
 /* bf16 tensor-core mode variants: hout_bf / proj_bf are the bf16 copies [X][L][H]; dpre_bf is written in
  * bf16 (the operand format of the Dense-gradient GEMMs); dsum_part [X][H] (optional) receives the
- * per-sentence fp32 sums of dpre over time (Dense-bias gradient partials).  Everything else as above. */
+ * per-sentence fp32 sums of dpre over time (Dense-bias gradient partials); enc_a_bf / enc_b_bf (optional)
+ * receive bf16 copies of the encodings in the same split layout.  Everything else as above. */
 int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
-                              const float* w_a2, float* enc_a, float* enc_b, float* alphas, int X, int L, int H,
-                              int group, int split);
+                              const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
+                              float* alphas, int X, int L, int H, int group, int split);
 int indnet_attn_pool_bwd_bf16(indnet_stream st, const float* denc_a, const float* denc_b, const void* hout_bf,
                               const void* proj_bf, const float* alphas, const float* w_a2, float* dhout,
                               void* dpre_bf, float* dw2_part, float* dsum_part, int X, int L, int H, int group,
                               int split);
 
 /* ---- a6/a7: dynamic_routing + squash, model/layer_module.py:101-162 ---------------------------
- * ehat [BC][K][H] = e_s*W_s; b_in [BC][K] or NULL (zeros, model/graph.py:71); cvec [BC][H]. K <= 32. */
-int indnet_routing_fwd(indnet_stream st, const float* ehat, const float* b_in, float* cvec, int BC, int K, int H,
-                       int iters);
+ * ehat [BC][K][H] = e_s*W_s; b_in [BC][K] or NULL (zeros, model/graph.py:71); cvec [BC][H]. K <= 32.
+ * cvec_bf / dehat_bf (optional, may be NULL): bf16 copies of the outputs written in the same pass (operands
+ * of the bf16-mode GEMMs that follow). */
+int indnet_routing_fwd(indnet_stream st, const float* ehat, const float* b_in, float* cvec, void* cvec_bf, int BC,
+                       int K, int H, int iters);
 int indnet_routing_bwd(indnet_stream st, const float* ehat, const float* b_in, const float* dcvec, float* dehat,
-                       int BC, int K, int H, int iters);
+                       void* dehat_bf, int BC, int K, int H, int iters);
 int indnet_squash_fwd(indnet_stream st, const float* v, float* out, int rows, int H);
 int indnet_squash_bwd(indnet_stream st, const float* v, const float* dout, float* dv, int rows, int H);
 
@@ -218,10 +221,11 @@ int indnet_ntn_head_fwd(indnet_stream st, const float* V, const float* w, const 
 /* out2[0] = loss (mean over rows*N), out2[1] = accuracy. */
 int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, int rows, int N);
 /* Upstream gradient: dprobs [rows][N] when not NULL, else the fused mean-squared-error gradient
- * scale*2(p-y) with scale = 1/(rows*N).  Overwrites dlogit [rows][N], dV [rows][N*S], dw, db. */
+ * scale*2(p-y) with scale = 1/(rows*N).  Overwrites dlogit [rows][N], dV [rows][N*S], dw, db; dV_bf (optional)
+ * receives a bf16 copy of dV with rows padded to ld_bf elements (zeros past N*S), the TMA operand format. */
 int indnet_ntn_head_bwd(indnet_stream st, const float* V, const float* w, const float* probs, const int* labels,
-                        const float* dprobs, float* dlogit, float* dV, float* dw, float* db, int rows, int N, int S,
-                        float scale);
+                        const float* dprobs, float* dlogit, float* dV, void* dV_bf, int ld_bf, float* dw, float* db,
+                        int rows, int N, int S, float scale);
 
 /* ---- a11: build_optimize, model/base.py:94-99 ---------------------------------------------------
  * One fused TF-form Adam update over a flat buffer.  global_step: device int64, read for the staircase

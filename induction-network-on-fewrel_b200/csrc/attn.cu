@@ -148,7 +148,8 @@ constexpr int ATT_TG = ATT_NT / 32;      // time groups
 __global__ void __launch_bounds__(ATT_NT)
 attn_pool_fwd_v8_kernel(const __nv_bfloat16* __restrict__ hout, const __nv_bfloat16* __restrict__ proj,
                         const int* __restrict__ mask, const float* __restrict__ w2, float* __restrict__ enc_a,
-                        float* __restrict__ enc_b, float* __restrict__ alphas, int L, int H, int group, int split) {
+                        float* __restrict__ enc_b, __nv_bfloat16* enc_a_bf, __nv_bfloat16* enc_b_bf,
+                        float* __restrict__ alphas, int L, int H, int group, int split) {
   extern __shared__ float sm[];   // sc[L] | red[ATT_TG][H]
   float* sc = sm;
   float* red = sm + L;
@@ -206,11 +207,13 @@ attn_pool_fwd_v8_kernel(const __nv_bfloat16* __restrict__ hout, const __nv_bfloa
   }
   __syncthreads();
   float* enc = split_row(enc_a, enc_b, x, group, split, H);
+  __nv_bfloat16* enc_bf = enc_a_bf ? split_row(enc_a_bf, enc_b_bf, x, group, split, H) : nullptr;
   for (int h = threadIdx.x; h < H; h += ATT_NT) {
     float acc = 0.f;
 #pragma unroll
     for (int g = 0; g < ATT_TG; ++g) acc += red[g * H + h];
     enc[h] = acc;
+    if (enc_bf) enc_bf[h] = __float2bfloat16(acc);      // operand copy for the bf16 GEMMs that follow
   }
 }
 
@@ -323,10 +326,11 @@ extern "C" int indnet_attn_pool_bwd(indnet_stream st_, const float* denc_a, cons
 // bf16 tensor-core mode: same kernels reading the bf16 copies of h and proj (and writing dpre in bf16,
 // the operand format of the Dense-gradient GEMMs), which halves their HBM traffic.
 extern "C" int indnet_attn_pool_fwd_bf16(indnet_stream st_, const void* hout_bf, const void* proj_bf, const int* mask,
-                                         const float* w_a2, float* enc_a, float* enc_b, float* alphas, int X, int L,
-                                         int H, int group, int split) {
+                                         const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
+                                         float* alphas, int X, int L, int H, int group, int split) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0 && H > 0 && L <= 8192, "attn_pool_fwd_bf16: bad sizes X=%d L=%d H=%d", X, L, H);
+  IN_REQUIRE(!enc_a_bf || split == group || enc_b_bf, "attn_pool_fwd_bf16: second bf16 output missing");
   if (X == 0) return INDNET_OK;
   IN_REQUIRE(hout_bf && proj_bf && mask && w_a2 && enc_a && alphas, "attn_pool_fwd_bf16: null pointer");
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_pool_fwd_bf16: bad group/split %d/%d", group, split);
@@ -335,13 +339,20 @@ extern "C" int indnet_attn_pool_fwd_bf16(indnet_stream st_, const void* hout_bf,
                   sizeof(float) * (L + ATT_TG * H) <= 48 * 1024;
   if (v8) {
     attn_pool_fwd_v8_kernel<<<X, ATT_NT, sizeof(float) * (L + ATT_TG * H), st>>>(
-        (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, mask, w_a2, enc_a, enc_b, alphas, L, H, group, split);
+        (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, mask, w_a2, enc_a, enc_b,
+        (__nv_bfloat16*)enc_a_bf, (__nv_bfloat16*)enc_b_bf, alphas, L, H, group, split);
     IN_LAUNCH_CHECK("attn_pool_fwd_v8_kernel");
     return INDNET_OK;
   }
   attn_pool_fwd_kernel<__nv_bfloat16><<<X, ATT_NT, sizeof(float) * L, st>>>(
       (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, mask, w_a2, enc_a, enc_b, alphas, L, H, group, split);
   IN_LAUNCH_CHECK("attn_pool_fwd_kernel<bf16>");
+  if (enc_a_bf) {                  // generic path: the copies are a separate cast
+    const long long na = (long long)(X / group) * split * H, nb = (long long)(X / group) * (group - split) * H;
+    int rc = indnet_cast_bf16(st_, enc_a, enc_a_bf, na);
+    if (rc) return rc;
+    if (nb > 0) { rc = indnet_cast_bf16(st_, enc_b, enc_b_bf, nb); if (rc) return rc; }
+  }
   return INDNET_OK;
 }
 

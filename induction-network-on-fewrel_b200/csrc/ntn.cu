@@ -7,6 +7,7 @@
 //   v = relu(V) ; logits[q, c'] = sum_{c,k} v[q, c*S+k] * w[(k*N + c), c'] + b[c'] ; probs = sigmoid
 // - w keeps the reference's slice-major row order k*N + c (concat(axis=0) at :35, transpose at :37) -
 // then the per-query squared error against the one-hot label and the first-max argmax hit.
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "../../include/indnet.h"
@@ -81,7 +82,8 @@ __global__ void loss_acc_reduce_kernel(const float* __restrict__ loss_part, cons
 __global__ void __launch_bounds__(NTN_NT)
 ntn_head_bwd_kernel(const float* __restrict__ V, const float* __restrict__ w, const float* __restrict__ probs,
                     const int* __restrict__ labels, const float* __restrict__ dprobs,
-                    float* __restrict__ dlogit, float* __restrict__ dV, int N, int S, float scale) {
+                    float* __restrict__ dlogit, float* __restrict__ dV, __nv_bfloat16* __restrict__ dV_bf, int ld_bf,
+                    int N, int S, float scale) {
   extern __shared__ float dl[];   // [N]
   const int row = blockIdx.x;
   const int NS = N * S;
@@ -105,7 +107,10 @@ ntn_head_bwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
       for (int cp = 0; cp < N; ++cp) g = fmaf(wr[cp], dl[cp], g);
     }
     dV[(long long)row * NS + r] = g;
+    if (dV_bf) dV_bf[(long long)row * ld_bf + r] = __float2bfloat16(g);
   }
+  // bf16 rows are padded to a 16-byte multiple for TMA: zero the tail
+  if (dV_bf) for (int r = NS + threadIdx.x; r < ld_bf; r += NTN_NT) dV_bf[(long long)row * ld_bf + r] = __float2bfloat16(0.f);
 }
 
 // dw[(k*N+c), c'] += sum_rows relu(V[row, c*S+k]) * dlogit[row, c'] over a chunk of rows.
@@ -166,15 +171,16 @@ extern "C" int indnet_loss_acc_reduce(indnet_stream st_, const float* loss_part,
 }
 
 extern "C" int indnet_ntn_head_bwd(indnet_stream st_, const float* V, const float* w, const float* probs,
-                                   const int* labels, const float* dprobs, float* dlogit, float* dV, float* dw,
-                                   float* db, int rows, int N, int S, float scale) {
+                                   const int* labels, const float* dprobs, float* dlogit, float* dV, void* dV_bf,
+                                   int ld_bf, float* dw, float* db, int rows, int N, int S, float scale) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(rows >= 0 && N > 0 && S > 0, "ntn_head_bwd: bad sizes rows=%d N=%d S=%d", rows, N, S);
   IN_REQUIRE(N <= NTN_NT, "ntn_head_bwd: N=%d classes exceeds %d", N, NTN_NT);
   IN_REQUIRE(V && w && probs && (labels || dprobs) && dlogit && dV && dw && db, "ntn_head_bwd: null pointer");
+  IN_REQUIRE(!dV_bf || ld_bf >= N * S, "ntn_head_bwd: bf16 row stride %d shorter than N*S", ld_bf);
   IN_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)N * S * N, st));
   if (rows == 0) { IN_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * N, st)); return INDNET_OK; }
-  ntn_head_bwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, probs, labels, dprobs, dlogit, dV, N, S, scale);
+  ntn_head_bwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, probs, labels, dprobs, dlogit, dV, (__nv_bfloat16*)dV_bf, ld_bf, N, S, scale);
   IN_LAUNCH_CHECK("ntn_head_bwd_kernel");
   int rpb = 64;
   int gy = ceil_div(rows, rpb);

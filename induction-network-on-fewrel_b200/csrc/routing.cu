@@ -5,6 +5,7 @@
 //   b += e_hat . c (:143-147).  The coupling logits live one-per-lane (K <= 32) and every reduction is
 //   a warp shuffle.  The backward recomputes the iterations and back-propagates through all of them
 //   (TF autodiff has no stop_gradient on this path).
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "../../include/indnet.h"
@@ -23,7 +24,7 @@ __device__ __forceinline__ float squash_factor_grad(float s) {
 
 __global__ void __launch_bounds__(RT_WARPS * 32)
 routing_fwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in, float* __restrict__ cvec,
-                   int BC, int K, int H, int iters) {
+                   __nv_bfloat16* __restrict__ cvec_bf, int BC, int K, int H, int iters) {
   extern __shared__ float sm[];
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int w = blockIdx.x * RT_WARPS + warp;
@@ -59,12 +60,16 @@ routing_fwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_i
     }
     __syncwarp();
   }
-  for (int h = lane; h < H; h += 32) cvec[(long long)w * H + h] = cv[h];
+  for (int h = lane; h < H; h += 32) {
+    cvec[(long long)w * H + h] = cv[h];
+    if (cvec_bf) cvec_bf[(long long)w * H + h] = __float2bfloat16(cv[h]);   // operand copy for the bf16 GEMMs
+  }
 }
 
 __global__ void __launch_bounds__(RT_WARPS * 32)
 routing_bwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in,
-                   const float* __restrict__ dcvec, float* __restrict__ dehat, int BC, int K, int H, int iters) {
+                   const float* __restrict__ dcvec, float* __restrict__ dehat, __nv_bfloat16* __restrict__ dehat_bf,
+                   int BC, int K, int H, int iters) {
   extern __shared__ float sm[];
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int w = blockIdx.x * RT_WARPS + warp;
@@ -148,7 +153,9 @@ routing_bwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_i
       for (int h = lane; h < H; h += 32) {
         const float val = dkk * dch[h] + dbk * cs[r * H + h];
         const long long o = (long long)k * H + h;
-        de[o] = last ? val : de[o] + val;
+        const float tot = last ? val : de[o] + val;
+        de[o] = tot;
+        if (dehat_bf && r == 0) dehat_bf[(long long)w * K * H + o] = __float2bfloat16(tot);   // final value
       }
     }
     __syncwarp();
@@ -189,8 +196,8 @@ __global__ void squash_bwd_kernel(const float* __restrict__ v, const float* __re
 
 using namespace indnet;
 
-extern "C" int indnet_routing_fwd(indnet_stream st_, const float* ehat, const float* b_in, float* cvec, int BC, int K,
-                                  int H, int iters) {
+extern "C" int indnet_routing_fwd(indnet_stream st_, const float* ehat, const float* b_in, float* cvec, void* cvec_bf,
+                                  int BC, int K, int H, int iters) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(BC >= 0 && K > 0 && H > 0 && iters > 0, "routing_fwd: bad sizes BC=%d K=%d H=%d iters=%d", BC, K, H, iters);
   IN_REQUIRE(K <= 32, "routing_fwd: K=%d support instances per class exceeds the warp-per-class limit of 32", K);
@@ -198,13 +205,13 @@ extern "C" int indnet_routing_fwd(indnet_stream st_, const float* ehat, const fl
   IN_REQUIRE(ehat && cvec, "routing_fwd: null pointer");
   size_t smem = sizeof(float) * RT_WARPS * (H + 32);
   IN_REQUIRE(smem <= 48 * 1024, "routing_fwd: H=%d too large", H);
-  routing_fwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, cvec, BC, K, H, iters);
+  routing_fwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, cvec, (__nv_bfloat16*)cvec_bf, BC, K, H, iters);
   IN_LAUNCH_CHECK("routing_fwd_kernel");
   return INDNET_OK;
 }
 
 extern "C" int indnet_routing_bwd(indnet_stream st_, const float* ehat, const float* b_in, const float* dcvec,
-                                  float* dehat, int BC, int K, int H, int iters) {
+                                  float* dehat, void* dehat_bf, int BC, int K, int H, int iters) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(BC >= 0 && K > 0 && H > 0 && iters > 0, "routing_bwd: bad sizes BC=%d K=%d H=%d iters=%d", BC, K, H, iters);
   IN_REQUIRE(K <= 32, "routing_bwd: K=%d support instances per class exceeds the warp-per-class limit of 32", K);
@@ -215,7 +222,7 @@ extern "C" int indnet_routing_bwd(indnet_stream st_, const float* ehat, const fl
   IN_REQUIRE(smem <= 227 * 1024, "routing_bwd: H=%d x iters=%d does not fit shared memory", H, iters);
   if (smem > 48 * 1024)
     IN_CUDA(cudaFuncSetAttribute(routing_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  routing_bwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, dcvec, dehat, BC, K, H, iters);
+  routing_bwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, dcvec, dehat, (__nv_bfloat16*)dehat_bf, BC, K, H, iters);
   IN_LAUNCH_CHECK("routing_bwd_kernel");
   return INDNET_OK;
 }

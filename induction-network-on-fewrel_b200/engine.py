@@ -380,7 +380,7 @@ class EpisodePipeline:
                    ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
         # a6/a7: e_hat = e_s W_s once, then the routing iterations
         self._gemm(0, 0, c.B * c.NK, c.H, c.H, ptr(self.es), c.H, ptr(p.view("W_s")), c.H, ptr(self.ehat), c.H, tag="routing_transform")
-        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
+        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), None, c.B * c.N, c.K, c.H, c.iters)
         # a8: T'[b,c][k][j] = cv M' ; V[b][q][c*S+k] = qe_b T'_b^T
         self._gemm(0, 0, c.B * c.N, c.S * c.H, c.H, ptr(self.cvec), c.H, ptr(p.view("M")), c.S * c.H,
                    ptr(self.Tp), c.S * c.H, tag="ntn_stage1")
@@ -423,16 +423,15 @@ class EpisodePipeline:
         self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, Cb=self.proj_bf, bias=p.view(ATT_B),
                  act=1, tag="attn_dense")
         self._call("indnet_attn_pool_fwd_bf16", ptr(self.hout_bf), ptr(self.proj_bf), ptr(self.mask),
-                   ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
-        self._cast(self.es, self.es_bf, "es")
+                   ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.es_bf), ptr(self.eq_bf), ptr(self.alphas),
+                   c.X, c.L, c.H, c.n_s, c.NK)
         self._tc(0, 1, c.B * c.NK, c.H, c.H, self.es_bf, c.H, p.view_bf("W_s"), c.H, C=self.ehat,
                  tag="routing_transform")
-        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), c.B * c.N, c.K, c.H, c.iters)
-        self._cast(self.cvec, self.cvec_bf, "cvec")
+        self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), ptr(self.cvec_bf), c.B * c.N, c.K, c.H,
+                   c.iters)
         self._tc(0, 1, c.B * c.N, c.S * c.H, c.H, self.cvec_bf, c.H, p.view_bf("M"), c.S * c.H, Cb=self.Tp_bf,
                  tag="ntn_stage1")
         NS = c.N * c.S
-        self._cast(self.eq, self.eq_bf, "eq")
         # V_b[n_q, N*S] = qe_b [n_q, H] * T'_b^T (T'_b stored [N*S][H]: K-major) - one batch entry per episode
         self._tc(0, 0, c.n_q, NS, c.H, self.eq_bf, c.H, self.Tp_bf, c.H, C=self.V, ldc=NS, batch=c.B,
                  sA=c.n_q * c.H, sB=NS * c.H, sC=c.n_q * NS, tag="ntn_stage2")
@@ -482,7 +481,7 @@ class EpisodePipeline:
         rows = c.B * c.n_q
         # loss + head
         self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
-                   None, ptr(self.dlogit), ptr(self.dV), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
+                   None, ptr(self.dlogit), ptr(self.dV), None, 0, ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
                    1.0 / (rows * c.N))
         # dqe_b = dV_b T'_b ; dT'_b = dV_b^T qe_b
         self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
@@ -497,7 +496,7 @@ class EpisodePipeline:
         self._gemm(0, 1, c.B * c.N, c.H, c.S * c.H, ptr(self.dTp), c.S * c.H, ptr(p.view("M")), c.S * c.H,
                    ptr(self.dcvec), c.H, tag="ntn_dcv")
         # routing
-        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
+        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), None,
                    c.B * c.N, c.K, c.H, c.iters)
         self._gemm(0, 1, c.B * c.NK, c.H, c.H, ptr(self.dehat), c.H, ptr(p.view("W_s")), c.H, ptr(self.des), c.H, tag="routing_des")
         self._gemm(1, 0, c.H, c.H, c.B * c.NK, ptr(self.es), c.H, ptr(self.dehat), c.H, ptr(p.grad("W_s")), c.H, tag="routing_dWs")
@@ -537,13 +536,10 @@ class EpisodePipeline:
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
+        # dV rows are N*S wide (1000 B in bf16): the bf16 copy has rows padded to a 16-byte multiple for TMA
         self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
-                   None, ptr(self.dlogit), ptr(self.dV), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
-                   1.0 / (rows * c.N))
-        # dV rows are N*S wide (1000 B in bf16): cast into rows padded to a 16-byte multiple for TMA
-        self._tag = "cast_bf16:dV"
-        self._call("indnet_cast_bf16_rows", ptr(self.dV), ptr(self.dV_bf), rows, NS, self.NSp)
-        self._tag = None
+                   None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, ptr(p.grad("w")), ptr(p.grad("b")),
+                   rows, c.N, c.S, 1.0 / (rows * c.N))
         # dqe_b = dV_b [n_q, N*S] * T'_b [N*S, H] ; dT'_b = dV_b^T [N*S, n_q] * qe_b [n_q, H]
         self._tc(0, 1, c.n_q, c.H, NS, self.dV_bf, self.NSp, self.Tp_bf, c.H, C=self.deq, ldc=c.H, batch=c.B,
                  sA=c.n_q * self.NSp, sB=NS * c.H, sC=c.n_q * c.H, splitk=1, tag="ntn_dqe")
@@ -556,9 +552,8 @@ class EpisodePipeline:
             self.grad_ready_hook("M")
         self._tc(0, 0, c.B * c.N, c.H, c.S * c.H, self.dTp_bf, c.S * c.H, p.view_bf("M"), c.S * c.H, C=self.dcvec,
                  tag="ntn_dcv")
-        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat),
+        self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), ptr(self.dehat_bf),
                    c.B * c.N, c.K, c.H, c.iters)
-        self._cast(self.dehat, self.dehat_bf, "dehat")
         self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
         self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
         # d(loss)/d(h): pooling path alpha_t * denc + Dense path dpre * W_a1^T.  With the tensor-core LSTM the

@@ -176,7 +176,7 @@ class _DynamicRouting(torch.autograd.Function):
         ehat = torch.empty_like(e)
         _gemm(0, 0, BC * K, H, H, e, H, w, H, ehat, H)
         cvec = torch.empty(BC, H, device=e.device)
-        _call("indnet_routing_fwd", ptr(ehat), ptr(b), ptr(cvec), BC, K, H, iters)
+        _call("indnet_routing_fwd", ptr(ehat), ptr(b), ptr(cvec), None, BC, K, H, iters)
         ctx.save_for_backward(e, w, b, ehat)
         ctx.meta = (tuple(inp.shape), BC, K, H, iters)
         return cvec.view(*lead, H)
@@ -186,7 +186,7 @@ class _DynamicRouting(torch.autograd.Function):
         e, w, b, ehat = ctx.saved_tensors
         shape, BC, K, H, iters = ctx.meta
         dehat = torch.empty_like(ehat)
-        _call("indnet_routing_bwd", ptr(ehat), ptr(b), ptr(_f32(dc).view(BC, H)), ptr(dehat), BC, K, H, iters)
+        _call("indnet_routing_bwd", ptr(ehat), ptr(b), ptr(_f32(dc).view(BC, H)), ptr(dehat), None, BC, K, H, iters)
         de = torch.empty_like(e)
         _gemm(0, 1, BC * K, H, H, dehat, H, w, H, de, H)
         dW = torch.empty_like(w)
@@ -250,8 +250,8 @@ class _NeuralTensorLayer(torch.autograd.Function):
         dV = torch.empty(B * nq, NS, device=dev)
         dw = torch.empty_like(wc)
         db = torch.empty(C, device=dev)
-        _call("indnet_ntn_head_bwd", ptr(V), ptr(wc), ptr(probs), None, ptr(dp), ptr(dlogit), ptr(dV), ptr(dw),
-              ptr(db), B * nq, C, S, 1.0)
+        _call("indnet_ntn_head_bwd", ptr(V), ptr(wc), ptr(probs), None, ptr(dp), ptr(dlogit), ptr(dV), None, 0,
+              ptr(dw), ptr(db), B * nq, C, S, 1.0)
         dqe = torch.empty_like(qeb)
         _gemm(0, 0, nq, H, NS, dV, NS, Tp, H, dqe, H, batch=B, sA=nq * NS, sB=NS * H, sC=nq * H)
         dTp = torch.empty_like(Tp)

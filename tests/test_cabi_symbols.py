@@ -24,14 +24,14 @@ def test_header_parses_and_library_exports_every_symbol():
 def test_argument_errors_are_reported_not_thrown():
     dll = _lib.LIB.load()
     # bad sizes are rejected before any CUDA call
-    rc = dll.indnet_routing_fwd(None, None, None, None, 4, 33, 16, 3)
+    rc = dll.indnet_routing_fwd(None, None, None, None, None, 4, 33, 16, 3)
     assert rc != 0 and "warp-per-class limit" in _lib.LIB.last_error()
     rc = dll.indnet_lstm_fwd(None, None, None, None, None, None, None, None, 2, 0, 8, 1.0, 0, None)
     assert rc != 0 and "bad sizes" in _lib.LIB.last_error()
     with pytest.raises(_lib.IndnetError, match="keep_prob"):
         _lib.LIB.call("indnet_lstm_fwd", None, None, None, None, None, None, None, None, 2, 3, 8, 0.0, 0, None)
     # empty inputs are a no-op success
-    assert dll.indnet_routing_fwd(None, None, None, None, 0, 3, 16, 3) == 0
+    assert dll.indnet_routing_fwd(None, None, None, None, None, 0, 3, 16, 3) == 0
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
