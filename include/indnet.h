@@ -192,14 +192,16 @@ int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* den
 /* bf16 tensor-core mode variants: hout_bf / proj_bf are the bf16 copies [X][L][H]; dpre_bf is written in
  * bf16 (the operand format of the Dense-gradient GEMMs); dsum_part [X][H] (optional) receives the
  * per-sentence fp32 sums of dpre over time (Dense-bias gradient partials); enc_a_bf / enc_b_bf (optional)
- * receive bf16 copies of the encodings in the same split layout.  Everything else as above. */
+ * receive bf16 copies of the encodings in the same split layout; dw2_sum / dsum_sum [H] (optional, H % 8 == 0)
+ * receive the sums over sentences of dw2_part / dsum_part directly (the W_a2 and Dense-bias gradients), in
+ * which case the partial buffers may be NULL.  Everything else as above. */
 int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
                               const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
                               float* alphas, int X, int L, int H, int group, int split);
 int indnet_attn_pool_bwd_bf16(indnet_stream st, const float* denc_a, const float* denc_b, const void* hout_bf,
                               const void* proj_bf, const float* alphas, const float* w_a2, float* dhout,
-                              void* dpre_bf, float* dw2_part, float* dsum_part, int X, int L, int H, int group,
-                              int split);
+                              void* dpre_bf, float* dw2_part, float* dsum_part, float* dw2_sum, float* dsum_sum,
+                              int X, int L, int H, int group, int split);
 
 /* ---- a6/a7: dynamic_routing + squash, model/layer_module.py:101-162 ---------------------------
  * ehat [BC][K][H] = e_s*W_s; b_in [BC][K] or NULL (zeros, model/graph.py:71); cvec [BC][H]. K <= 32.

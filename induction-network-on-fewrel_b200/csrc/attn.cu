@@ -221,8 +221,8 @@ __global__ void __launch_bounds__(ATT_NT)
 attn_pool_bwd_v8_kernel(const float* __restrict__ denc_a, const float* __restrict__ denc_b,
                         const __nv_bfloat16* __restrict__ hout, const __nv_bfloat16* proj /* may alias dpre */,
                         const float* __restrict__ alphas, const float* __restrict__ w2, float* __restrict__ dhout,
-                        __nv_bfloat16* dpre, float* __restrict__ dw2_part, float* __restrict__ dsum_part, int L, int H,
-                        int group, int split) {
+                        __nv_bfloat16* dpre, float* __restrict__ dw2_part, float* __restrict__ dsum_part,
+                        float* __restrict__ dw2_sum, float* __restrict__ dsum_sum, int L, int H, int group, int split) {
   extern __shared__ float sm[];   // dsc[L] | al[L] | red_w[ATT_TG][H] | red_s[ATT_TG][H]
   float* dsc = sm;
   float* al = sm + L;
@@ -284,8 +284,9 @@ attn_pool_bwd_v8_kernel(const float* __restrict__ denc_a, const float* __restric
     float a = 0.f, b = 0.f;
 #pragma unroll
     for (int g = 0; g < ATT_TG; ++g) { a += red_w[g * H + h]; b += red_s[g * H + h]; }
-    dw2_part[(long long)x * H + h] = a;
+    if (dw2_part) dw2_part[(long long)x * H + h] = a;
     if (dsum_part) dsum_part[(long long)x * H + h] = b;   // Dense-bias gradient partial, summed in fp32
+    if (dw2_sum) { atomicAdd(dw2_sum + h, a); atomicAdd(dsum_sum + h, b); }   // or summed right here
   }
 }
 
@@ -359,11 +360,17 @@ extern "C" int indnet_attn_pool_fwd_bf16(indnet_stream st_, const void* hout_bf,
 extern "C" int indnet_attn_pool_bwd_bf16(indnet_stream st_, const float* denc_a, const float* denc_b,
                                          const void* hout_bf, const void* proj_bf, const float* alphas,
                                          const float* w_a2, float* dhout, void* dpre_bf, float* dw2_part,
-                                         float* dsum_part, int X, int L, int H, int group, int split) {
+                                         float* dsum_part, float* dw2_sum, float* dsum_sum, int X, int L, int H,
+                                         int group, int split) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0 && H > 0 && L <= 4096, "attn_pool_bwd_bf16: bad sizes X=%d L=%d H=%d", X, L, H);
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && dpre_bf && dw2_part, "attn_pool_bwd_bf16: null pointer");
+  IN_REQUIRE((dw2_sum == nullptr) == (dsum_sum == nullptr), "attn_pool_bwd_bf16: pass both summed outputs or neither");
+  if (dw2_sum) {
+    IN_CUDA(cudaMemsetAsync(dw2_sum, 0, sizeof(float) * H, st));
+    IN_CUDA(cudaMemsetAsync(dsum_sum, 0, sizeof(float) * H, st));
+  }
+  IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && dpre_bf && (dw2_part || dw2_sum), "attn_pool_bwd_bf16: null pointer");
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_pool_bwd_bf16: bad group/split %d/%d", group, split);
   IN_REQUIRE(split == group || denc_b, "attn_pool_bwd_bf16: second gradient input missing");
   const size_t v8_smem = sizeof(float) * (2 * L + 2 * ATT_TG * H);
@@ -373,10 +380,12 @@ extern "C" int indnet_attn_pool_bwd_bf16(indnet_stream st_, const float* denc_a,
   if (v8) {
     attn_pool_bwd_v8_kernel<<<X, ATT_NT, v8_smem, st>>>(denc_a, denc_b, (const __nv_bfloat16*)hout_bf,
                                                         (const __nv_bfloat16*)proj_bf, alphas, w_a2, dhout,
-                                                        (__nv_bfloat16*)dpre_bf, dw2_part, dsum_part, L, H, group, split);
+                                                        (__nv_bfloat16*)dpre_bf, dw2_part, dsum_part, dw2_sum, dsum_sum,
+                                                        L, H, group, split);
     IN_LAUNCH_CHECK("attn_pool_bwd_v8_kernel");
     return INDNET_OK;
   }
+  IN_REQUIRE(dw2_sum == nullptr, "attn_pool_bwd_bf16: summed outputs need H %% 8 == 0 and 16-byte aligned buffers");
   attn_pool_bwd_kernel<__nv_bfloat16><<<X, ATT_NT, sizeof(float) * 2 * L, st>>>(
       denc_a, denc_b, (const __nv_bfloat16*)hout_bf, (const __nv_bfloat16*)proj_bf, alphas, w_a2, dhout,
       (__nv_bfloat16*)dpre_bf, dw2_part, dsum_part, L, H, group, split);

@@ -69,6 +69,41 @@ __global__ void embed_pos_bwd_kernel(const int* __restrict__ pos1, const int* __
   }
 }
 
+// Same scatter for the split input gradient of the fused BPTT path: dx_a / dx_b rows of 16 floats (64 B), the 2P
+// position columns first.  One thread per token: three 16-byte loads per direction, then 2P shared-memory adds.
+__global__ void embed_pos_bwd16_kernel(const int* __restrict__ pos1, const int* __restrict__ pos2,
+                                       const float* __restrict__ dx_a, const float* __restrict__ dx_b,
+                                       float* __restrict__ dp1, float* __restrict__ dp2, long long T, int P,
+                                       int pos_rows, long long tokens_per_block) {
+  extern __shared__ float sm[];  // [2][pos_rows*P]
+  const int n = pos_rows * P;
+  for (int i = threadIdx.x; i < 2 * n; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  const long long t0 = blockIdx.x * tokens_per_block, t1 = min(T, t0 + tokens_per_block);
+  for (long long t = t0 + threadIdx.x; t < t1; t += blockDim.x) {
+    float g[12];
+    const float4* a = reinterpret_cast<const float4*>(dx_a + t * 16);
+    const float4* b = dx_b ? reinterpret_cast<const float4*>(dx_b + t * 16) : nullptr;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      float4 v = a[q];
+      if (b) { const float4 w = b[q]; v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+      g[4 * q] = v.x; g[4 * q + 1] = v.y; g[4 * q + 2] = v.z; g[4 * q + 3] = v.w;
+    }
+    const int r1 = pos1[t] * P, r2 = n + pos2[t] * P;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      if (j < P) { atomicAdd(&sm[r1 + j], g[j]); atomicAdd(&sm[r2 + j], g[P + j]); }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float a = sm[i], b = sm[n + i];
+    if (a != 0.f) atomicAdd(dp1 + i, a);
+    if (b != 0.f) atomicAdd(dp2 + i, b);
+  }
+}
+
 __global__ void embed_word_bwd_kernel(const int* __restrict__ word, const float* __restrict__ dx,
                                       float* __restrict__ dwt, long long T, int E, int D) {
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -127,6 +162,11 @@ extern "C" int indnet_embed_pos_bwd2(indnet_stream st_, const int* pos1, const i
   IN_REQUIRE(smem <= 48 * 1024, "embed_pos_bwd2: position tables too large for the shared-memory accumulator (%zu B)", smem);
   long long tpb = 512;
   int blocks = ceil_div(T, tpb);
+  if (ld == 16 && col0 == 0 && P <= 6 && (((uintptr_t)dx_a | (uintptr_t)dx_b) & 15) == 0) {
+    embed_pos_bwd16_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx_a, dx_b, dpos1, dpos2, T, P, pos_rows, tpb);
+    IN_LAUNCH_CHECK("embed_pos_bwd16_kernel");
+    return INDNET_OK;
+  }
   embed_pos_bwd_kernel<<<blocks, 256, smem, st>>>(pos1, pos2, dx_a, dx_b, ld, dpos1, dpos2, T, col0, P, pos_rows, tpb);
   IN_LAUNCH_CHECK("embed_pos_bwd_kernel");
   return INDNET_OK;

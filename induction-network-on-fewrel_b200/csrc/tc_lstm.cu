@@ -336,7 +336,8 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 // Warps 0-15: gate-gradient threads; warp 16: MMA issuer.
 constexpr int LB_KB = 4 * LT_U / 64;                           // 8 K-blocks
 constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                // 32768
-constexpr int LB_WX_BYTES = LB_KB * 128 * 128;                 // 131072: W_x rows as a second A operand (dx path)
+constexpr int LB_WX_TKB = 6;                                   // dx path: K-blocks of the W_x rows held in tensor memory
+constexpr int LB_WX_BYTES = (LB_KB - LB_WX_TKB) * 128 * 128;   // ... the remaining two stay in shared memory (32 KB)
 constexpr int LB_SMEM = LB_Z_BYTES + 256 + 1024;
 constexpr int LB_SMEM_DX = 2 * LB_Z_BYTES + LB_WX_BYTES + 256 + 1024;   // dz double-buffered: dx MMAs outlive the step
 constexpr int LB_DX_LD = 16;                                   // dx2 row stride in floats (64-byte rows)
@@ -347,13 +348,16 @@ struct LstmTcBwdP {
   const __nv_bfloat16* wh_fw; const __nv_bfloat16* wh_bw;     // W_h = rows D.. of the bf16 TF kernels, [u][4u]
   float* dbias_fw; float* dbias_bw;     // optional: bias gradients (column sums of dz), accumulated with atomics
   float* dx2; int dxn;                  // optional: dx2[dir][tok][16], the first dxn (<= 16) input-gradient features
+  const __nv_bfloat16* wx_fw; const __nv_bfloat16* wx_bw; int wx_rows;   // rows dx_first.. of the TF kernels, valid rows
   int X, L;
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
 
 // DX: also form the input gradient dx^T[f, NS] = W_x[f, 4u] * dz^T of the step (rows n0.. of the TF kernel as a
-// second A operand, 128 KB in shared memory, its own accumulator and barrier): the MMAs run behind the
-// recurrent ones on an otherwise idle tensor pipe and replace a GEMM launch that re-read all of dz.
+// second A operand with its own accumulator and barrier): the MMAs run behind the recurrent ones on an
+// otherwise idle tensor pipe and replace a GEMM launch that re-read all of dz.  The operand fills what is left
+// of tensor memory (192 columns = 6 of its 8 K-blocks); the last two K-blocks come from shared memory (32 KB),
+// which keeps the shared-memory bandwidth for the gate threads.
 template <bool DROP, bool DX>
 __global__ void __launch_bounds__(LB_THREADS, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_constant__ CUtensorMap tmXb, LstmTcBwdP p) {
@@ -386,7 +390,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
       const CUtensorMap* tmX = dir ? &tmXb : &tmXf;
       tma_prefetch_desc(tmX);
       mbar_expect_tx(wx_full, LB_WX_BYTES);
-      for (int kb = 0; kb < LB_KB; ++kb) tma_load_3d(sWx + kb * 16384, tmX, wx_full, kb * 64, 0, 0);
+      for (int kb = LB_WX_TKB; kb < LB_KB; ++kb) tma_load_3d(sWx + (kb - LB_WX_TKB) * 16384, tmX, wx_full, kb * 64, 0, 0);
     }
   }
   __syncwarp();
@@ -395,7 +399,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t taddr = *tmem_slot;
-  const uint32_t wh_t = taddr, acc_t = taddr + 2 * LT_U, accx_t = acc_t + LT_NS;
+  const uint32_t wh_t = taddr, acc_t = taddr + 2 * LT_U, accx_t = acc_t + LT_NS, wx_t = accx_t + LT_NS;
   constexpr uint32_t idesc = idesc_bf16(128, LT_NS, false, false);
   const uint32_t z16 = smem_u32(sZ) >> 4;
   if (gate_warp) {
@@ -412,6 +416,22 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
         r[v * 4 + 0] = q.x; r[v * 4 + 1] = q.y; r[v * 4 + 2] = q.z; r[v * 4 + 3] = q.w;
       }
       tmem_st16(dst + c * 16, r);
+    }
+    if (DX) {
+      // W_x rows, K-blocks 0..5: warp w writes lane quarter w % 4, k range [(w / 4) * 96, +96) = 48 packed columns
+      const bool have = row < p.wx_rows;
+      const uint4* xs = reinterpret_cast<const uint4*>((dir ? p.wx_bw : p.wx_fw) + (long long)(have ? row : 0) * (4 * LT_U) + kq * 96);
+      const uint32_t xd = wx_t + ((uint32_t)((warp & 3) * 32) << 16) + kq * 48;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        uint32_t r[16];
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const uint4 q = have ? xs[c * 4 + v] : make_uint4(0, 0, 0, 0);
+          r[v * 4 + 0] = q.x; r[v * 4 + 1] = q.y; r[v * 4 + 2] = q.z; r[v * 4 + 3] = q.w;
+        }
+        tmem_st16(xd + c * 16, r);
+      }
     }
     tmem_st_wait();
   }
@@ -452,9 +472,13 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
           for (int kb = 0; kb < LB_KB; ++kb) {
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4) {
-              const uint64_t ad = smem_desc_sw128_k(wx16, kb * 16384 + k4 * 32);
               const uint64_t bd = smem_desc_sw128_k(zb16, kb * (LT_NS * 128) + k4 * 32);
-              umma_bf16(accx_t, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+              if (kb < LB_WX_TKB) {
+                umma_bf16_ts(accx_t, wx_t + kb * 32 + k4 * 8, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+              } else {
+                const uint64_t ad = smem_desc_sw128_k(wx16, (kb - LB_WX_TKB) * 16384 + k4 * 32);
+                umma_bf16(accx_t, ad, bd, idesc, 1u);
+              }
             }
           }
           umma_commit(dx_done);
@@ -706,6 +730,7 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
     IN_CUDA(cudaMemsetAsync(dbias_bw, 0, sizeof(float) * 4 * LT_U, st));
   }
   p.dx2 = dx2; p.dxn = 0;
+  p.wx_fw = p.wx_bw = nullptr; p.wx_rows = 0;
   CUtensorMap tmXf, tmXb;
   memset(&tmXf, 0, sizeof(tmXf));
   memset(&tmXb, 0, sizeof(tmXb));
@@ -716,6 +741,7 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
     // rows dx_first.. of the TF kernel [D+u][4u] as the A operand: box 64 (k) x 128 rows (rows past the matrix: zero fill)
     const __nv_bfloat16* xf = (const __nv_bfloat16*)kernel_fw_bf + (long long)dx_first * 4 * LT_U;
     const __nv_bfloat16* xb = (const __nv_bfloat16*)kernel_bw_bf + (long long)dx_first * 4 * LT_U;
+    p.wx_fw = xf; p.wx_bw = xb; p.wx_rows = D + LT_U - dx_first;
     int rc = make_tmap_bf16(&tmXf, xf, 4 * LT_U, D + LT_U - dx_first, 4 * LT_U, 1, 0, 64, 128);
     if (rc) return rc;
     rc = make_tmap_bf16(&tmXb, xb, 4 * LT_U, D + LT_U - dx_first, 4 * LT_U, 1, 0, 64, 128);

@@ -559,12 +559,19 @@ class EpisodePipeline:
         # d(loss)/d(h): pooling path alpha_t * denc + Dense path dpre * W_a1^T.  With the tensor-core LSTM the
         # sum is formed once in the GEMM epilogue and written in bf16; otherwise it is accumulated in fp32.
         fused = self.tc_lstm
+        # with the 16-byte kernel variant (H % 8 == 0) the W_a2 / Dense-bias gradients are summed over sentences
+        # inside the pooling kernel; otherwise per-sentence partials + two column sums
+        insum = c.H % 8 == 0 and c.H <= 512
         self._call("indnet_attn_pool_bwd_bf16", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
                    ptr(self.alphas), ptr(p.view(ATT_W2)), None if fused else ptr(self.dhout), ptr(self.dpre_bf),
-                   ptr(self.dw2_part), ptr(self.dba_part), c.X, c.L, c.H, c.n_s, c.NK)
-        self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
+                   None if insum else ptr(self.dw2_part), None if insum else ptr(self.dba_part),
+                   ptr(p.grad(ATT_W2)) if insum else None, ptr(p.grad(ATT_B)) if insum else None,
+                   c.X, c.L, c.H, c.n_s, c.NK)
+        if not insum:
+            self._call("indnet_colsum", ptr(self.dw2_part), c.X, c.H, c.H, ptr(p.grad(ATT_W2)), 0)
         self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
-        self._call("indnet_colsum", ptr(self.dba_part), c.X, c.H, c.H, ptr(p.grad(ATT_B)), 0)
+        if not insum:
+            self._call("indnet_colsum", ptr(self.dba_part), c.X, c.H, c.H, ptr(p.grad(ATT_B)), 0)
         if fused:
             self._tag = "tc_gemm:attn_dh"
             try:
