@@ -109,28 +109,98 @@ __device__ __forceinline__ uint32_t mt_g(uint32_t a, uint32_t b) {
   return (y >> 1) ^ ((y & 1u) ? 0x9908B0DFu : 0u);
 }
 
+// ---- persistent stream window ------------------------------------------------------------------
+// The NumPy stream and its tables live in rings addressed by ABSOLUTE draw / block index (origin = the first
+// word of the key block handed in at the last reset), kept in the caller's scratch across calls.  A call
+// only needs the window [win_start, win_start + nblk) of blocks to exist before it walks; while it walks,
+// the NEXT window is generated and tabulated on a forked stream (the continuation of the stream does not
+// depend on where this walk stops), so in steady state generation and tables are off the call's critical
+// path.  The header remembers the absolute position; a call whose np_state is not the state the ring
+// expects (first call, re-seeded or reloaded stream, different sizes) resets the origin.
+struct SmpPlan { long long gen_from, gen_to, tab_from, tab_to; };
+struct SmpHdr {
+  unsigned long long magic;      // identifies an initialised header for this layout
+  long long apos;                // absolute index of the next draw to consume
+  long long gen_front;           // words [.., gen_front) are generated
+  long long tab_front;           // blocks [.., tab_front) are tabulated
+  long long win_start;           // block of apos at the start of the current call
+  SmpPlan plan[2];               // [0] what this call must still build, [1] what it builds ahead
+  int nsec;
+};
+
+// One CTA.  ahead == 0: check that np_state is the state the ring continues from (else reset), open the
+// window; then plan what generation / table kernels of this phase have to do.
+__global__ void smp_plan_kernel(SmpHdr* __restrict__ h, const uint32_t* __restrict__ np_state,
+                                uint32_t* __restrict__ keys, uint32_t kmask, long long nblk, int ahead,
+                                unsigned long long magic) {
+  if (ahead == 0) {
+    bool ok = h->magic == magic;
+    long long blk = 0;
+    if (ok) {
+      const long long pos = h->apos;
+      blk = pos / MT_N;
+      int off = (int)(pos % MT_N);
+      if (off == 0 && blk > 0) { blk -= 1; off = MT_N; }
+      ok = np_state[MT_N] == (uint32_t)off;
+      if (ok)
+        for (int k = threadIdx.x; k < MT_N; k += blockDim.x)
+          if (keys[(uint32_t)(blk * MT_N + k) & kmask] != np_state[k]) ok = false;
+    }
+    const int all_ok = __syncthreads_and(ok ? 1 : 0);
+    if (!all_ok) {                                   // new origin: the handed-in key block is words [0, 624)
+      for (int k = threadIdx.x; k < MT_N; k += blockDim.x) keys[k] = np_state[k];
+      if (threadIdx.x == 0) {
+        h->magic = magic;
+        h->apos = (long long)np_state[MT_N];
+        h->gen_front = MT_N;
+        h->tab_front = 0;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) h->win_start = h->apos >> 6;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const long long target = ((h->win_start + nblk * (1 + ahead)) + 7) & ~7LL;     // whole chunks
+    SmpPlan pl;
+    pl.tab_from = h->tab_front;
+    pl.tab_to = target > pl.tab_from ? target : pl.tab_from;
+    h->tab_front = pl.tab_to;
+    const long long need = target * TB + MT_N;       // + one key block: the state handed back must be complete
+    pl.gen_from = h->gen_front;
+    const long long it = need > pl.gen_from ? (need - pl.gen_from + 453) / 454 : 0;
+    pl.gen_to = pl.gen_from + it * 454;              // whole double rounds of the generator
+    h->gen_front = pl.gen_to;
+    h->plan[ahead] = pl;
+  }
+}
+
 __global__ void __launch_bounds__(GEN_NT)
-smp_gen_kernel(const uint32_t* __restrict__ np_state, uint32_t* __restrict__ keys, int nb,
+smp_gen_kernel(const SmpHdr* __restrict__ h, int ahead, uint32_t* __restrict__ keys, uint32_t kmask,
                uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
                const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
   __shared__ uint32_t ring[2048];
   const int tid = threadIdx.x;
   if (blockIdx.x == 0) {
-    for (int k = tid; k < MT_N; k += GEN_NT) { const uint32_t v = np_state[k]; ring[k] = v; keys[k] = v; }
+    const long long from = h->plan[ahead].gen_from, total = h->plan[ahead].gen_to;
+    if (from >= total) return;
+    for (int k = tid; k < MT_N; k += GEN_NT) {
+      const long long n = from - MT_N + k;
+      ring[n & 2047] = keys[(uint32_t)n & kmask];
+    }
     __syncthreads();
-    const long long total = (long long)nb * MT_N;
     // Rounds of exactly 227 words: x[n-227] is then the word this thread produced one round earlier (kept in
     // a register), and the two mixed words lie 397..624 back, i.e. at least one whole round behind even for
     // the second of two consecutive rounds - so two rounds are produced per barrier.
     const bool act = tid < 227;                              // every thread runs the loop: the barrier stays converged
-    uint32_t prev = act ? ring[MT_M + tid] : 0u;
-    for (long long base = MT_N; base < total; base += 2 * 227) {
+    uint32_t prev = act ? ring[(from - 227 + tid) & 2047] : 0u;
+    for (long long base = from; base < total; base += 2 * 227) {
       if (act) {
         const long long nA = base + tid, nB = nA + 227;
         const uint32_t vA = prev ^ mt_g(ring[(nA - MT_N) & 2047], ring[(nA - MT_N + 1) & 2047]);
         const uint32_t vB = vA ^ mt_g(ring[(nB - MT_N) & 2047], ring[(nB - MT_N + 1) & 2047]);
-        if (nA < total) { ring[nA & 2047] = vA; keys[nA] = vA; }
-        if (nB < total) { ring[nB & 2047] = vB; keys[nB] = vB; }
+        ring[nA & 2047] = vA; keys[(uint32_t)nA & kmask] = vA;
+        ring[nB & 2047] = vB; keys[(uint32_t)nB & kmask] = vB;
         prev = vB;
       }
       __syncthreads();
@@ -246,18 +316,21 @@ __device__ __forceinline__ int walk_block(const uint32_t* y, const uint32_t* ym,
 
 // one CTA per pair of blocks (2p, 2p+1)
 __global__ void __launch_bounds__(256)
-smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ tab, int n_states) {
+smp_table_kernel(const SmpHdr* __restrict__ h, int ahead, const uint32_t* __restrict__ keys, uint32_t kmask,
+                 unsigned char* __restrict__ tab, int bcap, int n_states) {
   extern __shared__ unsigned short fs[];          // [2][n_states]: F of the even / odd block
   __shared__ uint32_t y[2][TB];
   __shared__ unsigned char es[2][TB + 1];         // E of the even / odd block
   __shared__ uint32_t yms[2][17][TB];             // the draws masked to b bits, b = 0..16
-  const long long b0 = 2LL * blockIdx.x;
+  const long long b0 = h->plan[ahead].tab_from + 2LL * blockIdx.x;      // absolute block (even)
+  if (b0 >= h->plan[ahead].tab_to) return;
   const long long rb = rec_bytes(n_states);
+  unsigned char* rec0 = tab + (b0 % bcap) * rb;                          // ring slot of b0; b0 + 1 follows it (bcap is even)
   if (threadIdx.x < 2 * TB) {
-    const int h = threadIdx.x / TB, k = threadIdx.x % TB;
-    const uint32_t v = mt_temper(keys[(b0 + h) * TB + k]);
-    y[h][k] = v;
-    reinterpret_cast<uint32_t*>(tab + (b0 + h) * rb + (long long)n_states * 4)[k] = v;
+    const int hh = threadIdx.x / TB, k = threadIdx.x % TB;
+    const uint32_t v = mt_temper(keys[(uint32_t)((b0 + hh) * TB + k) & kmask]);
+    y[hh][k] = v;
+    reinterpret_cast<uint32_t*>(rec0 + hh * rb + (long long)n_states * 4)[k] = v;
   }
   __syncthreads();
   for (int q = threadIdx.x; q < 2 * 17 * TB; q += 256) {      // draws masked to 0..16 bits
@@ -271,19 +344,19 @@ smp_table_kernel(const uint32_t* __restrict__ keys, unsigned char* __restrict__ 
       int e = 0xFF;
       const int s = (s0 >= 1) ? walk_block(y[h], yms[h][32 - __clz(s0)], s0, e) : 0;
       fs[h * n_states + s0] = (unsigned short)s;
-      unsigned char* rec = tab + (b0 + h) * rb;
+      unsigned char* rec = rec0 + h * rb;
       reinterpret_cast<unsigned short*>(rec)[s0] = (unsigned short)s;
       if (s0 < E_STRIDE) rec[(long long)n_states * 4 + TB * 4 + s0] = (unsigned char)((s0 >= 1 && s0 <= TB) ? e : 0xFF);
       if (s0 <= TB) es[h][s0] = (unsigned char)((s0 >= 1) ? e : 0xFF);
     }
   }
   __syncthreads();
-  unsigned short* F2 = reinterpret_cast<unsigned short*>(tab + b0 * rb + (long long)n_states * 2);
+  unsigned short* F2 = reinterpret_cast<unsigned short*>(rec0 + (long long)n_states * 2);
   for (int s0 = threadIdx.x; s0 < n_states; s0 += 256) {
     const int s1 = fs[s0];
     F2[s0] = s1 > 0 ? fs[n_states + s1] : (unsigned short)0;
   }
-  unsigned char* E2 = tab + b0 * rb + (long long)n_states * 4 + TB * 4 + E_STRIDE;
+  unsigned char* E2 = rec0 + (long long)n_states * 4 + TB * 4 + E_STRIDE;
   for (int s0 = threadIdx.x; s0 < E2_STRIDE; s0 += 256) {
     int e2 = 0xFF;
     if (s0 >= 1 && s0 <= 2 * TB && s0 < n_states) {
@@ -355,10 +428,10 @@ __device__ __forceinline__ void sts_release_s32(uint32_t a, int v) {
 // chain: for every run of table jumps it logs ONE record {first block, entry index, job}; the fill kernel
 // replays those runs in parallel from the same tables to recover the per-block indices and the j-lists.
 __global__ void __launch_bounds__(64)
-smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restrict__ tab, int n_states,
-                long long nblk, int cb_log, int rc, uint32_t* __restrict__ np_state,
+smp_walk_kernel(const uint32_t* __restrict__ keys, uint32_t kmask, const unsigned char* __restrict__ tab, int ccap,
+                int n_states, long long nblk, int cb_log, int rc, uint32_t* __restrict__ np_state,
                 const int* __restrict__ jsize, int jobs, int n_max, int* __restrict__ jlist,
-                int4* __restrict__ seclog, int* __restrict__ nsec_out, int* __restrict__ status) {
+                int4* __restrict__ seclog, SmpHdr* __restrict__ hdr, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char ring[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int CB = 1 << cb_log;
@@ -370,7 +443,10 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
   volatile uint32_t* zeros = reinterpret_cast<volatile uint32_t*>(bars + rc);   // [32]
   volatile int* ctl = reinterpret_cast<volatile int*>(bars + rc) + 32;          // [0] walker's chunk - c0, [1] done, [2] landed chunks
   const uint32_t ctl_s = tc::smem_u32(const_cast<int*>(ctl));
-  const int nchunks = (int)(nblk >> cb_log);
+  // absolute coordinates (see SmpHdr): this call may consume blocks [win_start, win_start + nblk) only
+  const long long win_start = hdr->win_start;
+  const long long blk_end = (win_start + nblk + 7) & ~7LL;     // tables exist up to here (whole chunks)
+  const int nchunks = (int)(blk_end >> cb_log);
   if (threadIdx.x == 0) {
     for (int r = 0; r < rc; ++r) tc::mbar_init(&bars[r], 1);
     tc::fence_barrier_init();
@@ -382,7 +458,7 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
   // in ordinary registers (see lds_u16 above).
   if (warp == 0) zeros[lane] = 0u;
   __syncthreads();
-  long long pos = (long long)np_state[MT_N];      // absolute draw index; keys[0] is the state handed in
+  long long pos = hdr->apos;                      // absolute draw index
   const int c0 = (int)(pos >> (6 + cb_log));
 
   if (warp == 1) {
@@ -399,7 +475,7 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
           const uint32_t r = (uint32_t)(issued - c0) % (uint32_t)rc;
           const uint32_t bar = bars_s + 8u * r;
           asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(slot_bytes) : "memory");
-          bulk_g2s(ring_s + r * slot_bytes, tab + (long long)issued * slot_bytes, slot_bytes, bar);
+          bulk_g2s(ring_s + r * slot_bytes, tab + (long long)(issued % ccap) * slot_bytes, slot_bytes, bar);
           ++issued;
         }
         while (landed < issued) {                  // in issue order; blocks only while a copy is in flight
@@ -443,7 +519,7 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
     while (i > 0) {
       const long long b = pos >> 6;
       const int off = (int)(pos & (TB - 1));
-      if (b >= nblk) { flag = SMP_STREAM_BUDGET; break; }
+      if (b >= win_start + nblk) { flag = SMP_STREAM_BUDGET; break; }
       const int c = (int)(b >> cb_log);
       SMP_T(tw0);
       while (ready < c) {                          // entering a new chunk: tell the producer, then make sure it landed
@@ -462,7 +538,7 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
       const int lb = (int)(b & (CB - 1));
       if (off == 0) {
         // ---- run of table jumps from block b to the end of this chunk (or of the permutation)
-        if (lane == 0) seclog[n_sec] = make_int4((int)b, i, job, 0);
+        if (lane == 0) seclog[n_sec] = make_int4((int)(b - win_start), i, job, 0);
         ++n_sec;
         const uint32_t cbase = slot_s;                     // block 0 of this chunk
         uint32_t v = (uint32_t)i;
@@ -561,15 +637,15 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
     long long blk = pos / MT_N;
     int off = (int)(pos % MT_N);
     if (off == 0 && blk > 0) { blk -= 1; off = MT_N; }
-    const uint32_t* fin = keys + blk * MT_N;
     uint32_t tmp[MT_N / 32 + 1];
     int cnt = 0;
-    for (int k = lane; k < MT_N; k += 32) tmp[cnt++] = fin[k];
+    for (int k = lane; k < MT_N; k += 32) tmp[cnt++] = keys[(uint32_t)(blk * MT_N + k) & kmask];
     cnt = 0;
     for (int k = lane; k < MT_N; k += 32) np_state[k] = tmp[cnt++];
     if (lane == 0) {
       np_state[MT_N] = (uint32_t)off;
-      *nsec_out = n_sec;
+      hdr->apos = pos;
+      hdr->nsec = n_sec;
       status[0] = flag;
       status[1] = (int)((clock64() - clk0) >> 4);     // diagnostics: walk cycles / 16, jump runs, exact rows
       status[2] = n_sec;
@@ -585,18 +661,19 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, const unsigned char* __restri
 // ---- kernel F: accepted (index, j) pairs of the blocks the walker jumped over --------------------
 // One thread per (logged run, block of its chunk): replay the run's chain through F / F2 in global memory
 // up to that block (at most CB / 2 + 1 dependent lookups), then offer the block's 64 draws.
-__global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int n_states, const int4* __restrict__ seclog,
-                                const int* __restrict__ nsec, int cb_log, int n_max, int* __restrict__ jlist) {
+__global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int bcap, int n_states,
+                                const int4* __restrict__ seclog, const SmpHdr* __restrict__ hdr, int cb_log, int n_max,
+                                int* __restrict__ jlist) {
   const int CB = 1 << cb_log;
   const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const int sec = (int)(id >> cb_log), k = (int)(id & (CB - 1));
-  if (sec >= *nsec) return;
+  if (sec >= hdr->nsec) return;
   const int4 lg = seclog[sec];
-  const long long b_start = lg.x, chunk0 = b_start & ~(long long)(CB - 1), mine = chunk0 + k;
+  const long long b_start = hdr->win_start + lg.x, chunk0 = b_start & ~(long long)(CB - 1), mine = chunk0 + k;
   if (mine < b_start) return;
   const long long rb = rec_bytes(n_states);
-  auto F = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + blk * rb)[s]; };
-  auto F2 = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + blk * rb + (long long)n_states * 2)[s]; };
+  auto F = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + (blk % bcap) * rb)[s]; };
+  auto F2 = [&](long long blk, int s) { return (int)reinterpret_cast<const unsigned short*>(tab + (blk % bcap) * rb + (long long)n_states * 2)[s]; };
   int s = lg.y;
   long long bb = b_start;
   bool found = false;
@@ -623,7 +700,7 @@ __global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int n_sta
   int* jrow = jlist + (long long)lg.z * n_max;
   uint32_t m = mask_for((uint32_t)s);
   int thr = (int)(m >> 1);
-  const uint32_t* yp = reinterpret_cast<const uint32_t*>(tab + mine * rb + (long long)n_states * 4);
+  const uint32_t* yp = reinterpret_cast<const uint32_t*>(tab + (mine % bcap) * rb + (long long)n_states * 4);
   for (int q = 0; q < TB && s >= 1; ++q) {
     if (s <= thr) { m >>= 1; thr >>= 1; }
     const uint32_t v = yp[q] & m;
@@ -697,10 +774,11 @@ using namespace indnet;
 namespace {
 // Scratch layout shared by the walk and gather halves (all offsets in bytes, 256-byte aligned).
 struct SmpLayout {
-  long long jobs, stride, pick_max, n_states, nb, nblk;
+  long long jobs, stride, pick_max, n_states, nblk;
+  long long kcap, bcap;            // key ring (words, power of two) and table ring (blocks): two windows + slack
   int cb_log, rc;                  // walker staging: 2^cb_log blocks per chunk, rc chunk slots (-1: does not fit)
   long long smem_bytes;
-  long long o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, o_nsec, sec_cap, bytes;
+  long long o_hdr, o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, sec_cap, bytes;
 };
 static double expected_draws(long long n) {      // E[draws] of NumPy's permutation(n) (rejection sampling)
   double e = 0.0;
@@ -722,7 +800,9 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   const long long budget = (long long)(e * 1.03) + 8192 + MT_N;
   L.nblk = (budget + TB - 1) / TB;
   L.nblk = (L.nblk + 15) / 16 * 16;                      // whole chunks for every chunk size the walker may pick
-  L.nb = (L.nblk * TB + MT_N - 1) / MT_N + 1;
+  L.bcap = 2 * L.nblk + 32;
+  L.kcap = 1;
+  while (L.kcap < L.bcap * TB + 8 * MT_N) L.kcap <<= 1;
   // walker staging ring: the largest chunk / ring that fits in 200 KB of shared memory
   const long long per_block = rec_bytes(L.n_states);
   // chunk = 8 blocks (or fewer for very wide tables), as many slots as fit (<= 8): a deep ring of small chunks
@@ -737,15 +817,15 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   }
   auto al = [](long long x) { return (x + 255) / 256 * 256; };
   long long o = 0;
+  L.o_hdr = o;     o = al(o + (long long)sizeof(SmpHdr));
   L.o_classes = o; o = al(o + 4LL * B * N);
   L.o_jsize = o;   o = al(o + 4LL * L.jobs);
   L.o_jlist = o;   o = al(o + 4LL * L.jobs * L.stride);
   L.o_picks = o;   o = al(o + 4LL * L.jobs * L.pick_max);
-  L.o_keys = o;    o = al(o + 4LL * L.nb * MT_N);
-  L.o_tab = o;     o = al(o + rec_bytes(L.n_states) * L.nblk);
+  L.o_keys = o;    o = al(o + 4LL * L.kcap);
+  L.o_tab = o;     o = al(o + rec_bytes(L.n_states) * L.bcap);
   L.sec_cap = (L.nblk >> (L.cb_log < 0 ? 0 : L.cb_log)) + L.jobs + 2;   // one run per chunk entered aligned + one per job
   L.o_seclog = o;  o = al(o + 16LL * L.sec_cap);
-  L.o_nsec = o;    o = al(o + 4);
   L.bytes = o;
   return L;
 }
@@ -773,30 +853,60 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   unsigned char* tab = (unsigned char*)(base + L.o_tab);
   int* jsize = (int*)(base + L.o_jsize);
   int4* seclog = (int4*)(base + L.o_seclog);
-  int* nsec = (int*)(base + L.o_nsec);
+  SmpHdr* hdr = (SmpHdr*)(base + L.o_hdr);
   IN_REQUIRE(L.cb_log >= 0, "sample_episodes: n_max=%d is too large for the walker's shared-memory table ring", n_max);
-  IN_REQUIRE(L.nblk <= 2147483647LL, "sample_episodes: stream too long");
-  static bool smem_set[64] = {};
+  IN_REQUIRE(L.bcap <= 2147483647LL && L.kcap <= 2147483648LL, "sample_episodes: stream window too long");
+  // per-device: kernel attributes, and the forked stream + events on which the next window is built
+  static bool dev_set[64] = {};
+  static cudaStream_t side_s[64] = {};
+  static cudaEvent_t ev_fork[64] = {}, ev_join[64] = {};
   int dev = 0;
   IN_CUDA(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64 || !smem_set[dev]) {
+  IN_REQUIRE(dev >= 0 && dev < 64, "sample_episodes: device index %d out of range", dev);
+  if (!dev_set[dev]) {
     IN_CUDA(cudaFuncSetAttribute(smp_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     IN_CUDA(cudaFuncSetAttribute(smp_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    if (dev >= 0 && dev < 64) smem_set[dev] = true;
+    IN_CUDA(cudaStreamCreateWithFlags(&side_s[dev], cudaStreamNonBlocking));
+    IN_CUDA(cudaEventCreateWithFlags(&ev_fork[dev], cudaEventDisableTiming));
+    IN_CUDA(cudaEventCreateWithFlags(&ev_join[dev], cudaEventDisableTiming));
+    dev_set[dev] = true;
   }
-  smp_gen_kernel<<<2, GEN_NT, 0, st>>>(np_state, keys, (int)L.nb, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
+  cudaStream_t side = side_s[dev];
+  const uint32_t kmask = (uint32_t)(L.kcap - 1);
+  const int bcap = (int)L.bcap, ccap = (int)(L.bcap >> L.cb_log);
+  unsigned long long magic = 0x534d5048ull;           // layout signature: a header left by other sizes is stale
+  for (long long v : {(long long)B, (long long)N, (long long)K, (long long)Q, (long long)n_max, L.nblk, L.n_states})
+    magic = magic * 1000003ull + (unsigned long long)v;
+  const unsigned tgrid = (unsigned)(L.nblk / 2 + 16);
+  const size_t tsmem = 4 * (size_t)L.n_states;
+  // what this call needs (normally already there: the previous call built it while it walked) ...
+  smp_plan_kernel<<<1, 256, 0, st>>>(hdr, np_state, keys, kmask, L.nblk, 0, magic);
+  IN_LAUNCH_CHECK("smp_plan_kernel");
+  smp_gen_kernel<<<2, GEN_NT, 0, st>>>(hdr, 0, keys, kmask, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
   IN_LAUNCH_CHECK("smp_gen_kernel");
-  smp_table_kernel<<<(unsigned)(L.nblk / 2), 256, 4 * (size_t)L.n_states, st>>>(keys, tab, (int)L.n_states);
+  smp_table_kernel<<<tgrid, 256, tsmem, st>>>(hdr, 0, keys, kmask, tab, bcap, (int)L.n_states);
   IN_LAUNCH_CHECK("smp_table_kernel");
-  smp_walk_kernel<<<1, 64, (size_t)L.smem_bytes, st>>>(keys, tab, (int)L.n_states, L.nblk, L.cb_log, L.rc, np_state,
-                                                      jsize, (int)L.jobs, (int)L.stride, jlist, seclog, nsec, status);
+  // ... and, forked, the window after it
+  IN_CUDA(cudaEventRecord(ev_fork[dev], st));
+  IN_CUDA(cudaStreamWaitEvent(side, ev_fork[dev], 0));
+  smp_plan_kernel<<<1, 256, 0, side>>>(hdr, np_state, keys, kmask, L.nblk, 1, magic);
+  IN_LAUNCH_CHECK("smp_plan_kernel");
+  smp_gen_kernel<<<1, GEN_NT, 0, side>>>(hdr, 1, keys, kmask, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
+  IN_LAUNCH_CHECK("smp_gen_kernel");
+  smp_table_kernel<<<tgrid, 256, tsmem, side>>>(hdr, 1, keys, kmask, tab, bcap, (int)L.n_states);
+  IN_LAUNCH_CHECK("smp_table_kernel");
+  IN_CUDA(cudaEventRecord(ev_join[dev], side));
+  smp_walk_kernel<<<1, 64, (size_t)L.smem_bytes, st>>>(keys, kmask, tab, ccap, (int)L.n_states, L.nblk, L.cb_log, L.rc,
+                                                      np_state, jsize, (int)L.jobs, (int)L.stride, jlist, seclog, hdr,
+                                                      status);
   IN_LAUNCH_CHECK("smp_walk_kernel");
-  smp_fill_kernel<<<ceil_div(L.sec_cap << L.cb_log, 128), 128, 0, st>>>(tab, (int)L.n_states, seclog, nsec, L.cb_log,
+  smp_fill_kernel<<<ceil_div(L.sec_cap << L.cb_log, 128), 128, 0, st>>>(tab, bcap, (int)L.n_states, seclog, hdr, L.cb_log,
                                                                         (int)L.stride, jlist);
   IN_LAUNCH_CHECK("smp_fill_kernel");
   sampler_trace_kernel<<<ceil_div(L.jobs * L.pick_max, 128), 128, 0, st>>>(scopes, classes, jlist, B, N, K, Q,
                                                                            (int)L.stride, (int)L.pick_max, picks);
   IN_LAUNCH_CHECK("sampler_trace_kernel");
+  IN_CUDA(cudaStreamWaitEvent(st, ev_join[dev], 0));    // join: the next call's plan must see the finished build
   return INDNET_OK;
 }
 
