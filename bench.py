@@ -400,7 +400,7 @@ def run_b200(args, w):
             # fwd: x in (64 bf16 per token, once per direction); out per (dir, token, unit): gates 8 + c 2 + h_prev 2 + h 2
             "indnet_lstm_fwd_tc": T * (2 * 64 * 2 + 2 * cfg.u * 14),
             # bwd: in gates 8 + c_prev 2 + dh 2, out dz 8, per (dir, token, unit)
-            "indnet_lstm_bwd_tc": T * 2 * cfg.u * 20,
+            "indnet_lstm_bwd_tc": T * (2 * cfg.u * 20 + 2 * 64),     # + the 16-float dx rows per direction
             "tc_gemm:lstm_dx": T * (4 * cfg.u * 2 + 10 * 4), "tc_gemm:lstm_dWx": T * (4 * cfg.u + 64) * 2,
             "tc_gemm:lstm_dWh": T * (4 * cfg.u + cfg.u) * 2,
             "indnet_attn_pool_bwd_bf16": T * H2 * 3, "indnet_attn_pool_fwd_bf16": T * H2 * 2,

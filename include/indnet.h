@@ -88,6 +88,11 @@ int indnet_memset(indnet_stream st, void* dst, int byte_value, long long bytes);
  * sampled relation has fewer than K+Q instances, 2 = a scope exceeds n_max, 3 = the pre-generated
  * stream budget (expected draws + 3 % + 8192) was exceeded; [1..3] diagnostics (SM cycles / 16 of the
  * stream walk, table-jump runs, exact rows); [4..9] are written only by the timeline build.
+ * scratch is PERSISTENT state: it holds the generated stream and its tables in rings across calls (the call
+ * builds the next call's window on a forked internal stream while it walks), keyed to np_state - hand the
+ * same scratch to consecutive calls of one sampler; a call whose np_state is not the continuation the scratch
+ * expects (first call, re-seeded stream, other sizes) rebuilds from np_state.  The first call on a device
+ * creates that internal stream: make it outside stream capture.
  * The NumPy stream is consumed through per-block transition tables (csrc/sampler.cu);
  * n_max bounds the table width (at most ~12k instances per relation fit the walker's shared-memory
  * ring, larger values are refused). */
