@@ -102,3 +102,33 @@ def test_too_few_instances_raises_like_numpy_choice():
         ld.next_one_tf(2, 3, 2)
     with pytest.raises(ValueError, match="Sample larger than population"):
         ld.next_one_tf(4, 1, 1)
+
+
+def test_stream_rings_survive_many_batches_shape_switches_and_reseeds():
+    """The stream / table rings in the sampler scratch persist across calls (the next window is built while
+    the current one is walked).  Eight batches in a row wrap the rings several times; switching between two
+    batch shapes and re-seeding in between must be noticed (the scratch no longer continues the stream handed
+    in) and rebuilt - every episode still equals the host reference drawing from the same streams."""
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    from induction_b200.util.synthetic import make_tables
+    tables = make_tables(24, 300, 16, 2000, 8, seed=3)
+    ld = JSONFileDataLoader.from_tables(tables)
+    scopes = ld.scopes()
+    plan = [(12, 5, 2, 3)] * 8 + [(5, 4, 1, 2), (12, 5, 2, 3), (5, 4, 1, 2), (5, 4, 1, 2)]
+
+    def check(seed):
+        random.seed(seed); np.random.seed(seed)
+        want = [[so.next_one_tf_stdlib(tables, scopes, N, K, Q) for _ in range(B)] for (B, N, K, Q) in plan]
+        tail = (random.random(), float(np.random.rand()))
+        random.seed(seed); np.random.seed(seed)
+        for step, (B, N, K, Q) in enumerate(plan):
+            inputs, label = ld.next_batch(B, N, K, Q)
+            for b in range(B):
+                for k in KEYS:
+                    assert np.array_equal(inputs[k][b].cpu().numpy(), want[step][b][0][k]), (seed, step, b, k)
+                assert np.array_equal(label[b].cpu().numpy(), want[step][b][1]), (seed, step, b)
+        assert (random.random(), float(np.random.rand())) == tail
+
+    check(5)
+    check(5)        # same seed again: the scratch holds a later part of this very stream
+    check(77)

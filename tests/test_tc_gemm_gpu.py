@@ -63,3 +63,32 @@ def test_tc_gemm_split_k(a_mn, b_mn):
     A, B, want = _operands(a_mn, b_mn, M, N, K, 1, seed=3)
     C, _ = _tc(a_mn, b_mn, M, N, K, A, B, splitk=0)
     assert float((C.double() - want).abs().max() / want.abs().max()) < 5e-5
+
+
+@pytest.mark.parametrize("M,N,rows,group,split", [(400, 256, 40, 5, 2), (203, 128, 7, 3, 3), (96, 48, 12, 4, 1)])
+def test_tc_gemm_rank1_epilogue(M, N, rows, group, split):
+    """C = A*B + rs[m] * v(m / rows)[n] with v taken from the (support, query) pair of matrices in the
+    split layout of the attention kernels - the fused d(loss)/d(h) of the self-attention block.  Covers the
+    16-byte row path (N % 32 == 0) and the transposing path (N = 48), fp32 and bf16 outputs."""
+    from induction_b200._lib import LIB, current_stream, ptr
+    K = 256
+    A, B, want = _operands(0, 0, M, N, K, 1, seed=M + N)
+    X = (M + rows - 1) // rows                       # vectors touched ("sentences")
+    X = (X + group - 1) // group * group
+    g = torch.Generator(device="cuda").manual_seed(9)
+    rs = torch.randn(M, generator=g, device="cuda")
+    va = torch.randn(X // group * split, N, generator=g, device="cuda")
+    vb = torch.randn(max(X // group * (group - split), 1), N, generator=g, device="cuda")
+    C = torch.full((M, N), float("nan"), device="cuda")
+    Cb = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    LIB.call("indnet_tc_gemm_rank1", current_stream(), 0, 0, M, N, K, ptr(A), K, ptr(B), K, ptr(C), ptr(Cb), N,
+             ptr(rs), ptr(va), ptr(vb) if split < group else None, rows, group, split)
+    torch.cuda.synchronize()
+    v = torch.empty(X, N, device="cuda")
+    for x in range(X):
+        e, r = divmod(x, group)
+        v[x] = va[e * split + r] if r < split else vb[e * (group - split) + (r - split)]
+    ref = want[0] + rs.double()[:, None] * v[torch.arange(M, device="cuda") // rows].double()
+    scale = float(ref.abs().max())
+    assert float((C.double() - ref).abs().max()) / scale < 2e-5
+    assert float((Cb.double() - ref).abs().max()) / scale < 1e-2
