@@ -207,50 +207,69 @@ smp_gen_kernel(const SmpHdr* __restrict__ h, int ahead, uint32_t* __restrict__ k
     }
     return;
   }
-  // ---- CTA 1
+  // ---- CTA 1.  One thread consumes the Python stream, one draw per loop iteration (random.sample's pool / set
+  // variants and _randbelow's rejection loop unrolled into a flat state machine), from a block of outputs the
+  // whole CTA has tempered; when the block runs out the CTA twists the state cooperatively and the thread
+  // resumes where it stopped.
   uint32_t* pkey = ring;                     // 624 words
+  uint32_t* pout = ring + 1024;              // their tempered outputs
   __shared__ int pool[1024];
   __shared__ uint32_t seen[32];
-  for (int i = tid; i < MT_N; i += GEN_NT) pkey[i] = py_state[i];
+  __shared__ int more;
+  for (int i = tid; i < MT_N; i += GEN_NT) { const uint32_t v = py_state[i]; pkey[i] = v; pout[i] = mt_temper(v); }
   for (int i = tid; i < R; i += GEN_NT) pool[i] = i;
+  if (tid < 32) seen[tid] = 0u;
   __syncthreads();
-  if (tid == 0) {
-    SerialMT mt{pkey, (int)py_state[MT_N]};
+  int pos = (int)py_state[MT_N], eb = 0, ei = 0, nt = 0;     // stream offset, episode, draw within it (thread 0)
+  int touched[64];
+  bool use_pool = true;
+  {
     int setsize = 21;
     if (N > 5) {   // setsize += 4 ** ceil(log(N*3, 4))
-      int p = 1;
-      while (p < 3 * N) p *= 4;
-      setsize += p;
+      int p4 = 1;
+      while (p4 < 3 * N) p4 *= 4;
+      setsize += p4;
     }
-    for (int b = 0; b < B; ++b) {
-      int* out = classes + (long long)b * N;
-      if (R <= setsize) {
-        // pool variant; the pool is restored after each episode instead of rebuilt (only the <= 2N
-        // entries the draws touched differ from the identity)
-        int touched[64];
-        int nt = 0;
-        for (int i = 0; i < N; ++i) {
-          const int j = mt.randbelow(R - i);
-          out[i] = pool[j];
-          pool[j] = pool[R - i - 1];
-          if (nt < 64) touched[nt++] = j;
+    use_pool = R <= setsize;
+  }
+  while (true) {
+    if (tid == 0) {
+      while (eb < B && pos < MT_N) {
+        const int n = use_pool ? R - ei : R;
+        const uint32_t r = pout[pos++] >> __clz(n);          // getrandbits(n.bit_length())
+        if (r >= (uint32_t)n) continue;                      // _randbelow rejects
+        int* out = classes + (long long)eb * N;
+        if (use_pool) {
+          out[ei] = pool[r];
+          pool[r] = pool[R - ei - 1];
+          if (nt < 64) touched[nt++] = (int)r;
+        } else {
+          if (seen[r >> 5] & (1u << (r & 31))) continue;     // already selected: draw again
+          seen[r >> 5] |= 1u << (r & 31);
+          out[ei] = (int)r;
         }
-        if (N <= 64) { for (int i = 0; i < nt; ++i) pool[touched[i]] = touched[i]; }
-        else { for (int i = 0; i < R; ++i) pool[i] = i; }
-      } else {
-        for (int i = 0; i < 32; ++i) seen[i] = 0u;
-        for (int i = 0; i < N; ++i) {
-          int j = mt.randbelow(R);
-          while (seen[j >> 5] & (1u << (j & 31))) j = mt.randbelow(R);
-          seen[j >> 5] |= 1u << (j & 31);
-          out[i] = j;
+        if (++ei == N) {                                     // episode complete: back to a fresh pool / empty set
+          if (use_pool) {
+            if (N <= 64) { for (int q = 0; q < nt; ++q) pool[touched[q]] = touched[q]; }
+            else { for (int q = 0; q < R; ++q) pool[q] = q; }
+          } else {
+            for (int q = 0; q < 32; ++q) seen[q] = 0u;
+          }
+          ei = 0; nt = 0; ++eb;
         }
       }
+      more = eb < B ? 1 : 0;
     }
-    py_state[MT_N] = (uint32_t)mt.pos;
+    __syncthreads();
+    if (!more) break;
+    mt_twist_block(pkey);                                    // block exhausted with episodes left: next 624 words
+    for (int i = tid; i < MT_N; i += GEN_NT) pout[i] = mt_temper(pkey[i]);
+    pos = 0;
+    __syncthreads();
   }
-  __syncthreads();
+  if (tid == 0) py_state[MT_N] = (uint32_t)pos;
   for (int i = tid; i < MT_N; i += GEN_NT) py_state[i] = pkey[i];
+  __syncthreads();
   // permutation length of every job of the walk (episode-major: N class scopes, then the N*Q query
   // permutation); negative = the error the walker reports when it reaches that job
   for (int j = tid; j < B * (N + 1); j += GEN_NT) {
