@@ -69,6 +69,11 @@ int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, co
 int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
                          const void* B, long long ldb, float* C, void* Cb, int ldc, const float* rs,
                          const float* rv_a, const float* rv_b, int rv_rows, int group, int split);
+/* Both weight gradients of one LSTM direction in one pass over dz (bf16 mode, hidden_size 128, D <= 64):
+ *   dkernel[D+u][4u] = [x | h_prev]^T * dz,  x_bf [T][64] (columns >= D zero), hprev_bf [T][u], dz_bf [T][4u]
+ * (autodiff of the LSTM kernel matmul, model/graph.py:44).  Overwrites dkernel (fp32, split-K reductions). */
+int indnet_tc_gemm_lstm_dw(indnet_stream st, const void* x_bf, const void* hprev_bf, const void* dz_bf,
+                           float* dkernel, long long T, int D, int u, int splitk);
 /* out (bf16) = in (fp32), n elements. */
 int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
 /* Row-wise cast with a padded output row stride: out[r][0..ldo) = in[r][0..cols), zeros beyond cols

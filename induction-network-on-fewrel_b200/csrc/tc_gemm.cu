@@ -258,6 +258,122 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1) tmem_dealloc(taddr, G_BN);
 }
 
+// ---------------------------------------------------------------- stacked weight-gradient GEMM
+// dW = [A1 | A2]^T * B for the LSTM kernels: A1 = x [K][64] and A2 = h_prev [K][128] (both stored token-major,
+// i.e. MN-major A), B = dz [K][N].  One CTA owns BOTH M tiles of the stacked operand [x(64); h(128); 0(64)]
+// for its N tile and K slice, so every dz tile is fetched once and multiplied twice (two accumulators, 256
+// TMEM columns).  Split-K over the tokens, fp32 atomics into the TF kernel gradient [D+u][N]: stacked row r
+// lands in row r (r < D, the x features), is dropped (D <= r < 64, padding), or in row D + r - 64 (h units).
+constexpr int D_STAGES = 4;
+constexpr int D_A_BYTES = 4 * 64 * G_BK * 2;      // four 64-wide M atoms of 8 KB: x, h[0:64], h[64:128], zeros
+constexpr int D_SMEM = D_STAGES * (D_A_BYTES + G_B_BYTES) + 256 + 1024;
+
+struct TcDualP { float* C; int D, N, K, ldc, kb_per_split; };
+
+__global__ void __launch_bounds__(G_THREADS, 1)
+tc_gemm_dual_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmH,
+                    const __grid_constant__ CUtensorMap tmB, TcDualP p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + D_STAGES * D_A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + D_STAGES * (D_A_BYTES + G_B_BYTES));
+  uint64_t* empty = full + D_STAGES;
+  uint64_t* tmem_full = empty + D_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * G_BN, ks = blockIdx.z;
+  const int total_kb = (p.K + G_BK - 1) / G_BK;
+  const int kb0 = ks * p.kb_per_split;
+  const int num_kb = min(total_kb, kb0 + p.kb_per_split) - kb0;
+
+  // the fourth atom of every stage is the zero padding of the stacked operand: written once, never loaded
+  for (int s = 0; s < D_STAGES; ++s)
+    for (int i = threadIdx.x; i < 8192 / 16; i += G_THREADS)
+      reinterpret_cast<uint4*>(sA + s * D_A_BYTES + 3 * 8192)[i] = make_uint4(0, 0, 0, 0);
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmH);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < D_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * G_BN);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t taddr = *tmem_slot;
+
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % D_STAGES, ph = (kb / D_STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], 3 * 8192 + G_B_BYTES);
+        const int k = (kb0 + kb) * G_BK;
+        uint8_t* a = sA + s * D_A_BYTES;
+        uint8_t* b = sB + s * G_B_BYTES;
+        tma_load_3d(a, &tmX, &full[s], 0, k, 0);                 // x: 64 features x 64 tokens
+        tma_load_3d(a + 8192, &tmH, &full[s], 0, k, 0);          // h_prev units 0..63
+        tma_load_3d(a + 16384, &tmH, &full[s], 64, k, 0);        // h_prev units 64..127
+        tma_load_3d(b, &tmB, &full[s], n0, k, 0);
+        tma_load_3d(b + G_B_BYTES / 2, &tmB, &full[s], n0 + 64, k, 0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = idesc_bf16(G_BM, G_BN, true, true);
+      constexpr uint32_t lbo = G_BK * 128, kstep = 16 * 128;     // MN-major operands, as in tc_gemm_kernel
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % D_STAGES, ph = (kb / D_STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + s * D_A_BYTES), b_base = smem_u32(sB + s * G_B_BYTES);
+#pragma unroll
+        for (int k = 0; k < G_BK / 16; ++k) {
+          const uint64_t bd = smem_desc_sw128(b_base + k * kstep, lbo, 1024);
+          const uint64_t a0 = smem_desc_sw128(a_base + k * kstep, lbo, 1024);            // atoms x | h[0:64]
+          const uint64_t a1 = smem_desc_sw128(a_base + 16384 + k * kstep, lbo, 1024);    // atoms h[64:128] | 0
+          umma_bf16(taddr, a0, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_bf16(taddr + G_BN, a1, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    // epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); lane = stacked row within the M tile
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int tile = 0; tile < 2; ++tile) {
+      const int sr = tile * G_BM + r;                                      // stacked row
+      const int dest = sr < 64 ? (sr < p.D ? sr : -1) : (sr < 64 + 128 ? p.D + sr - 64 : -1);
+#pragma unroll 1
+      for (int c = 0; c < G_BN / 32; ++c) {
+        float v[32];
+        tmem_ld32(taddr + tile * G_BN + ((uint32_t)(q * 32) << 16) + c * 32, v);
+        tmem_ld_wait();
+        if (dest >= 0) {
+          // N is a multiple of the tile width here, rows are 16-byte aligned: 16-byte vector reductions
+          float4* out = reinterpret_cast<float4*>(p.C + (long long)dest * p.ldc + n0 + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) atomicAdd(out + j, make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(taddr, 2 * G_BN);
+}
+
 // ---------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -429,4 +545,39 @@ extern "C" int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M,
   TcGemmRank1 r1{rs, rv_a, rv_b, rv_rows, group, split};
   return tc_gemm((cudaStream_t)st, a_mn != 0, b_mn != 0, M, N, K, A, lda, B, ldb, C, Cb, ldc, nullptr, 0, 0, 1, 0, 0, 0,
                  1, &r1);
+}
+
+extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const void* hprev_bf, const void* dz_bf,
+                                      float* dkernel, long long T, int D, int u, int splitk) {
+  cudaStream_t st = (cudaStream_t)st_;
+  const int N = 4 * u;
+  IN_REQUIRE(T > 0 && D > 0 && D <= 64 && u == 128, "tc_gemm_lstm_dw: needs E + 10 <= 64 and hidden_size 128 (D=%d u=%d)", D, u);
+  IN_REQUIRE(x_bf && hprev_bf && dz_bf && dkernel, "tc_gemm_lstm_dw: null pointer");
+  IN_REQUIRE(((uintptr_t)dkernel & 15) == 0, "tc_gemm_lstm_dw: gradient buffer not 16-byte aligned");
+  IN_REQUIRE(T <= 2147483647LL, "tc_gemm_lstm_dw: too many tokens");
+  const int total_kb = ceil_div((int)T, G_BK);
+  const int gx = N / G_BN;
+  if (splitk <= 0) splitk = 148 / gx;                        // one CTA per SM (160 KB of operand ring each)
+  if (splitk > total_kb) splitk = total_kb;
+  if (splitk < 1) splitk = 1;
+  TcDualP p;
+  p.C = dkernel; p.D = D; p.N = N; p.K = (int)T; p.ldc = N;
+  p.kb_per_split = ceil_div(total_kb, splitk);
+  splitk = ceil_div(total_kb, p.kb_per_split);
+  IN_CUDA(cudaMemsetAsync(dkernel, 0, sizeof(float) * (size_t)(D + u) * N, st));
+  CUtensorMap tmX, tmH, tmB;
+  int rc = make_tmap_bf16(&tmX, x_bf, 64, T, 64, 1, 0, 64, G_BK);           // [T][64]: box 64 features x 64 tokens
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmH, hprev_bf, u, T, u, 1, 0, 64, G_BK);             // [T][128]: boxes of 64 units
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmB, dz_bf, N, T, N, 1, 0, 64, G_BK);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IN_CUDA(cudaFuncSetAttribute(tc_gemm_dual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D_SMEM));
+    attr_set = true;
+  }
+  tc_gemm_dual_kernel<<<dim3(gx, 1, splitk), G_THREADS, D_SMEM, st>>>(tmX, tmH, tmB, p);
+  IN_LAUNCH_CHECK("tc_gemm_dual_kernel");
+  return INDNET_OK;
 }

@@ -600,19 +600,17 @@ class EpisodePipeline:
         n0 = 0 if self.trainable_words else c.E
         for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
             gk = p.grad(kn)
-            # dW_x and dW_h of a direction both stream the same dz: launched side by side (second one on an
-            # auxiliary stream, forked and joined here) their CTAs walk the token range together and the
-            # second reader of every dz tile hits L2 instead of HBM
-            cur = torch.cuda.current_stream()
-            aux = self._aux_stream if self.profile is None else None
-            if aux is not None:
-                aux.wait_stream(cur)
-                with torch.cuda.stream(aux):
-                    self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
-            self._tc(1, 1, c.D, u4, c.T, self.x_bf, 64, self.dz_bf[d], u4, C=gk, tag="lstm_dWx")
-            if aux is not None:
-                cur.wait_stream(aux)
+            if self.tc_lstm:
+                # both weight gradients of the direction in one pass over dz: one CTA multiplies every dz tile
+                # with the stacked [x | h_prev] operand (two accumulators)
+                self._tag = "tc_gemm:lstm_dW"
+                try:
+                    self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
+                               ptr(gk), c.T, c.D, c.u, 0)
+                finally:
+                    self._tag = None
             else:
+                self._tc(1, 1, c.D, u4, c.T, self.x_bf, 64, self.dz_bf[d], u4, C=gk, tag="lstm_dWx")
                 self._tc(1, 1, c.u, u4, c.T, self.hprev_bf[d], c.u, self.dz_bf[d], u4, C=gk[c.D:], tag="lstm_dWh")
             if not self.tc_lstm:
                 self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))

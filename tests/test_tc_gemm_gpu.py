@@ -92,3 +92,22 @@ def test_tc_gemm_rank1_epilogue(M, N, rows, group, split):
     scale = float(ref.abs().max())
     assert float((C.double() - ref).abs().max()) / scale < 2e-5
     assert float((Cb.double() - ref).abs().max()) / scale < 1e-2
+
+
+@pytest.mark.parametrize("T,D", [(4096, 60), (1000, 18), (77, 64)])
+def test_tc_gemm_lstm_dw_stacked_operand(T, D):
+    """dkernel[D+u][4u] = [x | h_prev]^T dz in one pass over dz (two accumulators per CTA, split-K over tokens,
+    16-byte vector reductions): rows < D from x, rows D.. from h_prev, the padding rows of x are dropped."""
+    from induction_b200._lib import LIB, current_stream, ptr
+    u = 128
+    g = torch.Generator(device="cuda").manual_seed(T + D)
+    x = torch.zeros(T, 64, device="cuda")
+    x[:, :D] = torch.randn(T, D, generator=g, device="cuda")
+    x = x.to(torch.bfloat16)
+    h = torch.randn(T, u, generator=g, device="cuda").to(torch.bfloat16)
+    dz = torch.randn(T, 4 * u, generator=g, device="cuda").to(torch.bfloat16)
+    out = torch.full((D + u, 4 * u), float("nan"), device="cuda")
+    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(x), ptr(h), ptr(dz), ptr(out), T, D, u, 0)
+    torch.cuda.synchronize()
+    ref = torch.cat([x[:, :D].double().t() @ dz.double(), h.double().t() @ dz.double()], 0)
+    assert float((out.double() - ref).abs().max() / ref.abs().max()) < 2e-5
