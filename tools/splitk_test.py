@@ -18,3 +18,16 @@ for M, Aop, lda, name in ((128, A, 128, "dWh"), (60, X, 64, "dWx")):
         for _ in range(20): run(M, Aop, lda, sk)
         e1.record(); torch.cuda.synchronize()
         print(name, "splitk", sk, "%.1f us" % (e0.elapsed_time(e1) / 20 * 1e3))
+
+# stacked [x | h_prev]^T dz kernel (indnet_tc_gemm_lstm_dw)
+out = torch.zeros(60 + 128, u4, device="cuda")
+def run_dual(sk):
+    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(X), ptr(A), ptr(B), ptr(out), T, 60, 128, sk)
+for sk in (0, 18, 37, 74, 111, 148):
+    for _ in range(3): run_dual(sk)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20): run_dual(sk)
+    e1.record(); torch.cuda.synchronize()
+    print("stacked dW splitk", sk, "%.1f us" % (e0.elapsed_time(e1) / 20 * 1e3))
