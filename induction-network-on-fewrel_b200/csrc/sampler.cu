@@ -68,25 +68,6 @@ __device__ void mt_twist_block(uint32_t* key) {
   if (t < 170) key[t + 454] = r;
   __syncthreads();
 }
-// Sequential twist by one thread (Python stream: a handful of draws per episode).
-__device__ void mt_twist_serial(uint32_t* key) {
-  for (int i = 0; i < MT_N; ++i) key[i] = mt_mix(key[i], key[(i + 1) % MT_N], key[(i + MT_M) % MT_N]);
-}
-struct SerialMT {
-  uint32_t* key; int pos;
-  __device__ uint32_t next() {
-    if (pos >= MT_N) { mt_twist_serial(key); pos = 0; }
-    return mt_temper(key[pos++]);
-  }
-  // CPython Random._randbelow_with_getrandbits
-  __device__ int randbelow(int n) {
-    const int k = 32 - __clz(n);
-    uint32_t r = next() >> (32 - k);
-    while (r >= (uint32_t)n) r = next() >> (32 - k);
-    return (int)r;
-  }
-};
-
 // NumPy random_interval mask: smallest 2^k - 1 >= mx (mx >= 1): all ones below the top set bit.
 __device__ __forceinline__ uint32_t mask_for(uint32_t mx) { return 0xFFFFFFFFu >> __clz(mx); }
 

@@ -267,7 +267,6 @@ class EpisodePipeline:
         self.correct = i32(c.B * c.n_q)
         self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
         self._bwd_ready = False
-        self._aux_stream = torch.cuda.Stream(device=self.dev)
         self.bf16 = cfg.mode == "bf16"
         if self.bf16:
             if c.D > 64 or c.u % 8:
