@@ -28,15 +28,23 @@ __global__ void embed_fwd_bf16_kernel(const int* __restrict__ word, const int* _
                                       const int* __restrict__ pos2, const float* __restrict__ wt,
                                       const float* __restrict__ p1t, const float* __restrict__ p2t,
                                       __nv_bfloat16* __restrict__ xb, long long T, int E, int P) {
+  // two adjacent columns per thread: one 4-byte store, half the threads; a warp covers a whole 64-column row
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (i >= T * 64) return;
-  long long t = i >> 6;
-  int d = (int)(i & 63);
-  float v = 0.f;
-  if (d < E) v = wt[(long long)word[t] * E + d];
-  else if (d < E + P) v = p1t[(long long)pos1[t] * P + (d - E)];
-  else if (d < E + 2 * P) v = p2t[(long long)pos2[t] * P + (d - E - P)];
-  xb[i] = __float2bfloat16(v);
+  if (i >= T * 32) return;
+  long long t = i >> 5;
+  const int d0 = (int)(i & 31) * 2;
+  const long long w = word[t], q1 = pos1[t], q2 = pos2[t];
+  float v[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int d = d0 + j;
+    float x = 0.f;
+    if (d < E) x = wt[w * E + d];
+    else if (d < E + P) x = p1t[q1 * P + (d - E)];
+    else if (d < E + 2 * P) x = p2t[q2 * P + (d - E - P)];
+    v[j] = x;
+  }
+  reinterpret_cast<__nv_bfloat162*>(xb)[i] = __floats2bfloat162_rn(v[0], v[1]);
 }
 
 // Position tables are tiny ([2L, P]) and every token hits them: accumulate in shared memory per
@@ -179,7 +187,7 @@ extern "C" int indnet_embed_fwd_bf16(indnet_stream st_, const int* word, const i
   IN_REQUIRE(T >= 0 && E > 0 && P > 0 && E + 2 * P <= 64, "embed_fwd_bf16: need E + 2P <= 64 (E=%d P=%d)", E, P);
   if (T == 0) return INDNET_OK;
   IN_REQUIRE(word && pos1 && pos2 && word_table && pos1_table && pos2_table && xb, "embed_fwd_bf16: null pointer");
-  embed_fwd_bf16_kernel<<<ceil_div(T * 64, 256), 256, 0, st>>>(word, pos1, pos2, word_table, pos1_table, pos2_table,
+  embed_fwd_bf16_kernel<<<ceil_div(T * 32, 256), 256, 0, st>>>(word, pos1, pos2, word_table, pos1_table, pos2_table,
                                                                (__nv_bfloat16*)xb, T, E, P);
   IN_LAUNCH_CHECK("embed_fwd_bf16_kernel");
   return INDNET_OK;
