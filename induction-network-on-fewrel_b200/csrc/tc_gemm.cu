@@ -468,11 +468,8 @@ int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const vo
   IN_REQUIRE(grid.z <= 65535, "tc_gemm: batch*splitk too large");
 #define LAUNCH_TC(AM, BM_)                                                                                      \
   do {                                                                                                          \
-    static bool attr_set = false;                                                                               \
-    if (!attr_set) {                                                                                            \
-      IN_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<AM, BM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM)); \
-      attr_set = true;                                                                                          \
-    }                                                                                                           \
+    /* per device and cheap: set on every launch (legal during stream capture) */                                 \
+    IN_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<AM, BM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM)); \
     tc_gemm_kernel<AM, BM_><<<grid, G_THREADS, G_SMEM, st>>>(tmA, tmB, p);                                      \
   } while (0)
   if (a_mn && b_mn) LAUNCH_TC(true, true);
@@ -572,11 +569,8 @@ extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const
   if (rc) return rc;
   rc = make_tmap_bf16(&tmB, dz_bf, N, T, N, 1, 0, 64, G_BK);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    IN_CUDA(cudaFuncSetAttribute(tc_gemm_dual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D_SMEM));
-    attr_set = true;
-  }
+  // the attribute is per device and cheap to set: do it on every launch (legal during stream capture)
+  IN_CUDA(cudaFuncSetAttribute(tc_gemm_dual_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D_SMEM));
   tc_gemm_dual_kernel<<<dim3(gx, 1, splitk), G_THREADS, D_SMEM, st>>>(tmX, tmH, tmB, p);
   IN_LAUNCH_CHECK("tc_gemm_dual_kernel");
   return INDNET_OK;

@@ -65,9 +65,12 @@ __global__ void lstm_pack_weights_kernel(const float* __restrict__ k_fw, const f
 // tools/lstm_dbg.py); compiled out of the product build.
 #ifdef INDNET_LSTM_TIMELINE
 __device__ long long g_lstm_dbg[64 * 8];
+__device__ long long g_lstm_dbg_b[64 * 8];
 #define LT_MARK(cond, s, k) do { if ((cond) && blockIdx.x == 0 && blockIdx.y == 0 && (s) < 64) g_lstm_dbg[(s) * 8 + (k)] = clock64(); } while (0)
+#define LB_MARK(cond, s, k) do { if ((cond) && blockIdx.x == 0 && blockIdx.y == 0 && (s) < 64) g_lstm_dbg_b[(s) * 8 + (k)] = clock64(); } while (0)
 #else
 #define LT_MARK(cond, s, k) do { } while (0)
+#define LB_MARK(cond, s, k) do { } while (0)
 #endif
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
@@ -445,6 +448,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
     for (int step = 0; step < (DX ? L : L - 1); ++step) {
       mbar_wait(z_ready, step & 1);
       tc_fence_after();
+      LB_MARK(lane == 0, step, 5);
       const uint32_t zb16 = z16 + (DX ? (uint32_t)(step & 1) * (LB_Z_BYTES >> 4) : 0u);
       if (elect_one()) {
         if (step + 1 < L) {                             // the last step's dh_rec has no consumer
@@ -460,6 +464,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
         }
       }
       __syncwarp();
+      LB_MARK(lane == 0, step, 6);
       if (DX) {
         // Off the recurrence's critical path, own barrier - and issued only once the recurrent MMAs are done
         // and the gate warps have had time to pull dh_rec out of tensor memory: shared-memory-operand MMAs
@@ -544,6 +549,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
     }
 
     for (int step = 0; step < L; ++step) {
+      LB_MARK(threadIdx.x == 0, step, 0);
       // ---- this step's saved activations: every load is issued before anything waits on them
       uint2 gw[LT_SPT];
       float dh[LT_SPT], cp[LT_SPT];
@@ -561,8 +567,10 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
         mbar_wait(mma_done, (step - 1) & 1);
         __syncwarp();
         tc_fence_after();
+        LB_MARK(threadIdx.x == 0, step, 1);
         tmem_ld_spt(lane_addr, dhr);
         tmem_ld_wait();
+        LB_MARK(threadIdx.x == 0, step, 2);
 #pragma unroll
         for (int q = 0; q < LT_SPT; ++q) dh[q] += dhr[q];      // the recurrent part is added after the dropout mask
       }
@@ -593,10 +601,12 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmXf, const __grid_consta
           gz[0] = bi; gz[LT_U] = bj; gz[2 * LT_U] = bf; gz[3 * LT_U] = bo;
         }
       }
+      LB_MARK(threadIdx.x == 0, step, 3);
       if (DX && step > 0) store_dx(step - 1);           // long complete by now; must precede this step's arrival
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(z_ready);
+      LB_MARK(threadIdx.x == 0, step, 4);
       g_ptr += estep * 8; c_ptr += estep * 2; do_ptr += ostep * 2; z_ptr += estep * 8; oi += ostep;
       if (DX && step > 0) x_ptr += (estep / LT_U) * (LB_DX_LD * 4);
     }
@@ -638,6 +648,9 @@ using namespace indnet;
 #ifdef INDNET_LSTM_TIMELINE
 extern "C" int indnet_debug_lstm(long long* out) {
   return (int)cudaMemcpyFromSymbol(out, g_lstm_dbg, sizeof(long long) * 512);
+}
+extern "C" int indnet_debug_lstm_bwd(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, g_lstm_dbg_b, sizeof(long long) * 512);
 }
 #endif
 extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
@@ -688,12 +701,9 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   const bool drop = keep_prob < 1.0f, h32 = hout != nullptr;
 #define LT_FWD_LAUNCH(DROP_, H32_)                                                                              \
   do {                                                                                                          \
-    static bool attr_set = false;                                                                               \
-    if (!attr_set) {                                                                                            \
-      IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel<DROP_, H32_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+    /* per device and cheap: set on every launch (legal during stream capture) */                                 \
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel<DROP_, H32_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                    LT_SMEM));                                                                   \
-      attr_set = true;                                                                                          \
-    }                                                                                                           \
     tc_lstm_fwd_kernel<DROP_, H32_><<<grid, LT_FWD_THREADS, LT_SMEM, st>>>(tmW, tmX, p);                          \
   } while (0)
   if (drop && h32) LT_FWD_LAUNCH(true, true);
@@ -751,12 +761,9 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   const bool drop = keep_prob < 1.0f;
 #define LB_LAUNCH(DROP_, DX_)                                                                                   \
   do {                                                                                                          \
-    static bool attr_set = false;                                                                               \
     const int smem = DX_ ? LB_SMEM_DX : LB_SMEM;                                                                \
-    if (!attr_set) {                                                                                            \
-      IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
-      attr_set = true;                                                                                          \
-    }                                                                                                           \
+    /* per device and cheap: set on every launch (legal during stream capture) */                                 \
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
     tc_lstm_bwd_kernel<DROP_, DX_><<<grid, LB_THREADS, smem, st>>>(tmXf, tmXb, p);                                \
   } while (0)
   if (drop && dx2) LB_LAUNCH(true, true);

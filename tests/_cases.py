@@ -16,10 +16,17 @@ CASES = {
     "u24": dict(N=4, K=3, Q=5, B=3, L=11, E=20, u=24, S=16),                # smallest bf16-mode-legal widths
     "cfg0_5w5s": dict(N=5, K=5, Q=5, B=2, L=40, E=50, u=128, S=100),      # BASELINE configs[0] shape, B=2
 }
+# BASELINE configs[1..3] shapes for the bf16 tensor-core tests (not in CASES: the FFMA parity mode would
+# spend minutes on them); configs[1] at its full batch (60 sentence tiles per direction, K = 1 routing)
+BENCH_CASES = {
+    "cfg1_5w1s_b64": dict(N=5, K=1, Q=5, B=64, L=40, E=50, u=128, S=100),
+    "cfg2_10w5s": dict(N=10, K=5, Q=5, B=2, L=40, E=50, u=128, S=100),
+    "cfg3_10w10s": dict(N=10, K=10, Q=5, B=2, L=40, E=50, u=128, S=100),
+}
 
 
 def make_case(name, seed=0, vocab=500, relations=12, per_relation=30, keep_prob=1.0, mode="fp32"):
-    cfg = EpisodeConfig(**CASES[name], keep_prob=keep_prob, mode=mode)
+    cfg = EpisodeConfig(**(CASES.get(name) or BENCH_CASES[name]), keep_prob=keep_prob, mode=mode)
     tables = make_tables(relations, per_relation, cfg.L, vocab, cfg.E, seed=seed, min_len=min(3, cfg.L))
     rs = np.random.RandomState(seed + 1)
     rows = np.zeros((cfg.B, cfg.n_s), dtype=np.int64)

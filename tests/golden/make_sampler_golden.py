@@ -82,6 +82,19 @@ def main():
                 st = np.random.get_state()
                 out["np_key_after"] = st[1]
                 out["np_pos_after"] = st[2]
+                # the reference's other sampler, next_one (data_loader.py:213-257): stacked support [N, K, L],
+                # separate permuted query set; drawn right after the next_one_tf episodes on the same streams
+                N1, K1, Q1 = plan[0][:3]
+                for r in range(2):
+                    sup, qry, lab = loader.next_one(N1, K1, Q1)
+                    for k in ("word", "pos1", "pos2", "mask"):
+                        out["one%d_sup_%s" % (r, k)] = sup[k]
+                        out["one%d_qry_%s" % (r, k)] = qry[k]
+                    out["one%d_label" % r] = lab
+                out["py_state_after_one"] = np.array(random.getstate()[1], dtype=np.uint64)
+                st = np.random.get_state()
+                out["np_key_after_one"] = st[1]
+                out["np_pos_after_one"] = st[2]
             finally:
                 os.chdir(cwd)
         np.savez_compressed(os.path.join(HERE, "sampler_%s.npz" % name), **out)

@@ -213,6 +213,93 @@ def test_bf16_mode_forward_and_backward_parity(name):
         assert e < BF16_GRAD_TOL, (name, k, e)
 
 
+@pytest.mark.parametrize("name", ["cfg1_5w1s_b64", "cfg2_10w5s", "cfg3_10w10s"])
+def test_bf16_mode_parity_at_benchmarked_shapes(name):
+    """The shapes bench.py times (BASELINE configs[1..3]; configs[1] at its full 64-episode batch = 60
+    sentence tiles per direction and the K = 1 routing path) through the tcgen05 recurrence / BPTT /
+    stacked weight-gradient kernels, against the float64 oracle on the whole batch."""
+    cfg, tables, inputs, label, params = make_case(name, seed=5, mode="bf16", relations=16, per_relation=40, vocab=3000)
+    pipe = build_pipeline(cfg, tables, params)
+    assert pipe.tc_lstm
+    pipe.set_inputs(inputs, label)
+    pipe.forward(train=True)
+    pipe.backward()
+    torch.cuda.synchronize()
+    ref, gref = oracle_grads(cfg, tables, inputs, label, params, dtype=torch.float64)
+    e_probs = rel_err(pipe.probs, ref["probs"])
+    e_hout = rel_err(pipe.hout_bf.float().view(cfg.X, cfg.L, cfg.H), ref["hout"])
+    e_loss = abs(pipe.loss() - float(ref["loss"])) / float(ref["loss"])
+    got = pipe.p.grad_dict()
+    errs = {k: rel_err(got[k], gref[k]) for k in gref}
+    print(name, "probs", e_probs, "hout", e_hout, "loss", e_loss, {k: "%.1e" % v for k, v in errs.items()})
+    assert e_probs < BF16_TOL and e_loss < BF16_TOL and e_hout < BF16_TOL
+    assert abs(pipe.accuracy() - float(ref["accuracy"])) < 2.0 / (cfg.B * cfg.n_q)   # at most one near-tie flips
+    for k, e in errs.items():
+        assert e < BF16_GRAD_TOL, (name, k, e)
+
+
+def test_bf16_mode_dropout_replays_in_oracle():
+    """keep_prob = 0.9 (the reference's training value, model/base.py:26,149) through the DROP
+    instantiations of the tcgen05 recurrence and BPTT kernels; the device mask is replayed in the oracle."""
+    from induction_b200.engine import dropout_keep_mask
+    cfg, tables, inputs, label, params = make_case("cfg0_5w5s", seed=4, keep_prob=0.9, mode="bf16")
+    pipe = build_pipeline(cfg, tables, params, seed=77)
+    assert pipe.tc_lstm
+    pipe.set_inputs(inputs, label)
+    pipe.forward(train=True)
+    pipe.backward()
+    torch.cuda.synchronize()
+    mask = dropout_keep_mask(77, (cfg.X, cfg.L, cfg.H), 0.9, step=0)
+    assert 0.88 < mask.mean() < 0.92
+    hb = pipe.hout_bf.float().view(cfg.X, cfg.L, cfg.H).cpu()
+    assert bool(((hb == 0) | torch.from_numpy(mask)).all())      # every dropped position is exactly zero
+    ref, gref = oracle_grads(cfg, tables, inputs, label, params, drop_mask=torch.from_numpy(mask))
+    assert rel_err(hb, ref["hout"]) < BF16_TOL
+    assert rel_err(pipe.probs, ref["probs"]) < BF16_TOL
+    assert abs(pipe.loss() - float(ref["loss"])) / float(ref["loss"]) < BF16_TOL
+    got = pipe.p.grad_dict()
+    errs = {k: rel_err(got[k], gref[k]) for k in gref}
+    print("dropout bf16", {k: "%.1e" % v for k, v in errs.items()})
+    for k, e in errs.items():
+        assert e < BF16_GRAD_TOL, (k, e)
+    # the mask of the next step differs (the seed is offset by global_step) and eval ignores keep_prob
+    pipe.adam()
+    pipe.forward(train=True)
+    mask1 = dropout_keep_mask(77, (cfg.X, cfg.L, cfg.H), 0.9, step=1)
+    hb1 = pipe.hout_bf.float().view(cfg.X, cfg.L, cfg.H).cpu()
+    assert bool(((hb1 == 0) | torch.from_numpy(mask1)).all()) and not np.array_equal(mask, mask1)
+
+
+def test_adam_staircase_is_crossed():
+    """101+ steps so global_step passes decay_steps = 100 and the learning rate drops to 0.9e-3
+    (model/base.py:96-97, staircase=True); trajectory against the float64 oracle."""
+    from oracle import induction_oracle as orc
+    cfg, tables, inputs, label, params = make_case("smoke", seed=6)
+    pipe = build_pipeline(cfg, tables, params)
+    pipe.set_inputs(inputs, label)
+    p = {k: v.double().clone() for k, v in params.items()}
+    m = {k: torch.zeros_like(v) for k, v in p.items()}
+    v = {k: torch.zeros_like(x) for k, x in p.items()}
+    lrs = []
+    for step in range(103):
+        _, g = oracle_grads(cfg, tables, inputs, label, p)
+        lrs.append(orc.tf_adam_step(p, g, m, v, global_step=step))
+        pipe.train_step()
+        if step in (98, 99, 100, 102):
+            assert float(pipe.p.hyper[1].item()) == pytest.approx(lrs[-1], rel=1e-6), step
+    assert lrs[99] == 1e-3 and lrs[100] == pytest.approx(9e-4)
+    assert int(pipe.p.global_step.item()) == 103
+    got = pipe.p.state_dict()
+    for k in p:
+        # Adam moves a weight whose gradient is at rounding-noise level by +-lr per step whatever the noise
+        # says, so the worst entry is not meaningful over 100 steps: bound the bulk of the entries
+        d = (got[k].cpu().double() - p[k]).abs().flatten()
+        assert float(d.quantile(0.9)) < 103e-3 * 2e-2, k
+    out = oracle_forward(cfg, tables, inputs, label, {k: v.float() for k, v in p.items()})
+    pipe.forward()
+    assert abs(pipe.loss() - float(out["loss"])) / float(out["loss"]) < 1e-3
+
+
 def test_bf16_mode_train_steps_track_fp32_mode():
     cfg, tables, inputs, label, params = make_case("u24", seed=6, mode="bf16")
     cfg32, *_ = make_case("u24", seed=6)

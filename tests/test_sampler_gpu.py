@@ -43,6 +43,18 @@ def test_next_one_tf_bit_exact_vs_reference_fixtures(golden_dir, name):
     a = np.random.randint(0, 2 ** 31 - 1, size=8)
     np.random.set_state(("MT19937", z["np_key_after"], int(z["np_pos_after"]), 0, 0.0))
     assert np.array_equal(a, np.random.randint(0, 2 ** 31 - 1, size=8))
+    np.random.set_state(("MT19937", z["np_key_after"], int(z["np_pos_after"]), 0, 0.0))
+    # next_one (reference data_loader.py:213-257) continues on the same streams
+    N1, K1, Q1 = (int(v) for v in z["plan"][0][:3])
+    for r in range(2):
+        sup, qry, lab = ld.next_one(N1, K1, Q1)
+        for k in KEYS:
+            assert sup[k].shape == (N1, K1, ld.max_length) and np.array_equal(sup[k], z["one%d_sup_%s" % (r, k)]), (name, r, k)
+            assert np.array_equal(qry[k], z["one%d_qry_%s" % (r, k)]), (name, r, k)
+        assert np.array_equal(lab, z["one%d_label" % r])
+    assert np.array_equal(np.array(random.getstate()[1], dtype=np.uint64), z["py_state_after_one"])
+    st = np.random.get_state()
+    assert np.array_equal(st[1], z["np_key_after_one"]) and int(st[2]) == int(z["np_pos_after_one"])
 
 
 @pytest.mark.parametrize("B,N,K,Q", [(64, 5, 1, 5), (16, 10, 5, 5), (3, 20, 10, 5)])

@@ -24,3 +24,11 @@ for s in range(1, 38):
     r, n = a[s], a[s + 1]
     print(s, r[1] - r[0], '|', r[2] - r[1], '|', r[3] - r[2], '|', r[4] - r[3], '||', r[5] - r[4], '|', r[6] - r[5], '|', r[7] - r[6],
           '||', n[1] - r[6], '|', n[1] - r[1])
+
+rc = LIB._dll.indnet_debug_lstm_bwd(buf)
+b = np.array(list(buf), dtype=np.int64).reshape(64, 8)
+print("BPTT rc", rc)
+print("gate thread 0: loads issued->mma_done seen | tmem_ld | gate-grad math+stores | dx store+fence+arrive || issuer: arrive->wake | issue || period (mma seen to mma seen)")
+for s in range(2, 38):
+    r, n = b[s], b[s + 1]
+    print(s, r[1] - r[0], '|', r[2] - r[1], '|', r[3] - r[2], '|', r[4] - r[3], '||', r[5] - r[4], '|', r[6] - r[5], '||', n[1] - r[1])
