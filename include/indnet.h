@@ -114,6 +114,17 @@ int indnet_sample_walk(indnet_stream st, unsigned int* py_state, unsigned int* n
 int indnet_sample_gather(indnet_stream st, const int* scopes, const int* t_word, const int* t_pos1, const int* t_pos2,
                          const int* t_mask, int L, int B, int N, int K, int Q, int n_max, const void* scratch,
                          int* rows, int* labels, int* o_word, int* o_pos1, int* o_pos2, int* o_mask);
+/* Stream budget of one call = E[draws] * (1 + pct) + slack (defaults 0.03 / 8192, > 40 sigma).  Process-wide;
+ * changes the scratch layout, so set it before the first indnet_sampler_scratch_bytes.  Used by the tests to
+ * force status 3. */
+int indnet_sampler_set_budget(double pct, long long slack);
+/* Episode-sharded data parallelism: every rank walks the SAME streams for the global batch of B
+ * episodes and gathers only its own episodes [b0, b0 + nb); outputs are [nb][...].  Episode b of the global
+ * batch is therefore bit-identical whatever the number of ranks. */
+int indnet_sample_gather_range(indnet_stream st, const int* scopes, const int* t_word, const int* t_pos1,
+                               const int* t_pos2, const int* t_mask, int L, int B, int N, int K, int Q, int n_max,
+                               const void* scratch, int b0, int nb, int* rows, int* labels, int* o_word, int* o_pos1,
+                               int* o_pos2, int* o_mask);
 
 /* ---- a2: Base.get_embedding, model/base.py:76-86 --------------------------------------------- */
 int indnet_embed_fwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* word_table,
@@ -230,8 +241,10 @@ int indnet_squash_bwd(indnet_stream st, const float* v, const float* dout, float
  * labels [rows]; probs [rows][N]; loss_part [rows] = sum_c (p-y)^2; correct [rows] = argmax hit. */
 int indnet_ntn_head_fwd(indnet_stream st, const float* V, const float* w, const float* b, const int* labels,
                         float* probs, float* loss_part, int* correct, int rows, int N, int S);
-/* out2[0] = loss (mean over rows*N), out2[1] = accuracy. */
-int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, int rows, int N);
+/* out2[0] = loss (mean over rows*N), out2[1] = accuracy.  running (optional, device float[3]): += {loss,
+ * accuracy, 1} - the running sums of model/base.py:156-158 kept on the device. */
+int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, float* running,
+                           int rows, int N);
 /* Upstream gradient: dprobs [rows][N] when not NULL, else the fused mean-squared-error gradient
  * scale*2(p-y) with scale = 1/(rows*N).  Overwrites dlogit [rows][N], dV [rows][N*S], dw, db; dV_bf (optional)
  * receives a bf16 copy of dV with rows padded to ld_bf elements (zeros past N*S), the TMA operand format. */

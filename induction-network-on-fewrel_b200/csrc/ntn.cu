@@ -59,7 +59,7 @@ ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
 // loss = sum(loss_part) / (rows*N)  (tf.losses.mean_squared_error == mean);
 // accuracy = mean(correct).  One block, fixed summation order => deterministic.
 __global__ void loss_acc_reduce_kernel(const float* __restrict__ loss_part, const int* __restrict__ correct,
-                                       float* __restrict__ out2, int rows, int N) {
+                                       float* __restrict__ out2, float* __restrict__ running, int rows, int N) {
   __shared__ float sl[32];
   __shared__ float sa[32];
   float l = 0.f, a = 0.f;
@@ -73,7 +73,12 @@ __global__ void loss_acc_reduce_kernel(const float* __restrict__ loss_part, cons
     l = lane < nw ? sl[lane] : 0.f;
     a = lane < nw ? sa[lane] : 0.f;
     l = warp_sum(l); a = warp_sum(a);
-    if (lane == 0) { out2[0] = l / ((float)rows * (float)N); out2[1] = a / (float)rows; }
+    if (lane == 0) {
+      const float loss = l / ((float)rows * (float)N), acc = a / (float)rows;
+      out2[0] = loss; out2[1] = acc;
+      // running sums so a training loop can read its means every n steps instead of synchronising each step
+      if (running) { running[0] += loss; running[1] += acc; running[2] += 1.0f; }
+    }
   }
 }
 
@@ -161,11 +166,11 @@ extern "C" int indnet_ntn_head_fwd(indnet_stream st_, const float* V, const floa
 }
 
 extern "C" int indnet_loss_acc_reduce(indnet_stream st_, const float* loss_part, const int* correct, float* out2,
-                                      int rows, int N) {
+                                      float* running, int rows, int N) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(rows > 0 && N > 0, "loss_acc_reduce: bad sizes");
   IN_REQUIRE(loss_part && correct && out2, "loss_acc_reduce: null pointer");
-  loss_acc_reduce_kernel<<<1, 1024, 0, st>>>(loss_part, correct, out2, rows, N);
+  loss_acc_reduce_kernel<<<1, 1024, 0, st>>>(loss_part, correct, out2, running, rows, N);
   IN_LAUNCH_CHECK("loss_acc_reduce_kernel");
   return INDNET_OK;
 }

@@ -107,6 +107,7 @@ struct SmpHdr {
   long long win_start;           // block of apos at the start of the current call
   SmpPlan plan[2];               // [0] what this call must still build, [1] what it builds ahead
   int nsec;
+  uint32_t py_backup[MT_N + 1];  // Python stream as handed in: a failing call puts it back (streams unchanged on error)
 };
 
 // One CTA.  ahead == 0: check that np_state is the state the ring continues from (else reset), open the
@@ -157,7 +158,7 @@ __global__ void smp_plan_kernel(SmpHdr* __restrict__ h, const uint32_t* __restri
 }
 
 __global__ void __launch_bounds__(GEN_NT)
-smp_gen_kernel(const SmpHdr* __restrict__ h, int ahead, uint32_t* __restrict__ keys, uint32_t kmask,
+smp_gen_kernel(SmpHdr* __restrict__ h, int ahead, uint32_t* __restrict__ keys, uint32_t kmask,
                uint32_t* __restrict__ py_state, int R, int B, int N, int* __restrict__ classes,
                const int* __restrict__ scopes, int K, int Q, int n_max, int* __restrict__ jsize) {
   __shared__ uint32_t ring[2048];
@@ -197,7 +198,8 @@ smp_gen_kernel(const SmpHdr* __restrict__ h, int ahead, uint32_t* __restrict__ k
   __shared__ int pool[1024];
   __shared__ uint32_t seen[32];
   __shared__ int more;
-  for (int i = tid; i < MT_N; i += GEN_NT) { const uint32_t v = py_state[i]; pkey[i] = v; pout[i] = mt_temper(v); }
+  for (int i = tid; i < MT_N; i += GEN_NT) { const uint32_t v = py_state[i]; pkey[i] = v; pout[i] = mt_temper(v); h->py_backup[i] = v; }
+  if (tid == 0) h->py_backup[MT_N] = py_state[MT_N];
   for (int i = tid; i < R; i += GEN_NT) pool[i] = i;
   if (tid < 32) seen[tid] = 0u;
   __syncthreads();
@@ -430,8 +432,8 @@ __device__ __forceinline__ void sts_release_s32(uint32_t a, int v) {
 __global__ void __launch_bounds__(64)
 smp_walk_kernel(const uint32_t* __restrict__ keys, uint32_t kmask, const unsigned char* __restrict__ tab, int ccap,
                 int n_states, long long nblk, int cb_log, int rc, uint32_t* __restrict__ np_state,
-                const int* __restrict__ jsize, int jobs, int n_max, int* __restrict__ jlist,
-                int4* __restrict__ seclog, SmpHdr* __restrict__ hdr, int* __restrict__ status) {
+                uint32_t* __restrict__ py_state, const int* __restrict__ jsize, int jobs, int n_max,
+                int* __restrict__ jlist, int4* __restrict__ seclog, SmpHdr* __restrict__ hdr, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char ring[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int CB = 1 << cb_log;
@@ -632,8 +634,19 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, uint32_t kmask, const unsigne
     }
   }
   if (lane == 0) ctl[1] = 1;                               // the producer drains its copies and leaves
-  // hand the stream back: the block the walk stopped in (offset 624 = "block exhausted")
-  {
+  // hand the stream back: the block the walk stopped in (offset 624 = "block exhausted").  A call that fails
+  // (status 1-3) leaves BOTH streams exactly as they were handed in, so the host can retry (e.g. in smaller
+  // batches) or raise without having lost draws.
+  if (flag != SMP_OK) {
+    for (int k = lane; k <= MT_N; k += 32) py_state[k] = hdr->py_backup[k];
+    if (lane == 0) {
+      hdr->nsec = 0;
+      status[0] = flag;
+      status[1] = (int)((clock64() - clk0) >> 4);
+      status[2] = n_sec;
+      status[3] = n_row;
+    }
+  } else {
     long long blk = pos / MT_N;
     int off = (int)(pos % MT_N);
     if (off == 0 && blk > 0) { blk -= 1; off = MT_N; }
@@ -745,19 +758,21 @@ __global__ void sampler_gather_kernel(const int* __restrict__ scopes, const int*
                                       int L, const int* __restrict__ t_word, const int* __restrict__ t_pos1,
                                       const int* __restrict__ t_pos2, const int* __restrict__ t_mask,
                                       int* __restrict__ rows, int* __restrict__ labels, int* __restrict__ o_word,
-                                      int* __restrict__ o_pos1, int* __restrict__ o_pos2, int* __restrict__ o_mask) {
+                                      int* __restrict__ o_pos1, int* __restrict__ o_pos2, int* __restrict__ o_mask,
+                                      int b0) {
   const int n_s = N * (K + Q), NK = N * K;
-  const int b = blockIdx.x / n_s, r = blockIdx.x % n_s;
+  const int bl = blockIdx.x / n_s, r = blockIdx.x % n_s;     // bl: episode within the output, b: within the walked batch
+  const int b = b0 + bl;
   int ci, slot;
   if (r < NK) { ci = r / K; slot = r % K; }
   else {
     const int pq = picks[((long long)b * (N + 1) + N) * pick_max + (r - NK)];
     ci = pq / Q; slot = K + pq % Q;
-    if (threadIdx.x == 0) labels[(long long)b * (N * Q) + (r - NK)] = ci;
+    if (threadIdx.x == 0) labels[(long long)bl * (N * Q) + (r - NK)] = ci;
   }
   const int c = classes[(long long)b * N + ci];
   const int row = scopes[2 * c] + picks[((long long)b * (N + 1) + ci) * pick_max + slot];
-  if (threadIdx.x == 0) rows[(long long)b * n_s + r] = row;
+  if (threadIdx.x == 0) rows[(long long)bl * n_s + r] = row;
   const long long src = (long long)row * L, dst = (long long)blockIdx.x * L;
   for (int t = threadIdx.x; t < L; t += blockDim.x) {
     o_word[dst + t] = t_word[src + t];
@@ -789,6 +804,10 @@ static double expected_draws(long long n) {      // E[draws] of NumPy's permutat
   }
   return e;
 }
+// stream budget of one call: E[draws] * (1 + g_budget_pct) + g_budget_slack (indnet_sampler_set_budget: tests
+// shrink it to exercise the "budget exceeded -> streams unchanged -> retry in smaller batches" path)
+static double g_budget_pct = 0.03;
+static long long g_budget_slack = 8192;
 static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   SmpLayout L;
   L.jobs = (long long)B * (N + 1);
@@ -797,7 +816,8 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   L.n_states = (L.stride + 7) / 8 * 8;
   // stream budget: expectation + 3 % + slack (std of one 700-permutation is ~21 draws; this is > 10 sigma)
   const double e = (double)B * ((double)N * expected_draws(n_max) + expected_draws((long long)N * Q));
-  const long long budget = (long long)(e * 1.03) + 8192 + MT_N;
+  long long budget = (long long)(e * (1.0 + g_budget_pct)) + g_budget_slack + MT_N;
+  if (budget < 4 * MT_N) budget = 4 * MT_N;
   L.nblk = (budget + TB - 1) / TB;
   L.nblk = (L.nblk + 15) / 16 * 16;                      // whole chunks for every chunk size the walker may pick
   L.bcap = 2 * L.nblk + 32;
@@ -897,8 +917,8 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   IN_LAUNCH_CHECK("smp_table_kernel");
   IN_CUDA(cudaEventRecord(ev_join[dev], side));
   smp_walk_kernel<<<1, 64, (size_t)L.smem_bytes, st>>>(keys, kmask, tab, ccap, (int)L.n_states, L.nblk, L.cb_log, L.rc,
-                                                      np_state, jsize, (int)L.jobs, (int)L.stride, jlist, seclog, hdr,
-                                                      status);
+                                                      np_state, py_state, jsize, (int)L.jobs, (int)L.stride, jlist, seclog,
+                                                      hdr, status);
   IN_LAUNCH_CHECK("smp_walk_kernel");
   smp_fill_kernel<<<ceil_div(L.sec_cap << L.cb_log, 128), 128, 0, st>>>(tab, bcap, (int)L.n_states, seclog, hdr, L.cb_log,
                                                                         (int)L.stride, jlist);
@@ -912,9 +932,12 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
 
 static int sample_gather(cudaStream_t st, const int* scopes, const int* t_word, const int* t_pos1, const int* t_pos2,
                          const int* t_mask, int L, int B, int N, int K, int Q, int n_max, const void* scratch,
-                         int* rows, int* labels, int* o_word, int* o_pos1, int* o_pos2, int* o_mask) {
+                         int* rows, int* labels, int* o_word, int* o_pos1, int* o_pos2, int* o_mask, int b0 = 0,
+                         int nb = -1) {
   IN_REQUIRE(B >= 0 && N > 0 && K > 0 && Q > 0 && L > 0 && n_max > 0, "sample_gather: bad sizes");
-  if (B == 0) return INDNET_OK;
+  if (nb < 0) nb = B;
+  IN_REQUIRE(b0 >= 0 && nb >= 0 && b0 + nb <= B, "sample_gather: episode range [%d, %d) outside the batch of %d", b0, b0 + nb, B);
+  if (B == 0 || nb == 0) return INDNET_OK;
   IN_REQUIRE(scopes && t_word && t_pos1 && t_pos2 && t_mask && scratch && rows && labels && o_word && o_pos1 &&
              o_pos2 && o_mask, "sample_gather: null pointer");
   const SmpLayout lay = smp_layout(B, N, K, Q, n_max);
@@ -922,9 +945,9 @@ static int sample_gather(cudaStream_t st, const int* scopes, const int* t_word, 
   const int* classes = (const int*)(base + lay.o_classes);
   const int* picks = (const int*)(base + lay.o_picks);
   const int pick_max = (int)lay.pick_max;
-  sampler_gather_kernel<<<B * N * (K + Q), 64, 0, st>>>(scopes, classes, picks, pick_max, B, N, K, Q, L, t_word,
-                                                       t_pos1, t_pos2, t_mask, rows, labels, o_word, o_pos1, o_pos2,
-                                                       o_mask);
+  sampler_gather_kernel<<<nb * N * (K + Q), 64, 0, st>>>(scopes, classes, picks, pick_max, B, N, K, Q, L, t_word,
+                                                        t_pos1, t_pos2, t_mask, rows, labels, o_word, o_pos1, o_pos2,
+                                                        o_mask, b0);
   IN_LAUNCH_CHECK("sampler_gather_kernel");
   return INDNET_OK;
 }
@@ -952,4 +975,19 @@ extern "C" int indnet_sample_gather(indnet_stream st, const int* scopes, const i
                                     int* o_pos2, int* o_mask) {
   return sample_gather((cudaStream_t)st, scopes, t_word, t_pos1, t_pos2, t_mask, L, B, N, K, Q, n_max, scratch, rows,
                        labels, o_word, o_pos1, o_pos2, o_mask);
+}
+
+extern "C" int indnet_sample_gather_range(indnet_stream st, const int* scopes, const int* t_word, const int* t_pos1,
+                                          const int* t_pos2, const int* t_mask, int L, int B, int N, int K, int Q,
+                                          int n_max, const void* scratch, int b0, int nb, int* rows, int* labels,
+                                          int* o_word, int* o_pos1, int* o_pos2, int* o_mask) {
+  return sample_gather((cudaStream_t)st, scopes, t_word, t_pos1, t_pos2, t_mask, L, B, N, K, Q, n_max, scratch, rows,
+                       labels, o_word, o_pos1, o_pos2, o_mask, b0, nb);
+}
+
+extern "C" int indnet_sampler_set_budget(double pct, long long slack) {
+  IN_REQUIRE(pct > -1.0 && slack >= 0, "sampler_set_budget: pct must be > -1 and slack >= 0");
+  g_budget_pct = pct;
+  g_budget_slack = slack;
+  return INDNET_OK;
 }

@@ -36,6 +36,7 @@ class EpisodeConfig:
     iters: int = 3    # routing iterations             (model/layer_module.py:101)
     keep_prob: float = 1.0
     mode: str = "fp32"   # "fp32" parity mode | "bf16" tensor-core mode
+    inference: bool = False   # encoder + induction forward only (BASELINE configs[4]): no BPTT / relation buffers
 
     @property
     def D(self): return self.E + 2 * POS_DIM
@@ -266,6 +267,7 @@ class EpisodePipeline:
         self.loss_part = f(c.B * c.n_q)
         self.correct = i32(c.B * c.n_q)
         self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
+        self.running = torch.zeros(3, dtype=torch.float32, device=self.dev)   # training-step sums {loss, accuracy, steps}
         self._bwd_ready = False
         self.bf16 = cfg.mode == "bf16"
         if self.bf16:
@@ -355,8 +357,16 @@ class EpisodePipeline:
 
     # ------------------------------------------------------------------ forward (model/graph.py:29-86)
     def forward(self, train: bool = False):
+        """InductionGraph.forward + loss / accuracy (model/graph.py:29-109, model/base.py:101-107)."""
+        self.encode(train)
+        self.induction()
+        self.relation(train)
+
+    def encode(self, train: bool = False):
+        """Encoder module: embedding -> BiLSTM -> self-attention pooling, split into support | query
+        (model/graph.py:29-62).  The `encoder sentences/sec` leg of bench.py times exactly this."""
         if self.bf16:
-            return self._forward_bf16(train)
+            return self._encode_bf16(train)
         c, p = self.cfg, self.p
         keep = c.keep_prob if train else 1.0
         wt = p.view("word_embedding") if self.trainable_words else self.word_table
@@ -377,9 +387,23 @@ class EpisodePipeline:
                    bias=p.view(ATT_B), act=1, tag="attn_dense")
         self._call("indnet_attn_pool_fwd", ptr(self.hout), ptr(self.proj), ptr(self.mask), ptr(p.view(ATT_W2)),
                    ptr(self.es), ptr(self.eq), ptr(self.alphas), c.X, c.L, c.H, c.n_s, c.NK)
-        # a6/a7: e_hat = e_s W_s once, then the routing iterations
+        self._last_keep = keep
+
+    def induction(self):
+        """Induction module: e_hat = e_s W_s once, then the routing iterations (model/graph.py:64-80)."""
+        if self.bf16:
+            return self._induction_bf16()
+        c, p = self.cfg, self.p
         self._gemm(0, 0, c.B * c.NK, c.H, c.H, ptr(self.es), c.H, ptr(p.view("W_s")), c.H, ptr(self.ehat), c.H, tag="routing_transform")
         self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), None, c.B * c.N, c.K, c.H, c.iters)
+
+    def relation(self, train: bool = False):
+        """Relation module + loss + accuracy (model/graph.py:82-109, model/base.py:101-107)."""
+        if self.cfg.inference:
+            raise IndnetError("this pipeline was built with inference=True (encoder + induction only)")
+        if self.bf16:
+            return self._relation_bf16(train)
+        c, p = self.cfg, self.p
         # a8: T'[b,c][k][j] = cv M' ; V[b][q][c*S+k] = qe_b T'_b^T
         self._gemm(0, 0, c.B * c.N, c.S * c.H, c.H, ptr(self.cvec), c.H, ptr(p.view("M")), c.S * c.H,
                    ptr(self.Tp), c.S * c.H, tag="ntn_stage1")
@@ -390,10 +414,9 @@ class EpisodePipeline:
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
         self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
-                   c.B * c.n_q, c.N)
-        self._last_keep = keep
+                   ptr(self.running) if train else None, c.B * c.n_q, c.N)
 
-    def _forward_bf16(self, train: bool):
+    def _encode_bf16(self, train: bool):
         """bf16 tensor-core mode: every large contraction runs on tcgen05 (fp32 accumulation); the
         reductions, softmaxes, routing and the loss stay in fp32."""
         c, p = self.cfg, self.p
@@ -424,10 +447,17 @@ class EpisodePipeline:
         self._call("indnet_attn_pool_fwd_bf16", ptr(self.hout_bf), ptr(self.proj_bf), ptr(self.mask),
                    ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.es_bf), ptr(self.eq_bf), ptr(self.alphas),
                    c.X, c.L, c.H, c.n_s, c.NK)
+        self._last_keep = keep
+
+    def _induction_bf16(self):
+        c, p = self.cfg, self.p
         self._tc(0, 1, c.B * c.NK, c.H, c.H, self.es_bf, c.H, p.view_bf("W_s"), c.H, C=self.ehat,
                  tag="routing_transform")
         self._call("indnet_routing_fwd", ptr(self.ehat), None, ptr(self.cvec), ptr(self.cvec_bf), c.B * c.N, c.K, c.H,
                    c.iters)
+
+    def _relation_bf16(self, train: bool):
+        c, p = self.cfg, self.p
         self._tc(0, 1, c.B * c.N, c.S * c.H, c.H, self.cvec_bf, c.H, p.view_bf("M"), c.S * c.H, Cb=self.Tp_bf,
                  tag="ntn_stage1")
         NS = c.N * c.S
@@ -437,8 +467,7 @@ class EpisodePipeline:
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
         self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
-                   c.B * c.n_q, c.N)
-        self._last_keep = keep
+                   ptr(self.running) if train else None, c.B * c.n_q, c.N)
 
     # ------------------------------------------------------------------ backward
     def _alloc_bwd(self):

@@ -43,7 +43,10 @@ class Base:
         self.out_size = kwds.get("out_size", 100)
         self.mode = kwds.get("mode", "fp32")
         self.seed = kwds.get("seed", 0)
+        # cuda_graph: run train() through EpisodeTrainer (device sampler in the loop, one CUDA graph per step,
+        # loss / accuracy read every 100 steps); implied when launched under torchrun with WORLD_SIZE > 1
         self.use_cuda_graph = kwds.get("cuda_graph", False)
+        self.scalar_log = kwds.get("scalar_log", None)       # JSONL file for the tf.summary scalars (base.py:110-113)
 
     # -------------------------------------------------------------------------------- build
     def build(self):
@@ -76,7 +79,7 @@ class Base:
         self.word_embedding = emb if emb is not None else self.store.view("word_embedding")
         self.pos1_embedding = self.store.view("pos1_embedding")
         self.pos2_embedding = self.store.view("pos2_embedding")
-        self._graph = None
+        self._trainer = None
 
     def feed(self, inputs, query_label, keep_prob=None):
         """The ``feed_dict`` of model/base.py:145-151."""
@@ -118,7 +121,8 @@ class Base:
     def run_step(self, inputs, query_label, train=True):
         """What one ``sess.run([loss, accuracy, optimize, ...])`` does (model/base.py:143-152)."""
         self.feed(inputs, query_label, self.keepProb if train else 1.0)
-        self.pipeline.cfg.keep_prob = float(self._keep)
+        if train:
+            self.pipeline.cfg.keep_prob = float(self._keep)     # eval runs forward(train=False): keep = 1 (base.py:199)
         self._train_mode = train
         self.forward()
         self.build_predict()
@@ -134,39 +138,89 @@ class Base:
         return loader.next_batch(c.B, c.N, c.K, c.Q)
 
     # -------------------------------------------------------------------------------- loops
+    def _log_scalars(self, step, loss, accuracy):
+        """The three tf.summary scalars of model/base.py:110-113 as one JSON line per logging point."""
+        if self.scalar_log:
+            import json
+            with open(self.scalar_log, "a") as f:
+                f.write(json.dumps({"step": int(step), "loss": float(loss), "accuracy": float(accuracy),
+                                    "learning_rate": float(self.learning_rate)}) + "\n")
+
+    def make_trainer(self, train_data_loader):
+        """EpisodeTrainer over this model's pipeline and the loader's device sampler; data parallel when the
+        process was launched with WORLD_SIZE > 1 (one process per GPU, torchrun)."""
+        from .. import dist as ddist
+        from ..trainer import EpisodeTrainer
+        rank, _local, world = ddist.init_from_env()
+        smp = train_data_loader._device()
+        smp.load_host_streams()
+        self.pipeline.cfg.keep_prob = float(self.keepProb)
+        if world > 1:                       # every rank starts from rank 0's weights
+            ddist.broadcast_(self.store.params)
+            self.store.refresh_bf16()
+        self._trainer = EpisodeTrainer(self.pipeline, smp, rank=rank, world=world, cuda_graph=True)
+        return self._trainer
+
     def train(self, dataloader, model_dir_path, model_name="inductionNetwork",
               train_iter=30000, val_iter=1000, val_step=2000, test_iter=3000):
         train_data_loader, val_data_loader = dataloader
         if not exists(model_dir_path):
             makedirs(model_dir_path)
         curr_iter, best_acc = 0, 0.0
-        print("training start ..")
+        from ..dist import env_world
+        rank, _, world = env_world()
+        fast = self.use_cuda_graph or world > 1
+        trainer = self.make_trainer(train_data_loader) if fast else None
+        say = print if rank == 0 else (lambda *a, **k: None)
+        say("training start ..")
         iter_loss, iter_right, iter_sample = 0.0, 0.0, 0.0
         for it in range(curr_iter, curr_iter + train_iter):
-            inputs, query_label = self._sample(train_data_loader)
-            curr_loss, curr_acc = self.run_step(inputs, query_label, train=True)
-            iter_loss += curr_loss
-            iter_right += curr_acc
-            iter_sample += 1
+            if fast:
+                # sampler + fwd + bwd + (all-reduce) + Adam as one graph replay; the running means of
+                # model/base.py:156-158 live on the device and are read only where the reference prints them
+                trainer.step()
+                if it % 100 == 0 or it % val_step == 0 or (it + 1) % val_step == 0:
+                    mean_loss, mean_acc, n = trainer.read_running(reset=(it % val_step == 0))
+                    self.loss, self.accuracy = trainer.read()
+                    self.learning_rate = float(self.store.hyper[1].item())
+                    self.global_step = int(self.store.global_step.item())
+                    iter_loss, iter_right, iter_sample = mean_loss * n, mean_acc * n, float(max(n, 1))
+            else:
+                inputs, query_label = self._sample(train_data_loader)
+                curr_loss, curr_acc = self.run_step(inputs, query_label, train=True)
+                iter_loss += curr_loss
+                iter_right += curr_acc
+                iter_sample += 1
             if it % 100 == 0:
-                print('[train] step:{0:4} | loss: {1:2.6f}, accuracy: {2:3.2f}%'.format(
+                say('[train] step:{0:4} | loss: {1:2.6f}, accuracy: {2:3.2f}%'.format(
                     it + 1, iter_loss / iter_sample, 100 * iter_right / iter_sample) + '\r')
+                if rank == 0:
+                    self._log_scalars(it + 1, iter_loss / iter_sample, iter_right / iter_sample)
             if it % val_step == 0:
                 iter_loss, iter_right, iter_sample = 0.0, 0.0, 0.0
             if (it + 1) % val_step == 0:
-                print("evaluate start ..")
+                say("evaluate start ..")
+                if fast:
+                    trainer.suspend()      # host streams back where the reference's loop would have them
                 acc_val = self.eval(val_data_loader, None, val_iter)
                 if acc_val > best_acc:
-                    print("Best checkpoint.[EVAL] accuracy :{}".format(acc_val))
+                    say("Best checkpoint.[EVAL] accuracy :{}".format(acc_val))
                     ckpt_dir = join(model_dir_path, "checkpoint")
                     if not exists(ckpt_dir):
                         makedirs(ckpt_dir)
-                    self.save(join(ckpt_dir, "%s-%d.npz" % (model_name, self.global_step)))
+                    if rank == 0:
+                        self.global_step = int(self.store.global_step.item())
+                        self.save(join(ckpt_dir, "%s-%d.npz" % (model_name, self.global_step)))
                     best_acc = acc_val
-        print("\n####################\n")
-        print("Finish training :" + model_name)
+        if fast:
+            trainer.suspend()
+        say("\n####################\n")
+        say("Finish training :" + model_name)
         test_acc = self.eval(val_data_loader, None, test_iter)
-        print("Test accuracy: {}".format(test_acc))
+        say("Test accuracy: {}".format(test_acc))
+        if fast:
+            trainer.close()
+            self._trainer = None
         return test_acc
 
     def eval(self, val_data_loader, sess, val_iter):
@@ -178,10 +232,15 @@ class Base:
             _, curr_acc_val = self.run_step(inputs_val, query_label_val, train=False)
             iter_right_val += curr_acc_val
             iter_sample_val += 1
-            if it_val % 100 == 0:
+            if it_val % 100 == 0 and self._quiet_rank() == 0:
                 print('[EVAL] step: {0:4} | accuracy: {1:3.2f}%'.format(
                     it_val + 1, 100 * iter_right_val / iter_sample_val) + '\r')
         return iter_right_val / iter_sample_val
+
+    @staticmethod
+    def _quiet_rank():
+        from ..dist import env_world
+        return env_world()[0]
 
     # -------------------------------------------------------------------------------- checkpoint
     def save(self, path):

@@ -93,16 +93,19 @@ class DeviceEpisodeSampler:
         LIB.call("indnet_sample_walk", current_stream(), ptr(self.py_state), ptr(self.np_state), ptr(self.scopes),
                  self.R, B, N, K, Q, self.n_max, ptr(bufs["scratch"]), ptr(self.status))
 
-    def enqueue_gather(self, B, N, K, Q, out=None):
-        """Second half: picks -> row ids, labels and the gathered [B, n_s, L] tables."""
+    def enqueue_gather(self, B, N, K, Q, out=None, b0=0, nb=None):
+        """Second half: picks -> row ids, labels and the gathered [nb, n_s, L] tables of episodes
+        [b0, b0 + nb) of the walked batch (default: all B).  Data-parallel ranks walk the same global batch
+        and gather only their own episodes, so episode b is the same whatever the world size."""
         bufs = self.buffers(B, N, K, Q)
         o = dict(bufs)
         if out is not None:
             o.update(out)
-        LIB.call("indnet_sample_gather", current_stream(), ptr(self.scopes), ptr(self.tables["word"]),
+        nb = B if nb is None else nb
+        LIB.call("indnet_sample_gather_range", current_stream(), ptr(self.scopes), ptr(self.tables["word"]),
                  ptr(self.tables["pos1"]), ptr(self.tables["pos2"]), ptr(self.tables["mask"]), self.L, B, N, K, Q,
-                 self.n_max, ptr(bufs["scratch"]), ptr(o["rows"]), ptr(o["label"]), ptr(o["word"]), ptr(o["pos1"]),
-                 ptr(o["pos2"]), ptr(o["mask"]))
+                 self.n_max, ptr(bufs["scratch"]), b0, nb, ptr(o["rows"]), ptr(o["label"]), ptr(o["word"]),
+                 ptr(o["pos1"]), ptr(o["pos2"]), ptr(o["mask"]))
         return o
 
     def check(self):
@@ -114,11 +117,21 @@ class DeviceEpisodeSampler:
             raise IndnetError("device sampler: a relation has more instances than n_max=%d" % self.n_max)
         if s == 3:
             raise IndnetError("device sampler: the batch consumed more NumPy draws than the pre-generated stream "
-                              "budget (expected draws + 3 % + 8192); the streams were not advanced consistently")
+                              "budget (expected draws + 3 % + 8192); both streams are unchanged - sample() retries "
+                              "in smaller batches, an asynchronous caller must re-issue the step")
         if s != 0:
             raise IndnetError("device sampler failed with status %d" % s)
 
     def sample(self, B, N, K, Q):
+        """Synchronous sampling.  A batch that outruns the pre-generated stream budget (status 3; the call
+        then leaves both streams untouched) is redone as two half batches - consecutive draws from the same
+        streams, i.e. the same episodes - each with the full fixed slack of its own."""
         o = self.enqueue(B, N, K, Q)
+        if int(self.status[0].item()) == 3 and B > 1:
+            self.status.zero_()
+            h = B // 2
+            first = {k: v.clone() for k, v in self.sample(h, N, K, Q).items() if k != "scratch"}
+            second = self.sample(B - h, N, K, Q)
+            return {k: torch.cat([first[k], second[k]], dim=0) for k in first}
         self.check()
         return o

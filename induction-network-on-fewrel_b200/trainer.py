@@ -1,0 +1,247 @@
+"""EpisodeTrainer: the train step the reference runs as ``next_one_tf`` + ``sess.run([loss, accuracy,
+optimize, ...])`` (model/base.py:136-152), as ONE replayable CUDA graph per step.
+
+  gather(step t picks) -> [fork: stream walk for step t+1 on a low-priority side stream] -> forward ->
+  loss -> backward -> gradient all-reduce (world > 1) -> TF Adam -> [join]
+
+* The device sampler (csrc/sampler.cu) draws the same episodes the reference would for the same seeds; the
+  serial walk of the NEXT step's draws hides under this step's kernels.
+* Data parallel, one process per GPU: every rank walks the SAME two streams for the global batch
+  of ``world * B`` episodes and gathers only its own episodes ``[rank*B, (rank+1)*B)``, so the global batch is
+  bit-identical for any world size.  Gradients: the slot of ``M`` (95 % of the bytes, final right after the
+  relation-module backward) is all-reduced on a communication stream under the encoder backward; the other
+  slots go in one trailing all-reduce; Adam applies the sum scaled by 1/world (loss = mean over the global
+  batch).  No other collective exists on this path.
+* Loss / accuracy stay on the device (``pipe.out2``; running sums in ``pipe.running``): a loop reads them
+  every n steps instead of synchronising each step.
+
+Used by ``Base.train`` (the product loop), ``train.py`` and ``bench.py`` - the timed code is the code users call.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from .engine import EpisodePipeline
+
+
+class EpisodeTrainer:
+    def __init__(self, pipe: EpisodePipeline, sampler=None, rank: int = 0, world: int = 1, process_group=None,
+                 cuda_graph: bool = True, overlap_allreduce: bool = True):
+        self.pipe, self.store, self.cfg = pipe, pipe.p, pipe.cfg
+        self.smp = sampler
+        self.rank, self.world = int(rank), int(world)
+        self.group = process_group
+        self.use_graph = bool(cuda_graph)
+        self.overlap = bool(overlap_allreduce) and self.world > 1
+        self.global_B = self.cfg.B * self.world
+        dev = pipe.dev
+        # the step's own stream (high priority), the sampler's side stream (low: its table kernel fills the
+        # GPU and would otherwise take SMs from the training kernels) and the communication stream
+        self.stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.side = torch.cuda.Stream(device=dev, priority=0)
+        self.comm = torch.cuda.Stream(device=dev, priority=-1)
+        self.m_end = self.store.offsets["w"]        # slots are laid out M, w, b, ... (engine.ParamStore)
+        self.inputs = dict(word=pipe.word, pos1=pipe.pos1, pos2=pipe.pos2, mask=pipe.mask, label=pipe.label)
+        self.graph_step: Optional[torch.cuda.CUDAGraph] = None     # sampler in the loop
+        self.graph_train: Optional[torch.cuda.CUDAGraph] = None    # host-fed / resident inputs
+        self._primed = False
+        self._need_walk = False
+        self.steps_done = 0
+        if sampler is not None:      # stream states as they were BEFORE the look-ahead walk (see suspend())
+            self._py_prev = torch.zeros_like(sampler.py_state)
+            self._np_prev = torch.zeros_like(sampler.np_state)
+        if self.world > 1:
+            pipe.grad_ready_hook = self._on_grad_ready
+
+    # ------------------------------------------------------------------ collectives
+    def _dist(self):
+        import torch.distributed as dist
+        return dist
+
+    def _on_grad_ready(self, name):
+        if self.overlap and name == "M":
+            self.comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm):
+                self._dist().all_reduce(self.store.grads[: self.m_end], group=self.group)
+
+    def _grad_sync(self):
+        if self.world <= 1:
+            return
+        if self.overlap:
+            self._dist().all_reduce(self.store.grads[self.m_end:], group=self.group)
+            torch.cuda.current_stream().wait_stream(self.comm)
+        else:
+            self._dist().all_reduce(self.store.grads, group=self.group)
+
+    # ------------------------------------------------------------------ step bodies (enqueue only, no host sync)
+    def train_body(self):
+        """fwd + bwd + all-reduce + Adam on the episodes in the pipeline's input buffers."""
+        self.pipe.forward(train=True)
+        self.pipe.backward()
+        self._grad_sync()
+        self.pipe.adam(grad_scale=1.0 / self.world)
+
+    def _walk(self):
+        c = self.cfg
+        self._py_prev.copy_(self.smp.py_state, non_blocking=True)
+        self._np_prev.copy_(self.smp.np_state, non_blocking=True)
+        self.smp.enqueue_walk(self.global_B, c.N, c.K, c.Q)
+
+    def _gather(self):
+        c = self.cfg
+        self.smp.enqueue_gather(self.global_B, c.N, c.K, c.Q, out=self.inputs, b0=self.rank * c.B, nb=c.B)
+
+    def step_body(self):
+        """This step's episodes = the picks drawn during the previous step; the walk for the NEXT step runs
+        on the side stream underneath this step's forward / backward / update."""
+        self._gather()
+        cur = torch.cuda.current_stream()
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            self._walk()
+        self.train_body()
+        cur.wait_stream(self.side)
+
+    # ------------------------------------------------------------------ set-up
+    def prime(self, warm: int = 2):
+        """Runs ``warm`` eager steps on the trainer's stream (allocates the backward buffers, creates the
+        sampler's internal stream, warms NCCL - all of which must happen outside stream capture), then
+        captures the CUDA graphs.  With a sampler the first walk happens here, so step 1 trains on the first
+        episodes the seeded streams produce."""
+        if self._primed:
+            return
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            # warm-up steps must not move the weights or the streams' episode sequence out from under the
+            # caller: they run on throw-away state that is restored afterwards
+            snap = self._snapshot()
+            if self.smp is not None:
+                self._walk()
+            for _ in range(max(1, warm)):
+                if self.smp is not None:
+                    self.step_body()
+                else:
+                    self.train_body()
+            self.stream.synchronize()
+            self._restore(snap)
+            if self.smp is not None:
+                self._walk()
+            self.stream.synchronize()
+            if self.use_graph:
+                self._capture()
+        self._primed = True
+
+    def _snapshot(self):
+        s = self.store
+        snap = dict(params=s.params.clone(), m=s.m.clone(), v=s.v.clone(), step=s.global_step.clone(),
+                    running=self.pipe.running.clone())
+        if self.smp is not None:
+            snap.update(py=self.smp.py_state.clone(), np=self.smp.np_state.clone())
+        return snap
+
+    def _restore(self, snap):
+        s = self.store
+        s.params.copy_(snap["params"]); s.m.copy_(snap["m"]); s.v.copy_(snap["v"])
+        s.global_step.copy_(snap["step"])
+        self.pipe.running.copy_(snap["running"])
+        s.refresh_bf16()
+        if self.smp is not None:
+            self.smp.py_state.copy_(snap["py"]); self.smp.np_state.copy_(snap["np"])
+
+    def _capture(self):
+        try:
+            if self.smp is not None:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.stream):
+                    self.step_body()
+                self.graph_step = g
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=self.stream):
+                self.train_body()
+            self.graph_train = g
+        except Exception as e:      # e.g. a collective that refuses capture: eager launches still work
+            import sys
+            print("EpisodeTrainer: CUDA graph capture failed, using eager launches: %r" % (e,), file=sys.stderr)
+            self.graph_step = self.graph_train = None
+            torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ stepping
+    def step(self):
+        """One train step on freshly sampled episodes (device sampler in the loop).  Asynchronous."""
+        if not self._primed:
+            self.prime()
+        if self.smp is None:
+            raise RuntimeError("EpisodeTrainer.step() needs a device sampler; use step_on(inputs, label)")
+        if self._need_walk:
+            self.resume()
+        with torch.cuda.stream(self.stream):
+            if self.graph_step is not None:
+                self.graph_step.replay()
+            else:
+                self.step_body()
+        self.steps_done += 1
+
+    def step_on(self, inputs=None, query_label=None):
+        """One train step on caller-supplied episodes (host or device tensors / arrays, [B, n_s, L]); with no
+        arguments, on whatever is in the pipeline's input buffers.  Asynchronous."""
+        if not self._primed:
+            self.prime()
+        with torch.cuda.stream(self.stream):
+            if inputs is not None:
+                self.pipe.set_inputs(inputs, query_label)
+            if self.graph_train is not None:
+                self.graph_train.replay()
+            else:
+                self.train_body()
+        self.steps_done += 1
+
+    def read(self):
+        """(loss, accuracy) of the last step - synchronises the trainer's stream (an 8-byte D2H copy)."""
+        with torch.cuda.stream(self.stream):
+            v = self.pipe.out2.cpu()
+        return float(v[0]), float(v[1])
+
+    def read_running(self, reset: bool = False):
+        """(mean loss, mean accuracy, steps) since the last reset - model/base.py:156-163's running means,
+        kept on the device.  Synchronises."""
+        with torch.cuda.stream(self.stream):
+            v = self.pipe.running.cpu()
+            if reset:
+                self.pipe.running.zero_()
+        n = max(float(v[2]), 1.0)
+        return float(v[0]) / n, float(v[1]) / n, int(v[2])
+
+    def suspend(self):
+        """Hands the two host streams back exactly where the reference's loop would have them after the steps
+        run so far: the look-ahead walk (the picks of the step that has not run yet) is discarded and the
+        streams rewound to just before it.  Call before anything else draws from ``random`` / ``numpy.random``
+        (the evaluation loop, model/base.py:168-170); ``step`` re-walks on its own afterwards."""
+        if self.smp is None or self._need_walk or not self._primed:
+            return
+        self.stream.synchronize()
+        self.smp.check()
+        self.smp.py_state.copy_(self._py_prev)
+        self.smp.np_state.copy_(self._np_prev)
+        self.smp.store_host_streams()
+        self._need_walk = True
+
+    def resume(self):
+        self.smp.load_host_streams()
+        with torch.cuda.stream(self.stream):
+            self._walk()
+        self._need_walk = False
+
+    def check_sampler(self):
+        if self.smp is not None:
+            self.stream.synchronize()
+            self.smp.check()
+
+    def close(self):
+        """Ordered teardown: drain, drop the graphs (they hold references to the NCCL communicator's work),
+        drain again.  The caller destroys the process group afterwards."""
+        torch.cuda.synchronize()
+        self.graph_step = self.graph_train = None
+        self.pipe.grad_ready_hook = None
+        torch.cuda.synchronize()

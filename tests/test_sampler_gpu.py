@@ -144,3 +144,36 @@ def test_stream_rings_survive_many_batches_shape_switches_and_reseeds():
     check(5)
     check(5)        # same seed again: the scratch holds a later part of this very stream
     check(77)
+
+
+def test_stream_budget_overrun_leaves_streams_unchanged_and_retries():
+    """Status 3 (the batch needs more NumPy draws than were pre-generated): the failing call must not consume
+    anything, and ``sample`` redoes the batch in halves - same episodes as one uninterrupted run."""
+    from induction_b200._lib import LIB
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    from induction_b200.util.synthetic import make_tables
+    tables = make_tables(24, 300, 16, 2000, 8, seed=3)
+    B, N, K, Q = 32, 5, 2, 3
+    random.seed(9); np.random.seed(9)
+    ld0 = JSONFileDataLoader.from_tables(tables)
+    want = [so.next_one_tf_stdlib(tables, ld0.scopes(), N, K, Q) for _ in range(B)]
+    tail = (random.random(), float(np.random.rand()))
+    LIB.call("indnet_sampler_set_budget", -0.5, 4096)        # half the expected draws + a little: B = 32 cannot fit
+    try:
+        ld = JSONFileDataLoader.from_tables(tables)
+        dev = ld._device()
+        random.seed(9); np.random.seed(9)
+        dev.load_host_streams()
+        py0, np0 = dev.py_state.clone(), dev.np_state.clone()
+        dev.enqueue(B, N, K, Q)
+        assert int(dev.status[0].item()) == 3
+        assert torch.equal(dev.py_state, py0) and torch.equal(dev.np_state, np0)     # nothing consumed
+        dev.status.zero_()
+        inputs, label = ld.next_batch(B, N, K, Q)            # retries in halves until every piece fits
+        for b in range(B):
+            for k in KEYS:
+                assert np.array_equal(inputs[k][b].cpu().numpy(), want[b][0][k]), (b, k)
+            assert np.array_equal(label[b].cpu().numpy(), want[b][1])
+        assert (random.random(), float(np.random.rand())) == tail
+    finally:
+        LIB.call("indnet_sampler_set_budget", 0.03, 8192)

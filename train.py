@@ -34,11 +34,29 @@ def main(argv=None):
     ap.add_argument("--val-step", type=int, default=2000)
     ap.add_argument("--test-iter", type=int, default=3000)
     ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--keep-prob", type=float, default=0.9)
+    ap.add_argument("--seed", type=int, default=None, help="random.seed / np.random.seed before training (the reference "
+                    "never seeds); REQUIRED to be the same on every rank under torchrun")
+    ap.add_argument("--cuda-graph", action="store_true", help="device sampler + whole step as one CUDA graph "
+                    "(EpisodeTrainer); implied under torchrun with WORLD_SIZE > 1, where --batch-size is per GPU")
+    ap.add_argument("--scalar-log", default=None, help="JSONL file for the loss / accuracy / learning_rate scalars")
     ap.add_argument("--model-dir", default="checkpoints/inductionNetwork_test")
     a = ap.parse_args(argv)
 
-    print("{}-way-{}-shot Few-Shot Relation Classification".format(a.N, a.K))
-    print("Model: {}".format(a.model_name))
+    import os
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    if world > 1:
+        import torch
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        if a.seed is None:
+            a.seed = 0          # one global episode stream: every rank must walk the same draws
+    if a.seed is not None:
+        import random
+        import numpy as np
+        random.seed(a.seed); np.random.seed(a.seed)
+    if rank == 0:
+        print("{}-way-{}-shot Few-Shot Relation Classification".format(a.N, a.K))
+        print("Model: {}".format(a.model_name))
 
     if a.synthetic:
         train_data_loader = JSONFileDataLoader.from_tables(make_tables(64, 700, a.max_length, 4000, 5, seed=0))
@@ -51,12 +69,18 @@ def main(argv=None):
     if a.model_name == "induction":
         model = InductionGraph(N=a.N, K=a.K, Q=a.Q, pred_embed=train_data_loader.word_vec_mat,
                                sequence_length=a.max_length, hidden_size=a.hidden_size,
-                               batch_size=a.batch_size, mode=a.mode)
+                               batch_size=a.batch_size, mode=a.mode, keep_prob=a.keep_prob, cuda_graph=a.cuda_graph,
+                               scalar_log=a.scalar_log)
         model.train(dataloader=(train_data_loader, val_data_loader), model_dir_path=a.model_dir,
                     train_iter=a.train_iter, val_iter=a.val_iter, val_step=a.val_step, test_iter=a.test_iter)
     else:
         print("unknown model: {}".format(a.model_name))
         return 1
+    if world > 1:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
     return 0
 
 
