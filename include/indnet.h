@@ -70,10 +70,12 @@ int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int
                          const void* B, long long ldb, float* C, void* Cb, int ldc, const float* rs,
                          const float* rv_a, const float* rv_b, int rv_rows, int group, int split);
 /* Both weight gradients of one LSTM direction in one pass over dz (bf16 mode, hidden_size 128, D <= 64):
- *   dkernel[D+u][4u] = [x | h_prev]^T * dz,  x_bf [T][64] (columns >= D zero), hprev_bf [T][u], dz_bf [T][4u]
- * (autodiff of the LSTM kernel matmul, model/graph.py:44).  Overwrites dkernel (fp32, split-K reductions). */
+ *   dkernel[D+u][4u] = [x | h_prev]^T * dz,  x_bf [T][64], hprev_bf [T][u], dz_bf [T][4u]
+ * (autodiff of the LSTM kernel matmul, model/graph.py:44).  Overwrites dkernel (fp32, split-K reductions).
+ * dbias (optional, [4u], overwritten): row D of the stacked product, i.e. the bias gradient sum_t dz[t] when
+ * x carries 1.0 in column D (indnet_embed_fwd_bf16 writes it when D <= 62). */
 int indnet_tc_gemm_lstm_dw(indnet_stream st, const void* x_bf, const void* hprev_bf, const void* dz_bf,
-                           float* dkernel, long long T, int D, int u, int splitk);
+                           float* dkernel, float* dbias, long long T, int D, int u, int splitk);
 /* out (bf16) = in (fp32), n elements. */
 int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
 /* Row-wise cast with a padded output row stride: out[r][0..ldo) = in[r][0..cols), zeros beyond cols
@@ -129,8 +131,10 @@ int indnet_sample_gather_range(indnet_stream st, const int* scopes, const int* t
 /* ---- a2: Base.get_embedding, model/base.py:76-86 --------------------------------------------- */
 int indnet_embed_fwd(indnet_stream st, const int* word, const int* pos1, const int* pos2, const float* word_table,
                      const float* pos1_table, const float* pos2_table, float* x /*[T][D]*/, long long T, int E, int P);
-/* bf16 tensor-core mode: same lookup written as bf16 rows padded with zeros to 64 columns (xb [T][64]),
- * the K-major operand of the input-projection MMAs.  Requires E + 2P <= 64. */
+/* bf16 tensor-core mode: same lookup written as bf16 rows of 64 columns (xb [T][64]), the K-major operand
+ * of the input-projection MMAs: columns [0, D) the embedding, columns D and D+1 = 1.0 when D <= 62 (they
+ * multiply the bias rows of the packed LSTM weights and make row D of the weight-gradient GEMM the bias
+ * gradient), zeros after.  Requires E + 2P <= 64. */
 int indnet_embed_fwd_bf16(indnet_stream st, const int* word, const int* pos1, const int* pos2,
                           const float* word_table, const float* pos1_table, const float* pos2_table, void* xb,
                           long long T, int E, int P);
@@ -158,12 +162,14 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
                     const float* Wh_bw, float* whT_scratch, float* dz, int X, int L, int u, float keep_prob,
                     unsigned long long seed, const long long* seed_step);
 
-/* bf16 tensor-core mode of indnet_lstm_fwd with the input projection fused in (hidden_size 128,
- * E+10 <= 64): x_bf [X][L][64] bf16 zero-padded embeddings (indnet_embed_fwd_bf16), kernel_* the TF
- * LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch: caller-provided bf16 [2][4u][192] (packed
- * transposed weights, rebuilt every call).  Writes hout_bf [X][L][2u] bf16 (and hout fp32 when not
- * NULL), and for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate_bf
- * [2][X][L][u] bf16 (the recurrence itself carries c in fp32 registers), hprev_bf [2][X][L][u] bf16. */
+/* bf16 tensor-core mode of indnet_lstm_fwd with the input projection AND the bias fused into the MMAs
+ * (hidden_size 128, E+10 <= 62): x_bf [X][L][64] bf16 embeddings with 1.0 in columns D and D+1
+ * (indnet_embed_fwd_bf16), kernel_* the TF LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch:
+ * caller-provided bf16 [2][4u][192] (packed transposed weights incl. the bias rows, rebuilt every call).
+ * hout (fp32 copy) must be NULL.  Writes hout_bf [X][L][2u] bf16 and, when given (training; pass all three
+ * or none), for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate_bf [2][X][L][u]
+ * bf16 (the recurrence itself carries c in fp32 registers), hprev_bf [2][X][L][u] bf16.  All buffers
+ * 16-byte aligned (they are moved as TMA tiles). */
 int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                        const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout, void* hout_bf,
                        void* gates_bf, void* cstate_bf, void* hprev_bf, int X, int L, int D, int u, float keep_prob,
@@ -172,16 +178,15 @@ int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_f
 /* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] and cstate_bf as
  * saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h = rows
  * D.., staged into tensor memory, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).
- * Writes dz_bf [2][X][L][4u] bf16 and, when dbias_fw / dbias_bw [4u] are given, the two LSTM bias
- * gradients (fp32 column sums of dz, formed in registers before the bf16 rounding).  When dx2 is given
+ * Writes dz_bf [2][X][L][4u] bf16 (the bias gradients are row D of indnet_tc_gemm_lstm_dw's product: x
+ * carries 1.0 in column D).  When dx2 is given
  * (fp32 [2][X][L][16]) the kernel also forms the input gradient of features dx_first..D-1 (at most 16:
  * the 2 x 5 position-embedding columns when the word table is frozen) per direction,
  * dx2[dir][tok][f - dx_first] = sum_k dz[dir][tok][k] * kernel[f][k]; the caller adds the two directions
  * (indnet_embed_pos_bwd2). */
 int indnet_lstm_bwd_tc(indnet_stream st, const void* dhout_bf, const void* gates_bf, const void* cstate_bf,
-                       const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dbias_fw,
-                       float* dbias_bw, float* dx2, int dx_first, int X, int L, int D, int u, float keep_prob,
-                       unsigned long long seed, const long long* seed_step);
+                       const void* kernel_fw_bf, const void* kernel_bw_bf, void* dz_bf, float* dx2, int dx_first, int X,
+                       int L, int D, int u, float keep_prob, unsigned long long seed, const long long* seed_step);
 /* out[c] = sum_r A[r][c] for a dense bf16 matrix [rows][cols] (bias gradients from the bf16 dz stream). */
 int indnet_colsum_bf16(indnet_stream st, const void* A, long long rows, int cols, float* out);
 

@@ -49,18 +49,28 @@ __device__ __forceinline__ float warp_max(float v) {
 
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
-// Counter-based uniform in [0,1) used for LSTM output dropout; the same integer mix is restated in
-// Python (induction_b200.engine.dropout_keep_mask) so a device mask can be replayed in the oracle.
-__host__ __device__ __forceinline__ uint32_t mix32(uint64_t seed, uint64_t idx) {
-  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1);
+// Counter-based Bernoulli stream for the LSTM output dropout (model/graph.py:36-38); the same integer mix is
+// restated in Python (induction_b200.engine.dropout_keep_mask) so a device mask can be replayed in the oracle.
+// key = one 64-bit mix of (seed + step * 1000003) per thread; per element a 32-bit murmur-style finaliser
+// (two multiplies) - the per-element cost matters inside the persistent recurrence kernels.
+__host__ __device__ __forceinline__ uint32_t dropout_key(uint64_t seed) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   z = z ^ (z >> 31);
   return (uint32_t)(z >> 32);
 }
+__host__ __device__ __forceinline__ uint32_t dropout_hash(uint32_t key, uint64_t idx) {
+  uint32_t h = (uint32_t)idx * 0x9E3779B1u + key + (uint32_t)(idx >> 32) * 0x7FEB352Du;
+  h ^= h >> 16; h *= 0x85EBCA6Bu;
+  h ^= h >> 13; h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return h;
+}
+// keep iff the top 24 bits, as an integer, are below keep_prob * 2^24
+__host__ __device__ __forceinline__ uint32_t dropout_threshold(float keep_prob) { return (uint32_t)(keep_prob * 16777216.0f); }
 __host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, float keep_prob) {
-  // keep iff u < keep_prob with u = top 24 bits / 2^24
-  return (float)(mix32(seed, idx) >> 8) * (1.0f / 16777216.0f) < keep_prob;
+  return (dropout_hash(dropout_key(seed), idx) >> 8) < dropout_threshold(keep_prob);
 }
 
 }  // namespace indnet

@@ -42,6 +42,7 @@ __global__ void embed_fwd_bf16_kernel(const int* __restrict__ word, const int* _
     if (d < E) x = wt[w * E + d];
     else if (d < E + P) x = p1t[q1 * P + (d - E)];
     else if (d < E + 2 * P) x = p2t[q2 * P + (d - E - P)];
+    else if (E + 2 * P + 2 <= 64 && d < E + 2 * P + 2) x = 1.0f;      // the two bias columns (see indnet.h)
     v[j] = x;
   }
   reinterpret_cast<__nv_bfloat162*>(xb)[i] = __floats2bfloat162_rn(v[0], v[1]);

@@ -268,7 +268,7 @@ constexpr int D_STAGES = 4;
 constexpr int D_A_BYTES = 4 * 64 * G_BK * 2;      // four 64-wide M atoms of 8 KB: x, h[0:64], h[64:128], zeros
 constexpr int D_SMEM = D_STAGES * (D_A_BYTES + G_B_BYTES) + 256 + 1024;
 
-struct TcDualP { float* C; int D, N, K, ldc, kb_per_split; };
+struct TcDualP { float* C; float* dbias; int D, N, K, ldc, kb_per_split; };
 
 __global__ void __launch_bounds__(G_THREADS, 1)
 tc_gemm_dual_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmH,
@@ -355,14 +355,16 @@ tc_gemm_dual_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     for (int tile = 0; tile < 2; ++tile) {
       const int sr = tile * G_BM + r;                                      // stacked row
       const int dest = sr < 64 ? (sr < p.D ? sr : -1) : (sr < 64 + 128 ? p.D + sr - 64 : -1);
+      // x's column D is 1.0: stacked row D is the column sum of dz = the LSTM bias gradient
+      float* bias_row = (p.dbias && sr == p.D && p.D < 64) ? p.dbias : nullptr;
 #pragma unroll 1
       for (int c = 0; c < G_BN / 32; ++c) {
         float v[32];
         tmem_ld32(taddr + tile * G_BN + ((uint32_t)(q * 32) << 16) + c * 32, v);
         tmem_ld_wait();
-        if (dest >= 0) {
+        if (dest >= 0 || bias_row) {
           // N is a multiple of the tile width here, rows are 16-byte aligned: 16-byte vector reductions
-          float4* out = reinterpret_cast<float4*>(p.C + (long long)dest * p.ldc + n0 + c * 32);
+          float4* out = reinterpret_cast<float4*>((bias_row ? bias_row : p.C + (long long)dest * p.ldc) + n0 + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; ++j) atomicAdd(out + j, make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
         }
@@ -409,6 +411,29 @@ int make_tmap_bf16(CUtensorMap* tm, const void* base, long long inner, long long
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(INDNET_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
+  return INDNET_OK;
+}
+
+// General tiled map: rank 3 or 4, element type bf16 (elem_bytes 2) or uint32 (4), innermost dimension contiguous;
+// strides_bytes[i] = byte stride of dimension i + 1; 128-byte swizzle or none; out-of-range reads give zeros.
+int make_tmap_nd(CUtensorMap* tm, const void* base, int elem_bytes, int rank, const unsigned long long* dims,
+                 const unsigned long long* strides_bytes, const unsigned* box, bool swizzle128) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return set_error(INDNET_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  IN_REQUIRE(rank >= 1 && rank <= 5 && (elem_bytes == 2 || elem_bytes == 4), "tensor map: bad rank / element size");
+  IN_REQUIRE(((uintptr_t)base & 15) == 0, "tensor map: base pointer not 16-byte aligned");
+  cuuint64_t d[5], sb[4];
+  cuuint32_t b[5], es[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) {
+    IN_REQUIRE(strides_bytes[i] % 16 == 0, "tensor map: stride %d is not a multiple of 16 bytes", i);
+    sb[i] = strides_bytes[i];
+  }
+  CUresult r = fn(tm, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32, (cuuint32_t)rank,
+                  const_cast<void*>(base), d, sb, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(INDNET_ERR_CUDA, "cuTensorMapEncodeTiled (rank %d) failed with %d", rank, (int)r);
   return INDNET_OK;
 }
 
@@ -545,7 +570,7 @@ extern "C" int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M,
 }
 
 extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const void* hprev_bf, const void* dz_bf,
-                                      float* dkernel, long long T, int D, int u, int splitk) {
+                                      float* dkernel, float* dbias, long long T, int D, int u, int splitk) {
   cudaStream_t st = (cudaStream_t)st_;
   const int N = 4 * u;
   IN_REQUIRE(T > 0 && D > 0 && D <= 64 && u == 128, "tc_gemm_lstm_dw: needs E + 10 <= 64 and hidden_size 128 (D=%d u=%d)", D, u);
@@ -558,7 +583,9 @@ extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const
   if (splitk > total_kb) splitk = total_kb;
   if (splitk < 1) splitk = 1;
   TcDualP p;
-  p.C = dkernel; p.D = D; p.N = N; p.K = (int)T; p.ldc = N;
+  IN_REQUIRE(!dbias || (((uintptr_t)dbias & 15) == 0 && D < 64), "tc_gemm_lstm_dw: dbias needs 16-byte alignment and D < 64");
+  p.C = dkernel; p.dbias = dbias; p.D = D; p.N = N; p.K = (int)T; p.ldc = N;
+  if (dbias) IN_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * N, st));
   p.kb_per_split = ceil_div(total_kb, splitk);
   splitk = ceil_div(total_kb, p.kb_per_split);
   IN_CUDA(cudaMemsetAsync(dkernel, 0, sizeof(float) * (size_t)(D + u) * N, st));

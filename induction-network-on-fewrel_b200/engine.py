@@ -198,20 +198,24 @@ class ParamStore:
 
 def dropout_keep_mask(seed: int, shape, keep_prob: float, step: int = 0) -> np.ndarray:
     """Host restatement of the device dropout stream (csrc/common.cuh ``dropout_keep``) so a mask the
-    LSTM kernel drew can be replayed through the oracle.  Element i of the flattened [X, L, 2u] output
-    is kept iff (mix32(seed + step*1000003, i) >> 8) / 2^24 < keep_prob."""
+    LSTM kernels drew can be replayed through the oracle.  Element i of the flattened [X, L, 2u] output is
+    kept iff (dropout_hash(dropout_key(seed + step*1000003), i) >> 8) < uint32(keep_prob * 2^24)."""
     n = int(np.prod(shape))
     M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
     with np.errstate(over="ignore"):
-        s = np.uint64((seed + step * 1000003) & 0xFFFFFFFFFFFFFFFF)
-        idx = np.arange(n, dtype=np.uint64)
-        z = (s + np.uint64(0x9E3779B97F4A7C15) * (idx + np.uint64(1))) & M64
+        z = (np.uint64((seed + step * 1000003) & 0xFFFFFFFFFFFFFFFF) + np.uint64(0x9E3779B97F4A7C15)) & M64
         z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & M64
         z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & M64
         z = z ^ (z >> np.uint64(31))
-    r = (z >> np.uint64(32)).astype(np.uint32) >> np.uint32(8)
-    u = r.astype(np.float32) * np.float32(1.0 / 16777216.0)
-    return (u < np.float32(keep_prob)).reshape(shape)
+        key = np.uint32(int(z) >> 32)
+        idx = np.arange(n, dtype=np.uint64)
+        h = ((idx & np.uint64(0xFFFFFFFF)).astype(np.uint32) * np.uint32(0x9E3779B1) + key
+             + (idx >> np.uint64(32)).astype(np.uint32) * np.uint32(0x7FEB352D))
+        h ^= h >> np.uint32(16); h *= np.uint32(0x85EBCA6B)
+        h ^= h >> np.uint32(13); h *= np.uint32(0xC2B2AE35)
+        h ^= h >> np.uint32(16)
+    thr = np.uint32(int(np.float32(keep_prob) * np.float32(16777216.0)))
+    return ((h >> np.uint32(8)) < thr).reshape(shape)
 
 
 class EpisodePipeline:
@@ -285,7 +289,8 @@ class EpisodePipeline:
             self.eq_bf = h(c.B * c.n_q, c.H)
             self.Tp_bf = h(c.B * c.N, c.S * c.H)
             self.NSp = (c.N * c.S + 7) // 8 * 8          # dV rows padded to 16 bytes for TMA
-            self.tc_lstm = (c.u == 128)        # persistent tcgen05 recurrence is specialised for u = 128
+            # the persistent tcgen05 recurrence is specialised for u = 128; its bias rides in two spare x columns
+            self.tc_lstm = (c.u == 128 and c.D <= 62)
             if self.tc_lstm:
                 self.wt_bf = h(2, 4 * c.u, 64 + c.u)
                 self.gates_bf = h(2, c.T, 4 * c.u)
@@ -616,8 +621,8 @@ class EpisodePipeline:
         fused_dx = self.tc_lstm and not self.trainable_words and c.D - c.E <= 16
         if self.tc_lstm:
             self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate_bf),
-                       ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf), ptr(p.grad(FW_B)),
-                       ptr(p.grad(BW_B)), ptr(self.dx2) if fused_dx else None, c.E if fused_dx else 0,
+                       ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf),
+                       ptr(self.dx2) if fused_dx else None, c.E if fused_dx else 0,
                        c.X, c.L, c.D, c.u, self._last_keep, self.seed, ptr(p.global_step))
         else:
             wh_fw = p.view(FW_K)[c.D:]
@@ -634,7 +639,7 @@ class EpisodePipeline:
                 self._tag = "tc_gemm:lstm_dW"
                 try:
                     self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
-                               ptr(gk), c.T, c.D, c.u, 0)
+                               ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0)
                 finally:
                     self._tag = None
             else:

@@ -103,11 +103,17 @@ def test_tc_gemm_lstm_dw_stacked_operand(T, D):
     g = torch.Generator(device="cuda").manual_seed(T + D)
     x = torch.zeros(T, 64, device="cuda")
     x[:, :D] = torch.randn(T, D, generator=g, device="cuda")
+    if D <= 62:
+        x[:, D:D + 2] = 1.0          # the bias columns indnet_embed_fwd_bf16 writes
     x = x.to(torch.bfloat16)
     h = torch.randn(T, u, generator=g, device="cuda").to(torch.bfloat16)
     dz = torch.randn(T, 4 * u, generator=g, device="cuda").to(torch.bfloat16)
     out = torch.full((D + u, 4 * u), float("nan"), device="cuda")
-    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(x), ptr(h), ptr(dz), ptr(out), T, D, u, 0)
+    dbias = torch.full((4 * u,), float("nan"), device="cuda") if D <= 62 else None
+    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(x), ptr(h), ptr(dz), ptr(out), ptr(dbias), T, D, u, 0)
     torch.cuda.synchronize()
     ref = torch.cat([x[:, :D].double().t() @ dz.double(), h.double().t() @ dz.double()], 0)
     assert float((out.double() - ref).abs().max() / ref.abs().max()) < 2e-5
+    if dbias is not None:            # row D of the stacked product = column sums of dz = the LSTM bias gradient
+        want = dz.double().sum(0)
+        assert float((dbias.double() - want).abs().max() / want.abs().max()) < 2e-5

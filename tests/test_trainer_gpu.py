@@ -53,12 +53,10 @@ def test_trainer_steps_on_the_reference_episode_sequence_and_hands_streams_back(
     # suspend() discards the look-ahead walk: the host streams are where 4 reference iterations leave them
     tr.suspend()
     assert (random.random(), float(np.random.rand())) == tail
-    # ... and stepping again resumes from whatever the host streams now are
-    random.seed(11); np.random.seed(11)
-    for _ in range(4 * cfg.B):
-        so.next_one_tf_stdlib(tables, ld.scopes(), cfg.N, cfg.K, cfg.Q)
-    random.random(); np.random.rand()
+    # ... and stepping again resumes from whatever the host streams now are (here: one draw further on each)
+    st_py, st_np = random.getstate(), np.random.get_state()
     nxt = [so.next_one_tf_stdlib(tables, ld.scopes(), cfg.N, cfg.K, cfg.Q) for _ in range(cfg.B)]
+    random.setstate(st_py); np.random.set_state(st_np)
     tr.step()
     tr.stream.synchronize()
     for b in range(cfg.B):
