@@ -67,10 +67,17 @@ __host__ __device__ __forceinline__ uint32_t dropout_hash(uint32_t key, uint64_t
   h ^= h >> 16;
   return h;
 }
-// keep iff the top 24 bits, as an integer, are below keep_prob * 2^24
-__host__ __device__ __forceinline__ uint32_t dropout_threshold(float keep_prob) { return (uint32_t)(keep_prob * 16777216.0f); }
-__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, float keep_prob) {
-  return (dropout_hash(dropout_key(seed), idx) >> 8) < dropout_threshold(keep_prob);
+// One hash serves TWO sentences (2x, 2x+1) of the same (time, feature): `idx_even` is the flat [X][L][F] index of
+// the even sentence's element, the even sentence takes the low 16 bits, the odd one the high 16 bits;
+// keep iff that field < keep_prob * 2^16.
+__host__ __device__ __forceinline__ uint32_t dropout_threshold(float keep_prob) { return (uint32_t)(keep_prob * 65536.0f); }
+__host__ __device__ __forceinline__ bool dropout_keep_field(uint32_t hash, bool odd, uint32_t thr) {
+  return (odd ? (hash >> 16) : (hash & 0xFFFFu)) < thr;
+}
+// element (sentence x, flat index idx) with `row` = L * F elements per sentence
+__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, int x, uint64_t row, float keep_prob) {
+  const bool odd = (x & 1) != 0;
+  return dropout_keep_field(dropout_hash(dropout_key(seed), odd ? idx - row : idx), odd, dropout_threshold(keep_prob));
 }
 
 }  // namespace indnet

@@ -93,7 +93,7 @@ lstm_fwd_kernel(const float* __restrict__ xproj, const float* __restrict__ Wh_fw
           hprev[tok * u + unit] = hcur[unit * SB + sl];
           const long long oi = ((long long)x * L + t) * (2 * u) + dir * u + unit;
           float ho = h;
-          if (keep_prob < 1.0f) ho = dropout_keep(seed, (unsigned long long)oi, keep_prob) ? h * inv_keep : 0.f;
+          if (keep_prob < 1.0f) ho = dropout_keep(seed, (unsigned long long)oi, x, (unsigned long long)L * 2 * u, keep_prob) ? h * inv_keep : 0.f;
           hout[oi] = ho;
         }
       }
@@ -135,7 +135,7 @@ lstm_bwd_kernel(const float* __restrict__ dhout, const float* __restrict__ gates
         const long long tok = ((long long)dir * X + x) * L + t;
         const long long oi = ((long long)x * L + t) * (2 * u) + dir * u + unit;
         float dh = dhout[oi];
-        if (keep_prob < 1.0f) dh = dropout_keep(seed, (unsigned long long)oi, keep_prob) ? dh * inv_keep : 0.f;
+        if (keep_prob < 1.0f) dh = dropout_keep(seed, (unsigned long long)oi, x, (unsigned long long)L * 2 * u, keep_prob) ? dh * inv_keep : 0.f;
         dh += dhr[unit * SB + sl];
         const float* gp = gates + tok * U4 + unit;
         const float gi = gp[0], gj = gp[u], gf = gp[2 * u], go = gp[3 * u];

@@ -313,20 +313,20 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       const int b = s & 1;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        LT_MARK(threadIdx.x == 0, s, h * 4 + 0);
         mbar_wait_wd(&mma_done[h], s & 1);
         tc_fence_after();
-        LT_MARK(threadIdx.x == 0, s, h * 4 + 1);
+        LT_MARK(threadIdx.x == 0, s, h * 4 + 0);
         float zi[4], zj[4], zf[4], zo[4];
         tmem_ld4(acc0 + h * LT_NH + 0 * 32, zi);
         tmem_ld4(acc0 + h * LT_NH + 1 * 32, zj);
         tmem_ld4(acc0 + h * LT_NH + 2 * 32, zf);
         tmem_ld4(acc0 + h * LT_NH + 3 * 32, zo);
         tmem_ld_wait();
-        LT_MARK(threadIdx.x == 0, s, h * 4 + 2);
+        LT_MARK(threadIdx.x == 0, s, h * 4 + 1);
         const uint32_t tile = (uint32_t)(h * 2 + b);
         const uint32_t hdst = sH_s + tile * LT_H_BYTES, odst = sO_s + tile * LT_H_BYTES;
         const uint32_t gdst = sG_s + tile * LT_G_BYTES + goff, cdst = sC_s + tile * LT_C_BYTES + coff;
+        uint32_t dhash = 0;
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) {
           // the accumulators already hold z/2 (i, f, o) resp. z (j) with the bias added
@@ -343,11 +343,12 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
             sts_bf16(cdst + qq * (LT_U * 2), __float2bfloat16(cn));
           }
           if (DROP) {
-            const uint32_t idx = didx + (uint32_t)(h * LT_NH + qq) * drow;
-            const bool keep = (dropout_hash(dkey, idx) >> 8) < dthr;
+            if ((qq & 1) == 0) dhash = dropout_hash(dkey, didx + (uint32_t)(h * LT_NH + qq) * drow);   // serves qq and qq + 1
+            const bool keep = dropout_keep_field(dhash, qq & 1, dthr);
             sts_bf16(odst + hoff[qq], __float2bfloat16(keep ? hv * inv_keep : 0.f));
           }
         }
+        LT_MARK(threadIdx.x == 0, s, h * 4 + 2);
         fence_proxy_async();      // shared-memory tiles -> visible to the MMA's operand reads and the TMA stores
         tc_fence_before();        // TMEM loads ordered before the next MMAs overwrite the accumulators
         mbar_arrive(&h_ready[h]);
@@ -363,19 +364,21 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
 // ------------------------------------------------------------------------------------------------
 // BPTT, bf16 tensor-core mode (see the file header).  Shared memory: per (half, stage) one input tile set
 // {gates [16][128] x 8 B, dh [16][128] bf16, c_prev [16][128] bf16}, the c tile of the first step, the dz
-// tiles (B operand, [8 K-blocks][16 rows][128 B] swizzled, double buffered) and, with DX, two K-blocks of W_x.
+// tile (B operand, [8 K-blocks][32 rows][128 B] swizzled, rows 0-15 / 16-31 = the halves, double buffered) and,
+// with DX, two K-blocks of W_x.
 constexpr int LB_KB = 4 * LT_U / 64;                            // 8 K-blocks of dz
 constexpr int LB_IN_G = LT_NH * LT_U * 8, LB_IN_D = LT_NH * LT_U * 2, LB_IN_C = LT_NH * LT_U * 2;
 constexpr int LB_IN_BYTES = LB_IN_G + LB_IN_D + LB_IN_C;       // 24576
-constexpr int LB_Z_BYTES = LB_KB * LT_NH * 128;                 // 16384
+constexpr int LB_Z_BYTES = LB_KB * LT_NS * 128;                 // 32768: dz of BOTH halves, [8 K-blocks][32 rows][128 B]
 constexpr int LB_WX_TKB = 6;                                    // dx path: K-blocks of the W_x rows held in tensor memory
 constexpr int LB_WX_BYTES = (LB_KB - LB_WX_TKB) * 128 * 128;    // ... the other two stay in shared memory (32 KB)
 constexpr int LB_OFF_IN = 0;                                    // [half][stage]
 constexpr int LB_OFF_C0 = LB_OFF_IN + 4 * LB_IN_BYTES;         // [half]
-constexpr int LB_OFF_Z = LB_OFF_C0 + 2 * LB_IN_C;              // [half][buf]
-constexpr int LB_OFF_WX = LB_OFF_Z + 4 * LB_Z_BYTES;
+constexpr int LB_OFF_Z = LB_OFF_C0 + 2 * LB_IN_C;              // [buf]
+constexpr int LB_OFF_WX = LB_OFF_Z + 2 * LB_Z_BYTES;
+constexpr int LB_DXT_BYTES = LT_NS * 16 * 4;                    // dx of a step: [32 sentences][16 features] fp32
 constexpr int LB_SMEM_NODX = LB_OFF_WX + 256 + 1024;
-constexpr int LB_SMEM_DX = LB_OFF_WX + LB_WX_BYTES + 256 + 1024;
+constexpr int LB_SMEM_DX = LB_OFF_WX + LB_WX_BYTES + 2 * LB_DXT_BYTES + 256 + 1024;
 static_assert(LB_OFF_Z % 1024 == 0 && LB_OFF_WX % 1024 == 0, "swizzled tiles need 1024-byte alignment");
 constexpr int LB_DX_LD = 16;                                    // dx2 row stride in floats (64-byte rows)
 constexpr uint32_t LB_TM_WH = 0, LB_TM_ACC = 256, LB_TM_ACCX = 288, LB_TM_WX = 320;
@@ -392,15 +395,17 @@ template <bool DROP, bool DX>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmC,
                    const __grid_constant__ CUtensorMap tmDh, const __grid_constant__ CUtensorMap tmDz,
-                   const __grid_constant__ CUtensorMap tmXf, const __grid_constant__ CUtensorMap tmXb, LstmTcBwdP p) {
+                   const __grid_constant__ CUtensorMap tmXf, const __grid_constant__ CUtensorMap tmXb,
+                   const __grid_constant__ CUtensorMap tmDx, LstmTcBwdP p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sWx = smem + LB_OFF_WX;                      // DX only: [2 kb][128 rows][128 B]
-  uint64_t* in_full = reinterpret_cast<uint64_t*>(smem + LB_OFF_WX + (DX ? LB_WX_BYTES : 0));   // [half][stage]
+  uint8_t* sDx = sWx + LB_WX_BYTES;                     // DX only: [2][32][16] fp32 staging of the dx rows
+  uint64_t* in_full = reinterpret_cast<uint64_t*>(smem + LB_OFF_WX + (DX ? LB_WX_BYTES + 2 * LB_DXT_BYTES : 0));   // [half][stage]
   uint64_t* c0_full = in_full + 4;                      // [half]
   uint64_t* z_ready = c0_full + 2;                      // [half]
   uint64_t* mma_done = z_ready + 2;                     // [half]
-  uint64_t* dx_done = mma_done + 2;                     // [half]
+  uint64_t* dx_done = mma_done + 2;                     // one per step (both halves)
   uint64_t* wx_full = dx_done + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wx_full + 1);
   const uint32_t sIn_s = smem_u32(smem + LB_OFF_IN), sC0_s = smem_u32(smem + LB_OFF_C0), sZ_s = smem_u32(smem + LB_OFF_Z);
@@ -419,8 +424,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       mbar_init(&c0_full[h], 1);
       mbar_init(&z_ready[h], LT_GATE_THREADS);
       mbar_init(&mma_done[h], 1);
-      mbar_init(&dx_done[h], 1);
     }
+    mbar_init(dx_done, 1);
     mbar_init(wx_full, 1);
     fence_barrier_init();
     if (DX) {
@@ -496,45 +501,85 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     }
     __syncwarp();
     if (DX) mbar_wait_wd(wx_full, 0);
+    // dx of a finished step: the 10 position features sit in TMEM lanes 0..9, which this warp (16 % 4 == 0) can
+    // read; they leave through a small staging tile and one TMA store, so no gate thread touches global memory
+    auto drain_dx = [&](int step_done) {
+      float v[32];
+      mbar_wait_wd(dx_done, step_done & 1);
+      tc_fence_after();
+      tmem_ld32(taddr + LB_TM_ACCX, v);
+      tmem_ld_wait();
+      float* tile = reinterpret_cast<float*>(sDx + (step_done & 1) * LB_DXT_BYTES);
+      if (lane < LB_DX_LD) {
+#pragma unroll
+        for (int q = 0; q < LT_NS; ++q) tile[q * LB_DX_LD + lane] = v[q];
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (elect_one()) {
+        tma_store_4d(&tmDx, smem_u32(tile), 0, tb(step_done), x0, dir);
+        bulk_commit();
+      }
+      __syncwarp();
+    };
     for (int step = 0; step < L; ++step) {
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
         mbar_wait_wd(&z_ready[h], step & 1);      // dz(step) of this half is in its tile; its input stage is free
         tc_fence_after();
-        LB_MARK(lane == 0, step, 5 + h);
         if (elect_one()) {
-          bulk_wait_read<1>();                    // the dz tile of step-1 (same half) has been read by its store
-          const uint32_t zsrc = sZ_s + (h * 2 + (step & 1)) * LB_Z_BYTES;
-          const uint32_t zb16 = zsrc >> 4;
+          // the gate threads start on dz(step+1) once the commit below fires; that buffer was last stored by the
+          // group of step-1 (committed a whole half step ago): its reads must have finished first
+          if (h == 0 && step > 0) bulk_wait_read<0>();
+          const uint32_t zsrc = sZ_s + (uint32_t)(step & 1) * LB_Z_BYTES;
+          const uint32_t zb16 = (zsrc + h * (LT_NH * 128)) >> 4;        // this half's 16 rows of every K-block
           if (step + 1 < L) {                     // the last step's dh_rec has no consumer
 #pragma unroll
             for (int kk = 0; kk < 4 * LB_KB; ++kk)
               umma_bf16_ts(taddr + LB_TM_ACC + h * LT_NH, taddr + LB_TM_WH + kk * 8,
-                           smem_desc_sw128_k(zb16, (kk >> 2) * (LT_NH * 128) + (kk & 3) * 32), idesc, kk > 0 ? 1u : 0u);
+                           smem_desc_sw128_k(zb16, (kk >> 2) * (LT_NS * 128) + (kk & 3) * 32), idesc, kk > 0 ? 1u : 0u);
             umma_commit(&mma_done[h]);
           }
-          if (DX) {
+        }
+        __syncwarp();
+        if (h == 1) {
+          // dx of the previous step has had a whole step to finish: drain it (this warp reads TMEM lanes 0..31)
+          // right before this step's dx MMAs reuse the accumulator - the issuer never waits on the tensor pipe
+          if (DX && step > 0) drain_dx(step - 1);
+          if (elect_one()) {
+            const uint32_t zsrc = sZ_s + (uint32_t)(step & 1) * LB_Z_BYTES;
+            if (DX) {
+              // once per step for both halves (N = 32): the two shared-memory K-blocks cost their 4 KB operand
+              // read per instruction whatever N is
+              constexpr uint32_t idesc32 = idesc_bf16(128, LT_NS, false, false);
+              const uint32_t zf16 = zsrc >> 4;
 #pragma unroll
-            for (int kk = 0; kk < 4 * LB_KB; ++kk) {
-              const uint64_t bd = smem_desc_sw128_k(zb16, (kk >> 2) * (LT_NH * 128) + (kk & 3) * 32);
-              if ((kk >> 2) < LB_WX_TKB)
-                umma_bf16_ts(taddr + LB_TM_ACCX + h * LT_NH, taddr + LB_TM_WX + kk * 8, bd, idesc, kk > 0 ? 1u : 0u);
-              else
-                umma_bf16(taddr + LB_TM_ACCX + h * LT_NH, smem_desc_sw128_k(wx16, ((kk >> 2) - LB_WX_TKB) * 16384 + (kk & 3) * 32),
-                          bd, idesc, 1u);
+              for (int kk = 0; kk < 4 * LB_KB; ++kk) {
+                const uint64_t bd = smem_desc_sw128_k(zf16, (kk >> 2) * (LT_NS * 128) + (kk & 3) * 32);
+                if ((kk >> 2) < LB_WX_TKB)
+                  umma_bf16_ts(taddr + LB_TM_ACCX, taddr + LB_TM_WX + kk * 8, bd, idesc32, kk > 0 ? 1u : 0u);
+                else
+                  umma_bf16(taddr + LB_TM_ACCX, smem_desc_sw128_k(wx16, ((kk >> 2) - LB_WX_TKB) * 16384 + (kk & 3) * 32),
+                            bd, idesc32, 1u);
+              }
+              umma_commit(dx_done);
             }
-            umma_commit(&dx_done[h]);
-          }
-          // dz of this step to HBM for the weight-gradient GEMMs: the operand tile itself is the source
-          const int t = tb(step), xs = x0 + h * LT_NH;
+            // dz of this step to HBM for the weight-gradient GEMMs: the operand tile itself is the source
+            const int t = tb(step);
 #pragma unroll
-          for (int kb = 0; kb < LB_KB; ++kb) tma_store_4d(&tmDz, zsrc + kb * (LT_NH * 128), kb * 64, t, xs, dir);
-          bulk_commit();
+            for (int kb = 0; kb < LB_KB; ++kb) tma_store_4d(&tmDz, zsrc + kb * (LT_NS * 128), kb * 64, t, x0, dir);
+            bulk_commit();
+          }
+          __syncwarp();
+        }
+        if (elect_one()) {
           if (step + 2 < L) load_in(step + 2, h);
         }
         __syncwarp();
       }
     }
+    if (DX) drain_dx(L - 1);
     if (elect_one()) bulk_wait_all<0>();
     __syncwarp();
   } else {
@@ -542,9 +587,9 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     const int lq = warp & 3, sg = warp >> 2;
     const int m = lq * 32 + lane;
     const uint32_t lane_sel = (uint32_t)(lq * 32) << 16;
-    const uint32_t acc0 = taddr + LB_TM_ACC + lane_sel + sg * 4, accx0 = taddr + LB_TM_ACCX + lane_sel + sg * 4;
+    const uint32_t acc0 = taddr + LB_TM_ACC + lane_sel + sg * 4;
     // dz element (row r, column g*128 + m) of the swizzled tile: K-block g*2 + m/64
-    const uint32_t zbase = (uint32_t)(m >> 6) * (LT_NH * 128) + (uint32_t)(m & 7) * 2;
+    const uint32_t zbase = (uint32_t)(m >> 6) * (LT_NS * 128) + (uint32_t)(m & 7) * 2;
     const uint32_t zchunk = (uint32_t)(m & 63) >> 3;
     uint32_t zoff[4];
 #pragma unroll
@@ -566,24 +611,6 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     }
     const uint32_t drow = (uint32_t)L * (2 * LT_U);
     const uint32_t dstep = dir ? (uint32_t)(2 * LT_U) : (uint32_t)(-(2 * LT_U));
-    const bool dx_warp = DX && lq == 0;                  // features live in TMEM lanes 0..dxn-1 (dxn <= 16)
-    auto store_dx = [&](int step_done, int h) {          // dx of processing step `step_done`, half h
-      if (dx_warp) {
-        float dxv[4];
-        mbar_wait_wd(&dx_done[h], step_done & 1);
-        tc_fence_after();
-        tmem_ld4(accx0 + h * LT_NH, dxv);
-        tmem_ld_wait();
-        if (m < p.dxn) {
-          const int t = tb(step_done);
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq) {
-            const int x = x0 + h * LT_NH + sg * 4 + qq;
-            if (x < p.X) p.dx2[(((long long)dir * p.X + x) * L + t) * LB_DX_LD + m] = dxv[qq];
-          }
-        }
-      }
-    };
     float dcr[8], cc[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) { dcr[q] = 0.f; cc[q] = 0.f; }
@@ -592,9 +619,9 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       const bool more = step + 1 < L;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        LB_MARK(threadIdx.x == 0, step, h * 2 + 0);
         const uint32_t in_s = sIn_s + (uint32_t)(h * 2 + (step & 1)) * LB_IN_BYTES;
         mbar_wait_wd(&in_full[h * 2 + (step & 1)], (step >> 1) & 1);
+        LB_MARK(threadIdx.x == 0, step, h * 4 + 0);
         if (step == 0) {
           mbar_wait_wd(&c0_full[h], 0);
 #pragma unroll
@@ -602,14 +629,15 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         }
         uint2 gw[4];
         float dh[4], cp[4];
+        uint32_t dhash = 0;
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) {
           gw[qq] = lds_u64(in_s + goff + qq * (LT_U * 8));
           dh[qq] = lds_bf16(in_s + LB_IN_G + coff + qq * (LT_U * 2));
           cp[qq] = more ? lds_bf16(in_s + LB_IN_G + LB_IN_D + coff + qq * (LT_U * 2)) : 0.f;
           if (DROP) {
-            const uint32_t idx = didx + (uint32_t)(h * LT_NH + qq) * drow;
-            dh[qq] = ((dropout_hash(dkey, idx) >> 8) < dthr) ? dh[qq] * inv_keep : 0.f;
+            if ((qq & 1) == 0) dhash = dropout_hash(dkey, didx + (uint32_t)(h * LT_NH + qq) * drow);   // serves qq and qq + 1
+            dh[qq] = dropout_keep_field(dhash, qq & 1, dthr) ? dh[qq] * inv_keep : 0.f;
           }
         }
         if (step > 0) {
@@ -621,8 +649,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 #pragma unroll
           for (int qq = 0; qq < 4; ++qq) dh[qq] += dhr[qq];      // the recurrent part is added after the dropout mask
         }
-        LB_MARK(threadIdx.x == 0, step, h * 2 + 1);
-        const uint32_t zdst = sZ_s + (uint32_t)(h * 2 + (step & 1)) * LB_Z_BYTES;
+        LB_MARK(threadIdx.x == 0, step, h * 4 + 1);
+        const uint32_t zdst = sZ_s + (uint32_t)(step & 1) * LB_Z_BYTES + h * (LT_NH * 128);
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) {
           const int q = h * 4 + qq;
@@ -637,18 +665,18 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           cc[q] = cp[qq];                        // c_{t_prev} is the cell state of the next step processed
           const uint32_t zp = zdst + zoff[qq];
           sts_bf16(zp, __float2bfloat16(di));
-          sts_bf16(zp + 2 * (LT_NH * 128), __float2bfloat16(dj));
-          sts_bf16(zp + 4 * (LT_NH * 128), __float2bfloat16(df));
-          sts_bf16(zp + 6 * (LT_NH * 128), __float2bfloat16(dob));
+          sts_bf16(zp + 2 * (LT_NS * 128), __float2bfloat16(dj));
+          sts_bf16(zp + 4 * (LT_NS * 128), __float2bfloat16(df));
+          sts_bf16(zp + 6 * (LT_NS * 128), __float2bfloat16(dob));
         }
-        if (DX && step > 0) store_dx(step - 1, h);          // long complete by now
+        LB_MARK(threadIdx.x == 0, step, h * 4 + 2);
         fence_proxy_async();
         tc_fence_before();
         mbar_arrive(&z_ready[h]);
+        LB_MARK(threadIdx.x == 0, step, h * 4 + 3);
       }
       if (DROP) didx += dstep;
     }
-    if (DX) { store_dx(L - 1, 0); store_dx(L - 1, 1); }
   }
   __syncthreads();
   if (warp == 0) tmem_dealloc(taddr, 512);
@@ -691,10 +719,11 @@ extern "C" int indnet_debug_lstm_bwd(long long* out) {
 namespace {
 typedef unsigned long long u64;
 // [2][X][L][inner] with `eb`-byte elements as a 4-D map (inner, L, X, 2), box (box_inner, 1, 16, 1)
-int map_dir_tok(CUtensorMap* tm, const void* base, int eb, int inner, int X, int L, int box_inner, bool sw) {
+int map_dir_tok(CUtensorMap* tm, const void* base, int eb, int inner, int X, int L, int box_inner, bool sw,
+                int rows = LT_NH) {
   const u64 dims[4] = {(u64)inner, (u64)L, (u64)X, 2};
   const u64 strides[3] = {(u64)inner * eb, (u64)L * inner * eb, (u64)X * L * inner * eb};
-  const unsigned box[4] = {(unsigned)box_inner, 1, (unsigned)LT_NH, 1};
+  const unsigned box[4] = {(unsigned)box_inner, 1, (unsigned)rows, 1};
   return make_tmap_nd(tm, base, eb, 4, dims, strides, box, sw);
 }
 // [X][L][inner] bf16 as a 3-D map (inner, L, X), box (box_inner, 1, rows)
@@ -786,10 +815,13 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   if (rc) return rc;
   rc = map_tok(&tmDh, dhout_bf, 2 * LT_U, X, L, LT_U, LT_NH, false);
   if (rc) return rc;
-  rc = map_dir_tok(&tmDz, dz_bf, 2, 4 * LT_U, X, L, 64, true);
+  rc = map_dir_tok(&tmDz, dz_bf, 2, 4 * LT_U, X, L, 64, true, LT_NS);
   if (rc) return rc;
-  tmXf = tmXb = tmDh;
+  CUtensorMap tmDx;
+  tmXf = tmXb = tmDx = tmDh;
   if (dx2) {
+    rc = map_dir_tok(&tmDx, dx2, 4, LB_DX_LD, X, L, LB_DX_LD, false, LT_NS);
+    if (rc) return rc;
     IN_REQUIRE(dx_first >= 0 && dx_first < D && D - dx_first <= LB_DX_LD,
                "lstm_bwd_tc: the fused input gradient covers at most %d features (got first=%d of D=%d)", LB_DX_LD, dx_first, D);
     p.dxn = D - dx_first;
@@ -808,7 +840,7 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   do {                                                                                                          \
     const int smem = DX_ ? LB_SMEM_DX : LB_SMEM_NODX;                                                           \
     IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
-    tc_lstm_bwd_kernel<DROP_, DX_><<<grid, LT_THREADS, smem, st>>>(tmG, tmC, tmDh, tmDz, tmXf, tmXb, p);          \
+    tc_lstm_bwd_kernel<DROP_, DX_><<<grid, LT_THREADS, smem, st>>>(tmG, tmC, tmDh, tmDz, tmXf, tmXb, tmDx, p);          \
   } while (0)
   if (drop && dx2) LB_LAUNCH(true, true);
   else if (drop) LB_LAUNCH(true, false);

@@ -198,9 +198,12 @@ class ParamStore:
 
 def dropout_keep_mask(seed: int, shape, keep_prob: float, step: int = 0) -> np.ndarray:
     """Host restatement of the device dropout stream (csrc/common.cuh ``dropout_keep``) so a mask the
-    LSTM kernels drew can be replayed through the oracle.  Element i of the flattened [X, L, 2u] output is
-    kept iff (dropout_hash(dropout_key(seed + step*1000003), i) >> 8) < uint32(keep_prob * 2^24)."""
-    n = int(np.prod(shape))
+    LSTM kernels drew can be replayed through the oracle.  ``shape`` = (X, L, 2u).  One 32-bit hash serves the
+    sentence pair (2x, 2x+1) at the same (time, feature): it is taken at the flat index of the even sentence's
+    element; the even sentence keeps iff its low 16 bits < uint32(keep_prob * 2^16), the odd one uses the high
+    16 bits.  key = dropout_key(seed + step * 1000003)."""
+    X, L, F = (int(v) for v in shape)
+    n = X * L * F
     M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
     with np.errstate(over="ignore"):
         z = (np.uint64((seed + step * 1000003) & 0xFFFFFFFFFFFFFFFF) + np.uint64(0x9E3779B97F4A7C15)) & M64
@@ -209,13 +212,16 @@ def dropout_keep_mask(seed: int, shape, keep_prob: float, step: int = 0) -> np.n
         z = z ^ (z >> np.uint64(31))
         key = np.uint32(int(z) >> 32)
         idx = np.arange(n, dtype=np.uint64)
+        odd = ((idx // np.uint64(L * F)) & np.uint64(1)).astype(bool)
+        idx = idx - odd.astype(np.uint64) * np.uint64(L * F)
         h = ((idx & np.uint64(0xFFFFFFFF)).astype(np.uint32) * np.uint32(0x9E3779B1) + key
              + (idx >> np.uint64(32)).astype(np.uint32) * np.uint32(0x7FEB352D))
         h ^= h >> np.uint32(16); h *= np.uint32(0x85EBCA6B)
         h ^= h >> np.uint32(13); h *= np.uint32(0xC2B2AE35)
         h ^= h >> np.uint32(16)
-    thr = np.uint32(int(np.float32(keep_prob) * np.float32(16777216.0)))
-    return ((h >> np.uint32(8)) < thr).reshape(shape)
+    thr = np.uint32(int(np.float32(keep_prob) * np.float32(65536.0)))
+    field = np.where(odd, h >> np.uint32(16), h & np.uint32(0xFFFF))
+    return (field < thr).reshape(shape)
 
 
 class EpisodePipeline:
@@ -618,7 +624,8 @@ class EpisodePipeline:
                      splitk=1, tag="attn_dh")
         # with a frozen word table only the 2 x 5 position columns of dx are needed: the BPTT kernel forms
         # them itself (per direction) instead of two GEMM launches that would re-read all of dz
-        fused_dx = self.tc_lstm and not self.trainable_words and c.D - c.E <= 16
+        import os as _os
+        fused_dx = self.tc_lstm and not self.trainable_words and c.D - c.E <= 16 and not _os.environ.get("INDNET_NO_FUSED_DX")
         if self.tc_lstm:
             self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate_bf),
                        ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf),

@@ -19,15 +19,16 @@ LIB._dll.indnet_debug_lstm.argtypes = [ctypes.c_void_p]
 rc = LIB._dll.indnet_debug_lstm(buf)
 a = np.array(list(buf), dtype=np.int64).reshape(64, 8)
 print("rc", rc)
-print("forward, gate thread 0, per step: half A {wait mma | tmem ld | math+sts | (end)} half B {...} || period")
+print("forward, gate thread 0, per step and half: wait for MMA | tmem ld | math + st.shared | fence + arrive   (A || B) || period")
 for s in range(1, 38):
-    r, n = a[s], a[s + 1]
-    print(s, r[1] - r[0], '|', r[2] - r[1], '|', r[3] - r[2], '||', r[5] - r[4], '|', r[6] - r[5], '|', r[7] - r[6],
-          '|| A->B gap', r[4] - r[3], '| period', n[0] - r[0])
+    r, n, pv = a[s], a[s + 1], a[s - 1]
+    print(s, r[0] - pv[7], '|', r[1] - r[0], '|', r[2] - r[1], '|', r[3] - r[2], '||', r[4] - r[3], '|', r[5] - r[4], '|', r[6] - r[5], '|', r[7] - r[6],
+          '|| period', n[0] - r[0])
 rc = LIB._dll.indnet_debug_lstm_bwd(buf)
 b = np.array(list(buf), dtype=np.int64).reshape(64, 8)
 print("BPTT rc", rc)
-print("gate thread 0, per step: half A {inputs+mma wait | math+sts+arrive} half B {...} || issuer wake after A, B arrivals || period")
+print("gate thread 0, per step and half: wait inputs | lds + dropout + wait MMA + tmem ld | math + st.shared | dx store + fence + arrive  (A || B) || period")
 for s in range(2, 38):
-    r, n = b[s], b[s + 1]
-    print(s, r[1] - r[0], '|', r[2] - r[1], '||', r[3] - r[2], '|', n[0] - r[3], '||', r[5] - r[2], '|', r[6] - n[0], '|| period', n[0] - r[0])
+    r, n, pv = b[s], b[s + 1], b[s - 1]
+    print(s, r[0] - pv[7], '|', r[1] - r[0], '|', r[2] - r[1], '|', r[3] - r[2], '||', r[4] - r[3], '|', r[5] - r[4], '|', r[6] - r[5], '|', r[7] - r[6],
+          '|| period', n[0] - r[0])
