@@ -165,6 +165,189 @@ routing_bwd_kernel(const float* __restrict__ ehat, const float* __restrict__ b_i
   }
 }
 
+// ---- fast path (H a multiple of 128, at most 4 iterations): still one warp per (episode, class), but e_hat is
+// staged ONCE into the warp's slice of shared memory with 16-byte loads and everything else lives in registers
+// (lane owns the features {128 j + 4 lane + i}); the generic kernels above re-read e_hat from L2 inside every
+// loop, which made them pure load latency (30-60 us for a few KB of data).
+constexpr int RT_MAX_IT = 4;
+
+template <int NV4>
+__device__ __forceinline__ void rt_stage(const float* __restrict__ e, float4* se, int K, int lane) {
+  const float4* e4 = reinterpret_cast<const float4*>(e);
+  for (int i = lane; i < K * NV4 * 32; i += 32) se[i] = e4[i];
+  __syncwarp();
+}
+// dots[k] = sum_h e[k][h] * v[h] for all k; lane k ends up holding dots[k] (others 0)
+template <int NV4>
+__device__ __forceinline__ float rt_dots(const float4* se, const float4* v, int K, int lane) {
+  float mine = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < K; ++k) {
+    float dot = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      const float4 a = se[(k * NV4 + j) * 32 + lane];
+      dot += a.x * v[j].x + a.y * v[j].y + a.z * v[j].z + a.w * v[j].w;
+    }
+    dot = warp_sum(dot);
+    if (lane == k) mine = dot;
+  }
+  return mine;
+}
+template <int NV4>
+__device__ __forceinline__ float rt_norm2(const float4* v) {
+  float n2 = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) n2 += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
+  return warp_sum(n2);
+}
+// acc[h] = sum_k coef_k e[k][h], coef_k held by lane k
+template <int NV4>
+__device__ __forceinline__ void rt_combine(const float4* se, float coef, float4* acc, int K, int lane) {
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int k = 0; k < K; ++k) {
+    const float ck = __shfl_sync(0xffffffffu, coef, k);
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      const float4 a = se[(k * NV4 + j) * 32 + lane];
+      acc[j].x = fmaf(ck, a.x, acc[j].x); acc[j].y = fmaf(ck, a.y, acc[j].y);
+      acc[j].z = fmaf(ck, a.z, acc[j].z); acc[j].w = fmaf(ck, a.w, acc[j].w);
+    }
+  }
+}
+__device__ __forceinline__ float rt_softmax(float b, int K, int lane) {
+  const float mx = warp_max(b);
+  const float ex = (lane < K) ? expf(b - mx) : 0.f;
+  return ex / warp_sum(ex);
+}
+
+template <int NV4>
+__global__ void __launch_bounds__(RT_WARPS * 32)
+routing_fwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in, float* __restrict__ cvec,
+                        __nv_bfloat16* __restrict__ cvec_bf, int BC, int K, int iters, int warps) {
+  extern __shared__ float4 sm4[];
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int w = blockIdx.x * warps + warp;
+  if (warp >= warps || w >= BC) return;
+  constexpr int H = NV4 * 128;
+  float4* se = sm4 + (size_t)warp * K * NV4 * 32;
+  rt_stage<NV4>(ehat + (long long)w * K * H, se, K, lane);
+  float b = (lane < K) ? (b_in ? b_in[(long long)w * K + lane] : 0.f) : -INFINITY;
+  float4 cv[NV4];
+  for (int it = 0; it < iters; ++it) {
+    const float d = rt_softmax(b, K, lane);
+    rt_combine<NV4>(se, d, cv, K, lane);
+    const float f = squash_factor(rt_norm2<NV4>(cv));
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) { cv[j].x *= f; cv[j].y *= f; cv[j].z *= f; cv[j].w *= f; }
+    if (it + 1 < iters) b += rt_dots<NV4>(se, cv, K, lane);        // lanes >= K add 0 to -inf
+  }
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) {
+    const long long o = (long long)w * H + j * 128 + lane * 4;
+    *reinterpret_cast<float4*>(cvec + o) = cv[j];
+    if (cvec_bf) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(cv[j].x, cv[j].y), hi = __floats2bfloat162_rn(cv[j].z, cv[j].w);
+      *reinterpret_cast<uint2*>(cvec_bf + o) = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+    }
+  }
+}
+
+template <int NV4>
+__global__ void __launch_bounds__(RT_WARPS * 32)
+routing_bwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in, const float* __restrict__ dcvec,
+                        float* __restrict__ dehat, __nv_bfloat16* __restrict__ dehat_bf, int BC, int K, int iters,
+                        int warps) {
+  extern __shared__ float4 sm4[];
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int w = blockIdx.x * warps + warp;
+  if (warp >= warps || w >= BC) return;
+  constexpr int H = NV4 * 128;
+  float4* se = sm4 + (size_t)warp * 2 * K * NV4 * 32;      // e_hat, then its gradient accumulator
+  float4* sde = se + (size_t)K * NV4 * 32;
+  rt_stage<NV4>(ehat + (long long)w * K * H, se, K, lane);
+  // ---- recompute the forward iterations, keeping d, c_hat, c and |c_hat|^2 of each (registers)
+  float4 chat[RT_MAX_IT][NV4], cs[RT_MAX_IT][NV4];
+  float dsm[RT_MAX_IT], sn[RT_MAX_IT];
+  float b = (lane < K) ? (b_in ? b_in[(long long)w * K + lane] : 0.f) : -INFINITY;
+#pragma unroll
+  for (int it = 0; it < RT_MAX_IT; ++it) {
+    if (it < iters) {
+      dsm[it] = rt_softmax(b, K, lane);
+      rt_combine<NV4>(se, dsm[it], chat[it], K, lane);
+      sn[it] = rt_norm2<NV4>(chat[it]);
+      const float f = squash_factor(sn[it]);
+#pragma unroll
+      for (int j = 0; j < NV4; ++j)
+        cs[it][j] = make_float4(chat[it][j].x * f, chat[it][j].y * f, chat[it][j].z * f, chat[it][j].w * f);
+      if (it + 1 < iters) b += rt_dots<NV4>(se, cs[it], K, lane);
+    }
+  }
+  // ---- reverse sweep (autodiff through every iteration: no stop_gradient in the reference)
+  float dbs = 0.f;           // gradient w.r.t. b^{r+1}_lane
+#pragma unroll
+  for (int r = RT_MAX_IT - 1; r >= 0; --r) {
+    if (r < iters) {
+      const bool last = (r == iters - 1);
+      float4 g[NV4], dch[NV4];
+      if (last) {
+#pragma unroll
+        for (int j = 0; j < NV4; ++j) g[j] = *reinterpret_cast<const float4*>(dcvec + (long long)w * H + j * 128 + lane * 4);
+      } else {
+        rt_combine<NV4>(se, dbs, g, K, lane);
+      }
+      float vg = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV4; ++j)
+        vg += chat[r][j].x * g[j].x + chat[r][j].y * g[j].y + chat[r][j].z * g[j].z + chat[r][j].w * g[j].w;
+      vg = warp_sum(vg);
+      const float f = squash_factor(sn[r]);
+      const float coef = 2.0f * squash_factor_grad(sn[r]) * vg;
+#pragma unroll
+      for (int j = 0; j < NV4; ++j)
+        dch[j] = make_float4(f * g[j].x + chat[r][j].x * coef, f * g[j].y + chat[r][j].y * coef,
+                             f * g[j].z + chat[r][j].z * coef, f * g[j].w + chat[r][j].w * coef);
+      const float dd = rt_dots<NV4>(se, dch, K, lane);
+      const float d = (lane < K) ? dsm[r] : 0.f;
+      const float dsum = warp_sum(d * dd);
+      const float db = (lane < K) ? (d * (dd - dsum) + dbs) : 0.f;
+      for (int k = 0; k < K; ++k) {
+        const float dkk = __shfl_sync(0xffffffffu, d, k), dbk = __shfl_sync(0xffffffffu, dbs, k);
+#pragma unroll
+        for (int j = 0; j < NV4; ++j) {
+          float4 val = make_float4(dkk * dch[j].x + dbk * cs[r][j].x, dkk * dch[j].y + dbk * cs[r][j].y,
+                                   dkk * dch[j].z + dbk * cs[r][j].z, dkk * dch[j].w + dbk * cs[r][j].w);
+          float4* dst = &sde[(k * NV4 + j) * 32 + lane];
+          if (!last) { const float4 o = *dst; val.x += o.x; val.y += o.y; val.z += o.z; val.w += o.w; }
+          *dst = val;
+        }
+      }
+      dbs = db;
+    }
+  }
+  __syncwarp();
+  float4* de4 = reinterpret_cast<float4*>(dehat + (long long)w * K * H);
+  for (int i = lane; i < K * NV4 * 32; i += 32) {
+    const float4 v = sde[i];
+    de4[i] = v;
+    if (dehat_bf) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+      reinterpret_cast<uint2*>(dehat_bf + (long long)w * K * H)[i] =
+          make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+    }
+  }
+}
+
+// warps per CTA (<= RT_WARPS) whose shared-memory slices fit; 0 = the fast path does not apply
+static int rt_fast_warps(int K, int H, int iters, int slices, const void* a, const void* b, const void* c, const void* d) {
+  if (H % 128 != 0 || H > 512 || iters > RT_MAX_IT) return 0;
+  if ((((uintptr_t)a | (uintptr_t)b | (uintptr_t)c) & 15) != 0 || ((uintptr_t)d & 7) != 0) return 0;
+  const size_t per_warp = (size_t)slices * K * H * sizeof(float);
+  int w = (int)((200 * 1024) / per_warp);
+  return w > RT_WARPS ? RT_WARPS : w;
+}
+
 __global__ void squash_fwd_kernel(const float* __restrict__ v, float* __restrict__ out, int rows, int H) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
   if (w >= rows) return;
@@ -203,6 +386,19 @@ extern "C" int indnet_routing_fwd(indnet_stream st_, const float* ehat, const fl
   IN_REQUIRE(K <= 32, "routing_fwd: K=%d support instances per class exceeds the warp-per-class limit of 32", K);
   if (BC == 0) return INDNET_OK;
   IN_REQUIRE(ehat && cvec, "routing_fwd: null pointer");
+  if (const int fw = rt_fast_warps(K, H, iters, 1, ehat, cvec, nullptr, cvec_bf)) {
+    const size_t fsm = (size_t)fw * K * H * sizeof(float);
+#define RT_FWD_FAST(NV4_)                                                                                          \
+    do {                                                                                                           \
+      IN_CUDA(cudaFuncSetAttribute(routing_fwd_fast_kernel<NV4_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+      routing_fwd_fast_kernel<NV4_><<<ceil_div(BC, fw), RT_WARPS * 32, fsm, st>>>(ehat, b_in, cvec, (__nv_bfloat16*)cvec_bf, \
+                                                                                 BC, K, iters, fw);                \
+    } while (0)
+    if (H == 128) RT_FWD_FAST(1); else if (H == 256) RT_FWD_FAST(2); else if (H == 384) RT_FWD_FAST(3); else RT_FWD_FAST(4);
+#undef RT_FWD_FAST
+    IN_LAUNCH_CHECK("routing_fwd_fast_kernel");
+    return INDNET_OK;
+  }
   size_t smem = sizeof(float) * RT_WARPS * (H + 32);
   IN_REQUIRE(smem <= 48 * 1024, "routing_fwd: H=%d too large", H);
   routing_fwd_kernel<<<ceil_div(BC, RT_WARPS), RT_WARPS * 32, smem, st>>>(ehat, b_in, cvec, (__nv_bfloat16*)cvec_bf, BC, K, H, iters);
@@ -218,6 +414,19 @@ extern "C" int indnet_routing_bwd(indnet_stream st_, const float* ehat, const fl
   IN_REQUIRE(iters <= 30, "routing_bwd: too many routing iterations (%d)", iters);
   if (BC == 0) return INDNET_OK;
   IN_REQUIRE(ehat && dcvec && dehat, "routing_bwd: null pointer");
+  if (const int fw = rt_fast_warps(K, H, iters, 2, ehat, dcvec, dehat, dehat_bf)) {
+    const size_t fsm = (size_t)fw * 2 * K * H * sizeof(float);
+#define RT_BWD_FAST(NV4_)                                                                                          \
+    do {                                                                                                           \
+      IN_CUDA(cudaFuncSetAttribute(routing_bwd_fast_kernel<NV4_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+      routing_bwd_fast_kernel<NV4_><<<ceil_div(BC, fw), RT_WARPS * 32, fsm, st>>>(ehat, b_in, dcvec, dehat,           \
+                                                                                 (__nv_bfloat16*)dehat_bf, BC, K, iters, fw); \
+    } while (0)
+    if (H == 128) RT_BWD_FAST(1); else if (H == 256) RT_BWD_FAST(2); else if (H == 384) RT_BWD_FAST(3); else RT_BWD_FAST(4);
+#undef RT_BWD_FAST
+    IN_LAUNCH_CHECK("routing_bwd_fast_kernel");
+    return INDNET_OK;
+  }
   size_t smem = sizeof(float) * RT_WARPS * ((size_t)(2 * iters + 2) * H + (iters + 2) * 32);
   IN_REQUIRE(smem <= 227 * 1024, "routing_bwd: H=%d x iters=%d does not fit shared memory", H, iters);
   if (smem > 48 * 1024)

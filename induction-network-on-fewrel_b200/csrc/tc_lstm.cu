@@ -142,7 +142,10 @@ struct LstmTcP {
 
 // DROP: DropoutWrapper(output_keep_prob) on the emitted h (the recurrent h stays un-dropped).
 // SAVE: also emit what BPTT needs (gates, c, h_{t-1}); off for inference.
-template <bool DROP, bool SAVE>
+// NHALF: 2 = a CTA owns 32 sentences as two phase-shifted halves (full chip); 1 = 16 sentences, no overlap but half
+// the gate work per step - the host picks it when that still fits the chip in one wave (small batches are pure
+// per-step latency).
+template <bool DROP, bool SAVE, int NHALF>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmHout,
                    const __grid_constant__ CUtensorMap tmHprev, const __grid_constant__ CUtensorMap tmC,
@@ -159,7 +162,8 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const bool gate_warp = warp < LT_GATE_THREADS / 32;
   const int dir = blockIdx.y;
-  const int x0 = blockIdx.x * LT_NS;
+  constexpr int NS = LT_NH * NHALF;
+  const int x0 = blockIdx.x * NS;
   const int L = p.L;
 
   // h_{-1} = 0: the B operand of step 0 (buffer 1 of each half); the other tiles are written before they are read
@@ -208,13 +212,13 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     constexpr uint32_t idesc = idesc_bf16(128, LT_NH, false, false);
     auto tn = [&](int s) { return dir ? (L - 1 - s) : s; };
     auto load_x = [&](int s) {
-      mbar_expect_tx(&x_full[s % LT_XBUFS], LT_X_BYTES);
+      mbar_expect_tx(&x_full[s % LT_XBUFS], NS * 128);
       tma_load_3d(smem + LT_OFF_X + (s % LT_XBUFS) * LT_X_BYTES, &tmX, &x_full[s % LT_XBUFS], 0, tn(s), x0);
     };
     if (elect_one()) {
       for (int s = 0; s < LT_XBUFS && s < L; ++s) load_x(s);
       if (SAVE) {             // h_{t-1} of the first step is zero
-        for (int h = 0; h < 2; ++h)
+        for (int h = 0; h < NHALF; ++h)
           for (int kb = 0; kb < 2; ++kb)
             tma_store_4d(&tmHprev, sH_s + (h * 2 + 1) * LT_H_BYTES + kb * (LT_NH * 128), kb * 64, tn(0), x0 + h * LT_NH, dir);
         bulk_commit();
@@ -223,7 +227,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     __syncwarp();
     for (int s = 0; s <= L; ++s) {
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < NHALF; ++h) {
         if (s > 0) {
           mbar_wait_wd(&h_ready[h], (s - 1) & 1);       // gate threads published step s-1 of this half, drained its accumulators
           tc_fence_after();
@@ -233,7 +237,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
           // tiles of step s-2 (same buffers as step s) must have been read by their stores before the gate
           // threads may overwrite them, i.e. before this step's MMAs are committed
           // (the prologue's zero tile of half 0 has only one younger group at s = 1: wait for everything there)
-          if (s == 1 && h == 0) bulk_wait_read<0>();
+          if (NHALF == 1 || (s == 1 && h == 0)) { if (s > 0) bulk_wait_read<0>(); }
           else if (s > 0) bulk_wait_read<1>();
           if (s < L) {
             const uint32_t xb16 = (sX_s + (s % LT_XBUFS) * LT_X_BYTES + h * (LT_NH * 128)) >> 4;
@@ -267,7 +271,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
             }
             bulk_commit();
             // both halves of step s-1 have consumed x_{s-1}: its slot takes x_{s-1+XBUFS}
-            if (h == 1 && s - 1 + LT_XBUFS < L) load_x(s - 1 + LT_XBUFS);
+            if (h == NHALF - 1 && s - 1 + LT_XBUFS < L) load_x(s - 1 + LT_XBUFS);
           }
         }
         __syncwarp();
@@ -312,7 +316,7 @@ tc_lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     for (int s = 0; s < L; ++s) {
       const int b = s & 1;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < NHALF; ++h) {
         mbar_wait_wd(&mma_done[h], s & 1);
         tc_fence_after();
         LT_MARK(threadIdx.x == 0, s, h * 4 + 0);
@@ -391,7 +395,7 @@ struct LstmTcBwdP {
   float keep_prob; unsigned long long seed; const long long* seed_step;
 };
 
-template <bool DROP, bool DX>
+template <bool DROP, bool DX, int NHALF>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmC,
                    const __grid_constant__ CUtensorMap tmDh, const __grid_constant__ CUtensorMap tmDz,
@@ -413,7 +417,8 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const bool gate_warp = warp < LT_GATE_THREADS / 32;
   const int dir = blockIdx.y;
-  const int x0 = blockIdx.x * LT_NS;
+  constexpr int NS = LT_NH * NHALF;
+  const int x0 = blockIdx.x * NS;
   const int L = p.L;
   auto tb = [&](int step) { return dir ? step : (L - 1 - step); };     // BPTT walks the processing order backwards
 
@@ -492,12 +497,12 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       if (more) tma_load_4d(dst + LB_IN_G + LB_IN_D, &tmC, bar, 0, tb(step + 1), xs, dir);
     };
     if (elect_one()) {
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < NHALF; ++h) {
         mbar_expect_tx(&c0_full[h], LB_IN_C);
         tma_load_4d(smem + LB_OFF_C0 + h * LB_IN_C, &tmC, &c0_full[h], 0, tb(0), x0 + h * LT_NH, dir);
       }
       for (int step = 0; step < 2 && step < L; ++step)
-        for (int h = 0; h < 2; ++h) load_in(step, h);
+        for (int h = 0; h < NHALF; ++h) load_in(step, h);
     }
     __syncwarp();
     if (DX) mbar_wait_wd(wx_full, 0);
@@ -512,7 +517,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       float* tile = reinterpret_cast<float*>(sDx + (step_done & 1) * LB_DXT_BYTES);
       if (lane < LB_DX_LD) {
 #pragma unroll
-        for (int q = 0; q < LT_NS; ++q) tile[q * LB_DX_LD + lane] = v[q];
+        for (int q = 0; q < NS; ++q) tile[q * LB_DX_LD + lane] = v[q];
       }
       fence_proxy_async();
       tc_fence_before();
@@ -525,7 +530,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     };
     for (int step = 0; step < L; ++step) {
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < NHALF; ++h) {
         mbar_wait_wd(&z_ready[h], step & 1);      // dz(step) of this half is in its tile; its input stage is free
         tc_fence_after();
         if (elect_one()) {
@@ -543,7 +548,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
           }
         }
         __syncwarp();
-        if (h == 1) {
+        if (h == NHALF - 1) {
           // dx of the previous step has had a whole step to finish: drain it (this warp reads TMEM lanes 0..31)
           // right before this step's dx MMAs reuse the accumulator - the issuer never waits on the tensor pipe
           if (DX && step > 0) drain_dx(step - 1);
@@ -552,7 +557,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
             if (DX) {
               // once per step for both halves (N = 32): the two shared-memory K-blocks cost their 4 KB operand
               // read per instruction whatever N is
-              constexpr uint32_t idesc32 = idesc_bf16(128, LT_NS, false, false);
+              constexpr uint32_t idesc32 = idesc_bf16(128, NS, false, false);
               const uint32_t zf16 = zsrc >> 4;
 #pragma unroll
               for (int kk = 0; kk < 4 * LB_KB; ++kk) {
@@ -618,7 +623,7 @@ tc_lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     for (int step = 0; step < L; ++step) {
       const bool more = step + 1 < L;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < NHALF; ++h) {
         const uint32_t in_s = sIn_s + (uint32_t)(h * 2 + (step & 1)) * LB_IN_BYTES;
         mbar_wait_wd(&in_full[h * 2 + (step & 1)], (step >> 1) & 1);
         LB_MARK(threadIdx.x == 0, step, h * 4 + 0);
@@ -755,7 +760,10 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
                                                                                     (__nv_bfloat16*)wt_scratch, D);
   IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
   CUtensorMap tmX, tmHout, tmHprev, tmC, tmG;
-  int rc = map_tok(&tmX, x_bf, LT_KX, X, L, LT_KX, LT_NS, true);
+  // one wave of 16-sentence CTAs when the batch is small enough, else 32-sentence CTAs with phase-shifted halves
+  const int nhalf = (2 * ceil_div(X, LT_NH) <= 148) ? 1 : 2;
+  const int ns = LT_NH * nhalf;
+  int rc = map_tok(&tmX, x_bf, LT_KX, X, L, LT_KX, ns, true);
   if (rc) return rc;
   rc = map_tok(&tmHout, hout_bf, 2 * LT_U, X, L, 64, LT_NH, true);
   if (rc) return rc;
@@ -771,19 +779,21 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   LstmTcP p;
   p.X = X; p.L = L; p.keep_prob = keep_prob; p.seed = seed; p.seed_step = seed_step;
   p.wt = (const __nv_bfloat16*)wt_scratch;
-  dim3 grid(ceil_div(X, LT_NS), 2);
+  dim3 grid(ceil_div(X, ns), 2);
   const bool drop = keep_prob < 1.0f;
-#define LT_FWD_LAUNCH(DROP_, SAVE_)                                                                             \
+#define LT_FWD_LAUNCH2(DROP_, SAVE_, NH_)                                                                       \
   do {                                                                                                          \
     /* per device and cheap: set on every launch (legal during stream capture) */                                 \
-    IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel<DROP_, SAVE_>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_fwd_kernel<DROP_, SAVE_, NH_>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  LT_SMEM));                                                                     \
-    tc_lstm_fwd_kernel<DROP_, SAVE_><<<grid, LT_THREADS, LT_SMEM, st>>>(tmX, tmHout, tmHprev, tmC, tmG, p);       \
+    tc_lstm_fwd_kernel<DROP_, SAVE_, NH_><<<grid, LT_THREADS, LT_SMEM, st>>>(tmX, tmHout, tmHprev, tmC, tmG, p);  \
   } while (0)
+#define LT_FWD_LAUNCH(DROP_, SAVE_) do { if (nhalf == 1) LT_FWD_LAUNCH2(DROP_, SAVE_, 1); else LT_FWD_LAUNCH2(DROP_, SAVE_, 2); } while (0)
   if (drop && save) LT_FWD_LAUNCH(true, true);
   else if (drop) LT_FWD_LAUNCH(true, false);
   else if (save) LT_FWD_LAUNCH(false, true);
   else LT_FWD_LAUNCH(false, false);
+#undef LT_FWD_LAUNCH2
 #undef LT_FWD_LAUNCH
   IN_LAUNCH_CHECK("tc_lstm_fwd_kernel");
   return INDNET_OK;
@@ -815,12 +825,14 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
   if (rc) return rc;
   rc = map_tok(&tmDh, dhout_bf, 2 * LT_U, X, L, LT_U, LT_NH, false);
   if (rc) return rc;
-  rc = map_dir_tok(&tmDz, dz_bf, 2, 4 * LT_U, X, L, 64, true, LT_NS);
+  const int nhalf = (2 * ceil_div(X, LT_NH) <= 148) ? 1 : 2;
+  const int ns = LT_NH * nhalf;
+  rc = map_dir_tok(&tmDz, dz_bf, 2, 4 * LT_U, X, L, 64, true, ns);
   if (rc) return rc;
   CUtensorMap tmDx;
   tmXf = tmXb = tmDx = tmDh;
   if (dx2) {
-    rc = map_dir_tok(&tmDx, dx2, 4, LB_DX_LD, X, L, LB_DX_LD, false, LT_NS);
+    rc = map_dir_tok(&tmDx, dx2, 4, LB_DX_LD, X, L, LB_DX_LD, false, ns);
     if (rc) return rc;
     IN_REQUIRE(dx_first >= 0 && dx_first < D && D - dx_first <= LB_DX_LD,
                "lstm_bwd_tc: the fused input gradient covers at most %d features (got first=%d of D=%d)", LB_DX_LD, dx_first, D);
@@ -834,19 +846,21 @@ extern "C" int indnet_lstm_bwd_tc(indnet_stream st_, const void* dhout_bf, const
     rc = make_tmap_bf16(&tmXb, xb, 4 * LT_U, D + LT_U - dx_first, 4 * LT_U, 1, 0, 64, 128);
     if (rc) return rc;
   }
-  dim3 grid(ceil_div(X, LT_NS), 2);
+  dim3 grid(ceil_div(X, ns), 2);
   const bool drop = keep_prob < 1.0f;
-#define LB_LAUNCH(DROP_, DX_)                                                                                   \
+#define LB_LAUNCH2(DROP_, DX_, NH_)                                                                             \
   do {                                                                                                          \
     const int smem = DX_ ? LB_SMEM_DX : LB_SMEM_NODX;                                                           \
-    IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
-    tc_lstm_bwd_kernel<DROP_, DX_><<<grid, LT_THREADS, smem, st>>>(tmG, tmC, tmDh, tmDz, tmXf, tmXb, tmDx, p);          \
+    IN_CUDA(cudaFuncSetAttribute(tc_lstm_bwd_kernel<DROP_, DX_, NH_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+    tc_lstm_bwd_kernel<DROP_, DX_, NH_><<<grid, LT_THREADS, smem, st>>>(tmG, tmC, tmDh, tmDz, tmXf, tmXb, tmDx, p);  \
   } while (0)
+#define LB_LAUNCH(DROP_, DX_) do { if (nhalf == 1) LB_LAUNCH2(DROP_, DX_, 1); else LB_LAUNCH2(DROP_, DX_, 2); } while (0)
   if (drop && dx2) LB_LAUNCH(true, true);
   else if (drop) LB_LAUNCH(true, false);
   else if (dx2) LB_LAUNCH(false, true);
   else LB_LAUNCH(false, false);
 #undef LB_LAUNCH
+#undef LB_LAUNCH2
   IN_LAUNCH_CHECK("tc_lstm_bwd_kernel");
   return INDNET_OK;
 }

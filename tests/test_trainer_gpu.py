@@ -76,8 +76,10 @@ def test_graph_replay_equals_eager_launches(mode):
         res.append((losses, pipe.p.params.clone()))
         assert (tr.graph_step is not None) == graph
         tr.close()
-    assert res[0][0] == res[1][0]
-    assert torch.equal(res[0][1], res[1][1])
+    # same kernels in the same order; split-K / scatter reductions use float atomics, so equality is up to
+    # their summation order
+    np.testing.assert_allclose(res[0][0], res[1][0], rtol=2e-4 if mode == "fp32" else 2e-2)
+    assert float((res[0][1] - res[1][1]).abs().max()) < (2e-5 if mode == "fp32" else 5e-3)
 
 
 def test_base_train_fast_path_prints_the_reference_lines_and_logs_scalars(tmp_path, capsys):
