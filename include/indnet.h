@@ -175,6 +175,14 @@ int indnet_lstm_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_f
                        void* gates_bf, void* cstate_bf, void* hprev_bf, int X, int L, int D, int u, float keep_prob,
                        unsigned long long seed, const long long* seed_step);
 
+/* hidden_size 256 (BASELINE configs[4], the encoder + induction inference sweep): forward only, a cluster of four
+ * CTAs per 32- or 64-sentence tile, each holding a quarter of the gate rows in tensor memory and exchanging h
+ * through distributed shared memory (csrc/tc_lstm256.cu).  Same inputs as indnet_lstm_fwd_tc; wt_scratch bf16
+ * [2][4u][320]; writes hout_bf [X][L][2u] bf16 only (eval: no dropout, no BPTT streams).  E+10 <= 62. */
+int indnet_lstm256_fwd_tc(indnet_stream st, const void* x_bf, const float* kernel_fw, const float* bias_fw,
+                          const float* kernel_bw, const float* bias_bw, void* wt_scratch, void* hout_bf, int X, int L,
+                          int D, int u);
+
 /* bf16 tensor-core mode of indnet_lstm_bwd (hidden_size 128): gates_bf [2][X][L][u][4] and cstate_bf as
  * saved by indnet_lstm_fwd_tc; kernel_*_bf = bf16 copies of the TF LSTM kernels [D+u][4u] (W_h = rows
  * D.., staged into tensor memory, no scratch); dhout_bf [X][L][2u] bf16 (see indnet_tc_gemm_rank1).

@@ -259,23 +259,29 @@ class EpisodePipeline:
         self.word, self.pos1, self.pos2, self.mask = (i32(c.B, c.n_s, c.L) for _ in range(4))
         self.label = i32(c.B, c.n_q)
         # forward activations
-        self.x = f(c.T, c.D)
-        self.xproj = f(2, c.T, 4 * c.u)
-        self.hout = f(c.T, c.H)
-        self.gates = f(2, c.T, 4 * c.u)
-        self.cstate = f(2, c.T, c.u)
-        self.hprev = f(2, c.T, c.u)
-        self.proj = f(c.T, c.H)
+        inf = bool(cfg.inference)
+        if inf and not (cfg.mode == "bf16" and c.u in (128, 256) and c.D <= 62):
+            raise ValueError("inference=True pipelines run the tcgen05 encoder only: mode='bf16', hidden_size 128 or 256, "
+                             "E + 10 <= 62")
+        if not inf:      # fp32 activations: the FFMA parity mode, and the generic-width fallback of the bf16 mode
+            self.x = f(c.T, c.D)
+            self.xproj = f(2, c.T, 4 * c.u)
+            self.hout = f(c.T, c.H)
+            self.gates = f(2, c.T, 4 * c.u)
+            self.cstate = f(2, c.T, c.u)
+            self.hprev = f(2, c.T, c.u)
+            self.proj = f(c.T, c.H)
         self.alphas = f(c.X, c.L)
         self.es = f(c.B, c.NK, c.H)          # support encodings (model/graph.py:57-58)
         self.eq = f(c.B, c.n_q, c.H)         # query encodings   (model/graph.py:60-62)
         self.ehat = f(c.B * c.NK, c.H)
         self.cvec = f(c.B * c.N, c.H)
-        self.Tp = f(c.B * c.N, c.S * c.H)
-        self.V = f(c.B * c.n_q, c.N * c.S)
-        self.probs = f(c.B, c.n_q, c.N)
-        self.loss_part = f(c.B * c.n_q)
-        self.correct = i32(c.B * c.n_q)
+        if not inf:
+            self.Tp = f(c.B * c.N, c.S * c.H)
+            self.V = f(c.B * c.n_q, c.N * c.S)
+            self.probs = f(c.B, c.n_q, c.N)
+            self.loss_part = f(c.B * c.n_q)
+            self.correct = i32(c.B * c.n_q)
         self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
         self.running = torch.zeros(3, dtype=torch.float32, device=self.dev)   # training-step sums {loss, accuracy, steps}
         self._bwd_ready = False
@@ -291,14 +297,18 @@ class EpisodePipeline:
             self.proj_bf = h(c.T, c.H)
             self.es_bf = h(c.B * c.NK, c.H)
             self.cvec_bf = h(c.B * c.N, c.H)
-            self.hprev_bf = h(2, c.T, c.u)
             self.eq_bf = h(c.B * c.n_q, c.H)
-            self.Tp_bf = h(c.B * c.N, c.S * c.H)
+            if not inf:
+                self.hprev_bf = h(2, c.T, c.u)
+                self.Tp_bf = h(c.B * c.N, c.S * c.H)
             self.NSp = (c.N * c.S + 7) // 8 * 8          # dV rows padded to 16 bytes for TMA
             # the persistent tcgen05 recurrence is specialised for u = 128; its bias rides in two spare x columns
             self.tc_lstm = (c.u == 128 and c.D <= 62)
-            if self.tc_lstm:
+            # hidden_size 256: forward-only cluster kernel (eval / inference); training at 256 takes the generic path
+            self.tc_lstm256 = (c.u == 256 and c.D <= 62)
+            if self.tc_lstm or self.tc_lstm256:
                 self.wt_bf = h(2, 4 * c.u, 64 + c.u)
+            if self.tc_lstm and not inf:
                 self.gates_bf = h(2, c.T, 4 * c.u)
                 self.cstate_bf = h(2, c.T, c.u)
 
@@ -437,11 +447,16 @@ class EpisodePipeline:
         self._call("indnet_embed_fwd_bf16", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(wt),
                    ptr(p.view("pos1_embedding")), ptr(p.view("pos2_embedding")), ptr(self.x_bf), c.T, c.E, POS_DIM)
         if self.tc_lstm:
-            # input projection + recurrence + gates in one persistent tcgen05 kernel
+            # input projection + recurrence + gates in one persistent tcgen05 kernel; eval / inference runs skip the
+            # BPTT streams (gates, c, h_prev)
+            save = train and not c.inference
             self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
                        ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), None, ptr(self.hout_bf),
-                       ptr(self.gates_bf), ptr(self.cstate_bf), ptr(self.hprev_bf), c.X, c.L, c.D, c.u,
-                       keep, self.seed, ptr(p.global_step))
+                       ptr(self.gates_bf) if save else None, ptr(self.cstate_bf) if save else None,
+                       ptr(self.hprev_bf) if save else None, c.X, c.L, c.D, c.u, keep, self.seed, ptr(p.global_step))
+        elif self.tc_lstm256 and not train:
+            self._call("indnet_lstm256_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
+                       ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), ptr(self.hout_bf), c.X, c.L, c.D, c.u)
         else:
             for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
                 # K = D exactly: TMA zero-fills the padded x columns and never reads kernel rows past W_x

@@ -318,3 +318,39 @@ def test_bf16_mode_rejects_unsupported_shapes():
     cfg, tables, inputs, label, params = make_case("ragged", seed=3, mode="bf16")   # u = 13
     with pytest.raises(ValueError, match="bf16 tensor-core mode needs"):
         build_pipeline(cfg, tables, params)
+
+
+@pytest.mark.parametrize("shape", [dict(N=3, K=2, Q=2, B=2, L=9), dict(N=5, K=1, Q=5, B=40, L=6), dict(N=4, K=3, Q=5, B=3, L=33)])
+def test_hidden_size_256_cluster_recurrence_inference_parity(shape):
+    """BASELINE configs[4] width (u = 256): the four-CTA cluster recurrence (tc_lstm256.cu) - both tile sizes,
+    partial tiles, several clusters - through encoder + induction against the float64 oracle."""
+    from induction_b200.engine import EpisodeConfig, EpisodePipeline, ParamStore, init_tf_params, tf_param_shapes
+    from induction_b200.util.synthetic import make_tables
+    from oracle import induction_oracle as orc
+    cfg = EpisodeConfig(E=50, u=256, S=8, mode="bf16", inference=True, **shape)
+    tables = make_tables(12, 30, cfg.L, 500, cfg.E, seed=2, min_len=min(3, cfg.L))
+    rs = np.random.RandomState(4)
+    rows = rs.randint(0, 12 * 30, size=(cfg.B, cfg.n_s))
+    inputs = {k: tables[k][rows] for k in ("word", "pos1", "pos2", "mask")}
+    label = rs.randint(0, cfg.N, size=(cfg.B, cfg.n_q))
+    params = init_tf_params(tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S), seed=1)
+    g = torch.Generator().manual_seed(9)
+    for k in params:
+        if k.endswith("bias"):
+            params[k] = (torch.randn(params[k].shape, generator=g) * 0.05).float()
+    store = ParamStore(tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S))
+    store.load_state_dict(params)
+    pipe = EpisodePipeline(cfg, store, torch.from_numpy(tables["word_vec_mat"]))
+    assert pipe.tc_lstm256
+    pipe.set_inputs(inputs, label)
+    pipe.encode(train=False)
+    pipe.induction()
+    torch.cuda.synchronize()
+    ref = oracle_forward(cfg, tables, inputs, label, params, dtype=torch.float64)
+    e_h = rel_err(pipe.hout_bf.float().view(cfg.X, cfg.L, cfg.H), ref["hout"])
+    e_enc = rel_err(torch.cat([pipe.es, pipe.eq], dim=1), ref["encoder"])
+    e_cv = rel_err(pipe.cvec.view(cfg.B, cfg.N, cfg.H), ref["class_vector"])
+    print(shape, "hout", e_h, "encoder", e_enc, "class_vector", e_cv)
+    assert e_h < BF16_TOL and e_enc < BF16_TOL and e_cv < BF16_TOL
+    with pytest.raises(Exception, match="inference"):
+        pipe.relation()
