@@ -229,6 +229,14 @@ int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* den
  * receive bf16 copies of the encodings in the same split layout; dw2_sum / dsum_sum [H] (optional, H % 8 == 0)
  * receive the sums over sentences of dw2_part / dsum_part directly (the W_a2 and Dense-bias gradients), in
  * which case the partial buffers may be NULL.  Everything else as above. */
+/* The whole attention block in one kernel (csrc/attn_fused.cu): tcgen05 GEMM h*Wa1 with bias + tanh + the dot with
+ * w_a2 taken while the accumulator is drained, masked softmax and weighted sum inside the same CTA (a CTA owns
+ * floor(128 / L) whole sentences).  wa1_bf = bf16 copy of the Dense kernel [H][H] (TF layout [in][out]); proj_bf
+ * (optional) receives tanh(h*Wa1 + ba1) in bf16 for the backward pass.  L <= 128; H a multiple of 64 up to 256, or
+ * 512 / 768 / 1024.  Outputs as indnet_attn_pool_fwd_bf16. */
+int indnet_attn_fused_fwd(indnet_stream st, const void* hout_bf, const void* wa1_bf, const float* ba1, const float* w_a2,
+                          const int* mask, void* proj_bf, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
+                          float* alphas, int X, int L, int H, int group, int split);
 int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
                               const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
                               float* alphas, int X, int L, int H, int group, int split);

@@ -294,7 +294,11 @@ class EpisodePipeline:
             h = lambda *s: torch.zeros(*s, dtype=torch.bfloat16, device=self.dev)  # noqa: E731
             self.x_bf = h(c.T, 64)
             self.hout_bf = h(c.T, c.H)
-            self.proj_bf = h(c.T, c.H)
+            import os as _os
+            self.fused_attn = (c.L <= 128 and c.H % 64 == 0 and (c.H <= 256 or c.H % 256 == 0) and c.H <= 1024
+                               and not _os.environ.get("INDNET_NO_FUSED_ATTN"))
+            if not (inf and self.fused_attn):
+                self.proj_bf = h(c.T, c.H)
             self.es_bf = h(c.B * c.NK, c.H)
             self.cvec_bf = h(c.B * c.N, c.H)
             self.eq_bf = h(c.B * c.n_q, c.H)
@@ -468,11 +472,18 @@ class EpisodePipeline:
                        ptr(self.cstate), ptr(self.hprev), c.X, c.L, c.u, keep, self.seed, ptr(p.global_step))
             self._cast(self.hout, self.hout_bf, "hout")
             self._cast(self.hprev, self.hprev_bf, "hprev")
-        self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, Cb=self.proj_bf, bias=p.view(ATT_B),
-                 act=1, tag="attn_dense")
-        self._call("indnet_attn_pool_fwd_bf16", ptr(self.hout_bf), ptr(self.proj_bf), ptr(self.mask),
-                   ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.es_bf), ptr(self.eq_bf), ptr(self.alphas),
-                   c.X, c.L, c.H, c.n_s, c.NK)
+        if self.fused_attn:
+            # Dense + tanh + score + masked softmax + weighted sum in one kernel; proj is kept only for the backward
+            self._call("indnet_attn_fused_fwd", ptr(self.hout_bf), ptr(p.view_bf(ATT_K)), ptr(p.view(ATT_B)),
+                       ptr(p.view(ATT_W2)), ptr(self.mask), ptr(self.proj_bf) if (train and not c.inference) else None,
+                       ptr(self.es), ptr(self.eq), ptr(self.es_bf), ptr(self.eq_bf), ptr(self.alphas),
+                       c.X, c.L, c.H, c.n_s, c.NK)
+        else:
+            self._tc(0, 1, c.T, c.H, c.H, self.hout_bf, c.H, p.view_bf(ATT_K), c.H, Cb=self.proj_bf, bias=p.view(ATT_B),
+                     act=1, tag="attn_dense")
+            self._call("indnet_attn_pool_fwd_bf16", ptr(self.hout_bf), ptr(self.proj_bf), ptr(self.mask),
+                       ptr(p.view(ATT_W2)), ptr(self.es), ptr(self.eq), ptr(self.es_bf), ptr(self.eq_bf), ptr(self.alphas),
+                       c.X, c.L, c.H, c.n_s, c.NK)
         self._last_keep = keep
 
     def _induction_bf16(self):
