@@ -237,6 +237,14 @@ int indnet_attn_pool_bwd(indnet_stream st, const float* denc_a, const float* den
 int indnet_attn_fused_fwd(indnet_stream st, const void* hout_bf, const void* wa1_bf, const float* ba1, const float* w_a2,
                           const int* mask, void* proj_bf, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
                           float* alphas, int X, int L, int H, int group, int split);
+/* Backward of the attention block up to d(loss)/d(h) in one kernel (H a multiple of 64 up to 256, L <= 128): softmax /
+ * weighted-sum / score / tanh backward on the CUDA cores, dpre written in place as the A operand of the tcgen05 GEMM
+ * dpre * Wa1^T, the pooling-path term alpha_t * denc added in the epilogue.  Writes dpre_bf [X*L][H] (operand of the
+ * Dense-kernel gradient GEMM), dhout_bf [X*L][H], and the W_a2 / Dense-bias gradients dw2_sum / dba_sum [H]
+ * (overwritten).  Autodiff of model/layer_module.py:65-96. */
+int indnet_attn_fused_bwd(indnet_stream st, const float* denc_a, const float* denc_b, const void* hout_bf,
+                          const void* proj_bf, const float* alphas, const float* w_a2, const void* wa1_bf, void* dpre_bf,
+                          void* dhout_bf, float* dw2_sum, float* dba_sum, int X, int L, int H, int group, int split);
 int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
                               const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
                               float* alphas, int X, int L, int H, int group, int split);

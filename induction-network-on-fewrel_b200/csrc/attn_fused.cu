@@ -39,8 +39,7 @@ __device__ __forceinline__ float af_tanh(float x) {
 
 __global__ void __launch_bounds__(AF_THREADS, 2)
 attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AttnFusedP p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];       // declared alignment keeps the shared address space visible (LDS / STS)
   const int B_BYTES = p.NP * AF_BK * 2;                 // NP / 64 boxes of 8 KB
   uint8_t* sA = smem;
   uint8_t* sB = smem + AF_STAGES * AF_A_BYTES;
@@ -248,9 +247,355 @@ extern "C" int indnet_attn_fused_fwd(indnet_stream st_, const void* hout_bf, con
   if (rc) return rc;
   rc = make_tmap_bf16(&tmB, wa1_bf, H, H, H, 1, 0, 64, AF_BK);                              // [K][N]: box 64 n x 64 k
   if (rc) return rc;
-  const int smem = AF_STAGES * (AF_A_BYTES + p.NP * AF_BK * 2) + (2 * H + 2 * AF_BM) * 4 + 128 + 1024;
+  const int smem = AF_STAGES * (AF_A_BYTES + p.NP * AF_BK * 2) + (2 * H + 2 * AF_BM) * 4 + 128;
   IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   attn_fused_fwd_kernel<<<ceil_div(X, p.spt), AF_THREADS, smem, st>>>(tmA, tmB, p);
   IN_LAUNCH_CHECK("attn_fused_fwd_kernel");
+  return INDNET_OK;
+}
+
+namespace indnet {
+
+// ------------------------------------------------------------------------------------------------
+// Backward of the attention block up to d(loss)/d(h), one kernel (H a multiple of 64, <= 256):
+//   dalpha_t = denc . h_t ; dscore_t = alpha_t (dalpha_t - sum_s alpha_s dalpha_s)          (softmax + weighted sum)
+//   dpre[t]  = dscore_t * w2 * (1 - proj_t^2) ; dw2 += dscore_t proj_t ; dba += dpre[t]     (score, tanh, bias)
+//   dh[t]    = alpha_t * denc + dpre[t] * Wa1^T                                              (pooling path + Dense path)
+// A CTA owns floor(128 / L) whole sentences.  h and proj tiles arrive by TMA (swizzled K-major tiles); dpre is
+// written IN PLACE over the proj tile, which makes it the A operand of the tcgen05 GEMM dpre * Wa1^T (B = the bf16
+// Dense kernel itself: [in][out] row-major is a K-major operand for this product), streamed through the shared
+// memory the h tile no longer needs.  dpre also goes to HBM once (bf16) for the Dense-kernel gradient GEMM.
+constexpr int AB_THREADS = 512;         // 16 row groups: the CUDA-core phases are latency bound, more warps hide it
+constexpr int AB_RG = AB_THREADS / 32;
+#ifdef INDNET_ATTN_TIMELINE
+__device__ long long g_attn_dbg[16 * 8];
+#define AB_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 0 && it < 16) g_attn_dbg[it * 8 + (k)] = clock64(); } while (0)
+#else
+#define AB_MARK(k) do { } while (0)
+#endif
+constexpr int AB_TILE = AF_BM * 256 * 2;          // 64 KB: one [128 x 256] bf16 tile as 4 K-blocks of 16 KB
+constexpr int AB_W_BYTES = 256 * 128;             // one K-block of Wa1: [<= 256 rows (in)][64 k (out)]
+
+struct AttnFusedBwdP {
+  const float* denc_a; const float* denc_b; const float* alphas; const float* w2;
+  const __nv_bfloat16* h;
+  __nv_bfloat16* dpre; __nv_bfloat16* dh;
+  float* dw2; float* dba;
+  int X, L, H, group, split, spt;
+};
+
+__device__ __forceinline__ void unpack8f(const uint4& q, float* f) {
+  f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xFFFF0000u);
+  f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xFFFF0000u);
+  f[4] = __uint_as_float(q.z << 16); f[5] = __uint_as_float(q.z & 0xFFFF0000u);
+  f[6] = __uint_as_float(q.w << 16); f[7] = __uint_as_float(q.w & 0xFFFF0000u);
+}
+__device__ __forceinline__ uint32_t pack2f(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Persistent: one CTA per SM loops over tiles.  Shared memory (about 200 KB):
+//   sW   the whole bf16 Dense kernel, resident (B operand, 4 K-blocks x [256 rows (in)][64 k (out)] swizzled) - loaded
+//        once per CTA instead of once per tile, and the 16 MMAs of a tile then issue back to back
+//   sP   proj tile -> dpre tile (A operand), 4 K-blocks x [128 rows][128 B] swizzled; the NEXT tile's proj is
+//        fetched as soon as this tile's MMAs have completed, under the epilogue
+//   sDenc [spt][H], sCol [2][H] (dw2 / dba column sums of the whole CTA), sAl [128], sDa [128]
+__global__ void __launch_bounds__(AB_THREADS, 1)
+attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmW,
+                      const __grid_constant__ CUtensorMap tmDpre, const __grid_constant__ CUtensorMap tmDh, AttnFusedBwdP p,
+                      int ntiles) {
+  extern __shared__ __align__(1024) uint8_t smem[];       // declared alignment keeps the shared address space visible
+  uint8_t* sW = smem;
+  uint8_t* sP = smem + 4 * AB_W_BYTES;
+  float* sCol = reinterpret_cast<float*>(smem + 4 * AB_W_BYTES + AB_TILE);      // [2][256]
+  float* sDenc = sCol + 2 * 256;
+  const int L = p.L, H = p.H;
+  const int rows_tile = p.spt * L;
+  float* sAl = sDenc + 2 * (size_t)p.spt * H;   // [2][128] alpha          (sDenc is [2][spt][H]: this tile / next tile)
+  float* sDa = sAl + 2 * AF_BM;                 // [128] dalpha, then dscore
+  int* sSent = reinterpret_cast<int*>(sDa + AF_BM);     // [128] row -> sentence of the tile (r / L)
+  float* sPart = reinterpret_cast<float*>(sSent + AF_BM);      // [128][33] partial dalpha sums (row, chunk)
+  uint64_t* in_full = reinterpret_cast<uint64_t*>(sPart + 33 * AF_BM);      // 16896 bytes: keeps 8-byte alignment
+  uint64_t* w_full = in_full + 1;
+  uint64_t* acc_full = w_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long T = (long long)p.X * L;
+  const int KB = H / 64;
+  auto load_proj = [&](int tile) {
+    mbar_expect_tx(in_full, (uint32_t)KB * AF_A_BYTES);
+    for (int kb = 0; kb < KB; ++kb) tma_load_3d(sP + kb * AF_A_BYTES, &tmP, in_full, kb * 64, tile * rows_tile, 0);
+  };
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmP); tma_prefetch_desc(&tmW);
+    mbar_init(in_full, 1); mbar_init(w_full, 1); mbar_init(acc_full, 1);
+    fence_barrier_init();
+    mbar_expect_tx(w_full, (uint32_t)KB * H * 128);
+    for (int kb = 0; kb < KB; ++kb) tma_load_3d(sW + kb * AB_W_BYTES, &tmW, w_full, kb * 64, 0, 0);   // Wa1 [n = in][k = out]
+    if ((int)blockIdx.x < ntiles) load_proj(blockIdx.x);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  for (int i = threadIdx.x; i < 2 * 256; i += AB_THREADS) sCol[i] = 0.f;
+  for (int r = threadIdx.x; r < AF_BM; r += AB_THREADS) sSent[r] = r / L;
+  // thread = (16-byte chunk c of a row: 8 features, row group g); a warp covers one whole row per step
+  const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const bool cvalid = c < H / 8;
+  // operands that come straight from L2 / HBM are fetched one tile AHEAD (h chunks into registers right after phase A
+  // has consumed the previous ones; denc rows and alphas into the other half of their double buffers)
+  // phase A operands: coalesced (a warp reads one whole row per instruction: lane = 16-byte chunk, rows g + 16 i)
+  constexpr int AB_RPT = AF_BM / AB_RG;                    // rows per thread
+  uint4 hv[AB_RPT];
+  auto fetch_h = [&](int tile) {
+    const long long row0 = (long long)tile * rows_tile;
+#pragma unroll
+    for (int i = 0; i < AB_RPT; ++i) {
+      const int r = g + AB_RG * i;
+      const long long gr = row0 + r;
+      hv[i] = (cvalid && r < rows_tile && gr < T) ? *reinterpret_cast<const uint4*>(p.h + gr * H + c * 8) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  auto fetch_small = [&](int tile, int buf) {
+    // asynchronous global -> shared copies (no thread waits for the data here): warp s copies sentence s's upstream
+    // gradient row (H floats, 16-byte pieces), the next warp the tile's attention weights
+    const int x_first = tile * p.spt;
+    float* dD = sDenc + (size_t)buf * p.spt * H;
+    for (int s = warp; s <= p.spt; s += AB_RG) {
+      if (s < p.spt) {
+        const int x = x_first + s;
+        if (x < p.X) {
+          const int gg = x / p.group, r = x - gg * p.group;
+          const float* src = (r < p.split) ? p.denc_a + ((long long)gg * p.split + r) * H
+                                           : p.denc_b + ((long long)gg * (p.group - p.split) + (r - p.split)) * H;
+          for (int n = lane * 4; n < H; n += 128)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&dD[s * H + n])), "l"(src + n) : "memory");
+        } else {
+          for (int n = lane; n < H; n += 32) dD[s * H + n] = 0.f;
+        }
+      } else {
+        const long long row0 = (long long)tile * rows_tile;
+        for (int r = lane; r < AF_BM; r += 32) {
+          const long long gr = row0 + r;
+          if (r < rows_tile && gr < T)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&sAl[buf * AF_BM + r])), "l"(p.alphas + gr) : "memory");
+          else sAl[buf * AF_BM + r] = 0.f;
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if ((int)blockIdx.x < ntiles) { fetch_h(blockIdx.x); fetch_small(blockIdx.x, 0); }
+  float w2v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) w2v[j] = cvalid ? p.w2[c * 8 + j] : 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t taddr = *tmem_slot;
+  float dw[8], db[8];              // this thread's share of the column sums, over all its tiles
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { dw[j] = 0.f; db[j] = 0.f; }
+
+  int it = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    const long long row0 = (long long)tile * rows_tile;
+    const int buf = it & 1;
+    const float* tDenc = sDenc + (size_t)buf * p.spt * H;
+    const float* tAl = sAl + buf * AF_BM;
+    AB_MARK(0);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();               // this tile's denc / alpha (fetched one tile ago) are in shared memory
+    AB_MARK(1);
+    // ---- phase A: dalpha_r = denc[sentence(r)] . h_r.  Each thread forms the partial sum of its 8 features for its
+    // rows and parks it in shared memory ([row][33]); 128 threads then add up the 32 partials of their row - no
+    // shuffle reductions on the path
+#pragma unroll
+    for (int i = 0; i < AB_RPT; ++i) {
+      const int r = g + AB_RG * i;
+      float dot = 0.f;
+      if (cvalid && r < rows_tile) {
+        float hf[8];
+        unpack8f(hv[i], hf);
+        const float4* de4 = reinterpret_cast<const float4*>(tDenc + sSent[r] * H + c * 8);
+        const float4 d0 = de4[0], d1 = de4[1];
+        dot = hf[0] * d0.x + hf[1] * d0.y + hf[2] * d0.z + hf[3] * d0.w + hf[4] * d1.x + hf[5] * d1.y + hf[6] * d1.z + hf[7] * d1.w;
+      }
+      sPart[r * 33 + c] = dot;
+    }
+    AB_MARK(2);
+    // the next tile's operands: in flight under everything that follows
+    if (tile + (int)gridDim.x < ntiles) { fetch_h(tile + gridDim.x); fetch_small(tile + gridDim.x, buf ^ 1); }
+    __syncthreads();
+    // dscore_r = alpha_r (dalpha_r - sum_s alpha_s dalpha_s): warp s reduces sentence s with shuffles
+    for (int sw = warp; sw < p.spt; sw += AB_RG) {
+      const int sb = sw * L;
+      float da[4] = {0.f, 0.f, 0.f, 0.f}, al[4] = {0.f, 0.f, 0.f, 0.f}, part = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int t = lane + 32 * k;
+        if (t < L) {
+          const int r = sb + t;
+          float v = 0.f;
+#pragma unroll 8
+          for (int q4 = 0; q4 < 32; ++q4) v += sPart[r * 33 + q4];
+          da[k] = v; al[k] = tAl[r];
+          part = fmaf(al[k], v, part);
+        }
+      }
+      const float dsum = warp_sum(part);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int t = lane + 32 * k;
+        if (t < L) sDa[sb + t] = al[k] * (da[k] - dsum);
+      }
+    }
+    for (int r = rows_tile + threadIdx.x; r < AF_BM; r += AB_THREADS) sDa[r] = 0.f;
+    __syncthreads();
+    AB_MARK(3);
+    // ---- phase B: dpre in place over proj (bf16), its copy to HBM, and the column sums dw2 / dba
+    mbar_wait(in_full, it & 1);
+    AB_MARK(4);
+    if (cvalid) {
+      const uint32_t tile_off = (uint32_t)(c >> 3) * AF_A_BYTES, cc = (uint32_t)(c & 7);
+#pragma unroll
+      for (int i = 0; i < AF_BM / AB_RG; ++i) {
+        const int r = g + AB_RG * i;
+        uint4* slot = reinterpret_cast<uint4*>(sP + tile_off + r * 128 + ((cc ^ (uint32_t)(r & 7)) << 4));
+        float pr[8], dp[8];
+        unpack8f(*slot, pr);
+        const float ds = sDa[r];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dp[j] = ds * w2v[j] * (1.0f - pr[j] * pr[j]);
+          dw[j] = fmaf(ds, pr[j], dw[j]);
+          db[j] += dp[j];
+        }
+        const uint4 o = make_uint4(pack2f(dp[0], dp[1]), pack2f(dp[2], dp[3]), pack2f(dp[4], dp[5]), pack2f(dp[6], dp[7]));
+        *slot = o;
+      }
+    }
+    AB_MARK(5);
+    fence_proxy_async();             // dpre tile -> visible to the MMA's operand reads
+    __syncthreads();
+    AB_MARK(6);
+    // ---- dh_acc[128, H] = dpre[128, H] * Wa1^T: one thread issues 4 x KB MMAs back to back; the same tile goes to
+    // HBM (bf16, for the Dense-kernel gradient GEMM) by TMA stores of exactly this tile's rows
+    if (warp == 1 && lane == 0) {
+      tc_fence_after();
+      if (it == 0) mbar_wait(w_full, 0);
+      tc_fence_after();
+      const uint32_t idesc = idesc_bf16(AF_BM, H, false, false);
+      for (int kb = 0; kb < KB; ++kb) {
+        const uint32_t a_base = smem_u32(sP + kb * AF_A_BYTES), b_base = smem_u32(sW + kb * AB_W_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(taddr, smem_desc_sw128(a_base + k * 32, 0, 1024), smem_desc_sw128(b_base + k * 32, 0, 1024), idesc,
+                    (kb > 0 || k > 0) ? 1u : 0u);
+      }
+      umma_commit(acc_full);
+      for (int kb = 0; kb < KB; ++kb) tma_store_3d(&tmDpre, smem_u32(sP + kb * AF_A_BYTES), kb * 64, (int)row0, 0);
+      bulk_commit();
+      bulk_wait_read<0>();           // sP has been read by the stores (the MMAs are tracked by acc_full)
+    }
+    // ---- epilogue: dh = acc + alpha_r * denc[sentence(r)] -> bf16 into the (now free) A tile in the swizzled layout,
+    // then TMA stores: global stores with lane = row would touch 32 lines per instruction
+    {
+      const int q = warp & 3, half = warp >> 2;          // column group of this warp (AB_RG / 4 groups)
+      const int r = q * 32 + lane;
+      const bool valid = r < rows_tile && row0 + r < T;
+      mbar_wait(acc_full, it & 1);
+      tc_fence_after();
+      AB_MARK(7);
+      __syncthreads();               // warp 1 lane 0 has also seen its dpre stores read the tile
+      const float al = tAl[r];
+      const float* de = tDenc + (valid ? sSent[r] : 0) * H;
+      const int nchunks = H / 32;
+      for (int ch = half; ch < nchunks; ch += AB_RG / 4) {
+        float v[32];
+        tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + ch * 32, v);
+        tmem_ld_wait();
+        uint8_t* rowp = sP + (ch >> 1) * AF_A_BYTES + r * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float o[8];
+          const float4 d0 = *reinterpret_cast<const float4*>(de + ch * 32 + j * 8), d1 = *reinterpret_cast<const float4*>(de + ch * 32 + j * 8 + 4);
+          o[0] = fmaf(al, d0.x, v[j * 8 + 0]); o[1] = fmaf(al, d0.y, v[j * 8 + 1]); o[2] = fmaf(al, d0.z, v[j * 8 + 2]); o[3] = fmaf(al, d0.w, v[j * 8 + 3]);
+          o[4] = fmaf(al, d1.x, v[j * 8 + 4]); o[5] = fmaf(al, d1.y, v[j * 8 + 5]); o[6] = fmaf(al, d1.z, v[j * 8 + 6]); o[7] = fmaf(al, d1.w, v[j * 8 + 7]);
+          const uint32_t chunk16 = (uint32_t)((ch & 1) * 4 + j);
+          *reinterpret_cast<uint4*>(rowp + ((chunk16 ^ (uint32_t)(r & 7)) << 4)) =
+              make_uint4(pack2f(o[0], o[1]), pack2f(o[2], o[3]), pack2f(o[4], o[5]), pack2f(o[6], o[7]));
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        for (int kb = 0; kb < KB; ++kb) tma_store_3d(&tmDh, smem_u32(sP + kb * AF_A_BYTES), kb * 64, (int)row0, 0);
+        bulk_commit();
+        bulk_wait_read<0>();
+        // the tile is free again: fetch the next tile's proj (it lands under the next tile's phase A)
+        if (tile + (int)gridDim.x < ntiles) load_proj(tile + gridDim.x);
+      }
+    }
+  }
+  if (threadIdx.x == 0) bulk_wait_all<0>();
+  __syncthreads();
+  // ---- the CTA's column sums: shared-memory reduction over the row groups, one global atomic per column
+  if (cvalid) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { atomicAdd(&sCol[c * 8 + j], dw[j]); atomicAdd(&sCol[256 + c * 8 + j], db[j]); }
+  }
+  __syncthreads();
+  if (threadIdx.x < H) {
+    atomicAdd(p.dw2 + threadIdx.x, sCol[threadIdx.x]);
+    atomicAdd(p.dba + threadIdx.x, sCol[256 + threadIdx.x]);
+  }
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(taddr, 256); }
+}
+
+}  // namespace indnet
+
+#ifdef INDNET_ATTN_TIMELINE
+extern "C" int indnet_debug_attn(long long* out) { return (int)cudaMemcpyFromSymbol(out, indnet::g_attn_dbg, sizeof(long long) * 128); }
+#endif
+extern "C" int indnet_attn_fused_bwd(indnet_stream st_, const float* denc_a, const float* denc_b, const void* hout_bf,
+                                     const void* proj_bf, const float* alphas, const float* w_a2, const void* wa1_bf,
+                                     void* dpre_bf, void* dhout_bf, float* dw2_sum, float* dba_sum, int X, int L, int H,
+                                     int group, int split) {
+  using namespace indnet;
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(X >= 0 && L > 0 && H > 0, "attn_fused_bwd: bad sizes X=%d L=%d H=%d", X, L, H);
+  IN_REQUIRE(L <= AF_BM && H % 64 == 0 && H <= 256, "attn_fused_bwd: needs L <= 128 and H a multiple of 64 up to 256 (L=%d H=%d)", L, H);
+  IN_REQUIRE(denc_a && hout_bf && proj_bf && alphas && w_a2 && wa1_bf && dpre_bf && dhout_bf && dw2_sum && dba_sum,
+             "attn_fused_bwd: null pointer");
+  IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_fused_bwd: bad group/split %d/%d", group, split);
+  IN_REQUIRE(split == group || denc_b, "attn_fused_bwd: second gradient input missing");
+  IN_REQUIRE((((uintptr_t)dpre_bf | (uintptr_t)dhout_bf) & 15) == 0, "attn_fused_bwd: outputs must be 16-byte aligned");
+  IN_CUDA(cudaMemsetAsync(dw2_sum, 0, sizeof(float) * H, st));
+  IN_CUDA(cudaMemsetAsync(dba_sum, 0, sizeof(float) * H, st));
+  if (X == 0) return INDNET_OK;
+  AttnFusedBwdP p;
+  p.denc_a = denc_a; p.denc_b = denc_b; p.alphas = alphas; p.w2 = w_a2;
+  p.h = (const __nv_bfloat16*)hout_bf;
+  p.dpre = (__nv_bfloat16*)dpre_bf; p.dh = (__nv_bfloat16*)dhout_bf; p.dw2 = dw2_sum; p.dba = dba_sum;
+  p.X = X; p.L = L; p.H = H; p.group = group; p.split = split; p.spt = AF_BM / L;
+  IN_REQUIRE(((uintptr_t)hout_bf & 15) == 0, "attn_fused_bwd: hout_bf must be 16-byte aligned");
+  CUtensorMap tmP, tmW;
+  int rc = make_tmap_bf16(&tmP, proj_bf, H, (long long)X * L, H, 1, 0, 64, AF_BM);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmW, wa1_bf, H, H, H, 1, 0, 64, H);              // [n = in][k = out]: box 64 k x H rows (n)
+  if (rc) return rc;
+  CUtensorMap tmDpre, tmDh;
+  rc = make_tmap_bf16(&tmDpre, dpre_bf, H, (long long)X * L, H, 1, 0, 64, p.spt * L);       // box = exactly this tile's rows
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmDh, dhout_bf, H, (long long)X * L, H, 1, 0, 64, p.spt * L);
+  if (rc) return rc;
+  const int smem = AB_TILE + 4 * AB_W_BYTES + (2 * 256 + 2 * p.spt * H + (4 + 33) * AF_BM + 2) * 4 + 128;
+  IN_REQUIRE(smem <= 227 * 1024, "attn_fused_bwd: L=%d H=%d does not fit shared memory", L, H);
+  IN_CUDA(cudaFuncSetAttribute(attn_fused_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int ntiles = ceil_div(X, p.spt);
+  attn_fused_bwd_kernel<<<ntiles < 148 ? ntiles : 148, AB_THREADS, smem, st>>>(tmP, tmW, tmDpre, tmDh, p, ntiles);
+  IN_LAUNCH_CHECK("attn_fused_bwd_kernel");
   return INDNET_OK;
 }

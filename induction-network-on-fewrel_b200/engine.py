@@ -624,6 +624,13 @@ class EpisodePipeline:
         # d(loss)/d(h): pooling path alpha_t * denc + Dense path dpre * W_a1^T.  With the tensor-core LSTM the
         # sum is formed once in the GEMM epilogue and written in bf16; otherwise it is accumulated in fp32.
         fused = self.tc_lstm
+        if fused and self.fused_attn and c.H <= 256:
+            # pooling / softmax / score / tanh backward + dpre * Wa1^T + alpha_t * denc in ONE kernel
+            self._call("indnet_attn_fused_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
+                       ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(p.view_bf(ATT_K)), ptr(self.dpre_bf), ptr(self.dhout_bf),
+                       ptr(p.grad(ATT_W2)), ptr(p.grad(ATT_B)), c.X, c.L, c.H, c.n_s, c.NK)
+            self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
+            return self._backward_bf16_lstm()
         # with the 16-byte kernel variant (H % 8 == 0) the W_a2 / Dense-bias gradients are summed over sentences
         # inside the pooling kernel; otherwise per-sentence partials + two column sums
         insum = c.H % 8 == 0 and c.H <= 512
@@ -648,6 +655,11 @@ class EpisodePipeline:
         else:
             self._tc(0, 0, c.T, c.H, c.H, self.dpre_bf, c.H, p.view_bf(ATT_K), c.H, C=self.dhout, accumulate=1,
                      splitk=1, tag="attn_dh")
+        return self._backward_bf16_lstm()
+
+    def _backward_bf16_lstm(self):
+        c, p = self.cfg, self.p
+        u4 = 4 * c.u
         # with a frozen word table only the 2 x 5 position columns of dx are needed: the BPTT kernel forms
         # them itself (per direction) instead of two GEMM launches that would re-read all of dz
         import os as _os
