@@ -258,8 +258,10 @@ def run_b200(args, w):
     pipe = EpisodePipeline(cfg, store, torch.from_numpy(tables["word_vec_mat"]), seed=0)
     loader = JSONFileDataLoader.from_tables(tables)
     smp = loader._device()
-    smp.seed(0)                  # random.seed(0); np.random.seed(0) on EVERY rank: one global episode stream
-    trainer = EpisodeTrainer(pipe, smp, rank=rank, world=world, cuda_graph=not args.no_graph)
+    # --stream global: random.seed(0); np.random.seed(0) on EVERY rank = one global episode stream;
+    # --stream per-rank: rank r seeds its own streams with r (the serial walk then covers only the rank's episodes)
+    smp.seed(0 if args.stream == "global" else rank)
+    trainer = EpisodeTrainer(pipe, smp, rank=rank, world=world, cuda_graph=not args.no_graph, stream_mode=args.stream)
     trainer.prime()
     stream = trainer.stream
     POOL = 4
@@ -434,7 +436,7 @@ def run_b200(args, w):
                    "sample": "%d episodes/step x %d steps of the same workload (host next_one_tf + fwd + autograd bwd + "
                              "TF Adam; sampler %.1f %% of the time), torch-CPU fp32 oracle; reference TF 1.x unavailable "
                              "on this box" % (Bc, done, 100 * smp_share)}
-        print(json.dumps({
+        line = json.dumps({
             "metric": "train-step episodes/sec", "value": value, "unit": "episodes/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": mean_ms, "ms_per_step_median": med_ms,
             "timed_blocks": blocks, "timed_steps": blocks * args.steps,
@@ -444,7 +446,9 @@ def run_b200(args, w):
                        "global_batch": cfg.B * world, "Q": Q, "E": E, "S": S, "routing_iters": 3,
                        "keep_prob": args.keep_prob, "mode": args.mode, "vocab": VOCAB, "relations": RELS,
                        "instances_per_relation": PER_REL,
-                       "parallelism": "episode-sharded dp%d (one global sampler stream, rank r owns episodes [r*B,(r+1)*B))" % world,
+                       "parallelism": ("episode-sharded dp%d (one global sampler stream, rank r owns episodes [r*B,(r+1)*B))" % world)
+                       if args.stream == "global" else ("episode-sharded dp%d (one sampler stream per rank)" % world),
+                       "sampler_stream": args.stream,
                        "cuda_graph": trainer.graph_step is not None,
                        "l2": "256 MB buffer written between timed iterations (outside each step's event pair)",
                        "timing": "blocks of --steps graph replays repeated until >= %.1f s of GPU time; value = B / mean step time" % MIN_TIMED_S},
@@ -473,9 +477,8 @@ def run_b200(args, w):
                         "walked_episodes": trainer.global_B},
             "cpu_baseline": cpu,
             "loss_after": loss_after, "accuracy_after": acc_after,
-        }))
-        sys.stdout.flush()
-    teardown(trainer, world)
+        })
+    teardown(trainer, world, line if rank == 0 else None)
 
 
 def roofline(args, cfg, store, prof, prof_steps, peaks, clocks):
@@ -646,7 +649,7 @@ def run_inference(args, w, world, rank, local, peaks):
         dom = max(prof.items(), key=lambda kv: kv[1][1])
         tot = sum(x[1] for x in prof.values())
         ach = flops / world / (mean_ms * 1e-3) / 1e12
-        print(json.dumps({
+        line = json.dumps({
             "metric": "encoder sentences/sec", "value": value, "unit": "sentences/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": mean_ms, "ms_per_step_median": med_ms, "timed_blocks": blocks,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -666,15 +669,21 @@ def run_inference(args, w, world, rank, local, peaks):
                          "dominant_call": dom[0], "dominant_share": dom[1][1] / tot},
             "step_share": {k: round(v[1] / tot, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])[:6]},
             "cpu_baseline": None,
-        }))
-        sys.stdout.flush()
-    teardown(None, world)
+        })
+    teardown(None, world, line if rank == 0 else None)
 
 
-def teardown(trainer, world):
-    """Ordered: drain, drop the graphs, then destroy the process group.  A watchdog turns a communicator that will
-    not shut down into a plain exit instead of a hung job."""
+def teardown(trainer, world, line):
+    """Ordered: drain, drop the graphs, destroy the process group - and only then print the JSON line, so that it is
+    the LAST line on stdout even when NCCL_DEBUG=INFO makes NCCL log its shutdown there.  A watchdog turns a
+    communicator that will not shut down into a plain exit (the line is printed first) instead of a hung job."""
     import torch
+
+    def emit():
+        if line is not None:
+            print(line)
+            sys.stdout.flush()
+
     if trainer is not None:
         trainer.close()
     torch.cuda.synchronize()
@@ -683,11 +692,17 @@ def teardown(trainer, world):
         dist.barrier()
         sys.stdout.flush()
         sys.stderr.flush()
-        t = threading.Timer(30.0, lambda: os._exit(0))
+
+        def bail():
+            emit()
+            os._exit(0)
+
+        t = threading.Timer(30.0, bail)
         t.daemon = True
         t.start()
         dist.destroy_process_group()
         t.cancel()
+    emit()
 
 
 def main():
@@ -699,6 +714,9 @@ def main():
     ap.add_argument("--config", type=int, default=1, choices=sorted(WORKLOADS),
                     help="SURVEY section 8 config number (1 = 5-way 5-shot, the metric's configuration)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--stream", default="global", choices=["global", "per-rank"],
+                    help="global: one episode stream for the job, every rank walks all of it (bit-identical global batch for "
+                         "any N); per-rank: independent streams, the walk covers only the rank's own episodes")
     ap.add_argument("--mode", default="bf16", choices=["fp32", "bf16"],
                     help="bf16 = tcgen05 tensor-core mode (default); fp32 = FFMA parity mode")
     ap.add_argument("--keep-prob", type=float, default=0.9, help="LSTM output dropout as the reference trains (base.py:26,149)")

@@ -579,7 +579,8 @@ extern "C" int indnet_attn_fused_bwd(indnet_stream st_, const float* denc_a, con
   p.denc_a = denc_a; p.denc_b = denc_b; p.alphas = alphas; p.w2 = w_a2;
   p.h = (const __nv_bfloat16*)hout_bf;
   p.dpre = (__nv_bfloat16*)dpre_bf; p.dh = (__nv_bfloat16*)dhout_bf; p.dw2 = dw2_sum; p.dba = dba_sum;
-  p.X = X; p.L = L; p.H = H; p.group = group; p.split = split; p.spt = AF_BM / L;
+  p.X = X; p.L = L; p.H = H; p.group = group; p.split = split;
+  p.spt = AF_BM / L < 4 ? AF_BM / L : 4;      // sentences per tile: their upstream-gradient rows are double buffered in shared memory
   IN_REQUIRE(((uintptr_t)hout_bf & 15) == 0, "attn_fused_bwd: hout_bf must be 16-byte aligned");
   CUtensorMap tmP, tmW;
   int rc = make_tmap_bf16(&tmP, proj_bf, H, (long long)X * L, H, 1, 0, 64, AF_BM);

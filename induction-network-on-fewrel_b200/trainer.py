@@ -28,14 +28,21 @@ from .engine import EpisodePipeline
 
 class EpisodeTrainer:
     def __init__(self, pipe: EpisodePipeline, sampler=None, rank: int = 0, world: int = 1, process_group=None,
-                 cuda_graph: bool = True, overlap_allreduce: bool = True):
+                 cuda_graph: bool = True, overlap_allreduce: bool = True, stream_mode: str = "global"):
         self.pipe, self.store, self.cfg = pipe, pipe.p, pipe.cfg
         self.smp = sampler
         self.rank, self.world = int(rank), int(world)
         self.group = process_group
         self.use_graph = bool(cuda_graph)
         self.overlap = bool(overlap_allreduce) and self.world > 1
-        self.global_B = self.cfg.B * self.world
+        # "global": one episode stream for the whole job - every rank walks the draws of all world * B episodes and
+        # gathers its own B (the global batch is bit-identical for any world size, the serial walk grows
+        # with the global batch).  "per-rank": every rank owns a stream (seed it differently per rank) and walks only
+        # its own B episodes - the sampler's cost stays constant under weak scaling.
+        if stream_mode not in ("global", "per-rank"):
+            raise ValueError("stream_mode must be 'global' or 'per-rank'")
+        self.stream_mode = stream_mode
+        self.global_B = self.cfg.B * (self.world if stream_mode == "global" else 1)
         dev = pipe.dev
         # the step's own stream (high priority), the sampler's side stream (low: its table kernel fills the
         # GPU and would otherwise take SMs from the training kernels) and the communication stream
@@ -91,7 +98,8 @@ class EpisodeTrainer:
 
     def _gather(self):
         c = self.cfg
-        self.smp.enqueue_gather(self.global_B, c.N, c.K, c.Q, out=self.inputs, b0=self.rank * c.B, nb=c.B)
+        b0 = self.rank * c.B if self.stream_mode == "global" else 0
+        self.smp.enqueue_gather(self.global_B, c.N, c.K, c.Q, out=self.inputs, b0=b0, nb=c.B)
 
     def step_body(self):
         """This step's episodes = the picks drawn during the previous step; the walk for the NEXT step runs
