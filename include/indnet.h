@@ -120,6 +120,11 @@ int indnet_sample_gather(indnet_stream st, const int* scopes, const int* t_word,
  * changes the scratch layout, so set it before the first indnet_sampler_scratch_bytes.  Used by the tests to
  * force status 3. */
 int indnet_sampler_set_budget(double pct, long long slack);
+/* 1 (default): the parallel path - "where does a permutation that starts at draw p end" is tabulated for every draw of
+ * the window by the whole GPU, the serial part is one table lookup per permutation, the permutations are then replayed
+ * in parallel (needs at most three distinct relation sizes, else the serial walker runs).  0: always the serial walker.
+ * Same draws, same results either way.  Process-wide. */
+int indnet_sampler_set_path(int allow_parallel);
 /* Episode-sharded data parallelism: every rank walks the SAME streams for the global batch of B
  * episodes and gathers only its own episodes [b0, b0 + nb); outputs are [nb][...].  Episode b of the global
  * batch is therefore bit-identical whatever the number of ranks. */

@@ -107,6 +107,9 @@ struct SmpHdr {
   long long win_start;           // block of apos at the start of the current call
   SmpPlan plan[2];               // [0] what this call must still build, [1] what it builds ahead
   int nsec;
+  int use_v2;                    // 1: the parallel path (jump tables + chain + replay) serves this call, 0: the serial walker
+  int ntab;                      // v2: number of distinct permutation lengths (class scopes + the query permutation)
+  int sizes[4];                  // v2: those lengths
   uint32_t py_backup[MT_N + 1];  // Python stream as handed in: a failing call puts it back (streams unchanged on error)
 };
 
@@ -114,7 +117,22 @@ struct SmpHdr {
 // window; then plan what generation / table kernels of this phase have to do.
 __global__ void smp_plan_kernel(SmpHdr* __restrict__ h, const uint32_t* __restrict__ np_state,
                                 uint32_t* __restrict__ keys, uint32_t kmask, long long nblk, int ahead,
-                                unsigned long long magic) {
+                                unsigned long long magic, const int* __restrict__ scopes, int R, int nq, int allow_v2) {
+  if (ahead == 0 && threadIdx.x == 0) {
+    // the parallel path tabulates "where does a permutation of length n end when it starts at draw p" for every
+    // distinct n: feasible when the relations have at most three distinct sizes (FewRel: one)
+    int nt = 0, sz[4] = {0, 0, 0, 0};
+    bool ok = allow_v2 != 0;
+    for (int r = 0; r <= R && ok; ++r) {
+      const int n = r < R ? scopes[2 * r + 1] - scopes[2 * r] : nq;
+      bool seen = false;
+      for (int k = 0; k < nt; ++k) seen = seen || sz[k] == n;
+      if (!seen) { if (nt < 4) sz[nt++] = n; else ok = false; }
+    }
+    h->use_v2 = ok ? 1 : 0;
+    h->ntab = ok ? nt : 0;
+    for (int k = 0; k < 4; ++k) h->sizes[k] = sz[k];
+  }
   if (ahead == 0) {
     bool ok = h->magic == magic;
     long long blk = 0;
@@ -435,6 +453,7 @@ smp_walk_kernel(const uint32_t* __restrict__ keys, uint32_t kmask, const unsigne
                 uint32_t* __restrict__ py_state, const int* __restrict__ jsize, int jobs, int n_max,
                 int* __restrict__ jlist, int4* __restrict__ seclog, SmpHdr* __restrict__ hdr, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char ring[];
+  if (hdr->use_v2) return;                        // the parallel path serves this call
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int CB = 1 << cb_log;
   const uint32_t f_bytes = (uint32_t)n_states * 2u, y_off = 2u * f_bytes, e_off = y_off + TB * 4u, e2_off = e_off + E_STRIDE;
@@ -678,6 +697,7 @@ __global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int bcap,
                                 const int4* __restrict__ seclog, const SmpHdr* __restrict__ hdr, int cb_log, int n_max,
                                 int* __restrict__ jlist) {
   const int CB = 1 << cb_log;
+  if (hdr->use_v2) return;
   const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   const int sec = (int)(id >> cb_log), k = (int)(id & (CB - 1));
   if (sec >= hdr->nsec) return;
@@ -718,6 +738,152 @@ __global__ void smp_fill_kernel(const unsigned char* __restrict__ tab, int bcap,
     if (s <= thr) { m >>= 1; thr >>= 1; }
     const uint32_t v = yp[q] & m;
     if (v <= (uint32_t)s) { jrow[s] = (int)v; --s; }
+  }
+}
+
+// ---- the parallel path ("v2") ---------------------------------------------------------------------
+// The serial walk exists because a permutation's first draw is the previous permutation's last draw plus one.
+// That chain is made trivially short instead of fast: for every draw position p of the window and every distinct
+// permutation length n the whole GPU tabulates G_n[p] = the position after a permutation(n) that starts at p (head
+// of the first block walked draw by draw, then one transition-table lookup per block pair, then the end table) -
+// all independent of where the jobs really start.  The chain is then ONE dependent table lookup per job
+// (smp_chain_kernel), and once every job's start is known the jobs are replayed in parallel, one warp each,
+// 32 draws per ballot fixed point straight from the generated stream (smp_replay_kernel).
+constexpr uint32_t SMP_NOEND = 0xFFFFFFFFu;
+
+__global__ void smp_jump_kernel(const SmpHdr* __restrict__ h, const unsigned char* __restrict__ tab, int bcap, int n_states,
+                                long long nblk, uint32_t* __restrict__ G) {
+  if (!h->use_v2) return;
+  const long long npos = nblk * TB;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= npos * h->ntab) return;
+  const int z = (int)(idx / npos);
+  const long long o = idx - (long long)z * npos;           // offset of the start position from the window base
+  const int n = h->sizes[z];
+  int s = n - 1;                                           // permutation(n): i = n-1 .. 1
+  if (s <= 0) { G[idx] = (uint32_t)o; return; }
+  const long long rb = rec_bytes(n_states);
+  const long long base_blk = h->win_start;
+  long long bo = o >> 6;
+  const int off = (int)(o & (TB - 1));
+  if (off) {                                               // head: the rest of the first block, draw by draw
+    const uint32_t* y = reinterpret_cast<const uint32_t*>(tab + ((base_blk + bo) % bcap) * rb + (long long)n_states * 4);
+    uint32_t m = mask_for((uint32_t)s);
+    int thr = (int)(m >> 1);
+    for (int k = off; k < TB; ++k) {
+      if (s <= thr) { m >>= 1; thr >>= 1; }
+      if ((y[k] & m) <= (uint32_t)s) {
+        if (--s == 0) { G[idx] = (uint32_t)((bo << 6) + k + 1); return; }
+      }
+    }
+    ++bo;
+  }
+  while (bo < nblk) {
+    const long long blk = base_blk + bo;
+    const unsigned char* rec = tab + (blk % bcap) * rb;
+    if (!(blk & 1) && bo + 1 < nblk) {                     // even block: try the pair table first
+      const int s2 = (int)reinterpret_cast<const unsigned short*>(rec + (long long)n_states * 2)[s];
+      if (s2 != 0) { s = s2; bo += 2; continue; }
+    }
+    const int s1 = (int)reinterpret_cast<const unsigned short*>(rec)[s];
+    if (s1 == 0) {                                         // ends inside this block (then s <= 64): E[s] draws consumed
+      G[idx] = (uint32_t)((bo << 6) + rec[(long long)n_states * 4 + TB * 4 + s]);
+      return;
+    }
+    s = s1;
+    ++bo;
+  }
+  G[idx] = SMP_NOEND;                                      // runs past the generated window
+}
+
+// One warp; lane 0 chains the jobs through the jump tables, then the warp hands the stream back.
+__global__ void smp_chain_kernel(SmpHdr* __restrict__ hdr, const uint32_t* __restrict__ keys, uint32_t kmask, long long nblk,
+                                 const uint32_t* __restrict__ G, const int* __restrict__ jsize, int jobs,
+                                 uint32_t* __restrict__ start, uint32_t* __restrict__ np_state, uint32_t* __restrict__ py_state,
+                                 int* __restrict__ status) {
+  if (!hdr->use_v2) return;
+  const int lane = threadIdx.x;
+  const long long clk0 = clock64();
+  const long long base = hdr->win_start << 6, npos = nblk * TB;
+  long long pos = hdr->apos;
+  int flag = SMP_OK;
+  if (lane == 0) {
+    uint32_t o = (uint32_t)(pos - base);
+    for (int j = 0; j < jobs; ++j) {
+      const int n = jsize[j];
+      if (n < 0) { flag = -n; break; }
+      int z = 0;
+      while (z < hdr->ntab && hdr->sizes[z] != n) ++z;
+      start[j] = o;
+      if ((long long)o >= npos) { flag = SMP_STREAM_BUDGET; break; }
+      const uint32_t e = G[(long long)z * npos + o];
+      if (e == SMP_NOEND) { flag = SMP_STREAM_BUDGET; break; }
+      o = e;
+    }
+    pos = base + o;
+  }
+  flag = __shfl_sync(0xffffffffu, flag, 0);
+  pos = __shfl_sync(0xffffffffu, pos, 0);
+  if (flag != SMP_OK) {                                    // leave both streams exactly as they were handed in
+    for (int k = lane; k <= MT_N; k += 32) py_state[k] = hdr->py_backup[k];
+    if (lane == 0) { hdr->nsec = -1; status[0] = flag; status[1] = (int)((clock64() - clk0) >> 4); status[2] = 0; status[3] = 0; }
+    return;
+  }
+  long long blk = pos / MT_N;
+  int off = (int)(pos % MT_N);
+  if (off == 0 && blk > 0) { blk -= 1; off = MT_N; }
+  uint32_t tmp[MT_N / 32 + 1];
+  int cnt = 0;
+  for (int k = lane; k < MT_N; k += 32) tmp[cnt++] = keys[(uint32_t)(blk * MT_N + k) & kmask];
+  cnt = 0;
+  for (int k = lane; k < MT_N; k += 32) np_state[k] = tmp[cnt++];
+  if (lane == 0) {
+    np_state[MT_N] = (uint32_t)off;
+    hdr->apos = pos;
+    hdr->nsec = 0;
+    status[0] = SMP_OK;
+    status[1] = (int)((clock64() - clk0) >> 4);     // chain cycles / 16
+    status[2] = jobs;
+    status[3] = 0;
+  }
+}
+
+// One warp per job: the accepted (index, draw) pairs of its permutation, 32 draws per step.  Lane l of a row holds
+// draw p + l; its index is i minus the accepts before it, which depends on the lanes below - a ballot fixed point
+// settles the row in a few rounds (the same scheme as the serial walker's exact rows).
+__global__ void __launch_bounds__(128)
+smp_replay_kernel(const SmpHdr* __restrict__ hdr, const uint32_t* __restrict__ keys, uint32_t kmask,
+                  const uint32_t* __restrict__ start, const int* __restrict__ jsize, int jobs, int stride,
+                  int* __restrict__ jlist) {
+  if (!hdr->use_v2 || hdr->nsec < 0) return;
+  const int lane = threadIdx.x & 31;
+  const int job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (job >= jobs) return;
+  int i = jsize[job] - 1;
+  long long pos = (hdr->win_start << 6) + start[job];
+  int* jrow = jlist + (long long)job * stride;
+  const uint32_t below = (1u << lane) - 1u;
+  while (i > 0) {
+    const uint32_t y = mt_temper(keys[(uint32_t)(pos + lane) & kmask]);
+    const uint32_t m0 = mask_for((uint32_t)i);
+    int cn = (lane * (i + 1)) >> (32 - __clz(m0));         // expected accepts before this lane
+    int ip = i - cn;
+    uint32_t v = y & mask_for((uint32_t)max(ip, 1));
+    uint32_t bal = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
+    while (true) {
+      cn = __popc(bal & below);
+      ip = i - cn;
+      v = y & mask_for((uint32_t)max(ip, 1));
+      const uint32_t bal2 = __ballot_sync(0xffffffffu, ip >= 1 && v <= (uint32_t)ip);
+      if (bal2 == bal) break;
+      bal = bal2;
+    }
+    const int acc = __popc(bal);
+    if ((bal >> lane) & 1u) jrow[ip] = (int)v;
+    int used = 32;
+    if (acc >= i) used = 32 - __clz(bal);                  // the permutation ends at its last accepted draw
+    i -= acc;
+    pos += used;
   }
 }
 
@@ -793,7 +959,7 @@ struct SmpLayout {
   long long kcap, bcap;            // key ring (words, power of two) and table ring (blocks): two windows + slack
   int cb_log, rc;                  // walker staging: 2^cb_log blocks per chunk, rc chunk slots (-1: does not fit)
   long long smem_bytes;
-  long long o_hdr, o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, sec_cap, bytes;
+  long long o_hdr, o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, o_jump, o_start, sec_cap, bytes;
 };
 static double expected_draws(long long n) {      // E[draws] of NumPy's permutation(n) (rejection sampling)
   double e = 0.0;
@@ -806,6 +972,7 @@ static double expected_draws(long long n) {      // E[draws] of NumPy's permutat
 }
 // stream budget of one call: E[draws] * (1 + g_budget_pct) + g_budget_slack (indnet_sampler_set_budget: tests
 // shrink it to exercise the "budget exceeded -> streams unchanged -> retry in smaller batches" path)
+static int g_allow_v2 = 1;          // indnet_sampler_set_path: 0 forces the serial walker
 static double g_budget_pct = 0.03;
 static long long g_budget_slack = 8192;
 static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
@@ -846,6 +1013,8 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   L.o_tab = o;     o = al(o + rec_bytes(L.n_states) * L.bcap);
   L.sec_cap = (L.nblk >> (L.cb_log < 0 ? 0 : L.cb_log)) + L.jobs + 2;   // one run per chunk entered aligned + one per job
   L.o_seclog = o;  o = al(o + 16LL * L.sec_cap);
+  L.o_start = o;   o = al(o + 4LL * L.jobs);
+  L.o_jump = o;    o = al(o + 4LL * 4 * L.nblk * TB);        // G_n[p] for up to four lengths n
   L.bytes = o;
   return L;
 }
@@ -900,7 +1069,7 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   const unsigned tgrid = (unsigned)(L.nblk / 2 + 16);
   const size_t tsmem = 4 * (size_t)L.n_states;
   // what this call needs (normally already there: the previous call built it while it walked) ...
-  smp_plan_kernel<<<1, 256, 0, st>>>(hdr, np_state, keys, kmask, L.nblk, 0, magic);
+  smp_plan_kernel<<<1, 256, 0, st>>>(hdr, np_state, keys, kmask, L.nblk, 0, magic, scopes, R, N * Q, g_allow_v2);
   IN_LAUNCH_CHECK("smp_plan_kernel");
   smp_gen_kernel<<<2, GEN_NT, 0, st>>>(hdr, 0, keys, kmask, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
   IN_LAUNCH_CHECK("smp_gen_kernel");
@@ -909,13 +1078,24 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   // ... and, forked, the window after it
   IN_CUDA(cudaEventRecord(ev_fork[dev], st));
   IN_CUDA(cudaStreamWaitEvent(side, ev_fork[dev], 0));
-  smp_plan_kernel<<<1, 256, 0, side>>>(hdr, np_state, keys, kmask, L.nblk, 1, magic);
+  smp_plan_kernel<<<1, 256, 0, side>>>(hdr, np_state, keys, kmask, L.nblk, 1, magic, scopes, R, N * Q, g_allow_v2);
   IN_LAUNCH_CHECK("smp_plan_kernel");
   smp_gen_kernel<<<1, GEN_NT, 0, side>>>(hdr, 1, keys, kmask, py_state, R, B, N, classes, scopes, K, Q, n_max, jsize);
   IN_LAUNCH_CHECK("smp_gen_kernel");
   smp_table_kernel<<<tgrid, 256, tsmem, side>>>(hdr, 1, keys, kmask, tab, bcap, (int)L.n_states);
   IN_LAUNCH_CHECK("smp_table_kernel");
   IN_CUDA(cudaEventRecord(ev_join[dev], side));
+  {
+    uint32_t* G = (uint32_t*)(base + L.o_jump);
+    uint32_t* jstart = (uint32_t*)(base + L.o_start);
+    const long long work = 4 * L.nblk * TB;                  // upper bound (ntab <= 4): surplus threads leave at once
+    smp_jump_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(hdr, tab, bcap, (int)L.n_states, L.nblk, G);
+    IN_LAUNCH_CHECK("smp_jump_kernel");
+    smp_chain_kernel<<<1, 32, 0, st>>>(hdr, keys, kmask, L.nblk, G, jsize, (int)L.jobs, jstart, np_state, py_state, status);
+    IN_LAUNCH_CHECK("smp_chain_kernel");
+    smp_replay_kernel<<<ceil_div(L.jobs, 4), 128, 0, st>>>(hdr, keys, kmask, jstart, jsize, (int)L.jobs, (int)L.stride, jlist);
+    IN_LAUNCH_CHECK("smp_replay_kernel");
+  }
   smp_walk_kernel<<<1, 64, (size_t)L.smem_bytes, st>>>(keys, kmask, tab, ccap, (int)L.n_states, L.nblk, L.cb_log, L.rc,
                                                       np_state, py_state, jsize, (int)L.jobs, (int)L.stride, jlist, seclog,
                                                       hdr, status);
@@ -989,5 +1169,10 @@ extern "C" int indnet_sampler_set_budget(double pct, long long slack) {
   IN_REQUIRE(pct > -1.0 && slack >= 0, "sampler_set_budget: pct must be > -1 and slack >= 0");
   g_budget_pct = pct;
   g_budget_slack = slack;
+  return INDNET_OK;
+}
+
+extern "C" int indnet_sampler_set_path(int allow_parallel) {
+  g_allow_v2 = allow_parallel ? 1 : 0;
   return INDNET_OK;
 }

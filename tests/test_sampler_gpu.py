@@ -177,3 +177,44 @@ def test_stream_budget_overrun_leaves_streams_unchanged_and_retries():
         assert (random.random(), float(np.random.rand())) == tail
     finally:
         LIB.call("indnet_sampler_set_budget", 0.03, 8192)
+
+
+def test_parallel_and_serial_sampler_paths_draw_the_same_episodes():
+    """The jump-table / chain / replay path and the serial walker are two evaluations of the same draws: same
+    episodes, same stream positions afterwards - with one relation size (parallel path), with three sizes (parallel
+    path, three tables + the query permutation) and with five (serial walker by necessity)."""
+    from induction_b200._lib import LIB
+    from induction_b200.util.data_loader import JSONFileDataLoader
+    from induction_b200.util.synthetic import make_tables
+    for sizes in ([300] * 12, [300, 120, 77] * 4, [300, 120, 77, 64, 51] * 3):
+        base = make_tables(len(sizes), max(sizes), 16, 2000, 8, seed=3)
+        keep = np.concatenate([np.arange(r * max(sizes), r * max(sizes) + n) for r, n in enumerate(sizes)])
+        tables = {k: base[k][keep] for k in ("word", "pos1", "pos2", "mask", "length")}
+        lo = np.concatenate([[0], np.cumsum(sizes)])
+        tables["rel2scope"] = {"P%d" % r: [int(lo[r]), int(lo[r + 1])] for r in range(len(sizes))}
+        tables["word_vec_mat"] = base["word_vec_mat"]
+        B, N, K, Q = 9, 5, 3, 4
+        got = []
+        for parallel in (1, 0):
+            LIB.call("indnet_sampler_set_path", parallel)
+            try:
+                ld = JSONFileDataLoader.from_tables(tables)
+                random.seed(21); np.random.seed(21)
+                ins, labs = [], []
+                for _ in range(2):           # the sampler hands out its static buffers: copy before the next call
+                    x = ld.next_batch(B, N, K, Q)
+                    ins.append({k: v.cpu().numpy().copy() for k, v in x[0].items()})
+                    labs.append(x[1].cpu().numpy().copy())
+                got.append((ins, labs, random.random(), float(np.random.rand())))
+            finally:
+                LIB.call("indnet_sampler_set_path", 1)
+        random.seed(21); np.random.seed(21)
+        ld = JSONFileDataLoader.from_tables(tables)
+        want = [so.next_one_tf_stdlib(tables, ld.scopes(), N, K, Q) for _ in range(2 * B)]
+        for path in got:
+            for half in range(2):
+                for b in range(B):
+                    for k in KEYS:
+                        assert np.array_equal(path[0][half][k][b], want[half * B + b][0][k]), (sizes[:5], half, b, k)
+                    assert np.array_equal(path[1][half][b], want[half * B + b][1])
+        assert got[0][2:] == got[1][2:]
