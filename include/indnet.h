@@ -10,7 +10,8 @@
  *  - Plain pointers and sizes only; every pointer is a DEVICE pointer unless the comment says host.
  *    All matrices are row-major, dense unless a leading dimension is given.
  *  - indnet_stream is a cudaStream_t; all work is enqueued on it, nothing synchronises, nothing
- *    allocates.  Scratch, when an op needs it, is passed in by the caller.
+ *    allocates.  Scratch, when an op needs it, is passed in by the caller (the one exception is
+ *    indnet_lstm_bwd_static, whose scratch is a fixed array inside the library).
  *  - Return 0 on success; non-zero (INDNET_ERR_*) on error with a message in indnet_last_error()
  *    (thread-local).  Nothing throws across this boundary.
  *  - FP32 entry points are the "parity mode" (1e-5 vs the reference graph); *_tc entry points are the
@@ -25,7 +26,7 @@
 extern "C" {
 #endif
 
-#define INDNET_ABI_VERSION 3
+#define INDNET_ABI_VERSION 4
 
 typedef void* indnet_stream; /* cudaStream_t */
 
@@ -76,6 +77,17 @@ int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int
  * x carries 1.0 in column D (indnet_embed_fwd_bf16 writes it when D <= 62). */
 int indnet_tc_gemm_lstm_dw(indnet_stream st, const void* x_bf, const void* hprev_bf, const void* dz_bf,
                            float* dkernel, float* dbias, long long T, int D, int u, int splitk);
+/* FP32-accurate tensor-core mode (the reference graph is fp32, model/graph.py:47): every fp32 operand is split into three
+ * bf16 matrices, x = head + middle + tail (24 mantissa bits), by indnet_cast_bf16_split3 - rows [rows][cols] with input
+ * stride ld_in are written with the padded stride ld_out (a multiple of 8, zeros in the padding) - and indnet_tc_gemm3
+ * issues the six cross products of weight >= 2^-16 per K step into one fp32 accumulator (tanh in the epilogue is
+ * tanhf).  Arguments otherwise as indnet_tc_gemm; fp32 output only.  Same call sites as indnet_sgemm. */
+int indnet_cast_bf16_split3(indnet_stream st, const float* in, long long ld_in, long long rows, int cols, int ld_out,
+                            void* hi, void* mid, void* lo);
+int indnet_tc_gemm3(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* Ah, const void* Am,
+                    const void* Al, long long lda, const void* Bh, const void* Bm, const void* Bl, long long ldb,
+                    float* C, int ldc, const float* bias, int act, int accumulate, int batch, long long sA,
+                    long long sB, long long sC, int splitk);
 /* out (bf16) = in (fp32), n elements. */
 int indnet_cast_bf16(indnet_stream st, const float* in, void* out, long long n);
 /* Row-wise cast with a padded output row stride: out[r][0..ldo) = in[r][0..cols), zeros beyond cols

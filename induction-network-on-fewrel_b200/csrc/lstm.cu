@@ -265,6 +265,9 @@ extern "C" int indnet_lstm_bwd(indnet_stream st_, const float* dhout, const floa
 //  * The device address of the array is looked up once per device, on the first call made with
 //    that device current (cudaGetSymbolAddress; the array's name in host code is only a host-side
 //    handle, not a device pointer).  Make that first call before starting any stream capture.
+//    A first call made while the stream is capturing is refused with a clear error instead of
+//    breaking the capture.  The cached address belongs to the device's current context: after
+//    cudaDeviceReset() the library has to be reloaded.
 //  * No cudaMalloc / cudaFree / allocating library routine is called here.
 #define INDNET_STATIC_MAX_U 128
 #define INDNET_STATIC_MAX_DEVICES 64
@@ -272,12 +275,17 @@ extern "C" int indnet_lstm_bwd(indnet_stream st_, const float* dhout, const floa
 static __device__ __align__(256) float g_whT_static[2 * 4 * INDNET_STATIC_MAX_U * INDNET_STATIC_MAX_U];
 static float* g_whT_static_addr[INDNET_STATIC_MAX_DEVICES] = {nullptr};
 
-static int static_scratch_for_current_device(float** out) {
+static int static_scratch_for_current_device(float** out, cudaStream_t st) {
   int dev = -1;
   IN_CUDA(cudaGetDevice(&dev));
   IN_REQUIRE(dev >= 0 && dev < INDNET_STATIC_MAX_DEVICES, "lstm_bwd_static: device ordinal %d out of range", dev);
   float* p = __atomic_load_n(&g_whT_static_addr[dev], __ATOMIC_ACQUIRE);
   if (p == nullptr) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    IN_CUDA(cudaStreamIsCapturing(st, &cap));
+    IN_REQUIRE(cap == cudaStreamCaptureStatusNone,
+               "lstm_bwd_static: the first call on a device looks up the scratch array's address and must be made "
+               "outside stream capture");
     IN_CUDA(cudaGetSymbolAddress((void**)&p, g_whT_static));
     IN_REQUIRE(p != nullptr, "lstm_bwd_static: cudaGetSymbolAddress returned a null address");
     __atomic_store_n(&g_whT_static_addr[dev], p, __ATOMIC_RELEASE);   // same value from any thread
@@ -298,7 +306,7 @@ extern "C" int indnet_lstm_bwd_static(indnet_stream st_, const float* dhout, con
   if (X == 0) return INDNET_OK;
   IN_REQUIRE(dhout && gates && cstate && Wh_fw && Wh_bw && dz, "lstm_bwd_static: null pointer");
   float* whT = nullptr;
-  int rc = static_scratch_for_current_device(&whT);
+  int rc = static_scratch_for_current_device(&whT, st);
   if (rc != INDNET_OK) return rc;
   size_t smem = sizeof(float) * 6 * u * SB;
   dim3 tg(ceil_div(4 * u, 32), ceil_div(u, 32));

@@ -9,6 +9,7 @@
 //   A "K-major"  : stored [M][K] row-major          A "MN-major" : stored [K][M] row-major
 //   B "K-major"  : stored [N][K] row-major (B^T)    B "MN-major" : stored [K][N] row-major
 // Batched (grid.z) through 3-D tensor maps, or split-K (grid.z) with fp32 atomic accumulation.
+#include <cstring>
 #include "common.cuh"
 #include "indnet_internal.h"
 #include "tc_common.cuh"
@@ -42,16 +43,25 @@ struct TcGemmP {
   int vec;        // 1: outputs / bias / rank-1 vectors are 16-byte aligned -> row-path epilogue
 };
 
-template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(G_THREADS, 2)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcGemmP p) {
+// NS = 1: plain bf16 operands.  NS = 3: FP32-accurate mode - every fp32 operand arrives as THREE bf16 matrices
+// (head, middle, tail: x = h + m + l to 24 mantissa bits, indnet_cast_bf16_split3) and every K step issues the six
+// products whose weight is at least 2^-16 of the leading one (hh, hm, mh, hl, lh, mm) into the same fp32
+// accumulator: the contraction of the reference's fp32 graph (model/graph.py:47 dtype=tf.float32) on the tensor
+// cores instead of FFMA.  tanh in the epilogue is then the accurate one.
+struct TcMaps { CUtensorMap a[3]; CUtensorMap b[3]; };
+
+template <bool A_MN, bool B_MN, int NS>
+__global__ void __launch_bounds__(G_THREADS, NS == 3 ? 1 : 2)
+tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
+  constexpr int STAGES = NS == 3 ? 2 : G_STAGES;
+  constexpr int A_ST = NS * G_A_BYTES, B_ST = NS * G_B_BYTES;       // one stage: NS tiles of each operand
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
-  uint8_t* sB = smem + G_STAGES * G_A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * (G_A_BYTES + G_B_BYTES));
-  uint64_t* empty = full + G_STAGES;
-  uint64_t* tmem_full = empty + G_STAGES;
+  uint8_t* sB = smem + STAGES * A_ST;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_ST + B_ST));
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -63,9 +73,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int num_kb = min(total_kb, kb0 + p.kb_per_split) - kb0;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    for (int i = 0; i < G_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int t = 0; t < NS; ++t) { tma_prefetch_desc(&tm.a[t]); tma_prefetch_desc(&tm.b[t]); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -78,23 +87,26 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0) {
     if (lane == 0) {
       for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        const int s = kb % STAGES, ph = (kb / STAGES) & 1;
         mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], G_A_BYTES + G_B_BYTES);
+        mbar_expect_tx(&full[s], A_ST + B_ST);
         const int k = (kb0 + kb) * G_BK;
-        uint8_t* a = sA + s * G_A_BYTES;
-        uint8_t* b = sB + s * G_B_BYTES;
-        if (A_MN) {   // stored [K][M]: two boxes of 64 (M) x 64 (K rows), one per 128-byte M atom
-          tma_load_3d(a, &tmA, &full[s], m0, k, batch);
-          tma_load_3d(a + G_A_BYTES / 2, &tmA, &full[s], m0 + 64, k, batch);
-        } else {      // stored [M][K]: one box of 64 (K) x 128 (M rows)
-          tma_load_3d(a, &tmA, &full[s], k, m0, batch);
-        }
-        if (B_MN) {
-          tma_load_3d(b, &tmB, &full[s], n0, k, batch);
-          tma_load_3d(b + G_B_BYTES / 2, &tmB, &full[s], n0 + 64, k, batch);
-        } else {
-          tma_load_3d(b, &tmB, &full[s], k, n0, batch);
+#pragma unroll
+        for (int t = 0; t < NS; ++t) {
+          uint8_t* a = sA + s * A_ST + t * G_A_BYTES;
+          uint8_t* b = sB + s * B_ST + t * G_B_BYTES;
+          if (A_MN) {   // stored [K][M]: two boxes of 64 (M) x 64 (K rows), one per 128-byte M atom
+            tma_load_3d(a, &tm.a[t], &full[s], m0, k, batch);
+            tma_load_3d(a + G_A_BYTES / 2, &tm.a[t], &full[s], m0 + 64, k, batch);
+          } else {      // stored [M][K]: one box of 64 (K) x 128 (M rows)
+            tma_load_3d(a, &tm.a[t], &full[s], k, m0, batch);
+          }
+          if (B_MN) {
+            tma_load_3d(b, &tm.b[t], &full[s], n0, k, batch);
+            tma_load_3d(b + G_B_BYTES / 2, &tm.b[t], &full[s], n0 + 64, k, batch);
+          } else {
+            tma_load_3d(b, &tm.b[t], &full[s], k, n0, batch);
+          }
         }
       }
     }
@@ -106,15 +118,26 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       constexpr uint32_t a_lbo = A_MN ? G_BK * 128 : 0, b_lbo = B_MN ? G_BK * 128 : 0;
       constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32, b_kstep = B_MN ? 16 * 128 : 32;
       for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        const int s = kb % STAGES, ph = (kb / STAGES) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(sA + s * G_A_BYTES), b_base = smem_u32(sB + s * G_B_BYTES);
+        const uint32_t a_base = smem_u32(sA + s * A_ST), b_base = smem_u32(sB + s * B_ST);
 #pragma unroll
         for (int k = 0; k < G_BK / 16; ++k) {
-          const uint64_t ad = smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
-          const uint64_t bd = smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
-          umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          if (NS == 1) {
+            const uint64_t ad = smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
+            umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          } else {
+            // smallest terms first: (m,m) (l,h) (h,l) (m,h) (h,m) (h,h); operand t sits t tiles into the stage
+            constexpr int TA_[6] = {1, 2, 0, 1, 0, 0}, TB_[6] = {1, 0, 2, 0, 1, 0};
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {
+              const uint64_t ad = smem_desc_sw128(a_base + TA_[q] * G_A_BYTES + k * a_kstep, a_lbo, 1024);
+              const uint64_t bd = smem_desc_sw128(b_base + TB_[q] * G_B_BYTES + k * b_kstep, b_lbo, 1024);
+              umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0 || q > 0) ? 1u : 0u);
+            }
+          }
         }
         umma_commit(&empty[s]);
       }
@@ -176,7 +199,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           if (p.act == 1) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = tanh_approx(v[j]);
+            for (int j = 0; j < 32; ++j) v[j] = NS == 3 ? tanhf(v[j]) : tanh_approx(v[j]);
           } else if (p.act == 2) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -241,7 +264,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rr < rmax) {
               float x = tile[rr * 33 + lane] + bv;
               if (p.accumulate || p.rs) x += old[rr];
-              if (p.act == 1) x = tanh_approx(x);       // bf16 mode: MUFU.TANH is well inside the 2e-2 budget
+              if (p.act == 1) x = NS == 3 ? tanhf(x) : tanh_approx(x);   // bf16 mode: MUFU.TANH is well inside the 2e-2 budget
               else if (p.act == 2) x = fmaxf(x, 0.f);
               const long long o = o0 + (long long)rr * p.ldc;
               if (Cbase) Cbase[o] = x;
@@ -437,9 +460,12 @@ int make_tmap_nd(CUtensorMap* tm, const void* base, int elem_bytes, int rank, co
   return INDNET_OK;
 }
 
+struct TcSplit { const void* a[2]; const void* b[2]; };      // middle and tail parts of A and B (FP32-accurate mode)
+
 int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const void* A, long long lda,
             const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act, int accumulate,
-            int batch, long long sA, long long sB, long long sC, int splitk, const TcGemmRank1* r1 = nullptr) {
+            int batch, long long sA, long long sB, long long sC, int splitk, const TcGemmRank1* r1 = nullptr,
+            const TcSplit* split = nullptr) {
   IN_REQUIRE(M > 0 && N > 0 && K > 0 && batch > 0, "tc_gemm: bad sizes M=%d N=%d K=%d batch=%d", M, N, K, batch);
   IN_REQUIRE(A && B && (C || Cb), "tc_gemm: null operand");
   const int total_kb = ceil_div(K, G_BK);
@@ -481,27 +507,37 @@ int tc_gemm(cudaStream_t st, bool a_mn, bool b_mn, int M, int N, int K, const vo
     IN_REQUIRE(ldc == N, "tc_gemm: split-K zero-fill expects a dense C");
     IN_CUDA(cudaMemsetAsync(C, 0, sizeof(float) * (size_t)M * N, st));
   }
-  CUtensorMap tmA, tmB;
-  int rc;
-  if (a_mn) rc = make_tmap_bf16(&tmA, A, M, K, lda, batch, sA, 64, G_BK);
-  else rc = make_tmap_bf16(&tmA, A, K, M, lda, batch, sA, G_BK, G_BM);
-  if (rc) return rc;
-  if (b_mn) rc = make_tmap_bf16(&tmB, B, N, K, ldb, batch, sB, 64, G_BK);
-  else rc = make_tmap_bf16(&tmB, B, K, N, ldb, batch, sB, G_BK, G_BN);
-  if (rc) return rc;
+  TcMaps tm;
+  memset(&tm, 0, sizeof(tm));
+  const int ns = split ? 3 : 1;
+  for (int t = 0; t < ns; ++t) {
+    const void* At = t == 0 ? A : split->a[t - 1];
+    const void* Bt = t == 0 ? B : split->b[t - 1];
+    IN_REQUIRE(At && Bt, "tc_gemm: missing operand part %d", t);
+    int rc;
+    if (a_mn) rc = make_tmap_bf16(&tm.a[t], At, M, K, lda, batch, sA, 64, G_BK);
+    else rc = make_tmap_bf16(&tm.a[t], At, K, M, lda, batch, sA, G_BK, G_BM);
+    if (rc) return rc;
+    if (b_mn) rc = make_tmap_bf16(&tm.b[t], Bt, N, K, ldb, batch, sB, 64, G_BK);
+    else rc = make_tmap_bf16(&tm.b[t], Bt, K, N, ldb, batch, sB, G_BK, G_BN);
+    if (rc) return rc;
+  }
   dim3 grid(gx, gy, batch * splitk);
   IN_REQUIRE(grid.z <= 65535, "tc_gemm: batch*splitk too large");
-#define LAUNCH_TC(AM, BM_)                                                                                      \
+  constexpr int G_SMEM3 = 2 * 3 * (G_A_BYTES + G_B_BYTES) + 256 + 1024;
+#define LAUNCH_TC2(AM, BM_, NS_, SM_)                                                                           \
   do {                                                                                                          \
     /* per device and cheap: set on every launch (legal during stream capture) */                                 \
-    IN_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<AM, BM_>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM)); \
-    tc_gemm_kernel<AM, BM_><<<grid, G_THREADS, G_SMEM, st>>>(tmA, tmB, p);                                      \
+    IN_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<AM, BM_, NS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_)); \
+    tc_gemm_kernel<AM, BM_, NS_><<<grid, G_THREADS, SM_, st>>>(tm, p);                                          \
   } while (0)
+#define LAUNCH_TC(AM, BM_) do { if (ns == 3) LAUNCH_TC2(AM, BM_, 3, G_SMEM3); else LAUNCH_TC2(AM, BM_, 1, G_SMEM); } while (0)
   if (a_mn && b_mn) LAUNCH_TC(true, true);
   else if (a_mn) LAUNCH_TC(true, false);
   else if (b_mn) LAUNCH_TC(false, true);
   else LAUNCH_TC(false, false);
 #undef LAUNCH_TC
+#undef LAUNCH_TC2
   IN_LAUNCH_CHECK("tc_gemm_kernel");
   return INDNET_OK;
 }
@@ -530,9 +566,46 @@ __global__ void cast_bf16_rows_kernel(const float* __restrict__ in, __nv_bfloat1
   out[i] = __float2bfloat16(c < cols ? in[r * cols + c] : 0.f);
 }
 
+// x = head + middle + tail, each a bf16 (24 mantissa bits in all): rows [rows][cols] with input stride ld_in are
+// written with the padded stride ld_out (a multiple of 8 elements for TMA), zeros in the padding
+__global__ void cast_split3_kernel(const float* __restrict__ in, long long ld_in, long long rows, int cols, int ld_out,
+                                   __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ mid, __nv_bfloat16* __restrict__ lo) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= rows * ld_out) return;
+  const long long r = i / ld_out;
+  const int c = (int)(i - r * ld_out);
+  const float x = c < cols ? in[r * ld_in + c] : 0.f;
+  const __nv_bfloat16 h = __float2bfloat16(x);
+  const float r1 = x - __bfloat162float(h);
+  const __nv_bfloat16 m = __float2bfloat16(r1);
+  const float r2 = r1 - __bfloat162float(m);
+  hi[i] = h; mid[i] = m; lo[i] = __float2bfloat16(r2);
+}
+
 }  // namespace indnet
 
 using namespace indnet;
+
+extern "C" int indnet_cast_bf16_split3(indnet_stream st, const float* in, long long ld_in, long long rows, int cols,
+                                       int ld_out, void* hi, void* mid, void* lo) {
+  IN_REQUIRE(rows >= 0 && cols >= 0 && ld_out >= cols && ld_in >= cols, "cast_bf16_split3: bad sizes");
+  if (rows == 0 || ld_out == 0) return INDNET_OK;
+  IN_REQUIRE(in && hi && mid && lo, "cast_bf16_split3: null pointer");
+  cast_split3_kernel<<<ceil_div(rows * ld_out, 256), 256, 0, (cudaStream_t)st>>>(in, ld_in, rows, cols, ld_out,
+                                                                                (__nv_bfloat16*)hi, (__nv_bfloat16*)mid,
+                                                                                (__nv_bfloat16*)lo);
+  IN_LAUNCH_CHECK("cast_split3_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_tc_gemm3(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* Ah, const void* Am,
+                               const void* Al, long long lda, const void* Bh, const void* Bm, const void* Bl,
+                               long long ldb, float* C, int ldc, const float* bias, int act, int accumulate, int batch,
+                               long long sA, long long sB, long long sC, int splitk) {
+  TcSplit sp{{Am, Al}, {Bm, Bl}};
+  return tc_gemm((cudaStream_t)st, a_mn != 0, b_mn != 0, M, N, K, Ah, lda, Bh, ldb, C, nullptr, ldc, bias, act, accumulate,
+                 batch, sA, sB, sC, splitk, nullptr, &sp);
+}
 
 extern "C" int indnet_tc_gemm(indnet_stream st, int a_mn, int b_mn, int M, int N, int K, const void* A, long long lda,
                               const void* B, long long ldb, float* C, void* Cb, int ldc, const float* bias, int act,

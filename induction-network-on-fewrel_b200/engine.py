@@ -286,6 +286,9 @@ class EpisodePipeline:
         self.running = torch.zeros(3, dtype=torch.float32, device=self.dev)   # training-step sums {loss, accuracy, steps}
         self._bwd_ready = False
         self.bf16 = cfg.mode == "bf16"
+        import os as _os0
+        self.tc3 = cfg.mode == "fp32" and not _os0.environ.get("INDNET_FP32_FFMA")     # FP32-accurate tensor-core GEMMs
+        self._tc3_buf = {}
         if self.bf16:
             if c.D > 64 or c.u % 8:
                 raise ValueError("bf16 tensor-core mode needs E + 10 <= 64 and hidden_size % 8 == 0 "
@@ -346,8 +349,33 @@ class EpisodePipeline:
         finally:
             self._tag = None
 
+    def _split3(self, key, base, ld_in, rows, cols):
+        """fp32 matrix -> its three bf16 parts (head, middle, tail) in persistent scratch with a padded row stride."""
+        ld = (cols + 7) // 8 * 8
+        buf = self._tc3_buf.get(key)
+        if buf is None or buf[0].numel() < rows * ld:
+            buf = tuple(torch.zeros(rows * ld, dtype=torch.bfloat16, device=self.dev) for _ in range(3))
+            self._tc3_buf[key] = buf
+        self._call("indnet_cast_bf16_split3", base, ld_in, rows, cols, ld, ptr(buf[0]), ptr(buf[1]), ptr(buf[2]))
+        return buf, ld
+
     def _gemm_call(self, tA, tB, M, N, K, A, lda, Bm, ldb, C, ldc, alpha, beta, bias, act, batch, inner,
                    sA, sB, sC, splitk):
+        # FP32-accurate mode on the tensor cores: operands split into three bf16 parts, six MMAs per K step
+        # (csrc/tc_gemm.cu NS = 3).  Anything the split path does not cover (alpha != 1, non-contiguous batches)
+        # stays on the FFMA kernel.
+        ra, ca = (K, M) if tA else (M, K)          # stored shape of A
+        rb, cb = (N, K) if tB else (K, N)          # stored shape of B
+        ok = (self.tc3 and alpha == 1.0 and beta in (0.0, 1.0) and inner == 1 and sA[1] == 0 and sB[1] == 0 and sC[1] == 0
+              and (batch == 1 or (sA[0] == ra * lda and sB[0] == rb * ldb)))
+        if ok:
+            tag = self._tag or "gemm"
+            (ah, am, al), la = self._split3((tag, "A"), A, lda, batch * ra, ca)
+            (bh, bm, bl), lb = self._split3((tag, "B"), Bm, ldb, batch * rb, cb)
+            self._call("indnet_tc_gemm3", int(tA), int(not tB), M, N, K, ptr(ah), ptr(am), ptr(al), la, ptr(bh), ptr(bm),
+                       ptr(bl), lb, C, ldc, ptr(bias) if isinstance(bias, torch.Tensor) else bias, act,
+                       1 if beta == 1.0 else 0, batch, ra * la, rb * lb, sC[0], splitk)
+            return
         self._call("indnet_sgemm", int(tA), int(tB), M, N, K, alpha, A, lda, Bm, ldb, beta, C, ldc,
                    ptr(bias) if isinstance(bias, torch.Tensor) else bias, act, batch, inner,
                    sA[0], sA[1], sB[0], sB[1], sC[0], sC[1], splitk)
