@@ -63,6 +63,12 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  // NS == 3 only: the head*head products of one 64-wide K block go to one of two "main" accumulators, which the
+  // epilogue warps drain into registers (round-to-nearest adds) while the other one fills; see the issuer below
+  uint64_t* acc_full = tmem_full + 2;
+  uint64_t* acc_empty = acc_full + 2;
+  constexpr uint32_t TM_COLS = NS == 3 ? 512 : G_BN;                // main[0], main[1], small (, unused)
+  constexpr uint32_t TM_SMALL = 2 * G_BN;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * G_BM, n0 = blockIdx.x * G_BN;
@@ -76,9 +82,10 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
     for (int t = 0; t < NS; ++t) { tma_prefetch_desc(&tm.a[t]); tma_prefetch_desc(&tm.b[t]); }
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(tmem_full, 1);
+    if (NS == 3) for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, G_BN);
+  if (warp == 1) tmem_alloc(tmem_slot, TM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -120,6 +127,7 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % STAGES, ph = (kb / STAGES) & 1;
         mbar_wait(&full[s], ph);
+        if (NS == 3 && kb >= 2) mbar_wait(&acc_empty[kb & 1], ((kb >> 1) - 1) & 1);
         tc_fence_after();
         const uint32_t a_base = smem_u32(sA + s * A_ST), b_base = smem_u32(sB + s * B_ST);
 #pragma unroll
@@ -129,17 +137,26 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
             const uint64_t bd = smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
             umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
           } else {
-            // smallest terms first: (m,m) (l,h) (h,l) (m,h) (h,m) (h,h); operand t sits t tiles into the stage
-            constexpr int TA_[6] = {1, 2, 0, 1, 0, 0}, TB_[6] = {1, 0, 2, 0, 1, 0};
+            // The tensor core adds each MMA's result to the TMEM accumulator with truncation, so a long chain
+            // into one large accumulator drifts towards zero (measured 2.6e-5 of max|C| at K = 4096, against
+            // 8e-7 for SGEMM).  Hence: the five cross terms of weight 2^-8 .. 2^-16 - (m,m) (l,h) (h,l) (m,h)
+            // (h,m), smallest first - go to their own accumulator, 2^8 smaller than the result, for the whole
+            // K range, and the head*head term of each K block goes to a fresh "main" accumulator that the
+            // epilogue warps add into registers.  Operand t sits t tiles into the stage.
+            constexpr int TA_[5] = {1, 2, 0, 1, 0}, TB_[5] = {1, 0, 2, 0, 1};
 #pragma unroll
-            for (int q = 0; q < 6; ++q) {
+            for (int q = 0; q < 5; ++q) {
               const uint64_t ad = smem_desc_sw128(a_base + TA_[q] * G_A_BYTES + k * a_kstep, a_lbo, 1024);
               const uint64_t bd = smem_desc_sw128(b_base + TB_[q] * G_B_BYTES + k * b_kstep, b_lbo, 1024);
-              umma_bf16(taddr, ad, bd, idesc, (kb > 0 || k > 0 || q > 0) ? 1u : 0u);
+              umma_bf16(taddr + TM_SMALL, ad, bd, idesc, (kb > 0 || k > 0 || q > 0) ? 1u : 0u);
             }
+            const uint64_t ad = smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
+            umma_bf16(taddr + (uint32_t)(kb & 1) * G_BN, ad, bd, idesc, k > 0 ? 1u : 0u);
           }
         }
         umma_commit(&empty[s]);
+        if (NS == 3) umma_commit(&acc_full[kb & 1]);
       }
       umma_commit(tmem_full);
     }
@@ -147,8 +164,43 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
     // epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32)
     const int q = warp & 3;
     const int row = m0 + q * 32 + lane;
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
+    if (NS == 3) {
+      const uint32_t lane_base = taddr + ((uint32_t)(q * 32) << 16);
+      float acc[G_BN];
+#pragma unroll
+      for (int j = 0; j < G_BN; ++j) acc[j] = 0.f;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&acc_full[kb & 1], (kb >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < G_BN / 32; ++c) {
+          float v[32];
+          tmem_ld32(lane_base + (uint32_t)(kb & 1) * G_BN + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c * 32 + j] += v[j];
+        }
+        tc_fence_before();
+        mbar_arrive(&acc_empty[kb & 1]);
+      }
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+      // total = sum of the K blocks + the small terms, parked in main[0] for the common epilogue below
+#pragma unroll
+      for (int c = 0; c < G_BN / 16; ++c) {
+        float v[16];
+        tmem_ld16(lane_base + TM_SMALL + c * 16, v);
+        tmem_ld_wait();
+        uint32_t r[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) r[j] = __float_as_uint(acc[c * 16 + j] + v[j]);
+        tmem_st16(lane_base + c * 16, r);
+      }
+      tmem_st_wait();
+    } else {
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+    }
     // All loads of this tile have been consumed once tmem_full fires, so the operand ring is free:
     // reuse it as a per-warp 32x33 fp32 transpose tile so that every global store instruction writes
     // one contiguous 128-byte row segment (lane = column) instead of 32 scattered rows.
@@ -278,7 +330,7 @@ tc_gemm_kernel(const __grid_constant__ TcMaps tm, TcGemmP p) {
     tc_fence_before();
   }
   __syncthreads();
-  if (warp == 1) tmem_dealloc(taddr, G_BN);
+  if (warp == 1) tmem_dealloc(taddr, TM_COLS);
 }
 
 // ---------------------------------------------------------------- stacked weight-gradient GEMM

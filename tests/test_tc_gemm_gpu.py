@@ -117,3 +117,77 @@ def test_tc_gemm_lstm_dw_stacked_operand(T, D):
     if dbias is not None:            # row D of the stacked product = column sums of dz = the LSTM bias gradient
         want = dz.double().sum(0)
         assert float((dbias.double() - want).abs().max() / want.abs().max()) < 2e-5
+
+
+def _split3(x, ld_out):
+    """fp32 [rows][cols] -> three bf16 [rows][ld_out] matrices through indnet_cast_bf16_split3."""
+    from induction_b200._lib import LIB, current_stream, ptr
+    rows, cols = x.shape
+    parts = [torch.full((rows, ld_out), 7.0, dtype=torch.bfloat16, device="cuda") for _ in range(3)]
+    LIB.call("indnet_cast_bf16_split3", current_stream(), ptr(x), x.stride(0), rows, cols, ld_out,
+             ptr(parts[0]), ptr(parts[1]), ptr(parts[2]))
+    return parts
+
+
+def test_split3_reconstructs_fp32_and_zero_pads():
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(37, 53, generator=g, device="cuda") * torch.logspace(-6, 6, 53, device="cuda")
+    hi, mid, lo = _split3(x, 56)
+    torch.cuda.synchronize()
+    back = hi[:, :53].double() + mid[:, :53].double() + lo[:, :53].double()
+    rel = ((back - x.double()).abs() / x.double().abs().clamp_min(1e-30)).max()
+    assert float(rel) < 2 ** -22, float(rel)                  # 3 x 8 mantissa bits cover fp32's 24
+    for p in (hi, mid, lo):
+        assert float(p[:, 53:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("M,N,K,act", [(128, 128, 64, 0), (320, 200, 136, 0), (25, 504, 256, 1), (192, 512, 4096, 0)])
+def test_tc_gemm3_is_fp32_accurate(a_mn, b_mn, M, N, K, act):
+    """The split GEMM against a float64 product of the SAME fp32 operands: the error budget is fp32
+    accumulation (K * 2^-24 relative), not bf16 rounding of the inputs (2^-9)."""
+    from induction_b200._lib import LIB, current_stream, ptr
+    if a_mn and M % 8:
+        pytest.skip("MN-major A needs a leading dimension that is a multiple of 8 elements")
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N + K)
+    A = torch.randn(*((K, M) if a_mn else (M, K)), generator=g, device="cuda")
+    B = torch.randn(*((K, N) if b_mn else (N, K)), generator=g, device="cuda")
+    if act:
+        A = A / K ** 0.5
+    bias = torch.randn(N, generator=g, device="cuda") if act else None
+    want = (A.double().t() if a_mn else A.double()) @ (B.double() if b_mn else B.double().t())
+    lda = (A.shape[1] + 7) // 8 * 8
+    ldb = (B.shape[1] + 7) // 8 * 8
+    Ah, Am, Al = _split3(A, lda)
+    Bh, Bm, Bl = _split3(B, ldb)
+    C = torch.full((M, N), float("nan"), device="cuda")
+    LIB.call("indnet_tc_gemm3", current_stream(), a_mn, b_mn, M, N, K, ptr(Ah), ptr(Am), ptr(Al), lda,
+             ptr(Bh), ptr(Bm), ptr(Bl), ldb, ptr(C), N, ptr(bias), act, 0, 1, 0, 0, M * N, 1)
+    torch.cuda.synchronize()
+    if act:
+        want = torch.tanh(want + bias.double())
+        # arguments up to ~5 in magnitude: the TMEM accumulator truncates, so ~1e-6 relative on the sum
+        assert float((C.double() - want).abs().max()) < 1e-5
+    else:
+        err = float((C.double() - want).abs().max() / want.abs().max())
+        assert err < 2e-6, err
+        bf = (A.to(torch.bfloat16).double().t() if a_mn else A.to(torch.bfloat16).double()) @ \
+             (B.to(torch.bfloat16).double() if b_mn else B.to(torch.bfloat16).double().t())
+        assert float((bf - want).abs().max() / want.abs().max()) > 50 * err     # and far better than one bf16 pass
+
+
+def test_tc_gemm3_split_k_and_accumulate():
+    from induction_b200._lib import LIB, current_stream, ptr
+    M, N, K = 192, 512, 20000
+    g = torch.Generator(device="cuda").manual_seed(8)
+    A = torch.randn(K, M, generator=g, device="cuda")
+    B = torch.randn(K, N, generator=g, device="cuda")
+    Ah, Am, Al = _split3(A, M)
+    Bh, Bm, Bl = _split3(B, N)
+    base = torch.randn(M, N, generator=g, device="cuda")
+    C = base.clone()
+    LIB.call("indnet_tc_gemm3", current_stream(), 1, 1, M, N, K, ptr(Ah), ptr(Am), ptr(Al), M,
+             ptr(Bh), ptr(Bm), ptr(Bl), N, ptr(C), N, None, 0, 1, 1, 0, 0, M * N, 0)
+    torch.cuda.synchronize()
+    want = A.double().t() @ B.double() + base.double()
+    assert float((C.double() - want).abs().max() / want.abs().max()) < 3e-6
