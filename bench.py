@@ -540,6 +540,8 @@ def roofline(args, cfg, store, prof, prof_steps, peaks, clocks):
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             tr = json.load(f)
         key = {"indnet_lstm_fwd_tc": "tc_lstm_fwd_kernel", "indnet_lstm_bwd_tc": "tc_lstm_bwd_kernel"}.get(dom[0], dom[0])
+        if args.config != 1:
+            key = "%s@config %d" % (key, args.config)
         if key in tr and tr[key].get("workload") == "config %d" % args.config and args.mode == "bf16":
             roof["traffic"] = tr[key]["dram_bytes_per_launch"]
             roof["traffic_source"] = tr[key].get("source", "profiles/ (dram__bytes_read.sum + dram__bytes_write.sum)")

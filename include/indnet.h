@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define INDNET_ABI_VERSION 4
+#define INDNET_ABI_VERSION 5
 
 typedef void* indnet_stream; /* cudaStream_t */
 
@@ -284,19 +284,27 @@ int indnet_squash_bwd(indnet_stream st, const float* v, const float* dout, float
 /* ---- a8-a10: neural_tensor_layer head + build_loss + build_predict/accuracy ---------------------
  * model/layer_module.py:35-47, model/graph.py:92-94, model/base.py:101-107.
  * V [rows][N*S] pre-ReLU bilinear products, column c*S+k; w [(k*N+c)][N] in the reference's row order;
- * labels [rows]; probs [rows][N]; loss_part [rows] = sum_c (p-y)^2; correct [rows] = argmax hit. */
+ * labels [rows]; probs [rows][N]; loss_part [rows] = sum_c (p-y)^2; correct [rows] = argmax hit.
+ * out2 / running / ticket (optional, out2 and ticket together): the block that finishes last also does what
+ * indnet_loss_acc_reduce does (same row order, hence the same bits); ticket is a zero-initialised device
+ * counter owned by the caller, left at zero again on return. */
 int indnet_ntn_head_fwd(indnet_stream st, const float* V, const float* w, const float* b, const int* labels,
-                        float* probs, float* loss_part, int* correct, int rows, int N, int S);
+                        float* probs, float* loss_part, int* correct, int rows, int N, int S, float* out2,
+                        float* running, unsigned int* ticket);
 /* out2[0] = loss (mean over rows*N), out2[1] = accuracy.  running (optional, device float[3]): += {loss,
  * accuracy, 1} - the running sums of model/base.py:156-158 kept on the device. */
 int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, float* running,
                            int rows, int N);
 /* Upstream gradient: dprobs [rows][N] when not NULL, else the fused mean-squared-error gradient
  * scale*2(p-y) with scale = 1/(rows*N).  Overwrites dlogit [rows][N], dV [rows][N*S], dw, db; dV_bf (optional)
- * receives a bf16 copy of dV with rows padded to ld_bf elements (zeros past N*S), the TMA operand format. */
+ * receives a bf16 copy of dV with rows padded to ld_bf elements (zeros past N*S), the TMA operand format.
+ * dw = db = NULL leaves the two parameter gradients to a later indnet_ntn_head_dw (reads V and dlogit only,
+ * so it can run beside the GEMMs that consume dV). */
 int indnet_ntn_head_bwd(indnet_stream st, const float* V, const float* w, const float* probs, const int* labels,
                         const float* dprobs, float* dlogit, float* dV, void* dV_bf, int ld_bf, float* dw, float* db,
                         int rows, int N, int S, float scale);
+int indnet_ntn_head_dw(indnet_stream st, const float* V, const float* dlogit, float* dw, float* db, int rows, int N,
+                       int S);
 
 /* ---- a11: build_optimize, model/base.py:94-99 ---------------------------------------------------
  * One fused TF-form Adam update over a flat buffer.  global_step: device int64, read for the staircase
@@ -305,6 +313,14 @@ int indnet_ntn_head_bwd(indnet_stream st, const float* V, const float* w, const 
 int indnet_adam_step(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
                      long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate, float beta1,
                      float beta2, float eps, float grad_scale, void* shadow_bf16);
+/* The same update in two halves (a slice whose gradient is final early - M - can be updated underneath the
+ * rest of the backward pass): indnet_adam_prep computes hyper = {lr_t, lr} from global_step and advances the
+ * counter only when advance != 0; indnet_adam_apply updates n elements starting at the given pointers with the
+ * lr_t found in hyper.  Sequence for one step: prep(0), apply(slice), ..., apply(rest), prep(1). */
+int indnet_adam_prep(indnet_stream st, long long* global_step, float* hyper, float lr0, int decay_steps,
+                     float decay_rate, float beta1, float beta2, int advance);
+int indnet_adam_apply(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
+                      const float* hyper, float beta1, float beta2, float eps, float grad_scale, void* shadow_bf16);
 
 #ifdef __cplusplus
 }

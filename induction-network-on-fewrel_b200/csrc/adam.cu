@@ -14,14 +14,14 @@
 namespace indnet {
 
 __global__ void adam_prep_kernel(long long* global_step, float* hyper, float lr0, int decay_steps, float decay_rate,
-                                 float beta1, float beta2) {
+                                 float beta1, float beta2, int advance) {
   const long long gs = *global_step;
   const float lr = lr0 * powf(decay_rate, floorf((float)gs / (float)decay_steps));
   const double t = (double)(gs + 1);
   const float lr_t = (float)((double)lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t)));
   hyper[0] = lr_t;
   hyper[1] = lr;
-  *global_step = gs + 1;
+  if (advance) *global_step = gs + 1;
 }
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
@@ -50,10 +50,38 @@ extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* g
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(n >= 0 && decay_steps > 0, "adam_step: bad sizes");
   IN_REQUIRE(global_step && hyper, "adam_step: null step/hyper pointer");
-  adam_prep_kernel<<<1, 1, 0, st>>>(global_step, hyper, lr0, decay_steps, decay_rate, beta1, beta2);
+  adam_prep_kernel<<<1, 1, 0, st>>>(global_step, hyper, lr0, decay_steps, decay_rate, beta1, beta2, 1);
   IN_LAUNCH_CHECK("adam_prep_kernel");
   if (n == 0) return INDNET_OK;
   IN_REQUIRE(params && grads && m && v, "adam_step: null pointer");
+  int blocks = ceil_div(n, 256 * 4);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
+                                           (__nv_bfloat16*)shadow_bf16);
+  IN_LAUNCH_CHECK("adam_kernel");
+  return INDNET_OK;
+}
+
+// The same update in two halves, so that a slice of the flat buffer whose gradient is final early in the
+// backward pass (M, 96 % of the parameters) can be updated on a side stream underneath the rest of the pass:
+// prep(advance = 0) -> apply(slice) ... apply(rest) -> prep(advance = 1).  prep is idempotent for a given
+// global_step, and the dropout streams of the step keep reading the un-advanced counter until the end.
+extern "C" int indnet_adam_prep(indnet_stream st_, long long* global_step, float* hyper, float lr0, int decay_steps,
+                                float decay_rate, float beta1, float beta2, int advance) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(decay_steps > 0 && global_step && hyper, "adam_prep: bad arguments");
+  adam_prep_kernel<<<1, 1, 0, st>>>(global_step, hyper, lr0, decay_steps, decay_rate, beta1, beta2, advance ? 1 : 0);
+  IN_LAUNCH_CHECK("adam_prep_kernel");
+  return INDNET_OK;
+}
+
+extern "C" int indnet_adam_apply(indnet_stream st_, float* params, const float* grads, float* m, float* v, long long n,
+                                 const float* hyper, float beta1, float beta2, float eps, float grad_scale,
+                                 void* shadow_bf16) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(n >= 0 && hyper, "adam_apply: bad arguments");
+  if (n == 0) return INDNET_OK;
+  IN_REQUIRE(params && grads && m && v, "adam_apply: null pointer");
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
   adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,

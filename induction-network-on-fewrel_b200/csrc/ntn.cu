@@ -22,8 +22,11 @@ __device__ __forceinline__ float relu_nan(float v) { return v < 0.f ? 0.f : v; }
 __global__ void __launch_bounds__(NTN_NT)
 ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, const float* __restrict__ bias,
                     const int* __restrict__ labels, float* __restrict__ probs, float* __restrict__ loss_part,
-                    int* __restrict__ correct, int N, int S) {
+                    int* __restrict__ correct, int N, int S, float* __restrict__ out2, float* __restrict__ running,
+                    unsigned int* __restrict__ ticket) {
   extern __shared__ float pr[];   // [N]
+  __shared__ bool last;
+  __shared__ float sl[NTN_NT / 32], sa[NTN_NT / 32];
   const int row = blockIdx.x;
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nw = NTN_NT / 32;
   const int NS = N * S;
@@ -53,6 +56,30 @@ ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
     }
     loss_part[row] = l;
     correct[row] = (arg == y) ? 1 : 0;
+    if (ticket) {
+      // the block that finishes last folds the per-row partials - in row order, whatever the block schedule,
+      // so the sum is deterministic - exactly as loss_acc_reduce_kernel would in a launch of its own
+      __threadfence();
+      last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+  }
+  if (!ticket) return;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  const int rows = gridDim.x;
+  float l = 0.f, a = 0.f;
+  for (int i = threadIdx.x; i < rows; i += NTN_NT) { l += __ldcg(loss_part + i); a += (float)__ldcg(correct + i); }
+  l = warp_sum(l); a = warp_sum(a);
+  if (lane == 0) { sl[warp] = l; sa[warp] = a; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    l = 0.f; a = 0.f;
+    for (int i = 0; i < NTN_NT / 32; ++i) { l += sl[i]; a += sa[i]; }
+    const float loss = l / ((float)rows * (float)N), acc = a / (float)rows;
+    out2[0] = loss; out2[1] = acc;
+    if (running) { running[0] += loss; running[1] += acc; running[2] += 1.0f; }
+    *ticket = 0u;                   // ready for the next launch
   }
 }
 
@@ -155,12 +182,15 @@ __global__ void permute021_kernel(const float* __restrict__ in, float* __restric
 using namespace indnet;
 
 extern "C" int indnet_ntn_head_fwd(indnet_stream st_, const float* V, const float* w, const float* b, const int* labels,
-                                   float* probs, float* loss_part, int* correct, int rows, int N, int S) {
+                                   float* probs, float* loss_part, int* correct, int rows, int N, int S, float* out2,
+                                   float* running, unsigned int* ticket) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(rows >= 0 && N > 0 && S > 0, "ntn_head_fwd: bad sizes rows=%d N=%d S=%d", rows, N, S);
   if (rows == 0) return INDNET_OK;
   IN_REQUIRE(V && w && b && labels && probs && loss_part && correct, "ntn_head_fwd: null pointer");
-  ntn_head_fwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, b, labels, probs, loss_part, correct, N, S);
+  IN_REQUIRE(!out2 == !ticket, "ntn_head_fwd: out2 and ticket go together");
+  ntn_head_fwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, b, labels, probs, loss_part, correct, N, S, out2,
+                                                               running, ticket);
   IN_LAUNCH_CHECK("ntn_head_fwd_kernel");
   return INDNET_OK;
 }
@@ -181,12 +211,22 @@ extern "C" int indnet_ntn_head_bwd(indnet_stream st_, const float* V, const floa
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(rows >= 0 && N > 0 && S > 0, "ntn_head_bwd: bad sizes rows=%d N=%d S=%d", rows, N, S);
   IN_REQUIRE(N <= NTN_NT, "ntn_head_bwd: N=%d classes exceeds %d", N, NTN_NT);
-  IN_REQUIRE(V && w && probs && (labels || dprobs) && dlogit && dV && dw && db, "ntn_head_bwd: null pointer");
+  IN_REQUIRE(V && w && probs && (labels || dprobs) && dlogit && dV && !dw == !db, "ntn_head_bwd: null pointer");
   IN_REQUIRE(!dV_bf || ld_bf >= N * S, "ntn_head_bwd: bf16 row stride %d shorter than N*S", ld_bf);
+  if (rows > 0) {
+    ntn_head_bwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, probs, labels, dprobs, dlogit, dV, (__nv_bfloat16*)dV_bf, ld_bf, N, S, scale);
+    IN_LAUNCH_CHECK("ntn_head_bwd_kernel");
+  }
+  return dw ? indnet_ntn_head_dw(st_, V, dlogit, dw, db, rows, N, S) : INDNET_OK;
+}
+
+extern "C" int indnet_ntn_head_dw(indnet_stream st_, const float* V, const float* dlogit, float* dw, float* db, int rows,
+                                  int N, int S) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(rows >= 0 && N > 0 && S > 0, "ntn_head_dw: bad sizes rows=%d N=%d S=%d", rows, N, S);
+  IN_REQUIRE(V && dlogit && dw && db, "ntn_head_dw: null pointer");
   IN_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)N * S * N, st));
   if (rows == 0) { IN_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * N, st)); return INDNET_OK; }
-  ntn_head_bwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, probs, labels, dprobs, dlogit, dV, (__nv_bfloat16*)dV_bf, ld_bf, N, S, scale);
-  IN_LAUNCH_CHECK("ntn_head_bwd_kernel");
   int rpb = 64;
   int gy = ceil_div(rows, rpb);
   while (gy > 65535) { rpb *= 2; gy = ceil_div(rows, rpb); }

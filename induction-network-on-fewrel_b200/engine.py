@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import math
 from dataclasses import dataclass
+import contextlib
 from typing import Dict, Optional
 
 import numpy as np
@@ -252,6 +253,16 @@ class EpisodePipeline:
         self.grad_ready_hook = None   # callable(name): fired when a gradient slot is final ("M" is 95 % of the bytes
                                       # and is produced first, so its all-reduce can hide under the encoder BPTT)
         self._tag = None
+        # The backward pass is a DAG, not a chain: the weight-gradient GEMMs and M's Adam update hang off the chain
+        # of activation gradients.  They are issued on two side streams (forked from / joined back to the caller's
+        # stream with events, which a CUDA-graph capture turns into parallel branches).  INDNET_SERIAL_BWD=1 keeps
+        # everything on one stream.
+        import os as _os
+        self.branches = not _os.environ.get("INDNET_SERIAL_BWD")
+        self._side = None             # [stream, stream], created on first use (same priority as the caller's)
+        self._ev_dcv = None           # "dcv GEMM has read M's bf16 shadow" - the early Adam update of M waits on it
+        self._adam_m_done = False     # M's slice has had its update in this step already
+        self._dirty = set()           # side streams holding work the caller's stream has not waited for yet
         c = cfg
         f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
         i32 = lambda *s: torch.zeros(*s, dtype=torch.int32, device=self.dev)  # noqa: E731
@@ -283,6 +294,7 @@ class EpisodePipeline:
             self.loss_part = f(c.B * c.n_q)
             self.correct = i32(c.B * c.n_q)
         self.out2 = torch.zeros(2, dtype=torch.float32, device=self.dev)   # {loss, accuracy}
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=self.dev)   # last-block counter of the head kernel
         self.running = torch.zeros(3, dtype=torch.float32, device=self.dev)   # training-step sums {loss, accuracy, steps}
         self._bwd_ready = False
         self.bf16 = cfg.mode == "bf16"
@@ -330,6 +342,45 @@ class EpisodePipeline:
             e1.record()
             self.profile.append((self._tag or name, e0, e1))
         self.launches += 1
+
+    class _Branch:
+        """``with pipe._branch(i):`` issues the enclosed launches on side stream i, ordered after everything the
+        caller's stream holds at entry (and after the branch's own earlier work).  ``_join`` makes the caller's
+        stream wait for the branches."""
+
+        def __init__(self, pipe, i):
+            self.pipe, self.i = pipe, i
+
+        def __enter__(self):
+            pipe = self.pipe
+            if not pipe.branches:
+                return self
+            if pipe._side is None:
+                cur = torch.cuda.current_stream()
+                pipe._side = [torch.cuda.Stream(device=pipe.dev, priority=cur.priority) for _ in range(2)]
+            side = pipe._side[self.i]
+            side.wait_stream(torch.cuda.current_stream())
+            self._ctx = torch.cuda.stream(side)
+            self._ctx.__enter__()
+            pipe._dirty.add(self.i)
+            return self
+
+        def __exit__(self, *exc):
+            if self.pipe.branches:
+                self._ctx.__exit__(*exc)
+            return False
+
+    def _branch(self, i):
+        return EpisodePipeline._Branch(self, i)
+
+    def _join(self, *which):
+        if not self.branches or self._side is None:
+            return
+        cur = torch.cuda.current_stream()
+        for i in (which or tuple(self._dirty)):
+            if i in self._dirty:
+                cur.wait_stream(self._side[i])
+                self._dirty.discard(i)
 
     def profile_summary(self):
         """{tag: (calls, total_ms)} from the events collected while ``self.profile`` was a list."""
@@ -465,9 +516,8 @@ class EpisodePipeline:
                    batch=c.B, sA=(c.n_q * c.H, 0), sB=(NS * c.H, 0), sC=(c.n_q * NS, 0), tag="ntn_stage2")
         # a8-a10: relu, FC, sigmoid, squared error, argmax hit
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
-                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
-        self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
-                   ptr(self.running) if train else None, c.B * c.n_q, c.N)
+                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S,
+                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket))   # + loss / accuracy means
 
     def _encode_bf16(self, train: bool):
         """bf16 tensor-core mode: every large contraction runs on tcgen05 (fp32 accumulation); the
@@ -530,9 +580,8 @@ class EpisodePipeline:
         self._tc(0, 0, c.n_q, NS, c.H, self.eq_bf, c.H, self.Tp_bf, c.H, C=self.V, ldc=NS, batch=c.B,
                  sA=c.n_q * c.H, sB=NS * c.H, sC=c.n_q * NS, tag="ntn_stage2")
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
-                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S)
-        self._call("indnet_loss_acc_reduce", ptr(self.loss_part), ptr(self.correct), ptr(self.out2),
-                   ptr(self.running) if train else None, c.B * c.n_q, c.N)
+                   ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S,
+                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket))   # + loss / accuracy means
 
     # ------------------------------------------------------------------ backward
     def _alloc_bwd(self):
@@ -563,12 +612,15 @@ class EpisodePipeline:
             self.dx2 = f(2, c.T, 16) if self.tc_lstm else None
         self._bwd_ready = True
 
-    def backward(self):
-        """Hand-written backward of every forward op, in reverse order; fills ``self.p.grads``."""
+    def backward(self, early_adam: bool = False):
+        """Hand-written backward of every forward op, in reverse order; fills ``self.p.grads``.
+        ``early_adam`` (tensor-core mode, single process): M's Adam update is issued as soon as its gradient
+        and the last reader of M are done, underneath the rest of the pass; ``adam()`` then finishes the other
+        slots.  Data-parallel callers do the same from their ``grad_ready_hook`` with ``adam_m``."""
         if not self._bwd_ready:
             self._alloc_bwd()
         if self.bf16:
-            return self._backward_bf16()
+            return self._backward_bf16(early_adam)
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
@@ -584,10 +636,10 @@ class EpisodePipeline:
         # dM' = cv^T dT' ; dcv = dT' M'^T
         self._gemm(1, 0, c.H, c.S * c.H, c.B * c.N, ptr(self.cvec), c.H, ptr(self.dTp), c.S * c.H,
                    ptr(p.grad("M")), c.S * c.H, tag="ntn_dM")
-        if self.grad_ready_hook is not None:
-            self.grad_ready_hook("M")
         self._gemm(0, 1, c.B * c.N, c.H, c.S * c.H, ptr(self.dTp), c.S * c.H, ptr(p.view("M")), c.S * c.H,
                    ptr(self.dcvec), c.H, tag="ntn_dcv")
+        if self.grad_ready_hook is not None:     # after the last reader of M: the hook may update M in place
+            self.grad_ready_hook("M")
         # routing
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), None,
                    c.B * c.N, c.K, c.H, c.iters)
@@ -625,30 +677,44 @@ class EpisodePipeline:
         self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
                    ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
 
-    def _backward_bf16(self):
+    def _backward_bf16(self, early_adam: bool = False):
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
         # dV rows are N*S wide (1000 B in bf16): the bf16 copy has rows padded to a 16-byte multiple for TMA
         self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
-                   None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, ptr(p.grad("w")), ptr(p.grad("b")),
+                   None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, None, None,
                    rows, c.N, c.S, 1.0 / (rows * c.N))
-        # dqe_b = dV_b [n_q, N*S] * T'_b [N*S, H] ; dT'_b = dV_b^T [N*S, n_q] * qe_b [n_q, H]
-        self._tc(0, 1, c.n_q, c.H, NS, self.dV_bf, self.NSp, self.Tp_bf, c.H, C=self.deq, ldc=c.H, batch=c.B,
-                 sA=c.n_q * self.NSp, sB=NS * c.H, sC=c.n_q * c.H, splitk=1, tag="ntn_dqe")
+        with self._branch(0):
+            # dqe_b = dV_b [n_q, N*S] * T'_b [N*S, H]; FC weight / bias gradients (read V and dlogit only)
+            self._tc(0, 1, c.n_q, c.H, NS, self.dV_bf, self.NSp, self.Tp_bf, c.H, C=self.deq, ldc=c.H, batch=c.B,
+                     sA=c.n_q * self.NSp, sB=NS * c.H, sC=c.n_q * c.H, splitk=1, tag="ntn_dqe")
+            self._call("indnet_ntn_head_dw", ptr(self.V), ptr(self.dlogit), ptr(p.grad("w")), ptr(p.grad("b")),
+                       rows, c.N, c.S)
+        # dT'_b = dV_b^T [N*S, n_q] * qe_b [n_q, H]
         self._tc(1, 1, NS, c.H, c.n_q, self.dV_bf, self.NSp, self.eq_bf, c.H, Cb=self.dTp_bf, ldc=c.H, batch=c.B,
                  sA=c.n_q * self.NSp, sB=c.n_q * c.H, sC=NS * c.H, splitk=1, tag="ntn_dT")
-        # dM' = cv^T dT' (both operands stored [K][.]) ; dcv = dT' M'^T (both K-major)
-        self._tc(1, 1, c.H, c.S * c.H, c.B * c.N, self.cvec_bf, c.H, self.dTp_bf, c.S * c.H, C=p.grad("M"),
-                 splitk=1, tag="ntn_dM")
-        if self.grad_ready_hook is not None:
-            self.grad_ready_hook("M")
+        with self._branch(1):
+            # dM' = cv^T dT' (both operands stored [K][.]) - 96 % of the gradient bytes, off the critical path
+            self._tc(1, 1, c.H, c.S * c.H, c.B * c.N, self.cvec_bf, c.H, self.dTp_bf, c.S * c.H, C=p.grad("M"),
+                     splitk=1, tag="ntn_dM")
+        # dcv = dT' M'^T (both K-major)
         self._tc(0, 0, c.B * c.N, c.H, c.S * c.H, self.dTp_bf, c.S * c.H, p.view_bf("M"), c.S * c.H, C=self.dcvec,
                  tag="ntn_dcv")
+        if self._ev_dcv is None:
+            self._ev_dcv = torch.cuda.Event()
+        self._ev_dcv.record()
+        with self._branch(1):
+            if self.grad_ready_hook is not None:
+                self.grad_ready_hook("M")
+            elif early_adam:
+                self.adam_m()
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), ptr(self.dehat_bf),
                    c.B * c.N, c.K, c.H, c.iters)
+        with self._branch(0):
+            self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
         self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
-        self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
+        self._join(0)                 # deq
         # d(loss)/d(h): pooling path alpha_t * denc + Dense path dpre * W_a1^T.  With the tensor-core LSTM the
         # sum is formed once in the GEMM epilogue and written in bf16; otherwise it is accumulated in fp32.
         fused = self.tc_lstm
@@ -657,7 +723,8 @@ class EpisodePipeline:
             self._call("indnet_attn_fused_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
                        ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(p.view_bf(ATT_K)), ptr(self.dpre_bf), ptr(self.dhout_bf),
                        ptr(p.grad(ATT_W2)), ptr(p.grad(ATT_B)), c.X, c.L, c.H, c.n_s, c.NK)
-            self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
+            with self._branch(0):
+                self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
             return self._backward_bf16_lstm()
         # with the 16-byte kernel variant (H % 8 == 0) the W_a2 / Dense-bias gradients are summed over sentences
         # inside the pooling kernel; otherwise per-sentence partials + two column sums
@@ -708,11 +775,12 @@ class EpisodePipeline:
             gk = p.grad(kn)
             if self.tc_lstm:
                 # both weight gradients of the direction in one pass over dz: one CTA multiplies every dz tile
-                # with the stacked [x | h_prev] operand (two accumulators)
+                # with the stacked [x | h_prev] operand (two accumulators); the two directions run side by side
                 self._tag = "tc_gemm:lstm_dW"
                 try:
-                    self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
-                               ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0)
+                    with self._branch(0) if d == 1 else contextlib.nullcontext():
+                        self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
+                                   ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0)
                 finally:
                     self._tag = None
             else:
@@ -723,23 +791,49 @@ class EpisodePipeline:
             if not fused_dx:
                 self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
                          C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
-        g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
-        self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
-        self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
-        gw = None
-        if self.trainable_words:
-            gw = p.grad("word_embedding")
-            self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
-        if fused_dx:
-            self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
-                       ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
-        else:
-            self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
-                       ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+        with self._branch(1) if fused_dx else contextlib.nullcontext():
+            g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
+            self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
+            self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
+            gw = None
+            if self.trainable_words:
+                gw = p.grad("word_embedding")
+                self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
+            if fused_dx:
+                self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
+                           ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
+            else:
+                self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
+                           ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+        self._join()
 
     # ------------------------------------------------------------------ update (model/base.py:94-99)
+    def adam_m(self, grad_scale: float = 1.0):
+        """Adam update of M's slice alone, on the current stream, as soon as that stream holds M's final gradient
+        (after ntn_dM, or after its all-reduce): waits for the last reader of M's bf16 shadow (ntn_dcv), leaves
+        global_step alone.  The next ``adam()`` then updates the other slots and advances the step."""
+        p = self.p
+        n = p.offsets["w"]                     # M is the first slot of the flat buffer
+        if self._ev_dcv is not None:
+            torch.cuda.current_stream().wait_event(self._ev_dcv)
+        self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
+                   0.9, 0.999, 0)
+        self._call("indnet_adam_apply", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), n, ptr(p.hyper),
+                   0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf))
+        self._adam_m_done = True
+
     def adam(self, grad_scale: float = 1.0):
         p = self.p
+        self._join()
+        if self._adam_m_done:
+            n0 = p.offsets["w"]
+            self._adam_m_done = False
+            bf = p.params_bf[n0:] if p.params_bf is not None else None
+            self._call("indnet_adam_apply", ptr(p.params[n0:]), ptr(p.grads[n0:]), ptr(p.m[n0:]), ptr(p.v[n0:]),
+                       p.numel - n0, ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf))
+            self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps,
+                       self.decay_rate, 0.9, 0.999, 1)
+            return
         self._call("indnet_adam_step", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), p.numel,
                    ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
                    0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf))
@@ -747,7 +841,7 @@ class EpisodePipeline:
     def train_step(self):
         """fwd + bwd + Adam on the inputs currently in the static buffers (no host sync)."""
         self.forward(train=True)
-        self.backward()
+        self.backward(early_adam=self.grad_ready_hook is None)
         self.adam()
 
     # ------------------------------------------------------------------ results

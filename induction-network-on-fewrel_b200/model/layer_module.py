@@ -232,7 +232,8 @@ class _NeuralTensorLayer(torch.autograd.Function):
         labels = torch.zeros(B * nq, dtype=torch.int32, device=dev)
         lp = torch.empty(B * nq, device=dev)
         cr = torch.empty(B * nq, dtype=torch.int32, device=dev)
-        _call("indnet_ntn_head_fwd", ptr(V), ptr(wc), ptr(bc), ptr(labels), ptr(probs), ptr(lp), ptr(cr), B * nq, C, S)
+        _call("indnet_ntn_head_fwd", ptr(V), ptr(wc), ptr(bc), ptr(labels), ptr(probs), ptr(lp), ptr(cr), B * nq, C, S,
+              None, None, None)
         ctx.save_for_backward(cvb, qeb, Mp, wc, Tp, V, probs)
         ctx.batched = batched
         return probs if batched else probs[0]

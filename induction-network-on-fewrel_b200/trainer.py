@@ -72,6 +72,7 @@ class EpisodeTrainer:
             self.comm.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.comm):
                 self._dist().all_reduce(self.store.grads[: self.m_end], group=self.group)
+                self.pipe.adam_m(1.0 / self.world)     # M's update too runs under the rest of the backward pass
 
     def _grad_sync(self):
         if self.world <= 1:
@@ -86,7 +87,7 @@ class EpisodeTrainer:
     def train_body(self):
         """fwd + bwd + all-reduce + Adam on the episodes in the pipeline's input buffers."""
         self.pipe.forward(train=True)
-        self.pipe.backward()
+        self.pipe.backward(early_adam=self.world == 1)
         self._grad_sync()
         self.pipe.adam(grad_scale=1.0 / self.world)
 

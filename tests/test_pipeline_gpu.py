@@ -345,3 +345,36 @@ def test_hidden_size_256_cluster_recurrence_inference_parity(shape):
     assert e_h < BF16_TOL and e_enc < BF16_TOL and e_cv < BF16_TOL
     with pytest.raises(Exception, match="inference"):
         pipe.relation()
+
+
+def test_branched_backward_and_early_adam_match_the_serial_step():
+    """The backward pass issued as a DAG over side streams, with M's Adam update hoisted under the encoder's
+    BPTT (engine._backward_bf16, adam_m), against the same step issued serially with one whole-buffer Adam."""
+    cfg, tables, inputs, label, params = make_case("cfg0_5w5s", seed=8, keep_prob=0.9, mode="bf16")
+    out = []
+    for branched in (True, False):
+        pipe = build_pipeline(cfg, tables, params, seed=5)
+        pipe.branches = branched
+        pipe.set_inputs(inputs, label)
+        pipe.forward(train=True)
+        pipe.backward(early_adam=branched)
+        g = pipe.p.grads.clone()
+        pipe.adam()
+        torch.cuda.synchronize()
+        first = (g, pipe.p.params.clone(), pipe.p.m.clone(), pipe.p.v.clone(), pipe.p.params_bf.clone(), pipe.loss())
+        pipe.forward(train=True)
+        pipe.backward(early_adam=branched)
+        pipe.adam()
+        torch.cuda.synchronize()
+        out.append(first + (int(pipe.p.global_step.item()), pipe.p.hyper.clone(), pipe.loss()))
+    a, b = out
+    assert a[6] == b[6] == 2 and torch.equal(a[7], b[7])
+    assert a[5] == b[5]                                          # the forward is deterministic
+    # split-K reductions use float atomics, so two runs agree to rounding, not bitwise
+    for i in (0, 2, 3):
+        assert float((a[i] - b[i]).abs().max()) <= 1e-4 * float(b[i].abs().max()), i
+    # the first Adam step moves every weight by ~lr * sign(g): only entries whose gradient is at noise level may differ
+    moved = (a[1] - b[1]).abs() > 1e-6
+    assert float(moved.float().mean()) < 0.02
+    assert torch.equal(a[4].float(), a[1].to(torch.bfloat16).float())      # the bf16 shadow tracks both halves
+    assert abs(a[8] - b[8]) < 2e-2 * abs(b[8])                   # second step: same trajectory
