@@ -74,9 +74,11 @@ int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M, int N, int
  *   dkernel[D+u][4u] = [x | h_prev]^T * dz,  x_bf [T][64], hprev_bf [T][u], dz_bf [T][4u]
  * (autodiff of the LSTM kernel matmul, model/graph.py:44).  Overwrites dkernel (fp32, split-K reductions).
  * dbias (optional, [4u], overwritten): row D of the stacked product, i.e. the bias gradient sum_t dz[t] when
- * x carries 1.0 in column D (indnet_embed_fwd_bf16 writes it when D <= 62). */
+ * x carries 1.0 in column D (indnet_embed_fwd_bf16 writes it when D <= 62).  accumulate != 0: the caller has
+ * zeroed dkernel / dbias already (one memset for several gradient slots, off the critical path) and the split-K
+ * partial sums are added to what is there. */
 int indnet_tc_gemm_lstm_dw(indnet_stream st, const void* x_bf, const void* hprev_bf, const void* dz_bf,
-                           float* dkernel, float* dbias, long long T, int D, int u, int splitk);
+                           float* dkernel, float* dbias, long long T, int D, int u, int splitk, int accumulate);
 /* FP32-accurate tensor-core mode (the reference graph is fp32, model/graph.py:47): every fp32 operand is split into three
  * bf16 matrices, x = head + middle + tail (24 mantissa bits), by indnet_cast_bf16_split3 - rows [rows][cols] with input
  * stride ld_in are written with the padded stride ld_out (a multiple of 8, zeros in the padding) - and indnet_tc_gemm3
@@ -134,7 +136,9 @@ int indnet_sample_gather(indnet_stream st, const int* scopes, const int* t_word,
 int indnet_sampler_set_budget(double pct, long long slack);
 /* 1 (default): the parallel path - "where does a permutation that starts at draw p end" is tabulated for every draw of
  * the window by the whole GPU, the serial part is one table lookup per permutation, the permutations are then replayed
- * in parallel (needs at most three distinct relation sizes, else the serial walker runs).  0: always the serial walker.
+ * in parallel (needs at most three distinct relation sizes, else the serial walker runs); when every relation has the
+ * same size (FewRel) the lookups are composed into one per EPISODE first, so the serial part is B lookups instead of
+ * B*(N+1).  2: the parallel path without that composition.  0: always the serial walker.
  * Same draws, same results either way.  Process-wide. */
 int indnet_sampler_set_path(int allow_parallel);
 /* Episode-sharded data parallelism: every rank walks the SAME streams for the global batch of B
@@ -258,10 +262,11 @@ int indnet_attn_fused_fwd(indnet_stream st, const void* hout_bf, const void* wa1
  * weighted-sum / score / tanh backward on the CUDA cores, dpre written in place as the A operand of the tcgen05 GEMM
  * dpre * Wa1^T, the pooling-path term alpha_t * denc added in the epilogue.  Writes dpre_bf [X*L][H] (operand of the
  * Dense-kernel gradient GEMM), dhout_bf [X*L][H], and the W_a2 / Dense-bias gradients dw2_sum / dba_sum [H]
- * (overwritten).  Autodiff of model/layer_module.py:65-96. */
+ * (overwritten; accumulate != 0: added to, the caller zeroed them).  Autodiff of model/layer_module.py:65-96. */
 int indnet_attn_fused_bwd(indnet_stream st, const float* denc_a, const float* denc_b, const void* hout_bf,
                           const void* proj_bf, const float* alphas, const float* w_a2, const void* wa1_bf, void* dpre_bf,
-                          void* dhout_bf, float* dw2_sum, float* dba_sum, int X, int L, int H, int group, int split);
+                          void* dhout_bf, float* dw2_sum, float* dba_sum, int X, int L, int H, int group, int split,
+                          int accumulate);
 int indnet_attn_pool_fwd_bf16(indnet_stream st, const void* hout_bf, const void* proj_bf, const int* mask,
                               const float* w_a2, float* enc_a, float* enc_b, void* enc_a_bf, void* enc_b_bf,
                               float* alphas, int X, int L, int H, int group, int split);

@@ -562,7 +562,7 @@ extern "C" int indnet_debug_attn(long long* out) { return (int)cudaMemcpyFromSym
 extern "C" int indnet_attn_fused_bwd(indnet_stream st_, const float* denc_a, const float* denc_b, const void* hout_bf,
                                      const void* proj_bf, const float* alphas, const float* w_a2, const void* wa1_bf,
                                      void* dpre_bf, void* dhout_bf, float* dw2_sum, float* dba_sum, int X, int L, int H,
-                                     int group, int split) {
+                                     int group, int split, int accumulate) {
   using namespace indnet;
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(X >= 0 && L > 0 && H > 0, "attn_fused_bwd: bad sizes X=%d L=%d H=%d", X, L, H);
@@ -572,8 +572,10 @@ extern "C" int indnet_attn_fused_bwd(indnet_stream st_, const float* denc_a, con
   IN_REQUIRE(group > 0 && split >= 0 && split <= group && X % group == 0, "attn_fused_bwd: bad group/split %d/%d", group, split);
   IN_REQUIRE(split == group || denc_b, "attn_fused_bwd: second gradient input missing");
   IN_REQUIRE((((uintptr_t)dpre_bf | (uintptr_t)dhout_bf) & 15) == 0, "attn_fused_bwd: outputs must be 16-byte aligned");
-  IN_CUDA(cudaMemsetAsync(dw2_sum, 0, sizeof(float) * H, st));
-  IN_CUDA(cudaMemsetAsync(dba_sum, 0, sizeof(float) * H, st));
+  if (!accumulate) {
+    IN_CUDA(cudaMemsetAsync(dw2_sum, 0, sizeof(float) * H, st));
+    IN_CUDA(cudaMemsetAsync(dba_sum, 0, sizeof(float) * H, st));
+  }
   if (X == 0) return INDNET_OK;
   AttnFusedBwdP p;
   p.denc_a = denc_a; p.denc_b = denc_b; p.alphas = alphas; p.w2 = w_a2;

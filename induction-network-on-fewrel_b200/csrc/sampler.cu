@@ -110,6 +110,9 @@ struct SmpHdr {
   int use_v2;                    // 1: the parallel path (jump tables + chain + replay) serves this call, 0: the serial walker
   int ntab;                      // v2: number of distinct permutation lengths (class scopes + the query permutation)
   int sizes[4];                  // v2: those lengths
+  int uni_zc, uni_zq;            // v2, every relation the same size (FewRel): table index of the class / query
+                                 // permutation length - every episode is then the same job sequence, and the chain
+                                 // steps one EPISODE per lookup through the composed table (smp_epi_kernel); else -1
   uint32_t py_backup[MT_N + 1];  // Python stream as handed in: a failing call puts it back (streams unchanged on error)
 };
 
@@ -121,17 +124,21 @@ __global__ void smp_plan_kernel(SmpHdr* __restrict__ h, const uint32_t* __restri
   if (ahead == 0 && threadIdx.x == 0) {
     // the parallel path tabulates "where does a permutation of length n end when it starts at draw p" for every
     // distinct n: feasible when the relations have at most three distinct sizes (FewRel: one)
-    int nt = 0, sz[4] = {0, 0, 0, 0};
+    int nt = 0, nt_rel = 0, zq = 0, sz[4] = {0, 0, 0, 0};
     bool ok = allow_v2 != 0;
     for (int r = 0; r <= R && ok; ++r) {
       const int n = r < R ? scopes[2 * r + 1] - scopes[2 * r] : nq;
       bool seen = false;
-      for (int k = 0; k < nt; ++k) seen = seen || sz[k] == n;
-      if (!seen) { if (nt < 4) sz[nt++] = n; else ok = false; }
+      for (int k = 0; k < nt; ++k) if (sz[k] == n) { seen = true; zq = k; }
+      if (!seen) { if (nt < 4) { zq = nt; sz[nt++] = n; } else ok = false; }
+      if (r == R - 1) nt_rel = nt;
     }
     h->use_v2 = ok ? 1 : 0;
     h->ntab = ok ? nt : 0;
     for (int k = 0; k < 4; ++k) h->sizes[k] = sz[k];
+    const bool uni = ok && allow_v2 == 1 && nt_rel == 1;
+    h->uni_zc = uni ? 0 : -1;
+    h->uni_zq = uni ? zq : -1;
   }
   if (ahead == 0) {
     bool ok = h->magic == magic;
@@ -796,9 +803,29 @@ __global__ void smp_jump_kernel(const SmpHdr* __restrict__ h, const unsigned cha
   G[idx] = SMP_NOEND;                                      // runs past the generated window
 }
 
-// One warp; lane 0 chains the jobs through the jump tables, then the warp hands the stream back.
+// Every relation the same size: an episode is always N class permutations of that length followed by the query
+// permutation, so E[p] = G_q(G_c(... G_c(p))) - the draw position after one whole EPISODE that starts at p - is
+// again job independent: one thread per position, N + 1 dependent lookups each, all positions in parallel.
+__global__ void smp_epi_kernel(const SmpHdr* __restrict__ h, const uint32_t* __restrict__ G, long long nblk, int N,
+                               uint32_t* __restrict__ E) {
+  if (!h->use_v2 || h->uni_zc < 0) return;
+  const long long npos = nblk * TB;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= npos) return;
+  const uint32_t* Gc = G + (long long)h->uni_zc * npos;
+  const uint32_t* Gq = G + (long long)h->uni_zq * npos;
+  uint32_t o = (uint32_t)idx;
+  for (int c = 0; c < N && o != SMP_NOEND; ++c) o = ((long long)o < npos) ? Gc[o] : SMP_NOEND;
+  if (o != SMP_NOEND) o = ((long long)o < npos) ? Gq[o] : SMP_NOEND;
+  E[idx] = o;
+}
+
+// One warp.  General case: lane 0 chains the jobs through the jump tables, one dependent lookup per job.  Uniform
+// relation sizes: lane 0 chains the EPISODES through E (N + 1 times fewer dependent lookups), then the lanes expand
+// the jobs inside the episodes in parallel.  Then the warp hands the stream back.
 __global__ void smp_chain_kernel(SmpHdr* __restrict__ hdr, const uint32_t* __restrict__ keys, uint32_t kmask, long long nblk,
-                                 const uint32_t* __restrict__ G, const int* __restrict__ jsize, int jobs,
+                                 const uint32_t* __restrict__ G, const uint32_t* __restrict__ E,
+                                 const int* __restrict__ jsize, int jobs, int N,
                                  uint32_t* __restrict__ start, uint32_t* __restrict__ np_state, uint32_t* __restrict__ py_state,
                                  int* __restrict__ status) {
   if (!hdr->use_v2) return;
@@ -807,7 +834,35 @@ __global__ void smp_chain_kernel(SmpHdr* __restrict__ hdr, const uint32_t* __res
   const long long base = hdr->win_start << 6, npos = nblk * TB;
   long long pos = hdr->apos;
   int flag = SMP_OK;
-  if (lane == 0) {
+  bool uni = hdr->uni_zc >= 0;
+  if (uni) {                                               // a job the generator flagged (jsize < 0): the serial chain reports it
+    bool bad = false;
+    for (int j = lane; j < jobs; j += 32) bad = bad || jsize[j] < 0;
+    uni = !__any_sync(0xffffffffu, bad);
+  }
+  if (uni) {
+    const int P = N + 1, B = jobs / P;
+    if (lane == 0) {
+      uint32_t o = (uint32_t)(pos - base);
+      for (int b = 0; b < B; ++b) {
+        start[(long long)b * P] = o;
+        if ((long long)o >= npos) { flag = SMP_STREAM_BUDGET; break; }
+        const uint32_t e = E[o];
+        if (e == SMP_NOEND) { flag = SMP_STREAM_BUDGET; break; }
+        o = e;
+      }
+      pos = base + o;
+    }
+    flag = __shfl_sync(0xffffffffu, flag, 0);
+    __syncwarp();
+    if (flag == SMP_OK) {
+      const uint32_t* Gc = G + (long long)hdr->uni_zc * npos;
+      for (int b = lane; b < B; b += 32) {                 // every start inside the episode precedes E[.] < npos
+        uint32_t o = start[(long long)b * P];
+        for (int c = 1; c < P; ++c) { o = Gc[o]; start[(long long)b * P + c] = o; }
+      }
+    }
+  } else if (lane == 0) {
     uint32_t o = (uint32_t)(pos - base);
     for (int j = 0; j < jobs; ++j) {
       const int n = jsize[j];
@@ -889,13 +944,12 @@ smp_replay_kernel(const SmpHdr* __restrict__ hdr, const uint32_t* __restrict__ k
 
 // Value that ends at position p after the Fisher-Yates swaps (i = n-1..1, swap a[i], a[j_i]) applied
 // to the identity: walk the swaps backwards (i ascending) moving the tracked position.
-__global__ void sampler_trace_kernel(const int* __restrict__ scopes, const int* __restrict__ classes,
-                                     const int* __restrict__ jlist, int B, int N, int K, int Q, int n_max,
-                                     int pick_max, int* __restrict__ picks) {
-  const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int jobs = B * (N + 1);
-  if (id >= (long long)jobs * pick_max) return;
-  const int job = (int)(id / pick_max), p = (int)(id % pick_max);
+__global__ void __launch_bounds__(128)
+sampler_trace_kernel(const int* __restrict__ scopes, const int* __restrict__ classes,
+                     const int* __restrict__ jlist, int B, int N, int K, int Q, int n_max,
+                     int pick_max, int* __restrict__ picks, int smem_ints) {
+  extern __shared__ int sj[];                       // the job's swap list, staged once (every thread walks all of it)
+  const int job = blockIdx.x;
   const int b = job / (N + 1), ci = job % (N + 1);
   int n, want;
   if (ci < N) {
@@ -906,15 +960,22 @@ __global__ void sampler_trace_kernel(const int* __restrict__ scopes, const int* 
     n = N * Q;
     want = N * Q;
   }
-  if (p >= want || p >= n) return;
   const int* jl = jlist + (long long)job * n_max;
-  int pos = p;
-  for (int i = 1; i < n; ++i) {
-    const int j = jl[i];
-    if (pos == i) pos = j;
-    else if (pos == j) pos = i;
+  const bool staged = n <= smem_ints;
+  if (staged) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) sj[i] = jl[i];
+    __syncthreads();
+    jl = sj;
   }
-  picks[(long long)job * pick_max + p] = pos;
+  for (int p = threadIdx.x; p < want && p < n; p += blockDim.x) {
+    int pos = p;
+#pragma unroll 4
+    for (int i = 1; i < n; ++i) {
+      const int j = jl[i];
+      pos = (pos == i) ? j : ((pos == j) ? i : pos);
+    }
+    picks[(long long)job * pick_max + p] = pos;
+  }
 }
 
 // rows[b][r]: r < N*K -> support (class-major); else query slot p = r - N*K holding pre-permutation
@@ -959,7 +1020,7 @@ struct SmpLayout {
   long long kcap, bcap;            // key ring (words, power of two) and table ring (blocks): two windows + slack
   int cb_log, rc;                  // walker staging: 2^cb_log blocks per chunk, rc chunk slots (-1: does not fit)
   long long smem_bytes;
-  long long o_hdr, o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, o_jump, o_start, sec_cap, bytes;
+  long long o_hdr, o_classes, o_jsize, o_jlist, o_picks, o_keys, o_tab, o_seclog, o_jump, o_epi, o_start, sec_cap, bytes;
 };
 static double expected_draws(long long n) {      // E[draws] of NumPy's permutation(n) (rejection sampling)
   double e = 0.0;
@@ -972,7 +1033,7 @@ static double expected_draws(long long n) {      // E[draws] of NumPy's permutat
 }
 // stream budget of one call: E[draws] * (1 + g_budget_pct) + g_budget_slack (indnet_sampler_set_budget: tests
 // shrink it to exercise the "budget exceeded -> streams unchanged -> retry in smaller batches" path)
-static int g_allow_v2 = 1;          // indnet_sampler_set_path: 0 forces the serial walker
+static int g_allow_v2 = 1;          // indnet_sampler_set_path: 0 forces the serial walker, 2 the per-job chain
 static double g_budget_pct = 0.03;
 static long long g_budget_slack = 8192;
 static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
@@ -1015,6 +1076,7 @@ static SmpLayout smp_layout(int B, int N, int K, int Q, int n_max) {
   L.o_seclog = o;  o = al(o + 16LL * L.sec_cap);
   L.o_start = o;   o = al(o + 4LL * L.jobs);
   L.o_jump = o;    o = al(o + 4LL * 4 * L.nblk * TB);        // G_n[p] for up to four lengths n
+  L.o_epi = o;     o = al(o + 4LL * L.nblk * TB);            // E[p]: the same for one whole episode
   L.bytes = o;
   return L;
 }
@@ -1091,7 +1153,10 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
     const long long work = 4 * L.nblk * TB;                  // upper bound (ntab <= 4): surplus threads leave at once
     smp_jump_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(hdr, tab, bcap, (int)L.n_states, L.nblk, G);
     IN_LAUNCH_CHECK("smp_jump_kernel");
-    smp_chain_kernel<<<1, 32, 0, st>>>(hdr, keys, kmask, L.nblk, G, jsize, (int)L.jobs, jstart, np_state, py_state, status);
+    uint32_t* E = (uint32_t*)(base + L.o_epi);
+    smp_epi_kernel<<<(unsigned)((L.nblk * TB + 255) / 256), 256, 0, st>>>(hdr, G, L.nblk, N, E);
+    IN_LAUNCH_CHECK("smp_epi_kernel");
+    smp_chain_kernel<<<1, 32, 0, st>>>(hdr, keys, kmask, L.nblk, G, E, jsize, (int)L.jobs, N, jstart, np_state, py_state, status);
     IN_LAUNCH_CHECK("smp_chain_kernel");
     smp_replay_kernel<<<ceil_div(L.jobs, 4), 128, 0, st>>>(hdr, keys, kmask, jstart, jsize, (int)L.jobs, (int)L.stride, jlist);
     IN_LAUNCH_CHECK("smp_replay_kernel");
@@ -1103,8 +1168,11 @@ static int sample_walk(cudaStream_t st, unsigned int* py_state, unsigned int* np
   smp_fill_kernel<<<ceil_div(L.sec_cap << L.cb_log, 128), 128, 0, st>>>(tab, bcap, (int)L.n_states, seclog, hdr, L.cb_log,
                                                                         (int)L.stride, jlist);
   IN_LAUNCH_CHECK("smp_fill_kernel");
-  sampler_trace_kernel<<<ceil_div(L.jobs * L.pick_max, 128), 128, 0, st>>>(scopes, classes, jlist, B, N, K, Q,
-                                                                           (int)L.stride, (int)L.pick_max, picks);
+  {
+    const int tr_ints = L.stride <= 11 * 1024 ? (int)L.stride : 0;     // <= 44 KB: within the default dynamic limit
+    sampler_trace_kernel<<<(unsigned)L.jobs, 128, sizeof(int) * (size_t)tr_ints, st>>>(
+        scopes, classes, jlist, B, N, K, Q, (int)L.stride, (int)L.pick_max, picks, tr_ints);
+  }
   IN_LAUNCH_CHECK("sampler_trace_kernel");
   IN_CUDA(cudaStreamWaitEvent(st, ev_join[dev], 0));    // join: the next call's plan must see the finished build
   return INDNET_OK;
@@ -1173,6 +1241,6 @@ extern "C" int indnet_sampler_set_budget(double pct, long long slack) {
 }
 
 extern "C" int indnet_sampler_set_path(int allow_parallel) {
-  g_allow_v2 = allow_parallel ? 1 : 0;
+  g_allow_v2 = (allow_parallel == 2) ? 2 : (allow_parallel ? 1 : 0);
   return INDNET_OK;
 }

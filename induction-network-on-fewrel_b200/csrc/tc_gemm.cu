@@ -695,7 +695,8 @@ extern "C" int indnet_tc_gemm_rank1(indnet_stream st, int a_mn, int b_mn, int M,
 }
 
 extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const void* hprev_bf, const void* dz_bf,
-                                      float* dkernel, float* dbias, long long T, int D, int u, int splitk) {
+                                      float* dkernel, float* dbias, long long T, int D, int u, int splitk,
+                                      int accumulate) {
   cudaStream_t st = (cudaStream_t)st_;
   const int N = 4 * u;
   IN_REQUIRE(T > 0 && D > 0 && D <= 64 && u == 128, "tc_gemm_lstm_dw: needs E + 10 <= 64 and hidden_size 128 (D=%d u=%d)", D, u);
@@ -710,10 +711,10 @@ extern "C" int indnet_tc_gemm_lstm_dw(indnet_stream st_, const void* x_bf, const
   TcDualP p;
   IN_REQUIRE(!dbias || (((uintptr_t)dbias & 15) == 0 && D < 64), "tc_gemm_lstm_dw: dbias needs 16-byte alignment and D < 64");
   p.C = dkernel; p.dbias = dbias; p.D = D; p.N = N; p.K = (int)T; p.ldc = N;
-  if (dbias) IN_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * N, st));
+  if (dbias && !accumulate) IN_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * N, st));
   p.kb_per_split = ceil_div(total_kb, splitk);
   splitk = ceil_div(total_kb, p.kb_per_split);
-  IN_CUDA(cudaMemsetAsync(dkernel, 0, sizeof(float) * (size_t)(D + u) * N, st));
+  if (!accumulate) IN_CUDA(cudaMemsetAsync(dkernel, 0, sizeof(float) * (size_t)(D + u) * N, st));
   CUtensorMap tmX, tmH, tmB;
   int rc = make_tmap_bf16(&tmX, x_bf, 64, T, 64, 1, 0, 64, G_BK);           // [T][64]: box 64 features x 64 tokens
   if (rc) return rc;

@@ -260,7 +260,6 @@ class EpisodePipeline:
         import os as _os
         self.branches = not _os.environ.get("INDNET_SERIAL_BWD")
         self._side = None             # [stream, stream], created on first use (same priority as the caller's)
-        self._ev_dcv = None           # "dcv GEMM has read M's bf16 shadow" - the early Adam update of M waits on it
         self._adam_m_done = False     # M's slice has had its update in this step already
         self._dirty = set()           # side streams holding work the caller's stream has not waited for yet
         c = cfg
@@ -685,7 +684,15 @@ class EpisodePipeline:
         self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
                    None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, None, None,
                    rows, c.N, c.S, 1.0 / (rows * c.N))
+        # every gradient slot that is reduced with atomics later in the pass (attention bias / W_a2, the LSTM kernels
+        # and biases, the position tables: adjacent slots of the flat buffer) is zeroed by ONE memset here, on a
+        # side branch, instead of seven memset nodes in front of the kernels on the critical path
+        self._pre0 = bool(self.tc_lstm and self.fused_attn and c.H <= 256 and self._fused_dx())
         with self._branch(0):
+            if self._pre0:
+                z0 = p.offsets[ATT_B]
+                z1 = p.offsets["pos2_embedding"] + p.grad("pos2_embedding").numel()
+                self._call("indnet_memset", ptr(p.grads[z0:]), 0, (z1 - z0) * 4)
             # dqe_b = dV_b [n_q, N*S] * T'_b [N*S, H]; FC weight / bias gradients (read V and dlogit only)
             self._tc(0, 1, c.n_q, c.H, NS, self.dV_bf, self.NSp, self.Tp_bf, c.H, C=self.deq, ldc=c.H, batch=c.B,
                      sA=c.n_q * self.NSp, sB=NS * c.H, sC=c.n_q * c.H, splitk=1, tag="ntn_dqe")
@@ -701,14 +708,9 @@ class EpisodePipeline:
         # dcv = dT' M'^T (both K-major)
         self._tc(0, 0, c.B * c.N, c.H, c.S * c.H, self.dTp_bf, c.S * c.H, p.view_bf("M"), c.S * c.H, C=self.dcvec,
                  tag="ntn_dcv")
-        if self._ev_dcv is None:
-            self._ev_dcv = torch.cuda.Event()
-        self._ev_dcv.record()
-        with self._branch(1):
-            if self.grad_ready_hook is not None:
-                self.grad_ready_hook("M")
-            elif early_adam:
-                self.adam_m()
+        if self.grad_ready_hook is not None:
+            with self._branch(1):
+                self.grad_ready_hook("M")          # after ntn_dM: the data-parallel all-reduce of M's gradient starts here
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), ptr(self.dehat_bf),
                    c.B * c.N, c.K, c.H, c.iters)
         with self._branch(0):
@@ -722,9 +724,17 @@ class EpisodePipeline:
             # pooling / softmax / score / tanh backward + dpre * Wa1^T + alpha_t * denc in ONE kernel
             self._call("indnet_attn_fused_bwd", ptr(self.des), ptr(self.deq), ptr(self.hout_bf), ptr(self.proj_bf),
                        ptr(self.alphas), ptr(p.view(ATT_W2)), ptr(p.view_bf(ATT_K)), ptr(self.dpre_bf), ptr(self.dhout_bf),
-                       ptr(p.grad(ATT_W2)), ptr(p.grad(ATT_B)), c.X, c.L, c.H, c.n_s, c.NK)
+                       ptr(p.grad(ATT_W2)), ptr(p.grad(ATT_B)), c.X, c.L, c.H, c.n_s, c.NK, int(self._pre0))
             with self._branch(0):
                 self._tc(1, 1, c.H, c.H, c.T, self.hout_bf, c.H, self.dpre_bf, c.H, C=p.grad(ATT_K), tag="attn_dW")
+            if early_adam:
+                # M's Adam update (207 MB of HBM traffic) goes under the BPTT kernel, whose input tiles are prefetched
+                # two steps ahead - beside the latency-bound routing / attention kernels it cost them 2.5x
+                with self._branch(1):
+                    if self.grad_ready_hook is not None:
+                        self.grad_ready_hook("M:update")
+                    else:
+                        self.adam_m()
             return self._backward_bf16_lstm()
         # with the 16-byte kernel variant (H % 8 == 0) the W_a2 / Dense-bias gradients are summed over sentences
         # inside the pooling kernel; otherwise per-sentence partials + two column sums
@@ -752,13 +762,19 @@ class EpisodePipeline:
                      splitk=1, tag="attn_dh")
         return self._backward_bf16_lstm()
 
+    def _fused_dx(self):
+        import os as _os
+        c = self.cfg
+        return bool(self.tc_lstm and not self.trainable_words and c.D - c.E <= 16
+                    and not _os.environ.get("INDNET_NO_FUSED_DX"))
+
     def _backward_bf16_lstm(self):
         c, p = self.cfg, self.p
         u4 = 4 * c.u
         # with a frozen word table only the 2 x 5 position columns of dx are needed: the BPTT kernel forms
         # them itself (per direction) instead of two GEMM launches that would re-read all of dz
-        import os as _os
-        fused_dx = self.tc_lstm and not self.trainable_words and c.D - c.E <= 16 and not _os.environ.get("INDNET_NO_FUSED_DX")
+        fused_dx = self._fused_dx()
+        pre0 = getattr(self, "_pre0", False)
         if self.tc_lstm:
             self._call("indnet_lstm_bwd_tc", ptr(self.dhout_bf), ptr(self.gates_bf), ptr(self.cstate_bf),
                        ptr(p.view_bf(FW_K)), ptr(p.view_bf(BW_K)), ptr(self.dz_bf),
@@ -771,7 +787,17 @@ class EpisodePipeline:
                        ptr(self.whT), ptr(self.dz), c.X, c.L, c.u, self._last_keep, self.seed, ptr(p.global_step))
             self._cast(self.dz, self.dz_bf, "dz")
         n0 = 0 if self.trainable_words else c.E
-        for d, (kn, bn) in enumerate(((FW_K, FW_B), (BW_K, BW_B))):
+        g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
+        if fused_dx:
+            # side branches first (a branch forks from what the caller's stream holds at that moment)
+            with self._branch(1):
+                if not pre0:
+                    self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
+                    self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
+                self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
+                           ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
+        for d in ((1, 0) if self.tc_lstm else (0, 1)):
+            kn, bn = ((FW_K, FW_B), (BW_K, BW_B))[d]
             gk = p.grad(kn)
             if self.tc_lstm:
                 # both weight gradients of the direction in one pass over dz: one CTA multiplies every dz tile
@@ -780,7 +806,7 @@ class EpisodePipeline:
                 try:
                     with self._branch(0) if d == 1 else contextlib.nullcontext():
                         self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
-                                   ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0)
+                                   ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0, int(pre0))
                 finally:
                     self._tag = None
             else:
@@ -791,31 +817,24 @@ class EpisodePipeline:
             if not fused_dx:
                 self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
                          C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
-        with self._branch(1) if fused_dx else contextlib.nullcontext():
-            g1, g2 = p.grad("pos1_embedding"), p.grad("pos2_embedding")
+        if not fused_dx:
             self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
             self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
             gw = None
             if self.trainable_words:
                 gw = p.grad("word_embedding")
                 self._call("indnet_memset", ptr(gw), 0, gw.numel() * 4)
-            if fused_dx:
-                self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
-                           ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
-            else:
-                self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
-                           ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
+            self._call("indnet_embed_bwd", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(self.dx), ptr(gw),
+                       ptr(g1), ptr(g2), c.T, c.E, POS_DIM, 2 * c.L)
         self._join()
 
     # ------------------------------------------------------------------ update (model/base.py:94-99)
     def adam_m(self, grad_scale: float = 1.0):
         """Adam update of M's slice alone, on the current stream, as soon as that stream holds M's final gradient
-        (after ntn_dM, or after its all-reduce): waits for the last reader of M's bf16 shadow (ntn_dcv), leaves
-        global_step alone.  The next ``adam()`` then updates the other slots and advances the step."""
+        (after ntn_dM, or after its all-reduce) AND is ordered after the last reader of M's bf16 shadow (ntn_dcv);
+        leaves global_step alone.  The next ``adam()`` then updates the other slots and advances the step."""
         p = self.p
         n = p.offsets["w"]                     # M is the first slot of the flat buffer
-        if self._ev_dcv is not None:
-            torch.cuda.current_stream().wait_event(self._ev_dcv)
         self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
                    0.9, 0.999, 0)
         self._call("indnet_adam_apply", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), n, ptr(p.hyper),

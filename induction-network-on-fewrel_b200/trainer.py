@@ -68,11 +68,16 @@ class EpisodeTrainer:
         return dist
 
     def _on_grad_ready(self, name):
-        if self.overlap and name == "M":
+        if not self.overlap:
+            return
+        if name == "M":                 # M's gradient is final: its all-reduce runs under the rest of the backward pass
             self.comm.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.comm):
                 self._dist().all_reduce(self.store.grads[: self.m_end], group=self.group)
-                self.pipe.adam_m(1.0 / self.world)     # M's update too runs under the rest of the backward pass
+        elif name == "M:update":        # ... and so does its Adam update, placed under the encoder's BPTT kernel
+            self.comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm):
+                self.pipe.adam_m(1.0 / self.world)
 
     def _grad_sync(self):
         if self.world <= 1:
@@ -87,7 +92,7 @@ class EpisodeTrainer:
     def train_body(self):
         """fwd + bwd + all-reduce + Adam on the episodes in the pipeline's input buffers."""
         self.pipe.forward(train=True)
-        self.pipe.backward(early_adam=self.world == 1)
+        self.pipe.backward(early_adam=self.world == 1 or self.overlap)
         self._grad_sync()
         self.pipe.adam(grad_scale=1.0 / self.world)
 
@@ -211,6 +216,31 @@ class EpisodeTrainer:
         with torch.cuda.stream(self.stream):
             v = self.pipe.out2.cpu()
         return float(v[0]), float(v[1])
+
+    class _Pending:
+        """Result of ``read_async``: ``get()`` waits for that step's copy only (not for later steps)."""
+
+        def __init__(self, buf, ev):
+            self.buf, self.ev = buf, ev
+
+        def get(self):
+            self.ev.synchronize()
+            return float(self.buf[0]), float(self.buf[1])
+
+    def read_async(self):
+        """Enqueues the 8-byte D2H copy of the last step's {loss, accuracy} into a pinned slot and returns a handle;
+        a loop that calls ``get()`` on the PREVIOUS step's handle logs every step without ever draining the GPU
+        (the reference's ``sess.run`` returns the same two numbers synchronously, model/base.py:148-152).  At most
+        ``len(self._rd)`` handles may be outstanding."""
+        if not hasattr(self, "_rd"):
+            self._rd = [(torch.zeros(2, dtype=torch.float32).pin_memory(), torch.cuda.Event()) for _ in range(8)]
+            self._rd_i = 0
+        buf, ev = self._rd[self._rd_i % len(self._rd)]
+        self._rd_i += 1
+        with torch.cuda.stream(self.stream):
+            buf.copy_(self.pipe.out2, non_blocking=True)
+            ev.record(self.stream)
+        return EpisodeTrainer._Pending(buf, ev)
 
     def read_running(self, reset: bool = False):
         """(mean loss, mean accuracy, steps) since the last reset - model/base.py:156-163's running means,

@@ -195,7 +195,7 @@ def test_parallel_and_serial_sampler_paths_draw_the_same_episodes():
         tables["word_vec_mat"] = base["word_vec_mat"]
         B, N, K, Q = 9, 5, 3, 4
         got = []
-        for parallel in (1, 0):
+        for parallel in (1, 2, 0):
             LIB.call("indnet_sampler_set_path", parallel)
             try:
                 ld = JSONFileDataLoader.from_tables(tables)
@@ -217,4 +217,4 @@ def test_parallel_and_serial_sampler_paths_draw_the_same_episodes():
                     for k in KEYS:
                         assert np.array_equal(path[0][half][k][b], want[half * B + b][0][k]), (sizes[:5], half, b, k)
                     assert np.array_equal(path[1][half][b], want[half * B + b][1])
-        assert got[0][2:] == got[1][2:]
+        assert got[0][2:] == got[1][2:] == got[2][2:]

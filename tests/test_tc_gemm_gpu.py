@@ -110,7 +110,7 @@ def test_tc_gemm_lstm_dw_stacked_operand(T, D):
     dz = torch.randn(T, 4 * u, generator=g, device="cuda").to(torch.bfloat16)
     out = torch.full((D + u, 4 * u), float("nan"), device="cuda")
     dbias = torch.full((4 * u,), float("nan"), device="cuda") if D <= 62 else None
-    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(x), ptr(h), ptr(dz), ptr(out), ptr(dbias), T, D, u, 0)
+    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(x), ptr(h), ptr(dz), ptr(out), ptr(dbias), T, D, u, 0, 0)
     torch.cuda.synchronize()
     ref = torch.cat([x[:, :D].double().t() @ dz.double(), h.double().t() @ dz.double()], 0)
     assert float((out.double() - ref).abs().max() / ref.abs().max()) < 2e-5

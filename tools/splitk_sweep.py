@@ -22,7 +22,7 @@ for M, Aop, lda, name in ((128, A, 128, "dWh"), (60, X, 64, "dWx")):
 # stacked [x | h_prev]^T dz kernel (indnet_tc_gemm_lstm_dw)
 out = torch.zeros(60 + 128, u4, device="cuda")
 def run_dual(sk):
-    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(X), ptr(A), ptr(B), ptr(out), T, 60, 128, sk)
+    LIB.call("indnet_tc_gemm_lstm_dw", current_stream(), ptr(X), ptr(A), ptr(B), ptr(out), None, T, 60, 128, sk, 0)
 for sk in (0, 18, 37, 74, 111, 148):
     for _ in range(3): run_dual(sk)
     torch.cuda.synchronize()
