@@ -321,11 +321,13 @@ int indnet_adam_step(indnet_stream st, float* params, const float* grads, float*
 /* The same update in two halves (a slice whose gradient is final early - M - can be updated underneath the
  * rest of the backward pass): indnet_adam_prep computes hyper = {lr_t, lr} from global_step and advances the
  * counter only when advance != 0; indnet_adam_apply updates n elements starting at the given pointers with the
- * lr_t found in hyper.  Sequence for one step: prep(0), apply(slice), ..., apply(rest), prep(1). */
+ * lr_t found in hyper; advance_step (optional): the counter, incremented once by this call - pass it with the
+ * step's last slice.  Sequence for one step: prep(0), apply(slice), ..., apply(rest, &global_step). */
 int indnet_adam_prep(indnet_stream st, long long* global_step, float* hyper, float lr0, int decay_steps,
                      float decay_rate, float beta1, float beta2, int advance);
 int indnet_adam_apply(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
-                      const float* hyper, float beta1, float beta2, float eps, float grad_scale, void* shadow_bf16);
+                      const float* hyper, float beta1, float beta2, float eps, float grad_scale, void* shadow_bf16,
+                      long long* advance_step);
 
 #ifdef __cplusplus
 }

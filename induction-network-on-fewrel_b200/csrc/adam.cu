@@ -26,8 +26,10 @@ __global__ void adam_prep_kernel(long long* global_step, float* hyper, float lr0
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, long long n, const float* __restrict__ hyper, float beta1,
-                            float beta2, float eps, float gscale, __nv_bfloat16* __restrict__ shadow) {
+                            float beta2, float eps, float gscale, __nv_bfloat16* __restrict__ shadow,
+                            long long* __restrict__ advance) {
   const float lr_t = hyper[0];
+  if (advance && blockIdx.x == 0 && threadIdx.x == 0) *advance += 1;    // the step's last slice closes the step
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float gi = g[i] * gscale;
     const float mi = beta1 * m[i] + (1.0f - beta1) * gi;
@@ -57,14 +59,14 @@ extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* g
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
   adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
-                                           (__nv_bfloat16*)shadow_bf16);
+                                           (__nv_bfloat16*)shadow_bf16, nullptr);
   IN_LAUNCH_CHECK("adam_kernel");
   return INDNET_OK;
 }
 
 // The same update in two halves, so that a slice of the flat buffer whose gradient is final early in the
 // backward pass (M, 96 % of the parameters) can be updated on a side stream underneath the rest of the pass:
-// prep(advance = 0) -> apply(slice) ... apply(rest) -> prep(advance = 1).  prep is idempotent for a given
+// prep(advance = 0) -> apply(slice) ... apply(rest, advance_step = &global_step).  prep is idempotent for a given
 // global_step, and the dropout streams of the step keep reading the un-advanced counter until the end.
 extern "C" int indnet_adam_prep(indnet_stream st_, long long* global_step, float* hyper, float lr0, int decay_steps,
                                 float decay_rate, float beta1, float beta2, int advance) {
@@ -77,15 +79,16 @@ extern "C" int indnet_adam_prep(indnet_stream st_, long long* global_step, float
 
 extern "C" int indnet_adam_apply(indnet_stream st_, float* params, const float* grads, float* m, float* v, long long n,
                                  const float* hyper, float beta1, float beta2, float eps, float grad_scale,
-                                 void* shadow_bf16) {
+                                 void* shadow_bf16, long long* advance_step) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(n >= 0 && hyper, "adam_apply: bad arguments");
+  IN_REQUIRE(n > 0 || !advance_step, "adam_apply: an empty slice cannot close the step");
   if (n == 0) return INDNET_OK;
   IN_REQUIRE(params && grads && m && v, "adam_apply: null pointer");
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
   adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
-                                           (__nv_bfloat16*)shadow_bf16);
+                                           (__nv_bfloat16*)shadow_bf16, advance_step);
   IN_LAUNCH_CHECK("adam_kernel");
   return INDNET_OK;
 }

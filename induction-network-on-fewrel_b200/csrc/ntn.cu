@@ -31,18 +31,38 @@ ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nw = NTN_NT / 32;
   const int NS = N * S;
   const float* v = V + (long long)row * NS;
-  for (int cp = warp; cp < N; cp += nw) {
-    float acc = 0.f;
-    for (int r = lane; r < NS; r += 32) {
-      const int c = r / S, k = r % S;
-      acc = fmaf(relu_nan(v[r]), w[(long long)(k * N + c) * N + cp], acc);
+  // thread t owns the V columns t, t + 128, ...: for each it reads the N-wide row of w once (contiguous) and
+  // keeps up to 8 class partial sums in registers - all loads of a thread are independent, one memory round
+  // trip instead of a dependent chain of NS / 32 of them per class
+  __shared__ float part[NTN_NT / 32][8];
+  for (int c0 = 0; c0 < N; c0 += 8) {
+    const int nc = min(8, N - c0);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int r = threadIdx.x; r < NS; r += NTN_NT) {
+      const float x = relu_nan(v[r]);
+      const int c = r / S, k = r - c * S;
+      const float* wr = w + (long long)(k * N + c) * N + c0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (i < nc) acc[i] = fmaf(x, wr[i], acc[i]);
     }
-    acc = warp_sum(acc);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = warp_sum(acc[i]);
     if (lane == 0) {
-      const float p = sigmoid_acc(acc + bias[cp]);
-      pr[cp] = p;
-      probs[(long long)row * N + cp] = p;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) part[warp][i] = acc[i];
     }
+    __syncthreads();
+    if (threadIdx.x < nc) {
+      float t = 0.f;
+      for (int q = 0; q < nw; ++q) t += part[q][threadIdx.x];
+      const float p = sigmoid_acc(t + bias[c0 + threadIdx.x]);
+      pr[c0 + threadIdx.x] = p;
+      probs[(long long)row * N + c0 + threadIdx.x] = p;
+    }
+    __syncthreads();
   }
   __syncthreads();
   if (threadIdx.x == 0) {

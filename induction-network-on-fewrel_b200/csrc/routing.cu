@@ -254,6 +254,10 @@ routing_fwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict_
   }
 }
 
+// The backward keeps every iteration's c_hat, c, d and |c_hat|^2 in the warp's shared-memory slice and runs both
+// sweeps as real loops: fully unrolled over the iterations with everything in registers it was ~100 KB of straight-line
+// code executed once by a handful of warps, i.e. bound by instruction fetch (ncu: 64 % of the stall samples "no
+// instruction", 21 us for 20 classes).
 template <int NV4>
 __global__ void __launch_bounds__(RT_WARPS * 32)
 routing_bwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict__ b_in, const float* __restrict__ dcvec,
@@ -264,67 +268,77 @@ routing_bwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict_
   const int w = blockIdx.x * warps + warp;
   if (warp >= warps || w >= BC) return;
   constexpr int H = NV4 * 128;
-  float4* se = sm4 + (size_t)warp * 2 * K * NV4 * 32;      // e_hat, then its gradient accumulator
+  const size_t slice = (size_t)2 * K * NV4 * 32 + (size_t)iters * (2 * NV4 * 32 + 16);     // in float4
+  float4* se = sm4 + (size_t)warp * slice;                 // e_hat, then its gradient accumulator
   float4* sde = se + (size_t)K * NV4 * 32;
+  float4* schat = sde + (size_t)K * NV4 * 32;              // [iters][NV4][32]
+  float4* scs = schat + (size_t)iters * NV4 * 32;          // [iters][NV4][32]
+  float* sdsm = reinterpret_cast<float*>(scs + (size_t)iters * NV4 * 32);   // [iters][32] coupling coefficients
+  float* ssn = sdsm + iters * 32;                          // [iters] |c_hat|^2
   rt_stage<NV4>(ehat + (long long)w * K * H, se, K, lane);
-  // ---- recompute the forward iterations, keeping d, c_hat, c and |c_hat|^2 of each (registers)
-  float4 chat[RT_MAX_IT][NV4], cs[RT_MAX_IT][NV4];
-  float dsm[RT_MAX_IT], sn[RT_MAX_IT];
+  // ---- recompute the forward iterations
   float b = (lane < K) ? (b_in ? b_in[(long long)w * K + lane] : 0.f) : -INFINITY;
+#pragma unroll 1
+  for (int it = 0; it < iters; ++it) {
+    const float d = rt_softmax(b, K, lane);
+    float4 chat[NV4], cs[NV4];
+    rt_combine<NV4>(se, d, chat, K, lane);
+    const float sn = rt_norm2<NV4>(chat);
+    const float f = squash_factor(sn);
 #pragma unroll
-  for (int it = 0; it < RT_MAX_IT; ++it) {
-    if (it < iters) {
-      dsm[it] = rt_softmax(b, K, lane);
-      rt_combine<NV4>(se, dsm[it], chat[it], K, lane);
-      sn[it] = rt_norm2<NV4>(chat[it]);
-      const float f = squash_factor(sn[it]);
-#pragma unroll
-      for (int j = 0; j < NV4; ++j)
-        cs[it][j] = make_float4(chat[it][j].x * f, chat[it][j].y * f, chat[it][j].z * f, chat[it][j].w * f);
-      if (it + 1 < iters) b += rt_dots<NV4>(se, cs[it], K, lane);
+    for (int j = 0; j < NV4; ++j) {
+      cs[j] = make_float4(chat[j].x * f, chat[j].y * f, chat[j].z * f, chat[j].w * f);
+      schat[(it * NV4 + j) * 32 + lane] = chat[j];
+      scs[(it * NV4 + j) * 32 + lane] = cs[j];
     }
+    sdsm[it * 32 + lane] = d;
+    if (lane == 0) ssn[it] = sn;
+    if (it + 1 < iters) b += rt_dots<NV4>(se, cs, K, lane);
   }
+  __syncwarp();
   // ---- reverse sweep (autodiff through every iteration: no stop_gradient in the reference)
   float dbs = 0.f;           // gradient w.r.t. b^{r+1}_lane
+#pragma unroll 1
+  for (int r = iters - 1; r >= 0; --r) {
+    const bool last = (r == iters - 1);
+    float4 g[NV4], dch[NV4], chat[NV4], cs[NV4];
 #pragma unroll
-  for (int r = RT_MAX_IT - 1; r >= 0; --r) {
-    if (r < iters) {
-      const bool last = (r == iters - 1);
-      float4 g[NV4], dch[NV4];
-      if (last) {
+    for (int j = 0; j < NV4; ++j) { chat[j] = schat[(r * NV4 + j) * 32 + lane]; cs[j] = scs[(r * NV4 + j) * 32 + lane]; }
+    if (last) {
 #pragma unroll
-        for (int j = 0; j < NV4; ++j) g[j] = *reinterpret_cast<const float4*>(dcvec + (long long)w * H + j * 128 + lane * 4);
-      } else {
-        rt_combine<NV4>(se, dbs, g, K, lane);
-      }
-      float vg = 0.f;
-#pragma unroll
-      for (int j = 0; j < NV4; ++j)
-        vg += chat[r][j].x * g[j].x + chat[r][j].y * g[j].y + chat[r][j].z * g[j].z + chat[r][j].w * g[j].w;
-      vg = warp_sum(vg);
-      const float f = squash_factor(sn[r]);
-      const float coef = 2.0f * squash_factor_grad(sn[r]) * vg;
-#pragma unroll
-      for (int j = 0; j < NV4; ++j)
-        dch[j] = make_float4(f * g[j].x + chat[r][j].x * coef, f * g[j].y + chat[r][j].y * coef,
-                             f * g[j].z + chat[r][j].z * coef, f * g[j].w + chat[r][j].w * coef);
-      const float dd = rt_dots<NV4>(se, dch, K, lane);
-      const float d = (lane < K) ? dsm[r] : 0.f;
-      const float dsum = warp_sum(d * dd);
-      const float db = (lane < K) ? (d * (dd - dsum) + dbs) : 0.f;
-      for (int k = 0; k < K; ++k) {
-        const float dkk = __shfl_sync(0xffffffffu, d, k), dbk = __shfl_sync(0xffffffffu, dbs, k);
-#pragma unroll
-        for (int j = 0; j < NV4; ++j) {
-          float4 val = make_float4(dkk * dch[j].x + dbk * cs[r][j].x, dkk * dch[j].y + dbk * cs[r][j].y,
-                                   dkk * dch[j].z + dbk * cs[r][j].z, dkk * dch[j].w + dbk * cs[r][j].w);
-          float4* dst = &sde[(k * NV4 + j) * 32 + lane];
-          if (!last) { const float4 o = *dst; val.x += o.x; val.y += o.y; val.z += o.z; val.w += o.w; }
-          *dst = val;
-        }
-      }
-      dbs = db;
+      for (int j = 0; j < NV4; ++j) g[j] = *reinterpret_cast<const float4*>(dcvec + (long long)w * H + j * 128 + lane * 4);
+    } else {
+      rt_combine<NV4>(se, dbs, g, K, lane);
     }
+    float vg = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV4; ++j)
+      vg += chat[j].x * g[j].x + chat[j].y * g[j].y + chat[j].z * g[j].z + chat[j].w * g[j].w;
+    vg = warp_sum(vg);
+    const float sn = ssn[r];
+    const float f = squash_factor(sn);
+    const float coef = 2.0f * squash_factor_grad(sn) * vg;
+#pragma unroll
+    for (int j = 0; j < NV4; ++j)
+      dch[j] = make_float4(f * g[j].x + chat[j].x * coef, f * g[j].y + chat[j].y * coef,
+                           f * g[j].z + chat[j].z * coef, f * g[j].w + chat[j].w * coef);
+    const float dd = rt_dots<NV4>(se, dch, K, lane);
+    const float d = (lane < K) ? sdsm[r * 32 + lane] : 0.f;
+    const float dsum = warp_sum(d * dd);
+    const float db = (lane < K) ? (d * (dd - dsum) + dbs) : 0.f;
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+      const float dkk = __shfl_sync(0xffffffffu, d, k), dbk = __shfl_sync(0xffffffffu, dbs, k);
+#pragma unroll
+      for (int j = 0; j < NV4; ++j) {
+        float4 val = make_float4(dkk * dch[j].x + dbk * cs[j].x, dkk * dch[j].y + dbk * cs[j].y,
+                                 dkk * dch[j].z + dbk * cs[j].z, dkk * dch[j].w + dbk * cs[j].w);
+        float4* dst = &sde[(k * NV4 + j) * 32 + lane];
+        if (!last) { const float4 o = *dst; val.x += o.x; val.y += o.y; val.z += o.z; val.w += o.w; }
+        *dst = val;
+      }
+    }
+    dbs = db;
   }
   __syncwarp();
   float4* de4 = reinterpret_cast<float4*>(dehat + (long long)w * K * H);
@@ -340,10 +354,13 @@ routing_bwd_fast_kernel(const float* __restrict__ ehat, const float* __restrict_
 }
 
 // warps per CTA (<= RT_WARPS) whose shared-memory slices fit; 0 = the fast path does not apply
+static size_t rt_fast_slice(int K, int H, int iters, int slices) {      // bytes of shared memory per warp
+  return (size_t)slices * K * H * sizeof(float) + (slices == 2 ? (size_t)iters * (2 * H * sizeof(float) + 256) : 0);
+}
 static int rt_fast_warps(int K, int H, int iters, int slices, const void* a, const void* b, const void* c, const void* d) {
   if (H % 128 != 0 || H > 512 || iters > RT_MAX_IT) return 0;
   if ((((uintptr_t)a | (uintptr_t)b | (uintptr_t)c) & 15) != 0 || ((uintptr_t)d & 7) != 0) return 0;
-  const size_t per_warp = (size_t)slices * K * H * sizeof(float);
+  const size_t per_warp = rt_fast_slice(K, H, iters, slices);
   int w = (int)((200 * 1024) / per_warp);
   return w > RT_WARPS ? RT_WARPS : w;
 }
@@ -415,7 +432,7 @@ extern "C" int indnet_routing_bwd(indnet_stream st_, const float* ehat, const fl
   if (BC == 0) return INDNET_OK;
   IN_REQUIRE(ehat && dcvec && dehat, "routing_bwd: null pointer");
   if (const int fw = rt_fast_warps(K, H, iters, 2, ehat, dcvec, dehat, dehat_bf)) {
-    const size_t fsm = (size_t)fw * 2 * K * H * sizeof(float);
+    const size_t fsm = (size_t)fw * rt_fast_slice(K, H, iters, 2);
 #define RT_BWD_FAST(NV4_)                                                                                          \
     do {                                                                                                           \
       IN_CUDA(cudaFuncSetAttribute(routing_bwd_fast_kernel<NV4_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \

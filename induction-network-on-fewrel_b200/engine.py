@@ -713,7 +713,7 @@ class EpisodePipeline:
                 self.grad_ready_hook("M")          # after ntn_dM: the data-parallel all-reduce of M's gradient starts here
         self._call("indnet_routing_bwd", ptr(self.ehat), None, ptr(self.dcvec), ptr(self.dehat), ptr(self.dehat_bf),
                    c.B * c.N, c.K, c.H, c.iters)
-        with self._branch(0):
+        with self._branch(1):
             self._tc(1, 1, c.H, c.H, c.B * c.NK, self.es_bf, c.H, self.dehat_bf, c.H, C=p.grad("W_s"), tag="routing_dWs")
         self._tc(0, 0, c.B * c.NK, c.H, c.H, self.dehat_bf, c.H, p.view_bf("W_s"), c.H, C=self.des, tag="routing_des")
         self._join(0)                 # deq
@@ -838,7 +838,7 @@ class EpisodePipeline:
         self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
                    0.9, 0.999, 0)
         self._call("indnet_adam_apply", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), n, ptr(p.hyper),
-                   0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf))
+                   0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf), None)
         self._adam_m_done = True
 
     def adam(self, grad_scale: float = 1.0):
@@ -849,9 +849,7 @@ class EpisodePipeline:
             self._adam_m_done = False
             bf = p.params_bf[n0:] if p.params_bf is not None else None
             self._call("indnet_adam_apply", ptr(p.params[n0:]), ptr(p.grads[n0:]), ptr(p.m[n0:]), ptr(p.v[n0:]),
-                       p.numel - n0, ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf))
-            self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps,
-                       self.decay_rate, 0.9, 0.999, 1)
+                       p.numel - n0, ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), ptr(p.global_step))
             return
         self._call("indnet_adam_step", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), p.numel,
                    ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
