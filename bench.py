@@ -471,7 +471,10 @@ def run_b200(args, w):
                        "timing": "blocks of --steps graph replays repeated until >= %.1f s of GPU time; value = B / mean step time" % MIN_TIMED_S},
             "e2e": {"value": e2e_value, "unit": "episodes/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                     "steps": e2e_steps,
-                    "timer": "host perf_counter around: pinned-host episodes H2D + step graph + D2H of {loss, acc}, every step",
+                    "timer": "host perf_counter around: pinned-host episodes H2D + step graph + D2H of {loss, acc}, every "
+                             "step; the host reads step t's result while step t+1 runs (EpisodeTrainer.read_async)",
+                    "synchronous": {"value": world * cfg.B * e2e_steps / (e2e_sync_ms / 1000.0), "unit": "episodes/s",
+                                    "note": "same loop, the host drains the GPU after every step (trainer.read())"},
                     "with_device_sampler": {"value": world * cfg.B * e2e_steps / (e2e_smp_ms / 1000.0), "unit": "episodes/s",
                                             "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 8,
                                             "note": "the loop Base.train runs: bit-exact device sampler inside the step graph "
