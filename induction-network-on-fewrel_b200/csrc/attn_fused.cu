@@ -220,44 +220,46 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 }
 
 
-// ---- H <= 256: the variant the training configs run.  The CTA's whole A tile (its 128 token rows of h, H/64 boxes of
-// 16 KB) is requested at once and STAYS in shared memory: the weighted sum at the end reads h from there instead of
-// going back to L2, and nothing of the A stream is serialised behind a two-slot ring.  Wa1 streams through two 16 KB
-// slots, 128 output columns per pass; each pass has its own accumulator columns, so pass 1's MMAs run while the
-// epilogue warps drain pass 0.  ~99 KB of shared memory: two CTAs per SM.
-constexpr int AR_NB_MAX = 128;
-__global__ void __launch_bounds__(AF_THREADS, 2)
-attn_fused_fwd_res_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AttnFusedP p) {
+// ---- H <= 256, persistent: one CTA per SM walks the tiles.  Wa1 (H x H bf16, <= 128 KB) is loaded ONCE per CTA and
+// stays in shared memory; the accumulator is double buffered in tensor memory (2 x 256 columns), so tile i+1's
+// A load and MMAs run under tile i's epilogue; eight epilogue warps (two per TMEM lane quarter, half of the columns
+// each) drain it.  The A buffer is released as soon as the tile's MMAs have completed, so the weighted sum reads h
+// back from L2 (where the TMA load just put it).
+constexpr int AP_THREADS = 64 + 256;
+__global__ void __launch_bounds__(AP_THREADS, 1)
+attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AttnFusedP p,
+                           int ntiles) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int L = p.L, H = p.H, NB = p.NP;                // NB = output columns per pass (<= 128)
-  const int KB = H / AF_BK, NPASS = H / NB;
-  const int B_BYTES = NB * AF_BK * 2;
-  uint8_t* sA = smem;                                   // [KB][128 rows][128 B], 128-byte swizzle
-  uint8_t* sB = smem + KB * AF_A_BYTES;                 // [2][B_BYTES]
-  float* sBias = reinterpret_cast<float*>(sB + 2 * B_BYTES);
+  const int L = p.L, H = p.H;
+  const int KB = H / AF_BK;
+  const int W_KB_BYTES = H * AF_BK * 2;                 // one K block of Wa1: H / 64 boxes of 8 KB
+  uint8_t* sW = smem;                                   // [KB][W_KB_BYTES]
+  uint8_t* sA = smem + KB * W_KB_BYTES;                 // [KB][16 KB]
+  float* sBias = reinterpret_cast<float*>(sA + KB * AF_A_BYTES);
   float* sW2 = sBias + H;
-  float* sSc = sW2 + H;
-  float* sAl = sSc + AF_BM;
-  uint64_t* a_full = reinterpret_cast<uint64_t*>(sAl + AF_BM);
-  uint64_t* b_full = a_full + 1;                        // [2]
-  uint64_t* b_empty = b_full + 2;                       // [2]
-  uint64_t* acc_full = b_empty + 2;                     // [NPASS <= 4]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 4);
+  float* sScP = sW2 + H;                                // [2][128] score halves
+  float* sSc = sScP + 2 * AF_BM;                        // [128]
+  float* sAl = sSc + AF_BM;                             // [128]
+  uint8_t* sStage = reinterpret_cast<uint8_t*>(sAl + AF_BM);     // [8 warps][32 rows][64 B]: proj chunk, row-major
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(sStage + 8 * 2048);
+  uint64_t* a_full = w_full + 1;
+  uint64_t* a_empty = a_full + 1;
+  uint64_t* acc_full = a_empty + 1;                     // [2]
+  uint64_t* acc_empty = acc_full + 2;                   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rows_tile = p.spt * L;
-  const long long row0 = (long long)blockIdx.x * rows_tile;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    mbar_init(a_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < 4; ++i) mbar_init(&acc_full[i], 1);
+    mbar_init(w_full, 1); mbar_init(a_full, 1); mbar_init(a_empty, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 256); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 256);
-  for (int i = threadIdx.x; i < H; i += AF_THREADS) { sBias[i] = p.bias[i]; sW2[i] = p.w2[i]; }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  for (int i = threadIdx.x; i < H; i += AP_THREADS) { sBias[i] = p.bias[i]; sW2[i] = p.w2[i]; }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -265,146 +267,177 @@ attn_fused_fwd_res_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(a_full, KB * AF_A_BYTES);
-      for (int kb = 0; kb < KB; ++kb) tma_load_3d(sA + kb * AF_A_BYTES, &tmA, a_full, kb * AF_BK, (int)row0, 0);
+      mbar_expect_tx(w_full, KB * W_KB_BYTES);
+      for (int kb = 0; kb < KB; ++kb)
+        for (int j = 0; j < H / 64; ++j)                                         // Wa1 [K][N]: 64 n x 64 k boxes
+          tma_load_3d(sW + kb * W_KB_BYTES + j * 8192, &tmB, w_full, j * 64, kb * AF_BK, 0);
       int it = 0;
-      for (int pass = 0; pass < NPASS; ++pass)
-        for (int kb = 0; kb < KB; ++kb, ++it) {
-          const int s = it & 1, ph = (it >> 1) & 1;
-          mbar_wait(&b_empty[s], ph ^ 1);
-          mbar_expect_tx(&b_full[s], B_BYTES);
-          for (int j = 0; j < NB / 64; ++j)                                       // Wa1 [K][N]: 64 n x 64 k boxes
-            tma_load_3d(sB + s * B_BYTES + j * 8192, &tmB, &b_full[s], pass * NB + j * 64, kb * AF_BK, 0);
-        }
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        if (it > 0) mbar_wait(a_empty, (it - 1) & 1);                            // the previous tile's MMAs have read sA
+        mbar_expect_tx(a_full, KB * AF_A_BYTES);
+        for (int kb = 0; kb < KB; ++kb)
+          tma_load_3d(sA + kb * AF_A_BYTES, &tmA, a_full, kb * AF_BK, tile * rows_tile, 0);
+      }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = idesc_bf16(AF_BM, NB, false, true);
-      mbar_wait(a_full, 0);
+      const uint32_t idesc = idesc_bf16(AF_BM, H, false, true);
+      mbar_wait(w_full, 0);
       int it = 0;
-      for (int pass = 0; pass < NPASS; ++pass) {
-        for (int kb = 0; kb < KB; ++kb, ++it) {
-          const int s = it & 1, ph = (it >> 1) & 1;
-          mbar_wait(&b_full[s], ph);
-          tc_fence_after();
-          const uint32_t a_base = smem_u32(sA + kb * AF_A_BYTES), b_base = smem_u32(sB + s * B_BYTES);
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int b = it & 1;
+        if (it >= 2) mbar_wait(&acc_empty[b], ((it >> 1) - 1) & 1);              // that accumulator has been drained
+        mbar_wait(a_full, it & 1);
+        tc_fence_after();
+        for (int kb = 0; kb < KB; ++kb) {
+          const uint32_t a_base = smem_u32(sA + kb * AF_A_BYTES), b_base = smem_u32(sW + kb * W_KB_BYTES);
 #pragma unroll
           for (int k = 0; k < AF_BK / 16; ++k) {
             const uint64_t ad = smem_desc_sw128(a_base + k * 32, 0, 1024);                    // K-major A
             const uint64_t bd = smem_desc_sw128(b_base + k * (16 * 128), AF_BK * 128, 1024);  // MN-major B, 64-wide N atoms 8 KB apart
-            umma_bf16(taddr + pass * NB, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_bf16(taddr + b * 256, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&b_empty[s]);
         }
-        umma_commit(&acc_full[pass]);
+        umma_commit(a_empty);
+        umma_commit(&acc_full[b]);
       }
     }
   } else {
-    // ---- epilogue warps: lane = token row of the tile
-    const int q = warp & 3;
+    // ---- epilogue warps: lane = token row of the tile, two warps per row (a half of the columns each)
+    const int e = warp - 2;                    // 0..7
+    const int q = warp & 3;                    // the TMEM lane quarter this warp may touch
+    const int half = e >> 2;
     const int row = q * 32 + lane;
-    const long long gr = row0 + row;
-    const bool valid = row < rows_tile && gr < (long long)p.X * L;
-    float score = 0.f;
-    for (int pass = 0; pass < NPASS; ++pass) {
-      mbar_wait(&acc_full[pass], 0);
+    const int NH = H / 2;                      // columns per half (a multiple of 32)
+    const int et = threadIdx.x - 64;           // 0..255
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int b = it & 1;
+      const long long row0 = (long long)tile * rows_tile;
+      const long long gr = row0 + row;
+      const bool valid = row < rows_tile && gr < (long long)p.X * L;
+      mbar_wait(&acc_full[b], (it >> 1) & 1);
       tc_fence_after();
+      float score = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < NB / 32; ++c) {
+      for (int c = 0; c < NH / 32; ++c) {
         float v[32];
-        tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + pass * NB + c * 32, v);
+        const int n0 = half * NH + c * 32;
+        tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + b * 256 + n0, v);
         tmem_ld_wait();
-        const int n0 = pass * NB + c * 32;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           v[j] = af_tanh(v[j] + sBias[n0 + j]);
           score = fmaf(v[j], sW2[n0 + j], score);
         }
-        if (p.proj && valid) {
-          uint4* dst = reinterpret_cast<uint4*>(p.proj + gr * H + n0);
+        if (p.proj) {
+          // lane = row would make every 16-byte store instruction touch 32 different 128-byte lines (the LSU works per
+          // line): the warp's 32 x 32 chunk goes through 2 KB of shared memory and leaves as 64-byte row segments,
+          // four lanes per row, eight lines per instruction
+          uint8_t* stg = sStage + e * 2048;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            __nv_bfloat162 a = __floats2bfloat162_rn(v[8 * j], v[8 * j + 1]), b = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
+            __nv_bfloat162 a = __floats2bfloat162_rn(v[8 * j], v[8 * j + 1]), bb = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
             __nv_bfloat162 cc = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]), d = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
-            dst[j] = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b),
-                                *reinterpret_cast<uint32_t*>(&cc), *reinterpret_cast<uint32_t*>(&d));
+            *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) =
+                make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&bb),
+                           *reinterpret_cast<uint32_t*>(&cc), *reinterpret_cast<uint32_t*>(&d));
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int rr = i * 8 + (lane >> 2), cj = lane & 3;          // row of the warp's 32, 16-byte piece of its 64 bytes
+            const uint4 w = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4));
+            const int trow = q * 32 + rr;
+            const long long grr = row0 + trow;
+            if (trow < rows_tile && grr < (long long)p.X * L)
+              *reinterpret_cast<uint4*>(p.proj + grr * H + n0 + cj * 8) = w;
+          }
+          __syncwarp();
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[b]);              // the issuer may overwrite this accumulator (tile it + 2)
+      sScP[half * AF_BM + row] = score;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // ---- masked softmax over each sentence's L rows (layer_module.py:84-87); one thread per row
+      float sc = -INFINITY, ex = 0.f;
+      const int sbase = (row / L) * L;
+      if (half == 0) {
+        if (valid) {
+          const float m = p.mask[gr] > 0 ? 1.0f : 0.0f;
+          sc = sScP[row] + sScP[AF_BM + row] + (1.0f - m) * (-2147483648.0f);
+        }
+        sSc[row] = sc;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0 && valid) {
+        float mx = -INFINITY;
+        for (int t = 0; t < L; ++t) mx = fmaxf(mx, sSc[sbase + t]);
+        ex = expf(sc - mx);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) sSc[row] = ex;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) {
+        float al = 0.f;
+        if (valid) {
+          float sum = 0.f;
+          for (int t = 0; t < L; ++t) sum += sSc[sbase + t];
+          al = ex / sum;
+          p.alphas[gr] = al;
+        }
+        sAl[row] = al;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // ---- e = sum_t alpha_t h_t.  lane = (16-byte chunk c of 4, time group tg of 8): the eight time groups of a chunk sit
+      // in one warp and meet through shuffles - no shared memory, no barrier between sentences, so the L2 loads of the
+      // CTA's sentences overlap.  h comes back from L2 (the TMA load just put it there).
+      const int x_first = (int)(row0 / L);
+      const int chunks = H / 8;                // <= 32
+      const int tg = lane & 7, c = e * 4 + (lane >> 3);
+      for (int s = 0; s < p.spt; ++s) {
+        const int x = x_first + s;
+        if (x >= p.X) break;
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (c < chunks) {
+          const uint4* hp = reinterpret_cast<const uint4*>(p.h + ((long long)x * L) * H);
+#pragma unroll 5
+          for (int t = tg; t < L; t += 8) {
+            const uint4 w = hp[(long long)t * chunks + c];
+            const float a = sAl[s * L + t];
+            acc[0] = fmaf(a, __uint_as_float(w.x << 16), acc[0]); acc[1] = fmaf(a, __uint_as_float(w.x & 0xFFFF0000u), acc[1]);
+            acc[2] = fmaf(a, __uint_as_float(w.y << 16), acc[2]); acc[3] = fmaf(a, __uint_as_float(w.y & 0xFFFF0000u), acc[3]);
+            acc[4] = fmaf(a, __uint_as_float(w.z << 16), acc[4]); acc[5] = fmaf(a, __uint_as_float(w.z & 0xFFFF0000u), acc[5]);
+            acc[6] = fmaf(a, __uint_as_float(w.w << 16), acc[6]); acc[7] = fmaf(a, __uint_as_float(w.w & 0xFFFF0000u), acc[7]);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+          acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 4);
+        }
+        if (tg == 0 && c < chunks) {
+          const int g = x / p.group, r = x - g * p.group;
+          const long long orow = (r < p.split) ? ((long long)g * p.split + r) : ((long long)g * (p.group - p.split) + (r - p.split));
+          float* enc = ((r < p.split) ? p.enc_a + orow * H : p.enc_b + orow * H) + c * 8;
+          *reinterpret_cast<float4*>(enc) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+          *reinterpret_cast<float4*>(enc + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+          if (p.enc_a_bf) {
+            __nv_bfloat16* eb = ((r < p.split) ? p.enc_a_bf + orow * H : p.enc_b_bf + orow * H) + c * 8;
+            __nv_bfloat162 a = __floats2bfloat162_rn(acc[0], acc[1]), bb = __floats2bfloat162_rn(acc[2], acc[3]);
+            __nv_bfloat162 cc = __floats2bfloat162_rn(acc[4], acc[5]), d = __floats2bfloat162_rn(acc[6], acc[7]);
+            *reinterpret_cast<uint4*>(eb) = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&bb),
+                                                       *reinterpret_cast<uint32_t*>(&cc), *reinterpret_cast<uint32_t*>(&d));
           }
         }
       }
-    }
-    tc_fence_before();
-    // ---- masked softmax over each sentence's L rows (layer_module.py:84-87)
-    float sc = -INFINITY;
-    if (valid) {
-      const float m = p.mask[gr] > 0 ? 1.0f : 0.0f;
-      sc = score + (1.0f - m) * (-2147483648.0f);
-    }
-    sSc[row] = sc;
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    const int sbase = (row / L) * L;
-    float e = 0.f;
-    if (valid) {
-      float mx = -INFINITY;
-      for (int t = 0; t < L; ++t) mx = fmaxf(mx, sSc[sbase + t]);
-      e = expf(sc - mx);
-    }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    sSc[row] = e;
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    float al = 0.f;
-    if (valid) {
-      float sum = 0.f;
-      for (int t = 0; t < L; ++t) sum += sSc[sbase + t];
-      al = e / sum;
-      p.alphas[gr] = al;
-    }
-    sAl[row] = al;
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    // ---- e = sum_t alpha_t h_t with h read from the resident A tile: thread = (time group tg of 4, 16-byte chunk c);
-    // a quarter warp reads one whole 128-byte row of one K box (conflict free under the swizzle).  The partial sums
-    // meet in the Wa1 slots (all MMAs have completed: acc_full of the last pass was seen).
-    mbar_wait(a_full, 0);                      // completed long ago; observing it makes the TMA-written tile visible here
-    const int tid = threadIdx.x - 64;          // 0..127
-    const int x_first = (int)(row0 / L);
-    const int chunks = H / 8;
-    float* red = reinterpret_cast<float*>(sB);              // [4][H] partial sums (<= 4 KB)
-    for (int s = 0; s < p.spt; ++s) {
-      const int x = x_first + s;
-      if (x >= p.X) break;
-      const int g = x / p.group, r = x - g * p.group;
-      const long long orow = (r < p.split) ? ((long long)g * p.split + r) : ((long long)g * (p.group - p.split) + (r - p.split));
-      float* enc = (r < p.split) ? p.enc_a + orow * H : p.enc_b + orow * H;
-      __nv_bfloat16* enc_bf = p.enc_a_bf ? ((r < p.split) ? p.enc_a_bf + orow * H : p.enc_b_bf + orow * H) : nullptr;
-      const int c = tid & 31, tg = tid >> 5;
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (c < chunks) {
-        const uint8_t* tile = sA + (c >> 3) * AF_A_BYTES;
-        const uint32_t cc = (uint32_t)(c & 7);
-#pragma unroll 4
-        for (int t = tg; t < L; t += 4) {
-          const uint32_t rr = (uint32_t)(s * L + t);
-          const uint4 w = *reinterpret_cast<const uint4*>(tile + rr * 128 + ((cc ^ (rr & 7u)) << 4));
-          const float a = sAl[rr];
-          acc[0] = fmaf(a, __uint_as_float(w.x << 16), acc[0]); acc[1] = fmaf(a, __uint_as_float(w.x & 0xFFFF0000u), acc[1]);
-          acc[2] = fmaf(a, __uint_as_float(w.y << 16), acc[2]); acc[3] = fmaf(a, __uint_as_float(w.y & 0xFFFF0000u), acc[3]);
-          acc[4] = fmaf(a, __uint_as_float(w.z << 16), acc[4]); acc[5] = fmaf(a, __uint_as_float(w.z & 0xFFFF0000u), acc[5]);
-          acc[6] = fmaf(a, __uint_as_float(w.w << 16), acc[6]); acc[7] = fmaf(a, __uint_as_float(w.w & 0xFFFF0000u), acc[7]);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) red[tg * H + c * 8 + j] = acc[j];
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      for (int n = tid * 2; n < H; n += 256) {
-        const float a0 = red[n] + red[H + n] + red[2 * H + n] + red[3 * H + n];
-        const float a1 = red[n + 1] + red[H + n + 1] + red[2 * H + n + 1] + red[3 * H + n + 1];
-        *reinterpret_cast<float2*>(enc + n) = make_float2(a0, a1);
-        if (enc_bf) *reinterpret_cast<__nv_bfloat162*>(enc_bf + n) = __floats2bfloat162_rn(a0, a1);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");      // sAl / sSc are rewritten by the next tile
     }
   }
   __syncthreads();
-  if (warp == 1) tmem_dealloc(taddr, 256);
+  if (warp == 1) tmem_dealloc(taddr, 512);
 }
 
 }  // namespace indnet
@@ -436,13 +469,14 @@ extern "C" int indnet_attn_fused_fwd(indnet_stream st_, const void* hout_bf, con
   if (rc) return rc;
   rc = make_tmap_bf16(&tmB, wa1_bf, H, H, H, 1, 0, 64, AF_BK);                              // [K][N]: box 64 n x 64 k
   if (rc) return rc;
-  if (H <= 256 && !getenv("INDNET_ATTN_FWD_RING")) {
-    // resident-A variant: NB = 128 output columns per pass when H allows, else 64
-    p.NP = (H % AR_NB_MAX == 0) ? AR_NB_MAX : 64;
-    const int smem = (H / AF_BK) * AF_A_BYTES + 2 * p.NP * AF_BK * 2 + (2 * H + 2 * AF_BM) * 4 + 128;
-    IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attn_fused_fwd_res_kernel<<<ceil_div(X, p.spt), AF_THREADS, smem, st>>>(tmA, tmB, p);
-    IN_LAUNCH_CHECK("attn_fused_fwd_res_kernel");
+  if (H <= 256 && H % 64 == 0 && !getenv("INDNET_ATTN_FWD_RING")) {
+    // persistent variant: Wa1 resident, double-buffered accumulator, eight epilogue warps
+    p.NP = H;
+    const int ntiles = ceil_div(X, p.spt);
+    const int smem = (H / AF_BK) * (H * AF_BK * 2 + AF_A_BYTES) + (2 * H + 4 * AF_BM) * 4 + 8 * 2048 + 128;
+    IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_pers_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attn_fused_fwd_pers_kernel<<<ntiles < 148 ? ntiles : 148, AP_THREADS, smem, st>>>(tmA, tmB, p, ntiles);
+    IN_LAUNCH_CHECK("attn_fused_fwd_pers_kernel");
     return INDNET_OK;
   }
   const int smem = AF_STAGES * (AF_A_BYTES + p.NP * AF_BK * 2) + (2 * H + 2 * AF_BM) * 4 + 128;

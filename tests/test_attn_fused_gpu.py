@@ -1,6 +1,6 @@
 """GPU: the fused attention kernels (indnet_attn_fused_fwd / _bwd, csrc/attn_fused.cu) on their own, against a
 float64 torch restatement of model/layer_module.py:49-98 on the same bf16-rounded operands.  Covers both forward
-variants (H <= 256: resident A tile; H = 512: two passes through the operand ring), every pass width, ragged
+variants (H <= 256: persistent, Wa1 resident; H = 512: two passes through the operand ring), every pass width, ragged
 sentence counts, padded sentences, and the support/query split of the outputs."""
 import pytest
 import torch
