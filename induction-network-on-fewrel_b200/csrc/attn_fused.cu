@@ -220,12 +220,20 @@ attn_fused_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 }
 
 
+#ifdef INDNET_ATTN_TIMELINE
+__device__ long long g_attnf_dbg[16 * 8];
+#define AF_MARK(k) do { if (blockIdx.x == 0 && threadIdx.x == 64 && it < 16) g_attnf_dbg[it * 8 + (k)] = clock64(); } while (0)
+#else
+#define AF_MARK(k) do { } while (0)
+#endif
+
 // ---- H <= 256, persistent: one CTA per SM walks the tiles.  Wa1 (H x H bf16, <= 128 KB) is loaded ONCE per CTA and
 // stays in shared memory; the accumulator is double buffered in tensor memory (2 x 256 columns), so tile i+1's
 // A load and MMAs run under tile i's epilogue; eight epilogue warps (two per TMEM lane quarter, half of the columns
 // each) drain it.  The A buffer is released as soon as the tile's MMAs have completed, so the weighted sum reads h
 // back from L2 (where the TMA load just put it).
 constexpr int AP_THREADS = 64 + 256;
+template <int SPT, int NK>        // SPT sentences per tile of NK = ceil(L / 8) rows per time group, known at compile time; 0: generic
 __global__ void __launch_bounds__(AP_THREADS, 1)
 attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AttnFusedP p,
                            int ntiles) {
@@ -316,19 +324,30 @@ attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       const long long row0 = (long long)tile * rows_tile;
       const long long gr = row0 + row;
       const bool valid = row < rows_tile && gr < (long long)p.X * L;
+      AF_MARK(0);
+      // the mask of this row is needed right after the drain: fetch it now (a DRAM round trip otherwise in the chain)
+      int mrow = 1;
+      if (half == 0 && valid) mrow = __ldg(p.mask + gr);
       mbar_wait(&acc_full[b], (it >> 1) & 1);
       tc_fence_after();
+      AF_MARK(1);
       float score = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < NH / 32; ++c) {
-        float v[32];
+      // two register buffers: the TMEM load of chunk c + 1 is in flight while chunk c is processed
+      const uint32_t tbase = taddr + ((uint32_t)(q * 32) << 16) + b * 256 + half * NH;
+      const int nch = NH / 32;
+      float va[32], vb[32];
+      tmem_ld32(tbase, va);
+      auto chunk = [&](float* v, int c) {
         const int n0 = half * NH + c * 32;
-        tmem_ld32(taddr + ((uint32_t)(q * 32) << 16) + b * 256 + n0, v);
-        tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(sBias + n0);
+        const float4* w4 = reinterpret_cast<const float4*>(sW2 + n0);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          v[j] = af_tanh(v[j] + sBias[n0 + j]);
-          score = fmaf(v[j], sW2[n0 + j], score);
+        for (int j = 0; j < 8; ++j) {
+          const float4 bb = b4[j], ww = w4[j];
+          v[4 * j] = af_tanh(v[4 * j] + bb.x); v[4 * j + 1] = af_tanh(v[4 * j + 1] + bb.y);
+          v[4 * j + 2] = af_tanh(v[4 * j + 2] + bb.z); v[4 * j + 3] = af_tanh(v[4 * j + 3] + bb.w);
+          score = fmaf(v[4 * j], ww.x, score); score = fmaf(v[4 * j + 1], ww.y, score);
+          score = fmaf(v[4 * j + 2], ww.z, score); score = fmaf(v[4 * j + 3], ww.w, score);
         }
         if (p.proj) {
           // lane = row would make every 16-byte store instruction touch 32 different 128-byte lines (the LSU works per
@@ -355,26 +374,44 @@ attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
           }
           __syncwarp();
         }
+      };
+#pragma unroll 1
+      for (int c = 0; c < nch; c += 2) {
+        tmem_ld_wait();
+        if (c + 1 < nch) tmem_ld32(tbase + (c + 1) * 32, vb);
+        chunk(va, c);
+        if (c + 1 < nch) {
+          tmem_ld_wait();
+          if (c + 2 < nch) tmem_ld32(tbase + (c + 2) * 32, va);
+          chunk(vb, c + 1);
+        }
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[b]);              // the issuer may overwrite this accumulator (tile it + 2)
       sScP[half * AF_BM + row] = score;
+      AF_MARK(2);
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      AF_MARK(3);
       // ---- masked softmax over each sentence's L rows (layer_module.py:84-87); one thread per row
       float sc = -INFINITY, ex = 0.f;
       const int sbase = (row / L) * L;
       if (half == 0) {
         if (valid) {
-          const float m = p.mask[gr] > 0 ? 1.0f : 0.0f;
+          const float m = mrow > 0 ? 1.0f : 0.0f;
           sc = sScP[row] + sScP[AF_BM + row] + (1.0f - m) * (-2147483648.0f);
         }
         sSc[row] = sc;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (half == 0 && valid) {
-        float mx = -INFINITY;
-        for (int t = 0; t < L; ++t) mx = fmaxf(mx, sSc[sbase + t]);
-        ex = expf(sc - mx);
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+        int t = 0;
+        for (; t + 4 <= L; t += 4) {
+          m0 = fmaxf(m0, sSc[sbase + t]); m1 = fmaxf(m1, sSc[sbase + t + 1]);
+          m2 = fmaxf(m2, sSc[sbase + t + 2]); m3 = fmaxf(m3, sSc[sbase + t + 3]);
+        }
+        for (; t < L; ++t) m0 = fmaxf(m0, sSc[sbase + t]);
+        ex = expf(sc - fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (half == 0) sSc[row] = ex;
@@ -382,7 +419,7 @@ attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       if (half == 0) {
         float al = 0.f;
         if (valid) {
-          float sum = 0.f;
+          float sum = 0.f;                     // same order as the reference sum over t (fp32, sequential)
           for (int t = 0; t < L; ++t) sum += sSc[sbase + t];
           al = ex / sum;
           p.alphas[gr] = al;
@@ -390,19 +427,73 @@ attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         sAl[row] = al;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      AF_MARK(4);
       // ---- e = sum_t alpha_t h_t.  lane = (16-byte chunk c of 4, time group tg of 8): the eight time groups of a chunk sit
-      // in one warp and meet through shuffles - no shared memory, no barrier between sentences, so the L2 loads of the
-      // CTA's sentences overlap.  h comes back from L2 (the TMA load just put it there).
+      // in one warp and meet through shuffles.  Every thread first requests ALL of its rows of the tile (rows tg, tg + 8,
+      // ... of up to 128: one L2 round trip for the whole tile, h was just put there by the TMA load), then adds each
+      // row into the accumulator of the sentence it belongs to (predicated, at most 4 sentences per tile here; tiles
+      // of more sentences take the loop below).
       const int x_first = (int)(row0 / L);
       const int chunks = H / 8;                // <= 32
       const int tg = lane & 7, c = e * 4 + (lane >> 3);
+      if (SPT > 0) {
+        // every load of the thread for the whole tile is requested first (one L2 round trip), then one accumulator
+        // set per sentence, eight time groups meeting through shuffles
+        uint4 w[SPT > 0 ? SPT * NK : 1];
+#pragma unroll
+        for (int s2 = 0; s2 < SPT; ++s2) {
+          const bool live = x_first + s2 < p.X && c < chunks;
+          const uint4* hp = reinterpret_cast<const uint4*>(p.h + (row0 + (long long)s2 * L) * H);
+#pragma unroll
+          for (int k = 0; k < NK; ++k) {
+            const int t = tg + 8 * k;
+            w[s2 * NK + k] = (live && t < L) ? __ldcg(hp + (long long)t * chunks + c) : make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+#pragma unroll
+        for (int s2 = 0; s2 < SPT; ++s2) {
+          if (x_first + s2 >= p.X) break;
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int k = 0; k < NK; ++k) {
+            const int t = tg + 8 * k;
+            const float a = t < L ? sAl[s2 * L + t] : 0.f;
+            const uint4 ww = w[s2 * NK + k];
+            acc[0] = fmaf(a, __uint_as_float(ww.x << 16), acc[0]); acc[1] = fmaf(a, __uint_as_float(ww.x & 0xFFFF0000u), acc[1]);
+            acc[2] = fmaf(a, __uint_as_float(ww.y << 16), acc[2]); acc[3] = fmaf(a, __uint_as_float(ww.y & 0xFFFF0000u), acc[3]);
+            acc[4] = fmaf(a, __uint_as_float(ww.z << 16), acc[4]); acc[5] = fmaf(a, __uint_as_float(ww.z & 0xFFFF0000u), acc[5]);
+            acc[6] = fmaf(a, __uint_as_float(ww.w << 16), acc[6]); acc[7] = fmaf(a, __uint_as_float(ww.w & 0xFFFF0000u), acc[7]);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+            acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+            acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 4);
+          }
+          if (tg == 0 && c < chunks) {
+            const int x = x_first + s2;
+            const int g = x / p.group, r = x - g * p.group;
+            const long long orow = (r < p.split) ? ((long long)g * p.split + r) : ((long long)g * (p.group - p.split) + (r - p.split));
+            float* enc = ((r < p.split) ? p.enc_a + orow * H : p.enc_b + orow * H) + c * 8;
+            *reinterpret_cast<float4*>(enc) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            *reinterpret_cast<float4*>(enc + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+            if (p.enc_a_bf) {
+              __nv_bfloat16* eb = ((r < p.split) ? p.enc_a_bf + orow * H : p.enc_b_bf + orow * H) + c * 8;
+              __nv_bfloat162 a = __floats2bfloat162_rn(acc[0], acc[1]), bb = __floats2bfloat162_rn(acc[2], acc[3]);
+              __nv_bfloat162 cc = __floats2bfloat162_rn(acc[4], acc[5]), d = __floats2bfloat162_rn(acc[6], acc[7]);
+              *reinterpret_cast<uint4*>(eb) = make_uint4(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&bb),
+                                                         *reinterpret_cast<uint32_t*>(&cc), *reinterpret_cast<uint32_t*>(&d));
+            }
+          }
+        }
+      } else {
       for (int s = 0; s < p.spt; ++s) {
         const int x = x_first + s;
         if (x >= p.X) break;
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (c < chunks) {
           const uint4* hp = reinterpret_cast<const uint4*>(p.h + ((long long)x * L) * H);
-#pragma unroll 5
+#pragma unroll 4
           for (int t = tg; t < L; t += 8) {
             const uint4 w = hp[(long long)t * chunks + c];
             const float a = sAl[s * L + t];
@@ -433,7 +524,10 @@ attn_fused_fwd_pers_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
           }
         }
       }
+      }
+      AF_MARK(5);
       asm volatile("bar.sync 1, 256;" ::: "memory");      // sAl / sSc are rewritten by the next tile
+      AF_MARK(6);
     }
   }
   __syncthreads();
@@ -474,8 +568,14 @@ extern "C" int indnet_attn_fused_fwd(indnet_stream st_, const void* hout_bf, con
     p.NP = H;
     const int ntiles = ceil_div(X, p.spt);
     const int smem = (H / AF_BK) * (H * AF_BK * 2 + AF_A_BYTES) + (2 * H + 4 * AF_BM) * 4 + 8 * 2048 + 128;
-    IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_pers_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attn_fused_fwd_pers_kernel<<<ntiles < 148 ? ntiles : 148, AP_THREADS, smem, st>>>(tmA, tmB, p, ntiles);
+    const int grid = ntiles < 148 ? ntiles : 148;
+    if (p.spt == 3 && (L + 7) / 8 == 5) {           // max_length 40 (the reference's default and every training config)
+      IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_pers_kernel<3, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attn_fused_fwd_pers_kernel<3, 5><<<grid, AP_THREADS, smem, st>>>(tmA, tmB, p, ntiles);
+    } else {
+      IN_CUDA(cudaFuncSetAttribute(attn_fused_fwd_pers_kernel<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      attn_fused_fwd_pers_kernel<0, 0><<<grid, AP_THREADS, smem, st>>>(tmA, tmB, p, ntiles);
+    }
     IN_LAUNCH_CHECK("attn_fused_fwd_pers_kernel");
     return INDNET_OK;
   }
@@ -789,6 +889,7 @@ attn_fused_bwd_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_cons
 }  // namespace indnet
 
 #ifdef INDNET_ATTN_TIMELINE
+extern "C" int indnet_debug_attn_fwd(long long* out) { return (int)cudaMemcpyFromSymbol(out, indnet::g_attnf_dbg, sizeof(long long) * 128); }
 extern "C" int indnet_debug_attn(long long* out) { return (int)cudaMemcpyFromSymbol(out, indnet::g_attn_dbg, sizeof(long long) * 128); }
 #endif
 extern "C" int indnet_attn_fused_bwd(indnet_stream st_, const float* denc_a, const float* denc_b, const void* hout_bf,

@@ -829,17 +829,22 @@ class EpisodePipeline:
         self._join()
 
     # ------------------------------------------------------------------ update (model/base.py:94-99)
-    def adam_m(self, grad_scale: float = 1.0):
-        """Adam update of M's slice alone, on the current stream, as soon as that stream holds M's final gradient
-        (after ntn_dM, or after its all-reduce) AND is ordered after the last reader of M's bf16 shadow (ntn_dcv);
-        leaves global_step alone.  The next ``adam()`` then updates the other slots and advances the step."""
+    def adam_m(self, grad_scale: float = 1.0, lo: int = 0, hi: Optional[int] = None):
+        """Adam update of M's slice alone (or of elements [lo, hi) of it), on the current stream, as soon as that
+        stream holds M's final gradient (after ntn_dM, or after its all-reduce) AND is ordered after the last reader
+        of M's bf16 shadow (ntn_dcv); leaves global_step alone.  The next ``adam()`` then updates the other slots
+        and advances the step.  A caller that updates M in pieces passes the pieces in ascending order."""
         p = self.p
         n = p.offsets["w"]                     # M is the first slot of the flat buffer
-        self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
-                   0.9, 0.999, 0)
-        self._call("indnet_adam_apply", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), n, ptr(p.hyper),
-                   0.9, 0.999, 1e-8, grad_scale, ptr(p.params_bf), None)
-        self._adam_m_done = True
+        hi = n if hi is None else int(hi)
+        if lo == 0:
+            self._call("indnet_adam_prep", ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,
+                       0.9, 0.999, 0)
+        bf = p.params_bf[lo:] if p.params_bf is not None else None
+        self._call("indnet_adam_apply", ptr(p.params[lo:]), ptr(p.grads[lo:]), ptr(p.m[lo:]), ptr(p.v[lo:]), hi - lo,
+                   ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), None)
+        if hi == n:
+            self._adam_m_done = True
 
     def adam(self, grad_scale: float = 1.0):
         p = self.p

@@ -249,10 +249,23 @@ class Base:
         sd.update({"adam_m/" + k: v.cpu().numpy() for k, v in self.store._export(self.store.m).items()})
         sd.update({"adam_v/" + k: v.cpu().numpy() for k, v in self.store._export(self.store.v).items()})
         sd["global_step"] = np.int64(self.store.global_step.item())
+        if self.embed is not None:
+            # the frozen word table is not a trainable and is not stored (the reference's Saver stores it): its shape
+            # and a CRC travel with the checkpoint so that restore() can refuse a different embedding file
+            sd["pred_embed/shape"] = np.asarray(np.asarray(self.embed).shape, dtype=np.int64)
+            sd["pred_embed/crc32"] = np.int64(self._embed_crc())
         np.savez(path, **sd)
+
+    def _embed_crc(self):
+        import zlib
+        return zlib.crc32(np.ascontiguousarray(np.asarray(self.embed), dtype=np.float32).tobytes()) & 0xFFFFFFFF
 
     def restore(self, path):
         z = np.load(path)
+        if "pred_embed/crc32" in z and self.embed is not None:
+            shape = tuple(int(x) for x in z["pred_embed/shape"])
+            if shape != tuple(np.asarray(self.embed).shape) or int(z["pred_embed/crc32"]) != self._embed_crc():
+                raise ValueError("checkpoint %s was trained with a different word embedding table (shape %s)" % (path, shape))
         self.store.load_state_dict({k: torch.from_numpy(z[k]) for k in self.store.tf_shapes})
         for slot, buf in (("adam_m/", self.store.m), ("adam_v/", self.store.v)):
             if slot + "M" in z:

@@ -29,8 +29,17 @@ class DeviceEpisodeSampler:
         self.R = len(sc)
         self.n_max = max(b - a for a, b in sc)
         self.scopes = torch.tensor(sc, dtype=torch.int32, device=self.device).contiguous()
-        self.tables = {k: torch.from_numpy(np.ascontiguousarray(getattr(loader, "data_" + k), dtype=np.int32))
-                       .to(self.device) for k in KEYS}
+        # the embedding kernels index their tables with these ids unchecked (TF raises on an out-of-range id): validate
+        # the instance tables once, here, where they enter the device
+        vocab = getattr(loader, "word_vec_mat", None)
+        host = {k: np.ascontiguousarray(getattr(loader, "data_" + k), dtype=np.int32) for k in KEYS}
+        if host["word"].size:
+            if vocab is not None and (host["word"].min() < 0 or host["word"].max() >= len(vocab) + 2):
+                raise ValueError("word ids outside [0, %d) in the instance table" % (len(vocab) + 2))
+            for k in ("pos1", "pos2"):
+                if host[k].min() < 0 or host[k].max() >= 2 * self.L:
+                    raise ValueError("%s ids outside [0, %d) in the instance table" % (k, 2 * self.L))
+        self.tables = {k: torch.from_numpy(host[k]).to(self.device) for k in KEYS}
         self.py_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.np_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.status = torch.zeros(16, dtype=torch.int32, device=self.device)  # {status, cycles/16, jumps, rows, timeline build: 6 more}

@@ -27,6 +27,8 @@ from .engine import EpisodePipeline
 
 
 class EpisodeTrainer:
+    M_CHUNKS = 4      # pieces of M's gradient all-reduced / updated as a pipeline (data parallel)
+
     def __init__(self, pipe: EpisodePipeline, sampler=None, rank: int = 0, world: int = 1, process_group=None,
                  cuda_graph: bool = True, overlap_allreduce: bool = True, stream_mode: str = "global"):
         self.pipe, self.store, self.cfg = pipe, pipe.p, pipe.cfg
@@ -61,6 +63,10 @@ class EpisodeTrainer:
             self._np_prev = torch.zeros_like(sampler.np_state)
         if self.world > 1:
             pipe.grad_ready_hook = self._on_grad_ready
+            n, k = self.m_end, self.M_CHUNKS
+            step = (n // k + 255) // 256 * 256
+            self._m_chunks = [(lo, min(n, lo + step)) for lo in range(0, n, step)]
+            self._m_events = [torch.cuda.Event() for _ in self._m_chunks]
 
     # ------------------------------------------------------------------ collectives
     def _dist(self):
@@ -70,14 +76,21 @@ class EpisodeTrainer:
     def _on_grad_ready(self, name):
         if not self.overlap:
             return
-        if name == "M":                 # M's gradient is final: its all-reduce runs under the rest of the backward pass
+        if name == "M":
+            # M's gradient is final: its all-reduce runs under the rest of the backward pass, in M_CHUNKS pieces so that
+            # the update of piece i (on the pipeline's side stream) can run while piece i + 1 is still being reduced
             self.comm.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self.comm):
-                self._dist().all_reduce(self.store.grads[: self.m_end], group=self.group)
-        elif name == "M:update":        # ... and so does its Adam update, placed under the encoder's BPTT kernel
-            self.comm.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(self.comm):
-                self.pipe.adam_m(1.0 / self.world)
+                for (lo, hi), ev in zip(self._m_chunks, self._m_events):
+                    self._dist().all_reduce(self.store.grads[lo:hi], group=self.group)
+                    ev.record(self.comm)
+        elif name == "M:update":
+            # ... and so does its Adam update, placed under the encoder's BPTT kernel (the caller's current stream is a
+            # side branch forked there)
+            cur = torch.cuda.current_stream()
+            for (lo, hi), ev in zip(self._m_chunks, self._m_events):
+                cur.wait_event(ev)
+                self.pipe.adam_m(1.0 / self.world, lo, hi)
 
     def _grad_sync(self):
         if self.world <= 1:

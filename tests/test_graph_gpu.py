@@ -80,6 +80,13 @@ def test_train_eval_loops_checkpoint_and_restore(tmp_path, capsys):
     e2 = model2.eval(va, None, 3)
     assert e1 == e2
     assert files == [] or files[0].startswith("m-")
+    # the frozen word table is not in the checkpoint: its fingerprint is, and a different table is refused
+    assert tuple(z["pred_embed/shape"]) == tuple(tr.word_vec_mat.shape)
+    other = tr.word_vec_mat.copy()
+    other[0, 0] += 1.0
+    model3 = InductionGraph(N=3, K=2, Q=5, pred_embed=other, sequence_length=12, hidden_size=8, out_size=10)
+    with pytest.raises(ValueError, match="different word embedding"):
+        model3.restore(str(tmp_path / "manual.npz"))
 
 
 def test_missing_vocab_size_is_an_error():

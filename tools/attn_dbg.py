@@ -20,3 +20,13 @@ for t in range(5):
     r = a[t]
     nxt = a[t + 1][0] if a[t + 1][0] else 0
     print(t, r[1]-r[0], '|', r[2]-r[1], '|', r[3]-r[2], '|', r[4]-r[3], '|', r[5]-r[4], '|', r[6]-r[5], '|', r[7]-r[6], '|', (nxt - r[7]) if nxt else -1)
+
+if hasattr(LIB._dll, "indnet_debug_attn_fwd"):
+    LIB._dll.indnet_debug_attn_fwd.argtypes = [ctypes.c_void_p]
+    print("fwd rc", LIB._dll.indnet_debug_attn_fwd(buf))
+    a = np.array(list(buf), dtype=np.int64).reshape(16, 8)
+    print("forward (persistent), CTA 0, epilogue warp 2 lane 0, per tile: wait acc | drain | bar | softmax (4 bars) | pooling | end bar | (-> next tile top)")
+    for t in range(5):
+        r = a[t]
+        nxt = a[t + 1][0] if a[t + 1][0] else 0
+        print(t, r[1]-r[0], '|', r[2]-r[1], '|', r[3]-r[2], '|', r[4]-r[3], '|', r[5]-r[4], '|', r[6]-r[5], '|', (nxt - r[6]) if nxt else -1)
