@@ -51,6 +51,8 @@ class EpisodeTrainer:
         self.stream = torch.cuda.Stream(device=dev, priority=-1)
         self.side = torch.cuda.Stream(device=dev, priority=0)
         self.comm = torch.cuda.Stream(device=dev, priority=-1)
+        self.upd = torch.cuda.Stream(device=dev, priority=-1)      # M's Adam update behind its all-reduce (data parallel)
+        self._upd_used = False
         self.m_end = self.store.offsets["w"]        # slots are laid out M, w, b, ... (engine.ParamStore)
         self.inputs = dict(word=pipe.word, pos1=pipe.pos1, pos2=pipe.pos2, mask=pipe.mask, label=pipe.label)
         self.graph_step: Optional[torch.cuda.CUDAGraph] = None     # sampler in the loop
@@ -63,7 +65,8 @@ class EpisodeTrainer:
             self._np_prev = torch.zeros_like(sampler.np_state)
         if self.world > 1:
             pipe.grad_ready_hook = self._on_grad_ready
-            n, k = self.m_end, self.M_CHUNKS
+            import os
+            n, k = self.m_end, int(os.environ.get("INDNET_M_CHUNKS", self.M_CHUNKS if self.world >= 4 else 1))
             step = (n // k + 255) // 256 * 256
             self._m_chunks = [(lo, min(n, lo + step)) for lo in range(0, n, step)]
             self._m_events = [torch.cuda.Event() for _ in self._m_chunks]
@@ -87,10 +90,13 @@ class EpisodeTrainer:
         elif name == "M:update":
             # ... and so does its Adam update, placed under the encoder's BPTT kernel (the caller's current stream is a
             # side branch forked there)
-            cur = torch.cuda.current_stream()
-            for (lo, hi), ev in zip(self._m_chunks, self._m_events):
-                cur.wait_event(ev)
-                self.pipe.adam_m(1.0 / self.world, lo, hi)
+            # on a stream of its own: the backward pass must not wait for it, nor the trailing all-reduce
+            self._upd_used = True
+            self.upd.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.upd):
+                for (lo, hi), ev in zip(self._m_chunks, self._m_events):
+                    self.upd.wait_event(ev)
+                    self.pipe.adam_m(1.0 / self.world, lo, hi)
 
     def _grad_sync(self):
         if self.world <= 1:
@@ -98,6 +104,9 @@ class EpisodeTrainer:
         if self.overlap:
             self._dist().all_reduce(self.store.grads[self.m_end:], group=self.group)
             torch.cuda.current_stream().wait_stream(self.comm)
+            if self._upd_used:                 # (a stream that took no part in this step must not be waited on under capture)
+                torch.cuda.current_stream().wait_stream(self.upd)
+                self._upd_used = False
         else:
             self._dist().all_reduce(self.store.grads, group=self.group)
 
