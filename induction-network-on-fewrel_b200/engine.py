@@ -805,8 +805,11 @@ class EpisodePipeline:
                 self._tag = "tc_gemm:lstm_dW"
                 try:
                     with self._branch(0) if d == 1 else contextlib.nullcontext():
+                        # the two directions run side by side, one CTA per SM each (160 KB of operand ring): half of the
+                        # SMs per direction so that both grids are resident at once instead of queueing as two waves
+                        sk = max(1, 148 // (4 * c.u // 128) // 2) if self.branches else 0
                         self._call("indnet_tc_gemm_lstm_dw", ptr(self.x_bf), ptr(self.hprev_bf[d]), ptr(self.dz_bf[d]),
-                                   ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, 0, int(pre0))
+                                   ptr(gk), ptr(p.grad(bn)), c.T, c.D, c.u, sk, int(pre0))
                 finally:
                     self._tag = None
             else:

@@ -153,6 +153,8 @@ class Base:
         from ..trainer import EpisodeTrainer
         rank, _local, world = ddist.init_from_env()
         smp = train_data_loader._device()
+        rows = self.pipeline.word_table.shape[0] if self.pipeline.word_table is not None else int(self.vocab_size)
+        smp.validate_ids(int(rows), self.cfg.L)      # out-of-range ids would be out-of-bounds reads in the embedding kernels
         smp.load_host_streams()
         self.pipeline.cfg.keep_prob = float(self.keepProb)
         if world > 1:                       # every rank starts from rank 0's weights

@@ -29,22 +29,25 @@ class DeviceEpisodeSampler:
         self.R = len(sc)
         self.n_max = max(b - a for a, b in sc)
         self.scopes = torch.tensor(sc, dtype=torch.int32, device=self.device).contiguous()
-        # the embedding kernels index their tables with these ids unchecked (TF raises on an out-of-range id): validate
-        # the instance tables once, here, where they enter the device
-        vocab = getattr(loader, "word_vec_mat", None)
         host = {k: np.ascontiguousarray(getattr(loader, "data_" + k), dtype=np.int32) for k in KEYS}
-        if host["word"].size:
-            if vocab is not None and (host["word"].min() < 0 or host["word"].max() >= len(vocab) + 2):
-                raise ValueError("word ids outside [0, %d) in the instance table" % (len(vocab) + 2))
-            for k in ("pos1", "pos2"):
-                if host[k].min() < 0 or host[k].max() >= 2 * self.L:
-                    raise ValueError("%s ids outside [0, %d) in the instance table" % (k, 2 * self.L))
+        self._id_ranges = {k: ((int(host[k].min()), int(host[k].max())) if host[k].size else (0, 0)) for k in ("word", "pos1", "pos2")}
         self.tables = {k: torch.from_numpy(host[k]).to(self.device) for k in KEYS}
         self.py_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.np_state = torch.zeros(625, dtype=torch.int32, device=self.device)
         self.status = torch.zeros(16, dtype=torch.int32, device=self.device)  # {status, cycles/16, jumps, rows, timeline build: 6 more}
         self._bufs = {}
         self.load_host_streams()
+
+    def validate_ids(self, vocab_rows: int, sequence_length: int):
+        """The embedding kernels index their tables with the sampled ids unchecked (TF raises on an out-of-range id):
+        a model checks the instance tables once against ITS table sizes before training on them."""
+        lo, hi = self._id_ranges["word"]
+        if lo < 0 or hi >= vocab_rows:
+            raise ValueError("word ids [%d, %d] outside the embedding table of %d rows" % (lo, hi, vocab_rows))
+        for k in ("pos1", "pos2"):
+            lo, hi = self._id_ranges[k]
+            if lo < 0 or hi >= 2 * sequence_length:
+                raise ValueError("%s ids [%d, %d] outside [0, %d)" % (k, lo, hi, 2 * sequence_length))
 
     # ------------------------------------------------------------------ stream hand-over
     def load_host_streams(self):

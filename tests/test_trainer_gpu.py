@@ -64,6 +64,26 @@ def test_trainer_steps_on_the_reference_episode_sequence_and_hands_streams_back(
     tr.close()
 
 
+def test_read_async_returns_every_step_one_step_behind():
+    """read_async(): the host reads step t's {loss, accuracy} while step t + 1 runs - same numbers as read()."""
+    cfg, tables, ld, smp, pipe, tr = _make(mode="bf16")
+    cfg2, tables2, ld2, smp2, pipe2, tr2 = _make(mode="bf16")
+    sync, lagged, pend = [], [], None
+    for _ in range(6):
+        tr.step()
+        sync.append(tr.read())
+        tr2.step()
+        nxt = tr2.read_async()
+        if pend is not None:
+            lagged.append(pend.get())
+        pend = nxt
+    lagged.append(pend.get())
+    assert len(lagged) == 6
+    np.testing.assert_allclose(np.array(lagged), np.array(sync), rtol=2e-2)      # float atomics: not bitwise
+    assert all(l > 0 for l, _ in lagged)
+    tr.close(); tr2.close()
+
+
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
 def test_graph_replay_equals_eager_launches(mode):
     res = []
