@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define INDNET_ABI_VERSION 5
+#define INDNET_ABI_VERSION 6
 
 typedef void* indnet_stream; /* cudaStream_t */
 
@@ -322,12 +322,14 @@ int indnet_adam_step(indnet_stream st, float* params, const float* grads, float*
  * rest of the backward pass): indnet_adam_prep computes hyper = {lr_t, lr} from global_step and advances the
  * counter only when advance != 0; indnet_adam_apply updates n elements starting at the given pointers with the
  * lr_t found in hyper; advance_step (optional): the counter, incremented once by this call - pass it with the
- * step's last slice.  Sequence for one step: prep(0), apply(slice), ..., apply(rest, &global_step). */
+ * step's last slice; enable (optional, device): the call is a no-op when *enable == 0 - for a slice whose update
+ * is deferred into the next step's graph, where a replay may find nothing pending.
+ * Sequence for one step: prep(0), apply(slice), ..., apply(rest, &global_step). */
 int indnet_adam_prep(indnet_stream st, long long* global_step, float* hyper, float lr0, int decay_steps,
                      float decay_rate, float beta1, float beta2, int advance);
 int indnet_adam_apply(indnet_stream st, float* params, const float* grads, float* m, float* v, long long n,
                       const float* hyper, float beta1, float beta2, float eps, float grad_scale, void* shadow_bf16,
-                      long long* advance_step);
+                      long long* advance_step, const int* enable);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,8 @@ __global__ void adam_prep_kernel(long long* global_step, float* hyper, float lr0
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, long long n, const float* __restrict__ hyper, float beta1,
                             float beta2, float eps, float gscale, __nv_bfloat16* __restrict__ shadow,
-                            long long* __restrict__ advance) {
+                            long long* __restrict__ advance, const int* __restrict__ enable) {
+  if (enable && *enable == 0) return;          // a deferred slice with nothing pending (first step, or already flushed)
   const float lr_t = hyper[0];
   if (advance && blockIdx.x == 0 && threadIdx.x == 0) *advance += 1;    // the step's last slice closes the step
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -59,7 +60,7 @@ extern "C" int indnet_adam_step(indnet_stream st_, float* params, const float* g
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
   adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
-                                           (__nv_bfloat16*)shadow_bf16, nullptr);
+                                           (__nv_bfloat16*)shadow_bf16, nullptr, nullptr);
   IN_LAUNCH_CHECK("adam_kernel");
   return INDNET_OK;
 }
@@ -79,7 +80,7 @@ extern "C" int indnet_adam_prep(indnet_stream st_, long long* global_step, float
 
 extern "C" int indnet_adam_apply(indnet_stream st_, float* params, const float* grads, float* m, float* v, long long n,
                                  const float* hyper, float beta1, float beta2, float eps, float grad_scale,
-                                 void* shadow_bf16, long long* advance_step) {
+                                 void* shadow_bf16, long long* advance_step, const int* enable) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(n >= 0 && hyper, "adam_apply: bad arguments");
   IN_REQUIRE(n > 0 || !advance_step, "adam_apply: an empty slice cannot close the step");
@@ -88,7 +89,7 @@ extern "C" int indnet_adam_apply(indnet_stream st_, float* params, const float* 
   int blocks = ceil_div(n, 256 * 4);
   if (blocks > 148 * 8) blocks = 148 * 8;
   adam_kernel<<<blocks, 256, 0, st>>>(params, grads, m, v, n, hyper, beta1, beta2, eps, grad_scale,
-                                           (__nv_bfloat16*)shadow_bf16, advance_step);
+                                           (__nv_bfloat16*)shadow_bf16, advance_step, enable);
   IN_LAUNCH_CHECK("adam_kernel");
   return INDNET_OK;
 }

@@ -252,6 +252,7 @@ class EpisodePipeline:
         self.profile = None      # set to [] to collect per-call CUDA-event timings
         self.grad_ready_hook = None   # callable(name): fired when a gradient slot is final ("M" is 95 % of the bytes
                                       # and is produced first, so its all-reduce can hide under the encoder BPTT)
+        self.step_hook = None         # callable(where): "begin" / "before_M" of a training forward pass (trainer.EpisodeTrainer)
         self._tag = None
         # The backward pass is a DAG, not a chain: the weight-gradient GEMMs and M's Adam update hang off the chain
         # of activation gradients.  They are issued on two side streams (forked from / joined back to the caller's
@@ -461,8 +462,12 @@ class EpisodePipeline:
     # ------------------------------------------------------------------ forward (model/graph.py:29-86)
     def forward(self, train: bool = False):
         """InductionGraph.forward + loss / accuracy (model/graph.py:29-109, model/base.py:101-107)."""
+        if train and self.step_hook is not None:
+            self.step_hook("begin")             # e.g. a deferred part of the previous step's update of M starts here ...
         self.encode(train)
         self.induction()
+        if train and self.step_hook is not None:
+            self.step_hook("before_M")          # ... and must be complete here: the relation module reads M
         self.relation(train)
 
     def encode(self, train: bool = False):
@@ -832,11 +837,14 @@ class EpisodePipeline:
         self._join()
 
     # ------------------------------------------------------------------ update (model/base.py:94-99)
-    def adam_m(self, grad_scale: float = 1.0, lo: int = 0, hi: Optional[int] = None):
+    def adam_m(self, grad_scale: float = 1.0, lo: int = 0, hi: Optional[int] = None, final: Optional[bool] = None,
+               enable=None):
         """Adam update of M's slice alone (or of elements [lo, hi) of it), on the current stream, as soon as that
         stream holds M's final gradient (after ntn_dM, or after its all-reduce) AND is ordered after the last reader
-        of M's bf16 shadow (ntn_dcv); leaves global_step alone.  The next ``adam()`` then updates the other slots
-        and advances the step.  A caller that updates M in pieces passes the pieces in ascending order."""
+        of M's bf16 shadow (ntn_dcv); leaves global_step alone.  ``final`` (default: hi reaches the end of M): the
+        next ``adam()`` updates only the other slots and advances the step.  A call with lo == 0 computes this step's
+        lr_t first; one with lo > 0 uses the lr_t in ``hyper`` as it stands (a deferred slice is applied with the
+        lr_t of the step its gradient belongs to).  ``enable``: device int32, the update is skipped when it is 0."""
         p = self.p
         n = p.offsets["w"]                     # M is the first slot of the flat buffer
         hi = n if hi is None else int(hi)
@@ -845,8 +853,8 @@ class EpisodePipeline:
                        0.9, 0.999, 0)
         bf = p.params_bf[lo:] if p.params_bf is not None else None
         self._call("indnet_adam_apply", ptr(p.params[lo:]), ptr(p.grads[lo:]), ptr(p.m[lo:]), ptr(p.v[lo:]), hi - lo,
-                   ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), None)
-        if hi == n:
+                   ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), None, ptr(enable))
+        if (hi == n) if final is None else final:
             self._adam_m_done = True
 
     def adam(self, grad_scale: float = 1.0):
@@ -857,7 +865,7 @@ class EpisodePipeline:
             self._adam_m_done = False
             bf = p.params_bf[n0:] if p.params_bf is not None else None
             self._call("indnet_adam_apply", ptr(p.params[n0:]), ptr(p.grads[n0:]), ptr(p.m[n0:]), ptr(p.v[n0:]),
-                       p.numel - n0, ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), ptr(p.global_step))
+                       p.numel - n0, ptr(p.hyper), 0.9, 0.999, 1e-8, grad_scale, ptr(bf), ptr(p.global_step), None)
             return
         self._call("indnet_adam_step", ptr(p.params), ptr(p.grads), ptr(p.m), ptr(p.v), p.numel,
                    ptr(p.global_step), ptr(p.hyper), self.lr0, self.decay_steps, self.decay_rate,

@@ -27,6 +27,7 @@ from .engine import EpisodePipeline
 
 
 class EpisodeTrainer:
+    M_DEFER = 0.0     # fraction of M whose all-reduce + update moves into the next step's forward window (see __init__)
     # Pieces of M's gradient all-reduced / updated as a pipeline (data parallel).  Measured on 8 B200 at config 1:
     # 1 piece 0.442 ms / step, 2 pieces 0.510, 4 pieces 0.597 - every extra NCCL call costs more (ring, LL protocol,
     # ~40 us each at 8 ranks) than the overlap of the update with the next piece's reduction returns.
@@ -66,10 +67,25 @@ class EpisodeTrainer:
         if sampler is not None:      # stream states as they were BEFORE the look-ahead walk (see suspend())
             self._py_prev = torch.zeros_like(sampler.py_state)
             self._np_prev = torch.zeros_like(sampler.np_state)
+        # Data parallel, optional: the tail [m_split, m_end) of M's gradient is all-reduced and applied at the START of
+        # the next step's graph, underneath the encoder's forward pass (which does not read M), the head [0, m_split)
+        # underneath the backward pass as before - two windows instead of one for the 26 MB that dominate the step's
+        # communication.  The update is exact (M is complete before the relation module reads it); between steps the
+        # tail is one step behind until flush() (suspend / close call it).  INDNET_M_DEFER = fraction deferred.
+        import os
+        frac = float(os.environ.get("INDNET_M_DEFER", self.M_DEFER))
+        ok = self.world > 1 and self.overlap and pipe.bf16 and pipe.tc_lstm and pipe.fused_attn and pipe.cfg.H <= 256
+        self.m_split = self.m_end - (int(frac * self.m_end) // 256 * 256 if ok and frac > 0 else 0)
+        self.defer = self.m_split < self.m_end
+        self.pending = torch.zeros(1, dtype=torch.int32, device=dev)     # 1: the deferred tail holds an un-applied gradient
+        self.comm2 = torch.cuda.Stream(device=dev, priority=-1)
+        self._comm2_used = False
         if self.world > 1:
             pipe.grad_ready_hook = self._on_grad_ready
+            if self.defer:
+                pipe.step_hook = self._on_step
             import os
-            n, k = self.m_end, int(os.environ.get("INDNET_M_CHUNKS", self.M_CHUNKS))
+            n, k = self.m_split, int(os.environ.get("INDNET_M_CHUNKS", self.M_CHUNKS))
             step = (n // k + 255) // 256 * 256
             self._m_chunks = [(lo, min(n, lo + step)) for lo in range(0, n, step)]
             self._m_events = [torch.cuda.Event() for _ in self._m_chunks]
@@ -99,7 +115,32 @@ class EpisodeTrainer:
             with torch.cuda.stream(self.upd):
                 for (lo, hi), ev in zip(self._m_chunks, self._m_events):
                     self.upd.wait_event(ev)
-                    self.pipe.adam_m(1.0 / self.world, lo, hi)
+                    self.pipe.adam_m(1.0 / self.world, lo, hi, final=(hi == self.m_split))
+
+    def _on_step(self, where):
+        if where == "begin":                    # the previous step's tail of M: reduce + apply under the encoder forward
+            self._comm2_used = True
+            self.comm2.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm2):
+                self._deferred_tail()
+        elif where == "before_M" and self._comm2_used:
+            torch.cuda.current_stream().wait_stream(self.comm2)
+            self._comm2_used = False
+
+    def _deferred_tail(self):
+        self._dist().all_reduce(self.store.grads[self.m_split: self.m_end], group=self.group)
+        self.pipe.adam_m(1.0 / self.world, self.m_split, self.m_end, final=False, enable=self.pending)
+
+    def flush(self):
+        """Applies what the deferred part of M's update still owes (collective: every rank calls it).  After it the
+        weights are exactly those of the synchronous step; the next step's graph finds nothing pending."""
+        if not self.defer or not self._primed:
+            return
+        from ._lib import LIB, current_stream, ptr
+        with torch.cuda.stream(self.stream):
+            self._deferred_tail()
+            LIB.call("indnet_memset", current_stream(), ptr(self.pending), 0, 4)
+        self.stream.synchronize()
 
     def _grad_sync(self):
         if self.world <= 1:
@@ -120,6 +161,9 @@ class EpisodeTrainer:
         self.pipe.backward(early_adam=self.world == 1 or self.overlap)
         self._grad_sync()
         self.pipe.adam(grad_scale=1.0 / self.world)
+        if self.defer:
+            from ._lib import LIB, current_stream, ptr
+            LIB.call("indnet_memset", current_stream(), ptr(self.pending), 1, 4)     # this step's tail of M is now owed
 
     def _walk(self):
         c = self.cfg
@@ -185,6 +229,7 @@ class EpisodeTrainer:
         s.params.copy_(snap["params"]); s.m.copy_(snap["m"]); s.v.copy_(snap["v"])
         s.global_step.copy_(snap["step"])
         self.pipe.running.copy_(snap["running"])
+        self.pending.zero_()
         s.refresh_bf16()
         if self.smp is not None:
             self.smp.py_state.copy_(snap["py"]); self.smp.np_state.copy_(snap["np"])
@@ -282,6 +327,7 @@ class EpisodeTrainer:
         run so far: the look-ahead walk (the picks of the step that has not run yet) is discarded and the
         streams rewound to just before it.  Call before anything else draws from ``random`` / ``numpy.random``
         (the evaluation loop, model/base.py:168-170); ``step`` re-walks on its own afterwards."""
+        self.flush()
         if self.smp is None or self._need_walk or not self._primed:
             return
         self.stream.synchronize()
@@ -305,7 +351,9 @@ class EpisodeTrainer:
     def close(self):
         """Ordered teardown: drain, drop the graphs (they hold references to the NCCL communicator's work),
         drain again.  The caller destroys the process group afterwards."""
+        self.flush()
         torch.cuda.synchronize()
         self.graph_step = self.graph_train = None
         self.pipe.grad_ready_hook = None
+        self.pipe.step_hook = None
         torch.cuda.synchronize()

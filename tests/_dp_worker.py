@@ -36,9 +36,12 @@ def main(out, global_B, mode, steps):
         tr.step()
         losses.append(tr.read()[0])
     tr.check_sampler()
+    tr.flush()                       # a deferred tail of M's update (INDNET_M_DEFER) is applied before the weights are read
     torch.cuda.synchronize()
     np.savez(out + ".%d.npz" % rank, word=pipe.word.cpu().numpy(), label=pipe.label.cpu().numpy(),
              grads=store.grads.cpu().numpy(), params=store.params.cpu().numpy(), losses=np.array(losses),
+             adam_m=store.m.cpu().numpy(), adam_v=store.v.cpu().numpy(), step=store.global_step.cpu().numpy(),
+             deferred=np.array(bool(tr.defer)),
              graph=np.array(tr.graph_step is not None))
     tr.close()
     if world > 1:

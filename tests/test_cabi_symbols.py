@@ -18,7 +18,7 @@ def test_header_parses_and_library_exports_every_symbol():
     dll = ctypes.CDLL(_lib.LIB_PATH)
     for name in protos:
         assert hasattr(dll, name), "libindnet.so does not export %s" % name
-    assert _lib.LIB.load().indnet_abi_version() == 5
+    assert _lib.LIB.load().indnet_abi_version() == 6
 
 
 def test_argument_errors_are_reported_not_thrown():

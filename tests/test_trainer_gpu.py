@@ -134,12 +134,12 @@ def test_base_train_fast_path_prints_the_reference_lines_and_logs_scalars(tmp_pa
         assert torch.allclose(outs[0][2][k], outs[1][2][k], rtol=0, atol=1e-4), k
 
 
-def _run_dp(tmp_path, world, global_B, mode, steps=2):
-    out = str(tmp_path / ("dp_w%d" % world))
+def _run_dp(tmp_path, world, global_B, mode, steps=2, env=None, tag=""):
+    out = str(tmp_path / ("dp_w%d%s" % (world, tag)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(29500 + world + os.getpid() % 500),
            os.path.join(ROOT, "tests", "_dp_worker.py"), out, str(global_B), mode, str(steps)]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stderr[-3000:]
     return [np.load(out + ".%d.npz" % k) for k in range(world)]
 
@@ -164,3 +164,21 @@ def test_two_gpu_step_equals_one_gpu_step_on_the_same_global_batch(tmp_path, mod
     l1, l2 = float(one["losses"][0]), float(np.mean([t["losses"][0] for t in two]))
     assert abs(l1 - l2) < (1e-5 if mode == "fp32" else 2e-2) * l1
     assert np.abs(one["params"] - two[0]["params"]).max() < 2 * 1e-3 * (2e-2 if mode == "fp32" else 1.0)
+
+
+def test_deferred_tail_of_M_is_the_synchronous_update(tmp_path):
+    """INDNET_M_DEFER: part of M's all-reduce + Adam update moves into the next step's graph (under the encoder's
+    forward pass).  After flush() the weights and Adam moments are those of the run that does it all inside the step."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    sync = _run_dp(tmp_path, 2, 4, "bf16", steps=4, tag="s")
+    late = _run_dp(tmp_path, 2, 4, "bf16", steps=4, env={"INDNET_M_DEFER": "0.4"}, tag="d")
+    assert bool(late[0]["deferred"]) and not bool(sync[0]["deferred"]) and bool(late[0]["graph"])
+    assert int(late[0]["step"][0]) == int(sync[0]["step"][0]) == 4
+    assert np.array_equal(late[0]["params"], late[1]["params"])              # the ranks stay bitwise in step
+    for k in ("adam_m", "adam_v"):                                              # one application per step, no more, no less
+        a, b = late[0][k], sync[0][k]
+        assert np.abs(a - b).max() <= 5e-2 * np.abs(b).max(), k
+    moved = np.abs(late[0]["params"] - sync[0]["params"]) > 1e-6              # Adam: +-lr flips where the gradient is noise
+    assert moved.mean() < 0.05
+    np.testing.assert_allclose(late[0]["losses"], sync[0]["losses"], rtol=3e-2)
