@@ -801,7 +801,7 @@ class EpisodePipeline:
                     self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)
                 self._call("indnet_embed_pos_bwd2", ptr(self.pos1), ptr(self.pos2), ptr(self.dx2[0]), ptr(self.dx2[1]), 16, 0,
                            ptr(g1), ptr(g2), c.T, POS_DIM, 2 * c.L)
-        for d in ((1, 0) if self.tc_lstm else (0, 1)):
+        for nth, d in enumerate((1, 0) if self.tc_lstm else (0, 1)):
             kn, bn = ((FW_K, FW_B), (BW_K, BW_B))[d]
             gk = p.grad(kn)
             if self.tc_lstm:
@@ -824,7 +824,7 @@ class EpisodePipeline:
                 self._call("indnet_colsum_bf16", ptr(self.dz_bf[d]), c.T, u4, ptr(p.grad(bn)))
             if not fused_dx:
                 self._tc(0, 0, c.T, c.D - n0, u4, self.dz_bf[d], u4, p.view_bf(kn)[n0:], u4,
-                         C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if d == 0 else 1), splitk=1, tag="lstm_dx")
+                         C=self.dx.data_ptr() + 4 * n0, ldc=c.D, accumulate=(0 if nth == 0 else 1), splitk=1, tag="lstm_dx")
         if not fused_dx:
             self._call("indnet_memset", ptr(g1), 0, g1.numel() * 4)
             self._call("indnet_memset", ptr(g2), 0, g2.numel() * 4)

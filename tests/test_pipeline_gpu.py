@@ -148,6 +148,35 @@ def test_trainable_word_embedding_gradient():
         assert rel_err(got[k], p[k].grad) < GRAD_TOL, k
 
 
+def test_trainable_word_embedding_gradient_bf16_tensor_core_path():
+    """No pred_embed (model/base.py:62-65): the word table is a trainable, so the BPTT kernel cannot keep only the
+    position columns of dx - the two dz * W_x^T GEMMs and the full embedding scatter run instead (also the
+    INDNET_NO_FUSED_DX path)."""
+    from induction_b200.engine import EpisodePipeline, ParamStore, tf_param_shapes
+    cfg, tables, inputs, label, params = make_case("cfg0_5w5s", seed=9, vocab=300, mode="bf16")
+    rows = tables["word_vec_mat"].shape[0]
+    shapes = tf_param_shapes(cfg.N, cfg.L, cfg.E, cfg.u, cfg.S, vocab_rows=rows)
+    full = dict(params)
+    full["word_embedding"] = torch.from_numpy(tables["word_vec_mat"]).clone()
+    store = ParamStore(shapes)
+    store.load_state_dict(full)
+    pipe = EpisodePipeline(cfg, store, None)
+    assert pipe.tc_lstm and pipe.trainable_words
+    pipe.set_inputs(inputs, label)
+    pipe.forward(train=True)
+    pipe.backward()
+    torch.cuda.synchronize()
+    from oracle import induction_oracle as orc
+    from _cases import to_torch_inputs
+    p = {k: v.double().requires_grad_(True) for k, v in full.items()}
+    ti, tl = to_torch_inputs(inputs, label)
+    out = orc.forward(p, p["word_embedding"], ti["word"], ti["pos1"], ti["pos2"], ti["mask"], tl, cfg.N, cfg.K, cfg.Q)
+    out["loss"].backward()
+    assert rel_err(pipe.probs, out["probs"]) < BF16_TOL
+    errs, worst, cos = bf16_grad_check(store.grad_dict(), {k: v.grad for k, v in p.items()}, "trainable words")
+    print("trainable words bf16: worst", worst, errs[worst], "cos", cos)
+
+
 def test_large_batch_properties():
     """BASELINE configs[1] at full size (5-way 1-shot, 64 episodes, L=40, u=128): too slow for the
     float64 oracle in a unit test, so check size-independent properties: episode independence (a
