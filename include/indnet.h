@@ -183,10 +183,15 @@ int indnet_lstm_bwd(indnet_stream st, const float* dhout, const float* gates, co
                     const float* Wh_bw, float* whT_scratch, float* dz, int X, int L, int u, float keep_prob,
                     unsigned long long seed, const long long* seed_step);
 
+/* The weight packing step of indnet_lstm_fwd_tc on its own (depends on the weights only): a caller may run it beside
+ * the embedding gather and then pass NULL for the four weight pointers of indnet_lstm_fwd_tc. */
+int indnet_lstm_pack_tc(indnet_stream st, const float* kernel_fw, const float* bias_fw, const float* kernel_bw,
+                        const float* bias_bw, void* wt_scratch, int D, int u);
 /* bf16 tensor-core mode of indnet_lstm_fwd with the input projection AND the bias fused into the MMAs
  * (hidden_size 128, E+10 <= 62): x_bf [X][L][64] bf16 embeddings with 1.0 in columns D and D+1
  * (indnet_embed_fwd_bf16), kernel_* the TF LSTM kernels [D+u][4u] fp32, bias_* [4u].  wt_scratch:
- * caller-provided bf16 [2][4u][192] (packed transposed weights incl. the bias rows, rebuilt every call).
+ * caller-provided bf16 [2][4u][192] (packed transposed weights incl. the bias rows, rebuilt every call; with the
+ * four weight pointers NULL it is taken as already packed by indnet_lstm_pack_tc).
  * hout (fp32 copy) must be NULL.  Writes hout_bf [X][L][2u] bf16 and, when given (training; pass all three
  * or none), for BPTT: gates_bf [2][X][L][u][4] bf16 (i, j, f, o of a unit adjacent), cstate_bf [2][X][L][u]
  * bf16 (the recurrence itself carries c in fp32 registers), hprev_bf [2][X][L][u] bf16.  All buffers

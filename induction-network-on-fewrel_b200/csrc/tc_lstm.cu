@@ -740,6 +740,19 @@ int map_tok(CUtensorMap* tm, const void* base, int inner, int X, int L, int box_
 }
 }  // namespace
 
+// The weight packing of indnet_lstm_fwd_tc as a call of its own (it depends on the weights only, so a caller can run it
+// beside the embedding gather and pass NULL weights to indnet_lstm_fwd_tc).
+extern "C" int indnet_lstm_pack_tc(indnet_stream st_, const float* kernel_fw, const float* bias_fw, const float* kernel_bw,
+                                   const float* bias_bw, void* wt_scratch, int D, int u) {
+  cudaStream_t st = (cudaStream_t)st_;
+  IN_REQUIRE(u == LT_U && D > 0 && D + 2 <= LT_KX, "lstm_pack_tc: needs hidden_size 128 and E + 12 <= 64 (u=%d D=%d)", u, D);
+  IN_REQUIRE(kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch, "lstm_pack_tc: null pointer");
+  lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw, bias_fw, bias_bw,
+                                                                                    (__nv_bfloat16*)wt_scratch, D);
+  IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
+  return INDNET_OK;
+}
+
 extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const float* kernel_fw, const float* bias_fw,
                                   const float* kernel_bw, const float* bias_bw, void* wt_scratch, float* hout,
                                   void* hout_bf, void* gates_bf, void* cstate_bf, void* hprev_bf, int X, int L, int D,
@@ -751,14 +764,17 @@ extern "C" int indnet_lstm_fwd_tc(indnet_stream st_, const void* x_bf, const flo
   IN_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "lstm_fwd_tc: keep_prob must be in (0, 1], got %f", keep_prob);
   IN_REQUIRE(hout == nullptr, "lstm_fwd_tc: the fp32 copy of the output is no longer produced - pass hout = NULL");
   if (X == 0) return INDNET_OK;
-  IN_REQUIRE(x_bf && kernel_fw && bias_fw && kernel_bw && bias_bw && wt_scratch && hout_bf, "lstm_fwd_tc: null pointer");
+  const bool packed = !kernel_fw && !bias_fw && !kernel_bw && !bias_bw;     // wt_scratch filled by indnet_lstm_pack_tc
+  IN_REQUIRE(x_bf && (packed || (kernel_fw && bias_fw && kernel_bw && bias_bw)) && wt_scratch && hout_bf, "lstm_fwd_tc: null pointer");
   const bool save = gates_bf != nullptr;
   IN_REQUIRE(save == (cstate_bf != nullptr) && save == (hprev_bf != nullptr),
              "lstm_fwd_tc: pass all of gates_bf / cstate_bf / hprev_bf (training) or none (inference)");
   IN_REQUIRE((long long)X * L * (2 * LT_U) < 4294967296LL, "lstm_fwd_tc: X*L*2u exceeds 32-bit element indexing");
-  lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw, bias_fw, bias_bw,
-                                                                                    (__nv_bfloat16*)wt_scratch, D);
-  IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
+  if (!packed) {
+    lstm_pack_weights_kernel<<<dim3(ceil_div(4 * LT_U * LT_K, 256), 2), 256, 0, st>>>(kernel_fw, kernel_bw, bias_fw, bias_bw,
+                                                                                      (__nv_bfloat16*)wt_scratch, D);
+    IN_LAUNCH_CHECK("lstm_pack_weights_kernel");
+  }
   CUtensorMap tmX, tmHout, tmHprev, tmC, tmG;
   // one wave of 16-sentence CTAs when the batch is small enough, else 32-sentence CTAs with phase-shifted halves
   const int nhalf = (2 * ceil_div(X, LT_NH) <= 148) ? 1 : 2;

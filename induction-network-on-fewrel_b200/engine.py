@@ -530,14 +530,18 @@ class EpisodePipeline:
         keep = c.keep_prob if train else 1.0
         wt = p.view("word_embedding") if self.trainable_words else self.word_table
         u4 = 4 * c.u
+        if self.tc_lstm:
+            with self._branch(0):       # the weight packing depends on the weights only: beside the embedding gather
+                self._call("indnet_lstm_pack_tc", ptr(p.view(FW_K)), ptr(p.view(FW_B)), ptr(p.view(BW_K)), ptr(p.view(BW_B)),
+                           ptr(self.wt_bf), c.D, c.u)
         self._call("indnet_embed_fwd_bf16", ptr(self.word), ptr(self.pos1), ptr(self.pos2), ptr(wt),
                    ptr(p.view("pos1_embedding")), ptr(p.view("pos2_embedding")), ptr(self.x_bf), c.T, c.E, POS_DIM)
         if self.tc_lstm:
             # input projection + recurrence + gates in one persistent tcgen05 kernel; eval / inference runs skip the
             # BPTT streams (gates, c, h_prev)
             save = train and not c.inference
-            self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), ptr(p.view(FW_K)), ptr(p.view(FW_B)),
-                       ptr(p.view(BW_K)), ptr(p.view(BW_B)), ptr(self.wt_bf), None, ptr(self.hout_bf),
+            self._join(0)
+            self._call("indnet_lstm_fwd_tc", ptr(self.x_bf), None, None, None, None, ptr(self.wt_bf), None, ptr(self.hout_bf),
                        ptr(self.gates_bf) if save else None, ptr(self.cstate_bf) if save else None,
                        ptr(self.hprev_bf) if save else None, c.X, c.L, c.D, c.u, keep, self.seed, ptr(p.global_step))
         elif self.tc_lstm256 and not train:
