@@ -29,3 +29,28 @@ def test_pytest_collects_only_tests_dir():
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "tools/" not in r.stdout
+
+
+def test_tools_compile():
+    import py_compile
+    for name in sorted(os.listdir(os.path.join(ROOT, "tools"))):
+        if name.endswith(".py"):
+            py_compile.compile(os.path.join(ROOT, "tools", name), doraise=True)
+
+
+def test_every_exported_entry_point_is_declared_in_the_header():
+    """include/indnet.h is the boundary: an `extern "C"` entry in csrc/ that the header does not declare is invisible to
+    the ctypes binding (which is generated from the header) - only the timeline-build debug readers are exempt."""
+    import re
+    import induction_b200  # noqa: F401
+    from induction_b200._lib import parse_header
+    declared = set(parse_header())
+    defined = set()
+    csrc = os.path.join(ROOT, "induction-network-on-fewrel_b200", "csrc")
+    for name in os.listdir(csrc):
+        if name.endswith(".cu"):
+            src = open(os.path.join(csrc, name)).read()
+            defined |= set(re.findall(r'extern\s+"C"\s+(?:const\s+char\s*\*|long long|int)\s+(indnet_\w+)\s*\(', src))
+    extra = {n for n in defined - declared if not n.startswith("indnet_debug")}
+    assert not extra, sorted(extra)
+    assert not (declared - defined), sorted(declared - defined)
