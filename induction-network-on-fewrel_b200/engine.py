@@ -267,8 +267,14 @@ class EpisodePipeline:
         f = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)  # noqa: E731
         i32 = lambda *s: torch.zeros(*s, dtype=torch.int32, device=self.dev)  # noqa: E731
         # inputs ("placeholders", model/base.py:44-52)
-        self.word, self.pos1, self.pos2, self.mask = (i32(c.B, c.n_s, c.L) for _ in range(4))
-        self.label = i32(c.B, c.n_q)
+        # the five placeholders are slices of ONE buffer, so a host that keeps its episodes in the same layout
+        # (pack_inputs) feeds a step with a single H2D copy
+        n_in, n_lab = c.B * c.n_s * c.L, c.B * c.n_q
+        seg = (n_in + 63) // 64 * 64
+        self._in_seg, self._in_n, self._in_lab = seg, n_in, n_lab
+        self.inbuf = i32(4 * seg + (n_lab + 63) // 64 * 64)
+        self.word, self.pos1, self.pos2, self.mask = (self.inbuf[k * seg: k * seg + n_in].view(c.B, c.n_s, c.L) for k in range(4))
+        self.label = self.inbuf[4 * seg: 4 * seg + n_lab].view(c.B, c.n_q)
         # forward activations
         inf = bool(cfg.inference)
         if inf and not (cfg.mode == "bf16" and c.u in (128, 256) and c.D <= 62):
@@ -454,10 +460,26 @@ class EpisodePipeline:
         """Copies one batch into the static input buffers.  Accepts torch tensors (any device) or
         numpy arrays shaped [B, n_s, L] (or [n_s, L] when B == 1)."""
         c = self.cfg
+        if isinstance(inputs, torch.Tensor) and query_label is None:       # a batch in the layout of pack_inputs
+            if inputs.dtype != torch.int32 or inputs.numel() != self.inbuf.numel():
+                raise ValueError("packed inputs must be the int32 tensor pack_inputs() returns")
+            self.inbuf.copy_(inputs.reshape(-1), non_blocking=True)
+            return
         for k, buf in (("word", self.word), ("pos1", self.pos1), ("pos2", self.pos2), ("mask", self.mask)):
             t = torch.as_tensor(inputs[k])
             buf.copy_(t.reshape(c.B, c.n_s, c.L).to(torch.int32), non_blocking=True)
         self.label.copy_(torch.as_tensor(query_label).reshape(c.B, c.n_q).to(torch.int32), non_blocking=True)
+
+    def pack_inputs(self, inputs, query_label, pin: bool = True) -> torch.Tensor:
+        """One batch ({word, pos1, pos2, mask} [B, n_s, L] + labels [B, n_q]) as ONE host int32 tensor in the layout
+        of the device input buffer (pinned by default): ``set_inputs(packed)`` / ``EpisodeTrainer.step_on(packed)`` then
+        move it with a single copy."""
+        c = self.cfg
+        out = torch.zeros(self.inbuf.numel(), dtype=torch.int32)
+        for i, k in enumerate(("word", "pos1", "pos2", "mask")):
+            out[i * self._in_seg: i * self._in_seg + self._in_n] = torch.as_tensor(inputs[k]).reshape(-1).to(torch.int32)
+        out[4 * self._in_seg: 4 * self._in_seg + self._in_lab] = torch.as_tensor(query_label).reshape(-1).to(torch.int32)
+        return out.pin_memory() if pin else out
 
     # ------------------------------------------------------------------ forward (model/graph.py:29-86)
     def forward(self, train: bool = False):

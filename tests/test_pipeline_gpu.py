@@ -177,6 +177,23 @@ def test_trainable_word_embedding_gradient_bf16_tensor_core_path():
     print("trainable words bf16: worst", worst, errs[worst], "cos", cos)
 
 
+def test_packed_inputs_equal_the_five_separate_copies():
+    """pack_inputs(): one host tensor in the layout of the device input buffer = one H2D copy per step."""
+    cfg, tables, inputs, label, params = make_case("smoke", seed=4)
+    pipe = build_pipeline(cfg, tables, params)
+    pipe.set_inputs(inputs, label)
+    ref = [t.clone() for t in (pipe.word, pipe.pos1, pipe.pos2, pipe.mask, pipe.label)]
+    pipe.inbuf.zero_()
+    packed = pipe.pack_inputs(inputs, label)
+    assert packed.is_pinned() and packed.dtype == torch.int32
+    pipe.set_inputs(packed, None)
+    torch.cuda.synchronize()
+    for a, b in zip(ref, (pipe.word, pipe.pos1, pipe.pos2, pipe.mask, pipe.label)):
+        assert torch.equal(a, b)
+    with pytest.raises(ValueError):
+        pipe.set_inputs(packed[:-1], None)
+
+
 def test_large_batch_properties():
     """BASELINE configs[1] at full size (5-way 1-shot, 64 episodes, L=40, u=128): too slow for the
     float64 oracle in a unit test, so check size-independent properties: episode independence (a
