@@ -297,10 +297,13 @@ int indnet_squash_bwd(indnet_stream st, const float* v, const float* dout, float
  * labels [rows]; probs [rows][N]; loss_part [rows] = sum_c (p-y)^2; correct [rows] = argmax hit.
  * out2 / running / ticket (optional, out2 and ticket together): the block that finishes last also does what
  * indnet_loss_acc_reduce does (same row order, hence the same bits); ticket is a zero-initialised device
- * counter owned by the caller, left at zero again on return. */
+ * counter owned by the caller, left at zero again on return.
+ * dlogit / dV / dV_bf / ld_bf / scale (optional, training): the head's backward for the fused mean-squared-error loss
+ * is local to a row, so the same launch also writes what indnet_ntn_head_bwd (dprobs = NULL, dw = db = NULL) would. */
 int indnet_ntn_head_fwd(indnet_stream st, const float* V, const float* w, const float* b, const int* labels,
                         float* probs, float* loss_part, int* correct, int rows, int N, int S, float* out2,
-                        float* running, unsigned int* ticket);
+                        float* running, unsigned int* ticket, float* dlogit, float* dV, void* dV_bf, int ld_bf,
+                        float scale);
 /* out2[0] = loss (mean over rows*N), out2[1] = accuracy.  running (optional, device float[3]): += {loss,
  * accuracy, 1} - the running sums of model/base.py:156-158 kept on the device. */
 int indnet_loss_acc_reduce(indnet_stream st, const float* loss_part, const int* correct, float* out2, float* running,

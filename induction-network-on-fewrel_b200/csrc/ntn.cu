@@ -23,8 +23,9 @@ __global__ void __launch_bounds__(NTN_NT)
 ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, const float* __restrict__ bias,
                     const int* __restrict__ labels, float* __restrict__ probs, float* __restrict__ loss_part,
                     int* __restrict__ correct, int N, int S, float* __restrict__ out2, float* __restrict__ running,
-                    unsigned int* __restrict__ ticket) {
-  extern __shared__ float pr[];   // [N]
+                    unsigned int* __restrict__ ticket, float* __restrict__ dlogit, float* __restrict__ dV,
+                    __nv_bfloat16* __restrict__ dV_bf, int ld_bf, float scale) {
+  extern __shared__ float pr[];   // [N] probs, then [N] dlogit (training)
   __shared__ bool last;
   __shared__ float sl[NTN_NT / 32], sa[NTN_NT / 32];
   const int row = blockIdx.x;
@@ -65,6 +66,30 @@ ntn_head_fwd_kernel(const float* __restrict__ V, const float* __restrict__ w, co
     __syncthreads();
   }
   __syncthreads();
+  if (dV) {
+    // training: the backward of the head is local to the row (fused MSE gradient, sigmoid, FC, ReLU mask - exactly
+    // ntn_head_bwd_kernel), so it is emitted here and the backward pass starts one launch further down the chain
+    float* dl = pr + N;
+    if (threadIdx.x < N) {
+      const int c = threadIdx.x;
+      const float p = pr[c];
+      const float g = scale * 2.0f * (p - ((c == labels[row]) ? 1.0f : 0.0f)) * p * (1.0f - p);
+      dl[c] = g;
+      dlogit[(long long)row * N + c] = g;
+    }
+    __syncthreads();
+    for (int r = threadIdx.x; r < NS; r += NTN_NT) {
+      float g = 0.f;
+      if (v[r] > 0.f) {
+        const int c = r / S, k = r % S;
+        const float* wr = w + (long long)(k * N + c) * N;
+        for (int cp = 0; cp < N; ++cp) g = fmaf(wr[cp], dl[cp], g);
+      }
+      dV[(long long)row * NS + r] = g;
+      if (dV_bf) dV_bf[(long long)row * ld_bf + r] = __float2bfloat16(g);
+    }
+    if (dV_bf) for (int r = NS + threadIdx.x; r < ld_bf; r += NTN_NT) dV_bf[(long long)row * ld_bf + r] = __float2bfloat16(0.f);
+  }
   if (threadIdx.x == 0) {
     const int y = labels[row];
     float l = 0.f, best = pr[0];
@@ -203,14 +228,19 @@ using namespace indnet;
 
 extern "C" int indnet_ntn_head_fwd(indnet_stream st_, const float* V, const float* w, const float* b, const int* labels,
                                    float* probs, float* loss_part, int* correct, int rows, int N, int S, float* out2,
-                                   float* running, unsigned int* ticket) {
+                                   float* running, unsigned int* ticket, float* dlogit, float* dV, void* dV_bf, int ld_bf,
+                                   float scale) {
   cudaStream_t st = (cudaStream_t)st_;
   IN_REQUIRE(rows >= 0 && N > 0 && S > 0, "ntn_head_fwd: bad sizes rows=%d N=%d S=%d", rows, N, S);
   if (rows == 0) return INDNET_OK;
   IN_REQUIRE(V && w && b && labels && probs && loss_part && correct, "ntn_head_fwd: null pointer");
   IN_REQUIRE(!out2 == !ticket, "ntn_head_fwd: out2 and ticket go together");
-  ntn_head_fwd_kernel<<<rows, NTN_NT, sizeof(float) * N, st>>>(V, w, b, labels, probs, loss_part, correct, N, S, out2,
-                                                               running, ticket);
+  IN_REQUIRE(!dV == !dlogit && (dV || !dV_bf), "ntn_head_fwd: dlogit and dV go together (dV_bf optional)");
+  IN_REQUIRE(!dV || N <= NTN_NT, "ntn_head_fwd: the fused backward needs N <= %d classes", NTN_NT);
+  IN_REQUIRE(!dV_bf || ld_bf >= N * S, "ntn_head_fwd: bf16 row stride %d shorter than N*S", ld_bf);
+  ntn_head_fwd_kernel<<<rows, NTN_NT, sizeof(float) * 2 * N, st>>>(V, w, b, labels, probs, loss_part, correct, N, S, out2,
+                                                                   running, ticket, dlogit, dV, (__nv_bfloat16*)dV_bf, ld_bf,
+                                                                   scale);
   IN_LAUNCH_CHECK("ntn_head_fwd_kernel");
   return INDNET_OK;
 }

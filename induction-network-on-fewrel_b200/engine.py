@@ -543,7 +543,21 @@ class EpisodePipeline:
         # a8-a10: relu, FC, sigmoid, squared error, argmax hit
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S,
-                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket))   # + loss / accuracy means
+                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket),   # + loss / accuracy means
+                   *self._head_bwd_args(train, False))
+
+    def _head_bwd_args(self, train: bool, bf: bool):
+        """Training: the head kernel also emits its own backward (dlogit, dV[, bf16 copy]) - it is local to a row - and
+        ``backward`` skips the launch that would have produced them."""
+        c = self.cfg
+        self._head_bwd_done = bool(train and c.N <= 128)
+        if not self._head_bwd_done:
+            return None, None, None, 0, 0.0
+        if not self._bwd_ready:
+            self._alloc_bwd()
+        rows = c.B * c.n_q
+        return (ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf) if bf else None, self.NSp if bf else 0,
+                1.0 / (rows * c.N))
 
     def _encode_bf16(self, train: bool):
         """bf16 tensor-core mode: every large contraction runs on tcgen05 (fp32 accumulation); the
@@ -611,7 +625,8 @@ class EpisodePipeline:
                  sA=c.n_q * c.H, sB=NS * c.H, sC=c.n_q * NS, tag="ntn_stage2")
         self._call("indnet_ntn_head_fwd", ptr(self.V), ptr(p.view("w")), ptr(p.view("b")), ptr(self.label),
                    ptr(self.probs), ptr(self.loss_part), ptr(self.correct), c.B * c.n_q, c.N, c.S,
-                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket))   # + loss / accuracy means
+                   ptr(self.out2), ptr(self.running) if train else None, ptr(self.ticket),   # + loss / accuracy means
+                   *self._head_bwd_args(train, True))
 
     # ------------------------------------------------------------------ backward
     def _alloc_bwd(self):
@@ -654,10 +669,14 @@ class EpisodePipeline:
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
-        # loss + head
-        self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
-                   None, ptr(self.dlogit), ptr(self.dV), None, 0, ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
-                   1.0 / (rows * c.N))
+        # loss + head (dlogit / dV came out of the forward's head kernel when that ran in training mode)
+        if getattr(self, "_head_bwd_done", False):
+            self._head_bwd_done = False
+            self._call("indnet_ntn_head_dw", ptr(self.V), ptr(self.dlogit), ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S)
+        else:
+            self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
+                       None, ptr(self.dlogit), ptr(self.dV), None, 0, ptr(p.grad("w")), ptr(p.grad("b")), rows, c.N, c.S,
+                       1.0 / (rows * c.N))
         # dqe_b = dV_b T'_b ; dT'_b = dV_b^T qe_b
         self._gemm(0, 0, c.n_q, c.H, NS, ptr(self.dV), NS, ptr(self.Tp), c.H, ptr(self.deq), c.H,
                    batch=c.B, sA=(c.n_q * NS, 0), sB=(NS * c.H, 0), sC=(c.n_q * c.H, 0), tag="ntn_dqe")
@@ -711,10 +730,14 @@ class EpisodePipeline:
         c, p = self.cfg, self.p
         u4, NS = 4 * c.u, c.N * c.S
         rows = c.B * c.n_q
-        # dV rows are N*S wide (1000 B in bf16): the bf16 copy has rows padded to a 16-byte multiple for TMA
-        self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
-                   None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, None, None,
-                   rows, c.N, c.S, 1.0 / (rows * c.N))
+        # dV rows are N*S wide (1000 B in bf16): the bf16 copy has rows padded to a 16-byte multiple for TMA.  In a
+        # training step the forward's head kernel has written dlogit / dV already.
+        if getattr(self, "_head_bwd_done", False):
+            self._head_bwd_done = False
+        else:
+            self._call("indnet_ntn_head_bwd", ptr(self.V), ptr(p.view("w")), ptr(self.probs), ptr(self.label),
+                       None, ptr(self.dlogit), ptr(self.dV), ptr(self.dV_bf), self.NSp, None, None,
+                       rows, c.N, c.S, 1.0 / (rows * c.N))
         # every gradient slot that is reduced with atomics later in the pass (attention bias / W_a2, the LSTM kernels
         # and biases, the position tables: adjacent slots of the flat buffer) is zeroed by ONE memset here, on a
         # side branch, instead of seven memset nodes in front of the kernels on the critical path

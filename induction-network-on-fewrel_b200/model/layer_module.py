@@ -233,7 +233,7 @@ class _NeuralTensorLayer(torch.autograd.Function):
         lp = torch.empty(B * nq, device=dev)
         cr = torch.empty(B * nq, dtype=torch.int32, device=dev)
         _call("indnet_ntn_head_fwd", ptr(V), ptr(wc), ptr(bc), ptr(labels), ptr(probs), ptr(lp), ptr(cr), B * nq, C, S,
-              None, None, None)
+              None, None, None, None, None, None, 0, 0.0)
         ctx.save_for_backward(cvb, qeb, Mp, wc, Tp, V, probs)
         ctx.batched = batched
         return probs if batched else probs[0]
